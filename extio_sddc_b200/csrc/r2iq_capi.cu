@@ -1,0 +1,514 @@
+// r2iq_capi.cu -- implementation of the C ABI declared in include/r2iq_cuda.h.
+//
+// Owns what the reference operator owns (filter spectra, per-worker scratch -- here device
+// buffers, streams and lookup tables) and borrows what its caller owns (the sample buffers).
+// All arithmetic on samples happens in the kernels of r2iq_kernels.cu; this file only designs
+// filters, builds the small per-tune tables, and moves data.
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <complex>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <new>
+#include <vector>
+
+#include "../../include/r2iq_cuda.h"
+#include "fir_design.h"
+#include "r2iq_kernels.cuh"
+
+using namespace r2iq;
+
+namespace {
+
+thread_local char g_err[512] = "";
+
+int fail(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+constexpr double kPiD = 3.14159265358979323846;
+constexpr int kDefaultChunkBlocks = 256;
+constexpr int kSlots = 3;                 // pipelined chunks in flight on the host-buffer path
+constexpr size_t kMaxTableSets = 1024;    // cached (d, tunebin) table sets before the cache is recycled
+
+struct TableSet {   // device tables for one (decimation, tune bin)
+    float2* gk = nullptr;
+    float2* gck = nullptr;
+    float2* tw_inv = nullptr;
+    int band_lo = 0, band_hi = 0;
+};
+
+struct Slot {
+    cudaStream_t stream = nullptr;
+    cudaEvent_t done = nullptr;
+    int16_t* d_in = nullptr;     // [halfFft | chunk_blocks * 65536]
+    float* d_out = nullptr;      // chunk_blocks * 32768 complex (sized for d = 0)
+    bool busy = false;
+};
+
+}  // namespace
+
+struct r2iq_cuda_s {
+    int device = 0;
+    int sm_count = 0;
+    int cc_major = 0, cc_minor = 0;
+    float gain = 0.f;
+    int chunk_blocks = kDefaultChunkBlocks;
+
+    // control state (r2iqControlClass members, Core/r2iq.h:38-47; mtunebin, Core/fft_mt_r2iq.h:90)
+    int decimate = 0;
+    int tunebin = kHalfFft / 4;
+    bool rand_on = false;
+    bool sideband = false;
+    bool on = false;
+    int latched_decimate = 0;     // worker prologue latches these at TurnOn (impl.hpp:3-6)
+    bool latched_sideband = false;
+
+    bool poisoned = false;        // a CUDA error happened: refuse further work
+    std::mutex mu;
+
+    std::vector<std::complex<float>> hw[kNDec];   // filterHw[d], host copy
+    uint64_t hw_version[kNDec] = {0};
+    float2* d_tw_fwd = nullptr;
+    std::map<long long, TableSet> tables;          // key = version<<20 | d<<12 | tunebin... see table_key
+    Slot slots[kSlots];
+    int16_t* carry = nullptr;                      // pinned: last halfFft samples of the stream
+    bool carry_valid = false;
+    cudaStream_t util_stream = nullptr;
+
+    r2iq_cuda_stats stats{};
+};
+
+namespace {
+
+#define CU(h, call)                                                                                       \
+    do {                                                                                                  \
+        cudaError_t e__ = (call);                                                                         \
+        if (e__ != cudaSuccess) {                                                                         \
+            if (h) (h)->poisoned = true;                                                                  \
+            return fail(R2IQ_E_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, __LINE__); \
+        }                                                                                                 \
+    } while (0)
+
+int check_handle(r2iq_cuda_t h) {
+    if (!h) return fail(R2IQ_E_INVALID, "null handle");
+    if (h->poisoned) return fail(R2IQ_E_CUDA, "handle is unusable after an earlier CUDA error: %s", g_err);
+    return R2IQ_OK;
+}
+
+void free_tables(r2iq_cuda_t h) {
+    for (auto& kv : h->tables) {
+        cudaFree(kv.second.gk);
+        cudaFree(kv.second.gck);
+        cudaFree(kv.second.tw_inv);
+    }
+    h->tables.clear();
+}
+
+long long table_key(r2iq_cuda_t h, int d, int tunebin) {
+    return ((long long)h->hw_version[d] << 16) | ((long long)d << 12) | (long long)tunebin;
+}
+
+// Build (or fetch) the per-(d, tunebin) tables:
+//   gk[k]   = 0.5 * H_d[(k - tunebin) mod halfFft]  for bins k inside the band, else 0
+//             (band = tunebin + [-mfft/2, mfft/2) clipped to [0, halfFft): impl.hpp:76-96)
+//   gck[k]  = (-i * exp(-2 pi i k / FFTN)) * gk[k]   (the odd-part twiddle of the real-FFT split)
+//   tw_inv  = inter-pass twiddles of the backward transform (see r2iq_kernels.cu)
+int get_tables(r2iq_cuda_t h, int d, int tunebin, TableSet* out) {
+    const long long key = table_key(h, d, tunebin);
+    auto it = h->tables.find(key);
+    if (it != h->tables.end()) {
+        *out = it->second;
+        return R2IQ_OK;
+    }
+    if (h->tables.size() >= kMaxTableSets) {
+        CU(h, cudaDeviceSynchronize());   // nobody may still be reading the tables we are about to free
+        free_tables(h);
+    }
+    const int M = kHalfFft >> d;
+    std::vector<float2> gk(kHalfFft), gck(kHalfFft);
+    const std::vector<std::complex<float>>& H = h->hw[d];
+    TableSet ts;
+    ts.band_lo = tunebin - M / 2 < 0 ? 0 : tunebin - M / 2;
+    ts.band_hi = tunebin + M / 2 > kHalfFft ? kHalfFft : tunebin + M / 2;
+    for (int k = 0; k < kHalfFft; k++) {
+        const int s = k - tunebin;
+        if (s >= -M / 2 && s < M / 2) {
+            const std::complex<double> hh = std::complex<double>(H[(s + kHalfFft) % kHalfFft]) * 0.5;
+            const double th = 2.0 * kPiD * (double)k / (double)kFftN;
+            const std::complex<double> c(-sin(th), -cos(th));   // -i * exp(-i th)
+            const std::complex<double> gc = c * hh;
+            gk[k] = make_float2((float)hh.real(), (float)hh.imag());
+            gck[k] = make_float2((float)gc.real(), (float)gc.imag());
+        } else {
+            gk[k] = make_float2(0.f, 0.f);
+            gck[k] = make_float2(0.f, 0.f);
+        }
+    }
+    std::vector<float2> tw(32 * 32);
+    if (d == 0) {
+        // lane l plays residue n1' = (l - tunebin) mod 1024: twiddle exp(+2 pi i n1' k2 / 1024)
+        for (int k2 = 0; k2 < 32; k2++)
+            for (int l = 0; l < 32; l++) {
+                const long long n1 = ((l - tunebin) % kHalfFft + kHalfFft) % kHalfFft;
+                const long long e = (n1 * k2) % kHalfFft;
+                const double th = 2.0 * kPiD * (double)e / (double)kHalfFft;
+                tw[k2 * 32 + l] = make_float2((float)cos(th), (float)sin(th));
+            }
+    } else {
+        const int L = d <= 5 ? (32 >> d) : 1;
+        for (int k2 = 0; k2 < 32; k2++)
+            for (int n1 = 0; n1 < L; n1++) {
+                const double th = 2.0 * kPiD * (double)((n1 * k2) % M) / (double)M;
+                tw[k2 * L + n1] = make_float2((float)cos(th), (float)sin(th));
+            }
+    }
+    CU(h, cudaMalloc(&ts.gk, sizeof(float2) * kHalfFft));
+    CU(h, cudaMalloc(&ts.gck, sizeof(float2) * kHalfFft));
+    CU(h, cudaMalloc(&ts.tw_inv, sizeof(float2) * 32 * 32));
+    CU(h, cudaMemcpy(ts.gk, gk.data(), sizeof(float2) * kHalfFft, cudaMemcpyHostToDevice));
+    CU(h, cudaMemcpy(ts.gck, gck.data(), sizeof(float2) * kHalfFft, cudaMemcpyHostToDevice));
+    CU(h, cudaMemcpy(ts.tw_inv, tw.data(), sizeof(float2) * 32 * 32, cudaMemcpyHostToDevice));
+    h->tables[key] = ts;
+    *out = ts;
+    return R2IQ_OK;
+}
+
+int launch(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d_out, cudaStream_t stream) {
+    TableSet ts;
+    const int d = h->latched_decimate;
+    int rc = get_tables(h, d, h->tunebin, &ts);
+    if (rc != R2IQ_OK) return rc;
+    FusedParams p;
+    p.in_words = (const uint32_t*)d_in;
+    p.out = (float2*)d_out;
+    p.total_frames = (long long)n_blocks * kFramesPerBlock;
+    p.tw_fwd = h->d_tw_fwd;
+    p.gk = ts.gk;
+    p.gck = ts.gck;
+    p.tw_inv = ts.tw_inv;
+    p.tunebin = h->tunebin;
+    p.band_lo = ts.band_lo;
+    p.band_hi = ts.band_hi;
+    p.rand_mul = h->rand_on ? 0xFFFEu : 0u;
+    p.imag_sign = h->latched_sideband ? -1.0f : 1.0f;
+    CU(h, launch_fused(d, p, h->sm_count, stream));
+    h->stats.kernel_launches++;
+    h->stats.blocks_processed += (uint64_t)n_blocks;
+    return R2IQ_OK;
+}
+
+int ensure_slots(r2iq_cuda_t h) {
+    for (int i = 0; i < kSlots; i++) {
+        Slot& s = h->slots[i];
+        if (s.d_in) continue;
+        CU(h, cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+        CU(h, cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
+        CU(h, cudaMalloc(&s.d_in, sizeof(int16_t) * ((size_t)kHalfFft + (size_t)h->chunk_blocks * kTransferSamples)));
+        CU(h, cudaMalloc(&s.d_out, sizeof(float) * 2 * (size_t)h->chunk_blocks * (kTransferSamples / 2)));
+    }
+    return R2IQ_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* r2iq_cuda_last_error(void) { return g_err; }
+const char* r2iq_cuda_version(void) { return "r2iq-b200 0.1 sm_100a fftn=2048"; }
+
+int r2iq_cuda_create(const r2iq_cuda_config* cfg, r2iq_cuda_t* out) {
+    if (!cfg || !out) return fail(R2IQ_E_INVALID, "null argument");
+    *out = nullptr;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return fail(R2IQ_E_NODEVICE, "no CUDA device (%s); this backend has no CPU path",
+                    e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+    int dev = cfg->device;
+    if (dev < 0) {
+        if (cudaGetDevice(&dev) != cudaSuccess) return fail(R2IQ_E_NODEVICE, "cudaGetDevice failed");
+    }
+    if (dev >= ndev) return fail(R2IQ_E_INVALID, "device %d out of range (%d devices)", dev, ndev);
+    cudaDeviceProp prop;
+    if ((e = cudaGetDeviceProperties(&prop, dev)) != cudaSuccess)
+        return fail(R2IQ_E_CUDA, "cudaGetDeviceProperties: %s", cudaGetErrorString(e));
+    if (prop.major != 10)
+        return fail(R2IQ_E_NODEVICE, "device %d is sm_%d%d; kernels are built for sm_100a only", dev, prop.major,
+                    prop.minor);
+    r2iq_cuda_s* h = new (std::nothrow) r2iq_cuda_s();
+    if (!h) return fail(R2IQ_E_NOMEM, "out of host memory");
+    h->device = dev;
+    h->sm_count = prop.multiProcessorCount;
+    h->cc_major = prop.major;
+    h->cc_minor = prop.minor;
+    h->gain = cfg->gain;
+    h->chunk_blocks = cfg->chunk_blocks > 0 ? cfg->chunk_blocks : kDefaultChunkBlocks;
+    h->stats.sm_count = h->sm_count;
+    h->stats.cc_major = prop.major;
+    h->stats.cc_minor = prop.minor;
+    auto bail = [&](int rc) {
+        r2iq_cuda_destroy(h);
+        return rc;
+    };
+    if ((e = cudaSetDevice(dev)) != cudaSuccess) return bail(fail(R2IQ_E_CUDA, "cudaSetDevice: %s", cudaGetErrorString(e)));
+    if ((e = setup_fused_kernels()) != cudaSuccess)
+        return bail(fail(R2IQ_E_CUDA, "kernel setup: %s", cudaGetErrorString(e)));
+    // forward inter-pass twiddles exp(-2 pi i k2 l / 1024)
+    std::vector<float2> tw(32 * 32);
+    for (int k2 = 0; k2 < 32; k2++)
+        for (int l = 0; l < 32; l++) {
+            const double th = -2.0 * kPiD * (double)(k2 * l) / (double)kHalfFft;
+            tw[k2 * 32 + l] = make_float2((float)cos(th), (float)sin(th));
+        }
+    if ((e = cudaMalloc(&h->d_tw_fwd, sizeof(float2) * 32 * 32)) != cudaSuccess ||
+        (e = cudaMemcpy(h->d_tw_fwd, tw.data(), sizeof(float2) * 32 * 32, cudaMemcpyHostToDevice)) != cudaSuccess ||
+        (e = cudaMallocHost(&h->carry, sizeof(int16_t) * kHalfFft)) != cudaSuccess ||
+        (e = cudaStreamCreateWithFlags(&h->util_stream, cudaStreamNonBlocking)) != cudaSuccess)
+        return bail(fail(R2IQ_E_CUDA, "device setup: %s", cudaGetErrorString(e)));
+    memset(h->carry, 0, sizeof(int16_t) * kHalfFft);
+    for (int d = 0; d < kNDec; d++) {
+        h->hw[d] = design_filter_response(h->gain, d, kFftN);
+        h->hw_version[d] = 1;
+    }
+    *out = h;
+    return R2IQ_OK;
+}
+
+int r2iq_cuda_destroy(r2iq_cuda_t h) {
+    if (!h) return R2IQ_OK;
+    cudaSetDevice(h->device);
+    cudaDeviceSynchronize();
+    free_tables(h);
+    for (int i = 0; i < kSlots; i++) {
+        Slot& s = h->slots[i];
+        if (s.stream) cudaStreamDestroy(s.stream);
+        if (s.done) cudaEventDestroy(s.done);
+        cudaFree(s.d_in);
+        cudaFree(s.d_out);
+    }
+    if (h->util_stream) cudaStreamDestroy(h->util_stream);
+    cudaFree(h->d_tw_fwd);
+    if (h->carry) cudaFreeHost(h->carry);
+    delete h;
+    return R2IQ_OK;
+}
+
+int r2iq_cuda_set_filter(r2iq_cuda_t h, int d, const float* hw, int n_complex) {
+    int rc = check_handle(h);
+    if (rc) return rc;
+    if (d < 0 || d >= kNDec || !hw || n_complex != kHalfFft)
+        return fail(R2IQ_E_INVALID, "set_filter: d=%d n_complex=%d (want 0..6, %d)", d, n_complex, kHalfFft);
+    std::lock_guard<std::mutex> lk(h->mu);
+    for (int k = 0; k < kHalfFft; k++) h->hw[d][k] = std::complex<float>(hw[2 * k], hw[2 * k + 1]);
+    h->hw_version[d]++;   // cached tables of older versions are simply never looked up again
+    return R2IQ_OK;
+}
+
+int r2iq_cuda_get_filter(r2iq_cuda_t h, int d, float* hw, int n_complex) {
+    int rc = check_handle(h);
+    if (rc) return rc;
+    if (d < 0 || d >= kNDec || !hw || n_complex != kHalfFft)
+        return fail(R2IQ_E_INVALID, "get_filter: d=%d n_complex=%d (want 0..6, %d)", d, n_complex, kHalfFft);
+    std::lock_guard<std::mutex> lk(h->mu);
+    for (int k = 0; k < kHalfFft; k++) {
+        hw[2 * k] = h->hw[d][k].real();
+        hw[2 * k + 1] = h->hw[d][k].imag();
+    }
+    return R2IQ_OK;
+}
+
+int r2iq_cuda_set_decimate(r2iq_cuda_t h, int d) {
+    int rc = check_handle(h);
+    if (rc) return rc;
+    if (d < 0 || d >= kNDec) return fail(R2IQ_E_INVALID, "decimation index %d out of 0..%d", d, kNDec - 1);
+    h->decimate = d;
+    return R2IQ_OK;
+}
+int r2iq_cuda_get_decimate(r2iq_cuda_t h) { return h ? h->decimate : R2IQ_E_INVALID; }
+int r2iq_cuda_get_ratio(r2iq_cuda_t h) { return h ? (1 << h->decimate) : R2IQ_E_INVALID; }
+
+float r2iq_cuda_set_freq_offset(r2iq_cuda_t h, float offset) {
+    if (!h) return 0.f;
+    // float arithmetic and truncation exactly as the reference (Core/fft_mt_r2iq.cpp:104-106)
+    int tb = int(offset * kHalfFft / 4) * 4;
+    float delta = ((float)tb / kHalfFft) - offset;
+    float ret = delta * (float)(1 << h->decimate);
+    // The reference stores whatever comes out; bins outside [0, halfFft) would index out of
+    // bounds there (offset is documented as [0,1)), so clamp instead of reading garbage.
+    if (tb < 0) tb = 0;
+    if (tb > kHalfFft - 4) tb = kHalfFft - 4;
+    h->tunebin = tb;
+    return ret;
+}
+
+int r2iq_cuda_set_tunebin(r2iq_cuda_t h, int tunebin) {
+    int rc = check_handle(h);
+    if (rc) return rc;
+    if (tunebin < 0 || tunebin >= kHalfFft || (tunebin & 3))
+        return fail(R2IQ_E_INVALID, "tune bin %d must be a multiple of 4 in [0,%d)", tunebin, kHalfFft);
+    h->tunebin = tunebin;
+    return R2IQ_OK;
+}
+int r2iq_cuda_get_tunebin(r2iq_cuda_t h) { return h ? h->tunebin : R2IQ_E_INVALID; }
+
+int r2iq_cuda_set_rand(r2iq_cuda_t h, int on) {
+    if (!h) return fail(R2IQ_E_INVALID, "null handle");
+    h->rand_on = on != 0;
+    return R2IQ_OK;
+}
+int r2iq_cuda_get_rand(r2iq_cuda_t h) { return h ? (int)h->rand_on : R2IQ_E_INVALID; }
+int r2iq_cuda_set_sideband(r2iq_cuda_t h, int lsb) {
+    if (!h) return fail(R2IQ_E_INVALID, "null handle");
+    h->sideband = lsb != 0;
+    return R2IQ_OK;
+}
+int r2iq_cuda_get_sideband(r2iq_cuda_t h) { return h ? (int)h->sideband : R2IQ_E_INVALID; }
+
+int r2iq_cuda_turn_on(r2iq_cuda_t h) {
+    int rc = check_handle(h);
+    if (rc) return rc;
+    std::lock_guard<std::mutex> lk(h->mu);
+    h->latched_decimate = h->decimate;
+    h->latched_sideband = h->sideband;
+    memset(h->carry, 0, sizeof(int16_t) * kHalfFft);
+    h->carry_valid = false;
+    h->on = true;
+    return R2IQ_OK;
+}
+
+int r2iq_cuda_turn_off(r2iq_cuda_t h) {
+    if (!h) return fail(R2IQ_E_INVALID, "null handle");
+    h->on = false;
+    if (h->poisoned) return R2IQ_OK;
+    return r2iq_cuda_sync(h);
+}
+int r2iq_cuda_is_on(r2iq_cuda_t h) { return h ? (int)h->on : 0; }
+
+long r2iq_cuda_out_per_block(r2iq_cuda_t h) { return h ? (long)((kTransferSamples / 2) >> h->latched_decimate) : 0; }
+
+int r2iq_cuda_process(r2iq_cuda_t h, const int16_t* blocks, long n_blocks, const int16_t* history, float* iq_out) {
+    int rc = check_handle(h);
+    if (rc) return rc;
+    if (!h->on) return fail(R2IQ_E_STATE, "process called while the operator is off (call r2iq_cuda_turn_on)");
+    if (n_blocks < 0 || (n_blocks > 0 && (!blocks || !iq_out))) return fail(R2IQ_E_INVALID, "process: bad buffers");
+    if (n_blocks == 0) return R2IQ_OK;
+    std::lock_guard<std::mutex> lk(h->mu);
+    CU(h, cudaSetDevice(h->device));
+    if ((rc = ensure_slots(h)) != R2IQ_OK) return rc;
+    const int d = h->latched_decimate;
+    const size_t out_per_block = (size_t)((kTransferSamples / 2) >> d);
+    if (history) memcpy(h->carry, history, sizeof(int16_t) * kHalfFft);
+    long done = 0;
+    int si = 0;
+    while (done < n_blocks) {
+        Slot& s = h->slots[si];
+        if (s.busy) {
+            CU(h, cudaEventSynchronize(s.done));
+            s.busy = false;
+        }
+        const long nb = (n_blocks - done) < h->chunk_blocks ? (n_blocks - done) : h->chunk_blocks;
+        if (done == 0) {
+            CU(h, cudaMemcpyAsync(s.d_in, h->carry, sizeof(int16_t) * kHalfFft, cudaMemcpyHostToDevice, s.stream));
+            CU(h, cudaMemcpyAsync(s.d_in + kHalfFft, blocks, sizeof(int16_t) * (size_t)nb * kTransferSamples,
+                                  cudaMemcpyHostToDevice, s.stream));
+        } else {
+            // history of this chunk = tail of the previous block, contiguous in the caller's buffer
+            CU(h, cudaMemcpyAsync(s.d_in, blocks + (size_t)done * kTransferSamples - kHalfFft,
+                                  sizeof(int16_t) * ((size_t)kHalfFft + (size_t)nb * kTransferSamples),
+                                  cudaMemcpyHostToDevice, s.stream));
+        }
+        h->stats.h2d_bytes += sizeof(int16_t) * ((size_t)kHalfFft + (size_t)nb * kTransferSamples);
+        if ((rc = launch(h, s.d_in, nb, s.d_out, s.stream)) != R2IQ_OK) return rc;
+        const size_t out_bytes = sizeof(float) * 2 * (size_t)nb * out_per_block;
+        CU(h, cudaMemcpyAsync(iq_out + 2 * (size_t)done * out_per_block, s.d_out, out_bytes, cudaMemcpyDeviceToHost,
+                              s.stream));
+        h->stats.d2h_bytes += out_bytes;
+        CU(h, cudaEventRecord(s.done, s.stream));
+        s.busy = true;
+        done += nb;
+        si = (si + 1) % kSlots;
+    }
+    // the first chunk reads h->carry asynchronously: drain before overwriting it
+    for (int i = 0; i < kSlots; i++) {
+        if (h->slots[i].busy) {
+            CU(h, cudaEventSynchronize(h->slots[i].done));
+            h->slots[i].busy = false;
+        }
+    }
+    memcpy(h->carry, blocks + (size_t)n_blocks * kTransferSamples - kHalfFft, sizeof(int16_t) * kHalfFft);
+    h->carry_valid = true;
+    return R2IQ_OK;
+}
+
+int r2iq_cuda_process_device(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d_iq_out, void* stream) {
+    int rc = check_handle(h);
+    if (rc) return rc;
+    if (!h->on) return fail(R2IQ_E_STATE, "process called while the operator is off (call r2iq_cuda_turn_on)");
+    if (n_blocks < 0 || (n_blocks > 0 && (!d_in || !d_iq_out))) return fail(R2IQ_E_INVALID, "process_device: bad buffers");
+    if (((uintptr_t)d_in & 3) || ((uintptr_t)d_iq_out & 7))
+        return fail(R2IQ_E_INVALID, "process_device: input must be 4-byte and output 8-byte aligned");
+    if (n_blocks == 0) return R2IQ_OK;
+    std::lock_guard<std::mutex> lk(h->mu);
+    return launch(h, d_in, n_blocks, d_iq_out, (cudaStream_t)stream);
+}
+
+int r2iq_cuda_sync(r2iq_cuda_t h) {
+    int rc = check_handle(h);
+    if (rc) return rc;
+    CU(h, cudaSetDevice(h->device));
+    CU(h, cudaDeviceSynchronize());
+    return R2IQ_OK;
+}
+
+void* r2iq_cuda_host_alloc(size_t bytes) {
+    void* p = nullptr;
+    cudaError_t e = cudaMallocHost(&p, bytes ? bytes : 1);
+    if (e != cudaSuccess) {
+        fail(R2IQ_E_NOMEM, "cudaMallocHost(%zu): %s", bytes, cudaGetErrorString(e));
+        return nullptr;
+    }
+    return p;
+}
+int r2iq_cuda_host_free(void* p) {
+    if (!p) return R2IQ_OK;
+    cudaError_t e = cudaFreeHost(p);
+    if (e != cudaSuccess) return fail(R2IQ_E_CUDA, "cudaFreeHost: %s", cudaGetErrorString(e));
+    return R2IQ_OK;
+}
+
+int r2iq_cuda_convert(r2iq_cuda_t h, const int16_t* in, long n, int rand, float* out) {
+    int rc = check_handle(h);
+    if (rc) return rc;
+    if (n < 0 || (n & 1) || (n > 0 && (!in || !out))) return fail(R2IQ_E_INVALID, "convert: n must be even and buffers non-null");
+    if (n == 0) return R2IQ_OK;
+    std::lock_guard<std::mutex> lk(h->mu);
+    CU(h, cudaSetDevice(h->device));
+    int16_t* d_in = nullptr;
+    float* d_out = nullptr;
+    CU(h, cudaMalloc(&d_in, sizeof(int16_t) * (size_t)n));
+    CU(h, cudaMalloc(&d_out, sizeof(float) * (size_t)n));
+    CU(h, cudaMemcpy(d_in, in, sizeof(int16_t) * (size_t)n, cudaMemcpyHostToDevice));
+    CU(h, launch_convert(d_in, d_out, n, rand, h->util_stream));
+    CU(h, cudaStreamSynchronize(h->util_stream));
+    CU(h, cudaMemcpy(out, d_out, sizeof(float) * (size_t)n, cudaMemcpyDeviceToHost));
+    cudaFree(d_in);
+    cudaFree(d_out);
+    return R2IQ_OK;
+}
+
+int r2iq_cuda_get_stats(r2iq_cuda_t h, r2iq_cuda_stats* out) {
+    if (!h || !out) return fail(R2IQ_E_INVALID, "null argument");
+    *out = h->stats;
+    return R2IQ_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,323 @@
+// r2iq_kernels.cu -- the fused real->IQ down-converter kernels for sm_100a (B200), FFTN = 2048.
+//
+// One kernel per decimation index d = 0..6 replaces the whole per-block worker loop of the
+// reference (Core/fft_mt_r2iq_impl.hpp:15-151): de-randomise + int16->float (impl.hpp:40-54),
+// 2048-point real forward FFT (impl.hpp:88), tune-bin select times filter response with edge
+// zero-fill (impl.hpp:76-96), mfft-point backward FFT (impl.hpp:98), overlap-save discard,
+// optional conjugate and placement in the output stream (impl.hpp:117-138).
+//
+// Mapping (see DESIGN.md for the derivation and the measured rooflines):
+//   * a WARP owns a frame: lane n1 holds the 32 complex points z[n1 + 32*j] (z = packed int16
+//     pairs x[2n] + i*x[2n+1]) and runs a radix-32 DFT entirely in registers (dft_regs.cuh);
+//     one padded shared-memory transposition later the second radix-32 pass leaves
+//     Z[32*k1 + lane] in register k1.  Only __syncwarp is ever needed -- no block barriers.
+//   * the real-FFT split needs Z[k] and Z[1024-k]: the partner lives in lane (32-lane)&31,
+//     register 31-k1, so it arrives by warp shuffle; split, tune rotation and filter multiply
+//     collapse into  Y = GK[k]*(a+conj b) + GCK[k]*(a-conj b)  with two per-tune tables.
+//   * d = 0: the tune rotation is absorbed into the inverse transform's inter-pass twiddles
+//     (lane l simply plays residue (l - tunebin) mod 32), so Y never leaves registers between
+//     the forward and the backward FFT.
+//   * d >= 1: a warp runs 2^d forward frames, stages their mfft-bin bands in shared memory and
+//     then transforms all of them at once, 32>>d lanes per frame, again 32 points per lane.
+// No cuFFT, no tensor cores, no CPU fallback.
+#include "r2iq_kernels.cuh"
+
+#include "dft_regs.cuh"
+
+namespace r2iq {
+
+constexpr int kWarpsPerCta = 8;
+constexpr int kThreads = kWarpsPerCta * 32;
+constexpr int kScratch = 32 * 33;   // float2 per warp: 32x32 transposition tile, row pitch 33
+constexpr int kStage = 64 * 17;     // float2 per warp: staged bands of 2^d frames (max over d)
+
+template <int D>
+struct Geo {
+    static constexpr int M = kHalfFft >> D;                  // mfft: inverse FFT size
+    static constexpr int ROUNDS = 1 << D;                    // frames a warp runs per unit of work
+    static constexpr int L = (D <= 5) ? (32 >> D) : 1;       // lanes per frame in the inverse transform
+    static constexpr int GS = (D == 6) ? 17 : (M + L);       // staging pitch per frame (bank-conflict free)
+    static constexpr int OUT_PER_BLOCK = (kTransferSamples / 2) >> D;
+    static constexpr int WARP_SMEM = kScratch + (D > 0 ? kStage : 0);   // float2 per warp
+    static constexpr size_t SMEM_BYTES = (size_t)kWarpsPerCta * WARP_SMEM * sizeof(float2);
+};
+
+__device__ __forceinline__ int brev(int v, int bits) { return (int)(__brev((unsigned)v) >> (32 - bits)); }
+
+// De-randomise (Core/fft_mt_r2iq.h:41-44: `val = input ^ (-2)` when the LSB is set) both int16
+// halves of a word at once, then convert each to float (exact).
+__device__ __forceinline__ float2 unpack_pair(uint32_t w, uint32_t rand_mul) {
+    w ^= (w & 0x00010001u) * rand_mul;
+    return make_float2((float)(short)(w & 0xFFFFu), (float)((int)w >> 16));
+}
+
+struct FrameOut {
+    long long base;   // out[base + idx] receives inverse-FFT sample idx
+    int lo, hi;       // kept range of idx
+};
+
+// Output placement of frame f = block*43 + k (impl.hpp:117-138): k == 0 keeps y[mfft/4, 3mfft/4),
+// k >= 1 keeps y[0, 3mfft/4) at offset mfft/2 + (k-1)*3mfft/4 inside the block's output.
+template <int D>
+__device__ __forceinline__ FrameOut frame_out(long long f) {
+    constexpr int M = Geo<D>::M;
+    long long b = f / kFramesPerBlock;
+    int k = (int)(f - b * kFramesPerBlock);
+    FrameOut o;
+    o.lo = k ? 0 : M / 4;
+    o.hi = 3 * M / 4;
+    o.base = b * (long long)Geo<D>::OUT_PER_BLOCK + (k ? (M / 2 + (k - 1) * (3 * M / 4)) : 0) - o.lo;
+    return o;
+}
+
+__device__ __forceinline__ void store_iq(float2* out, const FrameOut& fo, int idx, float2 v, float imag_sign) {
+    if (idx >= fo.lo && idx < fo.hi) out[fo.base + idx] = make_float2(v.x, v.y * imag_sign);
+}
+
+// Forward transform of frame f: on return v[k1] = Z[32*k1 + lane], Z = FFT_1024 of the packed frame.
+__device__ __forceinline__ void forward_frame(const FusedParams& p, long long f, int lane, float2* S, float2 (&v)[32]) {
+    const long long b = f / kFramesPerBlock;
+    const int k = (int)(f - b * kFramesPerBlock);
+    // frame k of block b starts k*1536 samples into [halo | block b]  (impl.hpp:88)
+    const uint32_t* src = p.in_words + b * (kTransferSamples / 2) + k * (kHop / 2) + lane;
+    uint32_t w[32];
+#pragma unroll
+    for (int j = 0; j < 32; j++) w[j] = __ldg(src + 32 * j);
+#pragma unroll
+    for (int j = 0; j < 32; j++) v[brev(j, 5)] = unpack_pair(w[j], p.rand_mul);
+    dit<32, false>(v);                                  // pass 1: DFT over n2, lane = n1
+#pragma unroll
+    for (int k2 = 1; k2 < 32; k2++) v[k2] = cmul(v[k2], __ldg(&p.tw_fwd[k2 * 32 + lane]));
+#pragma unroll
+    for (int k2 = 0; k2 < 32; k2++) S[lane * 33 + k2] = v[k2];
+    __syncwarp();
+#pragma unroll
+    for (int n1 = 0; n1 < 32; n1++) v[brev(n1, 5)] = S[n1 * 33 + lane];
+    __syncwarp();
+    dit<32, false>(v);                                  // pass 2: DFT over n1, lane = k2
+}
+
+// Real-FFT split + tune rotation + filter for the bin k = 32*k1 + lane held in v[k1]:
+//   X[k] = 0.5*(a + conj b) + 0.5*(-i W_2048^k)*(a - conj b),  a = Z[k], b = Z[1024-k]
+//   Y    = X[k] * H[...]  ->  GK[k]*(a + conj b) + GCK[k]*(a - conj b)
+template <int K1>
+__device__ __forceinline__ float2 split_filter(const FusedParams& p, const float2 (&v)[32], int lane) {
+    const float2 a = v[K1];
+    const float2 bs = v[31 - K1];
+    float bx = __shfl_sync(0xffffffffu, bs.x, (32 - lane) & 31);
+    float by = __shfl_sync(0xffffffffu, bs.y, (32 - lane) & 31);
+    if (lane == 0) {   // bins 32*k1: the mirror 1024-32*k1 is lane 0's own register (32-k1)&31
+        bx = v[(32 - K1) & 31].x;
+        by = v[(32 - K1) & 31].y;
+    }
+    const float ux = a.x + bx, uy = a.y - by;
+    const float wx = a.x - bx, wy = a.y + by;
+    const float2 g = __ldg(&p.gk[32 * K1 + lane]);
+    const float2 gc = __ldg(&p.gck[32 * K1 + lane]);
+    float2 y;
+    y.x = fmaf(gc.x, wx, fmaf(-gc.y, wy, fmaf(g.x, ux, -g.y * uy)));
+    y.y = fmaf(gc.x, wy, fmaf(gc.y, wx, fmaf(g.x, uy, g.y * ux)));
+    return y;
+}
+
+template <int D, int... K1>
+__device__ __forceinline__ void band_d0(const FusedParams& p, const float2 (&v)[32], int lane, float2 (&t)[32],
+                                        std::integer_sequence<int, K1...>) {
+    ((t[brev(K1, 5)] = split_filter<K1>(p, v, lane)), ...);
+}
+
+template <int D, int K1>
+__device__ __forceinline__ void band_row(const FusedParams& p, const float2 (&v)[32], int lane, float2* stage) {
+    constexpr int M = Geo<D>::M;
+    if (32 * K1 + 31 >= p.band_lo && 32 * K1 < p.band_hi) {      // warp-uniform
+        float2 y = split_filter<K1>(p, v, lane);
+        const int k = 32 * K1 + lane;
+        if (k >= p.band_lo && k < p.band_hi) stage[(k - p.tunebin) & (M - 1)] = y;
+    }
+}
+template <int D, int... K1>
+__device__ __forceinline__ void band_rows(const FusedParams& p, const float2 (&v)[32], int lane, float2* stage,
+                                          std::integer_sequence<int, K1...>) {
+    (band_row<D, K1>(p, v, lane, stage), ...);
+}
+
+template <int D>
+__global__ void __launch_bounds__(kThreads) r2iq_fused_kernel(const FusedParams p) {
+    using G = Geo<D>;
+    extern __shared__ float2 smem[];
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    float2* S = smem + warp * G::WARP_SMEM;
+    float2* stage = S + kScratch;
+
+    if constexpr (D > 0) {
+        // bins of the band that fall outside [0, halfFft) are never written: they must read as
+        // zero (the memset calls of impl.hpp:91-96)
+        for (int i = lane; i < kStage; i += 32) stage[i] = make_float2(0.f, 0.f);
+        __syncwarp();
+    }
+
+    const long long n_units = (p.total_frames + G::ROUNDS - 1) / G::ROUNDS;
+    for (long long unit = (long long)blockIdx.x * kWarpsPerCta + warp; unit < n_units;
+         unit += (long long)gridDim.x * kWarpsPerCta) {
+        const long long f0 = unit * G::ROUNDS;
+        if constexpr (D == 0) {
+            float2 v[32], t[32];
+            forward_frame(p, f0, lane, S, v);
+            band_d0<D>(p, v, lane, t, std::make_integer_sequence<int, 32>{});
+            // backward pass 1 over the register index; lane l is residue (l - tunebin) mod 32
+            dit<32, true>(t);
+#pragma unroll
+            for (int k2 = 1; k2 < 32; k2++) t[k2] = cmul(t[k2], __ldg(&p.tw_inv[k2 * 32 + lane]));
+            const int n1 = (lane - p.tunebin) & 31;
+#pragma unroll
+            for (int k2 = 0; k2 < 32; k2++) S[n1 * 33 + k2] = t[k2];
+            __syncwarp();
+#pragma unroll
+            for (int n = 0; n < 32; n++) t[brev(n, 5)] = S[n * 33 + lane];
+            __syncwarp();
+            dit<32, true>(t);                            // t[k1'] = y[lane + 32*k1']
+            const FrameOut fo = frame_out<D>(f0);
+#pragma unroll
+            for (int k1 = 0; k1 < 32; k1++) store_iq(p.out, fo, lane + 32 * k1, t[k1], p.imag_sign);
+        } else {
+            for (int r = 0; r < G::ROUNDS; r++) {
+                const long long f = f0 + r;
+                if (f < p.total_frames) {                // warp-uniform
+                    float2 v[32];
+                    forward_frame(p, f, lane, S, v);
+                    band_rows<D>(p, v, lane, stage + r * G::GS, std::make_integer_sequence<int, 32>{});
+                }
+            }
+            __syncwarp();
+            if constexpr (D <= 5) {
+                constexpr int L = G::L;
+                constexpr int NI = 32 / L;
+                constexpr int LB = ilog2(L);
+                const int g = lane / L;
+                const int n = lane % L;
+                float2 t[32];
+#pragma unroll
+                for (int n2 = 0; n2 < 32; n2++) t[brev(n2, 5)] = stage[g * G::GS + n + L * n2];
+                __syncwarp();
+                dit<32, true>(t);                        // pass 1: DFT over n2 within the frame
+                const long long f = f0 + g;
+                const FrameOut fo = frame_out<D>(f);
+                const bool live = f < p.total_frames;
+                if constexpr (L > 1) {
+#pragma unroll
+                    for (int k2 = 1; k2 < 32; k2++) t[k2] = cmul(t[k2], __ldg(&p.tw_inv[k2 * L + n]));
+                    float2* Sg = S + g * (33 * L);
+#pragma unroll
+                    for (int k2 = 0; k2 < 32; k2++) Sg[n * 33 + k2] = t[k2];
+                    __syncwarp();
+#pragma unroll
+                    for (int i = 0; i < NI; i++) {
+                        float2 x[L];
+#pragma unroll
+                        for (int n1 = 0; n1 < L; n1++) x[brev(n1, LB)] = Sg[n1 * 33 + n + L * i];
+                        dit<L, true>(x);                 // pass 2: DFT over n1
+                        if (live) {
+#pragma unroll
+                            for (int k1 = 0; k1 < L; k1++) store_iq(p.out, fo, n + L * i + 32 * k1, x[k1], p.imag_sign);
+                        }
+                    }
+                    __syncwarp();
+                } else {
+                    if (live) {
+#pragma unroll
+                        for (int k2 = 0; k2 < 32; k2++) store_iq(p.out, fo, k2, t[k2], p.imag_sign);
+                    }
+                }
+            } else {
+                // d = 6: mfft = 16, 64 frames per unit, two whole 16-point transforms per lane
+#pragma unroll
+                for (int h = 0; h < 2; h++) {
+                    const int g = lane + 32 * h;
+                    float2 x[16];
+#pragma unroll
+                    for (int n = 0; n < 16; n++) x[brev(n, 4)] = stage[g * G::GS + n];
+                    dit<16, true>(x);
+                    const long long f = f0 + g;
+                    if (f < p.total_frames) {
+                        const FrameOut fo = frame_out<D>(f);
+#pragma unroll
+                        for (int n = 0; n < 16; n++) store_iq(p.out, fo, n, x[n], p.imag_sign);
+                    }
+                }
+                __syncwarp();
+            }
+        }
+    }
+}
+
+template <int D>
+static cudaError_t launch_one(const FusedParams& p, int sm_count, cudaStream_t stream) {
+    using G = Geo<D>;
+    int ctas_per_sm = 1;
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, r2iq_fused_kernel<D>, kThreads,
+                                                                 G::SMEM_BYTES);
+    if (e != cudaSuccess) return e;
+    if (ctas_per_sm < 1) ctas_per_sm = 1;
+    const long long n_units = (p.total_frames + G::ROUNDS - 1) / G::ROUNDS;
+    long long want = (n_units + kWarpsPerCta - 1) / kWarpsPerCta;
+    long long grid = (long long)sm_count * ctas_per_sm;     // persistent: every CTA strides over units
+    if (grid > want) grid = want;
+    if (grid < 1) grid = 1;
+    r2iq_fused_kernel<D><<<(unsigned)grid, kThreads, G::SMEM_BYTES, stream>>>(p);
+    return cudaGetLastError();
+}
+
+template <int D>
+static cudaError_t setup_one() {
+    return cudaFuncSetAttribute(r2iq_fused_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)Geo<D>::SMEM_BYTES);
+}
+
+cudaError_t setup_fused_kernels() {
+    cudaError_t e;
+    if ((e = setup_one<0>()) != cudaSuccess) return e;
+    if ((e = setup_one<1>()) != cudaSuccess) return e;
+    if ((e = setup_one<2>()) != cudaSuccess) return e;
+    if ((e = setup_one<3>()) != cudaSuccess) return e;
+    if ((e = setup_one<4>()) != cudaSuccess) return e;
+    if ((e = setup_one<5>()) != cudaSuccess) return e;
+    if ((e = setup_one<6>()) != cudaSuccess) return e;
+    return cudaSuccess;
+}
+
+cudaError_t launch_fused(int d, const FusedParams& p, int sm_count, cudaStream_t stream) {
+    switch (d) {
+        case 0: return launch_one<0>(p, sm_count, stream);
+        case 1: return launch_one<1>(p, sm_count, stream);
+        case 2: return launch_one<2>(p, sm_count, stream);
+        case 3: return launch_one<3>(p, sm_count, stream);
+        case 4: return launch_one<4>(p, sm_count, stream);
+        case 5: return launch_one<5>(p, sm_count, stream);
+        case 6: return launch_one<6>(p, sm_count, stream);
+        default: return cudaErrorInvalidValue;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// the bit-exact stage on its own (parity hook): convert_float<rand> of Core/fft_mt_r2iq.h:36-51
+// ---------------------------------------------------------------------------------------------
+__global__ void convert_kernel(const uint32_t* __restrict__ in, float2* __restrict__ out, long long n_words,
+                               uint32_t rand_mul) {
+    long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (; i < n_words; i += stride) out[i] = unpack_pair(__ldg(in + i), rand_mul);
+}
+
+cudaError_t launch_convert(const int16_t* in, float* out, long long n, int rand, cudaStream_t stream) {
+    if (n & 1) return cudaErrorInvalidValue;
+    const long long n_words = n / 2;
+    if (n_words == 0) return cudaSuccess;
+    long long blocks = (n_words + 255) / 256;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    convert_kernel<<<(unsigned)blocks, 256, 0, stream>>>((const uint32_t*)in, (float2*)out, n_words,
+                                                         rand ? 0xFFFEu : 0u);
+    return cudaGetLastError();
+}
+
+}  // namespace r2iq

@@ -1,0 +1,38 @@
+// r2iq_kernels.cuh -- launch parameters shared by the kernels and the C-ABI layer.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace r2iq {
+
+// Sizes of the FFTN = 2048 path (north-star configuration).  Reference: Core/fft_mt_r2iq.h:18-19,
+// Core/config.h:80-81.
+constexpr int kFftN = 2048;                       // FFTN_R_ADC
+constexpr int kHalfFft = kFftN / 2;               // halfFft: complex bins of the forward FFT
+constexpr int kTransferSamples = 65536;           // int16 samples per input block
+constexpr int kHop = 3 * kHalfFft / 2;            // frame hop inside a block (1536 samples)
+constexpr int kFramesPerBlock = kTransferSamples / kHop + 1;   // fftPerBuf = 43
+constexpr int kNDec = 7;                          // NDECIDX
+
+struct FusedParams {
+    const uint32_t* in_words;   // [halfFft/2 halo words | n_blocks * 32768 words]; one word = 2 int16
+    float2* out;                // n_blocks * (32768 >> d) complex
+    long long total_frames;     // n_blocks * 43
+    const float2* tw_fwd;       // [32][32]  W_1024^(k2*lane), forward inter-pass twiddles
+    const float2* gk;           // [1024]    0.5*H[(k-tunebin) mod 1024] inside the band, else 0
+    const float2* gck;          // [1024]    (-i*W_2048^k) * gk[k]
+    const float2* tw_inv;       // d=0: [32][32] conj(W_1024)^((lane-tunebin)*k2); d>=1: [32][L] conj(W_M)^(n1*k2)
+    int tunebin;
+    int band_lo, band_hi;       // forward-FFT bins [lo,hi) that feed the inverse transform
+    uint32_t rand_mul;          // 0xFFFE when the ADC randomizer is on, else 0
+    float imag_sign;            // -1 when sideband inversion (copy<true>) is requested, else +1
+};
+
+// Launch the fused kernel for decimation index d on `stream`.  Returns cudaGetLastError().
+cudaError_t launch_fused(int d, const FusedParams& p, int sm_count, cudaStream_t stream);
+// One-time per-device setup (opt-in shared memory sizes).
+cudaError_t setup_fused_kernels();
+// int16 -> float with optional de-randomisation (the bit-exact stage, exposed for parity tests).
+cudaError_t launch_convert(const int16_t* in, float* out, long long n, int rand, cudaStream_t stream);
+
+}  // namespace r2iq

@@ -1,0 +1,148 @@
+/* r2iq_cuda.h -- C ABI of the B200 (sm_100a) real->IQ down-converter backend.
+ *
+ * This is the drop-in boundary: plain C, opaque handle, pointers and sizes only.  It carries
+ * exactly the operations the reference's `r2iqControlClass` / `fft_mt_r2iq` operator exposes to
+ * its single caller RadioHandlerClass, so a `cuda_r2iq : r2iqControlClass` adapter (see
+ * extio_sddc_b200/host/cuda_r2iq.h and INTEGRATION.md) can sit beside the FFTW/AVX/NEON workers.
+ * Each entry point cites the reference interface it replaces (paths relative to the reference
+ * tree, ShadowLive/ExtIO_sddc).
+ *
+ * Conventions: every function returning int yields 0 on success and a negative R2IQ_E_* code on
+ * failure; r2iq_cuda_last_error() then returns a thread-local description (same style as
+ * libsddc/libsddc.cpp:31-46).  Nothing throws across this boundary.  There is NO CPU fallback:
+ * without a usable CUDA device r2iq_cuda_create fails.
+ *
+ * Stream model: the ADC stream is a sequence of blocks of R2IQ_TRANSFER_SAMPLES int16 samples
+ * (Core/config.h:80-81).  Every block yields exactly R2IQ_TRANSFER_SAMPLES/2 >> d complex float
+ * samples (interleaved re,im), d = decimation index 0..6; 2^d input blocks fill one 32768-complex
+ * output slot of the reference's output ring (Core/fft_mt_r2iq_impl.hpp:117-148).  Block b needs
+ * the last halfFft samples of block b-1 ("history", impl.hpp:32,42).
+ */
+#ifndef R2IQ_CUDA_H
+#define R2IQ_CUDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define R2IQ_API __attribute__((visibility("default")))
+#else
+#define R2IQ_API
+#endif
+
+#define R2IQ_TRANSFER_SAMPLES 65536   /* Core/config.h:80-81  transferSize / sizeof(int16_t) */
+#define R2IQ_NDECIDX 7                /* Core/r2iq.h:5 */
+#define R2IQ_FFTN 2048                /* FFTN_R_ADC of the north-star configuration (Core/config.h:49 ships 8192) */
+#define R2IQ_HALF_FFT (R2IQ_FFTN / 2) /* Core/fft_mt_r2iq.h:18 */
+
+enum {
+    R2IQ_OK = 0,
+    R2IQ_E_INVALID = -1,    /* bad argument */
+    R2IQ_E_CUDA = -2,       /* CUDA runtime error (sticky: the handle refuses further work) */
+    R2IQ_E_NOMEM = -3,
+    R2IQ_E_STATE = -4,      /* call order violated (e.g. process before filters exist) */
+    R2IQ_E_NODEVICE = -5    /* no CUDA device / wrong architecture: there is no CPU path */
+};
+
+typedef struct r2iq_cuda_s* r2iq_cuda_t;
+
+typedef struct r2iq_cuda_config {
+    int device;            /* CUDA device ordinal; -1 = current device */
+    float gain;            /* RadioHardware::getGain(), the `gain` argument of fft_mt_r2iq::Init */
+    int chunk_blocks;      /* host-buffer path: blocks per pipelined H2D/compute/D2H chunk; 0 = default (256) */
+} r2iq_cuda_config;
+
+typedef struct r2iq_cuda_stats {
+    uint64_t kernel_launches;    /* fused kernels launched since create */
+    uint64_t blocks_processed;   /* input blocks */
+    uint64_t h2d_bytes;          /* host->device bytes moved by r2iq_cuda_process */
+    uint64_t d2h_bytes;          /* device->host bytes moved by r2iq_cuda_process */
+    int sm_count;
+    int cc_major, cc_minor;
+} r2iq_cuda_stats;
+
+/* Thread-local description of the last failure on this thread. */
+R2IQ_API const char* r2iq_cuda_last_error(void);
+/* Library / kernel build identification, e.g. "r2iq-b200 0.1 sm_100a fftn=2048". */
+R2IQ_API const char* r2iq_cuda_version(void);
+
+/* fft_mt_r2iq::fft_mt_r2iq() + fft_mt_r2iq::Init(gain, in, out)  (Core/fft_mt_r2iq.cpp:39-49,147-227).
+ * Designs the seven decimation filters on the host exactly as Init does (KaiserWindow, Core/fir.cpp:48-105;
+ * tap placement and gain, fft_mt_r2iq.cpp:185-205), uploads their spectra, and sets the constructor
+ * defaults: decimation 0, tune bin halfFft/4, rand off, sideband off. */
+R2IQ_API int r2iq_cuda_create(const r2iq_cuda_config* cfg, r2iq_cuda_t* out);
+/* fft_mt_r2iq::~fft_mt_r2iq()  (Core/fft_mt_r2iq.cpp:71-98). */
+R2IQ_API int r2iq_cuda_destroy(r2iq_cuda_t h);
+
+/* filterHw[d] (Core/fft_mt_r2iq.h:101): replace / read back one filter spectrum, halfFft complex
+ * floats interleaved.  A host that designs its own filter (Core/fir.cpp) uploads it once per
+ * Init/setDecimate as the north star describes. */
+R2IQ_API int r2iq_cuda_set_filter(r2iq_cuda_t h, int d, const float* hw_interleaved, int n_complex);
+R2IQ_API int r2iq_cuda_get_filter(r2iq_cuda_t h, int d, float* hw_interleaved, int n_complex);
+
+/* r2iqControlClass::setDecimate / getRatio  (Core/r2iq.h:22,30).  Like the reference, a new
+ * decimation takes effect at the next TurnOn (the worker latches it once, impl.hpp:3-6). */
+R2IQ_API int r2iq_cuda_set_decimate(r2iq_cuda_t h, int d);
+R2IQ_API int r2iq_cuda_get_decimate(r2iq_cuda_t h);
+R2IQ_API int r2iq_cuda_get_ratio(r2iq_cuda_t h);
+
+/* fft_mt_r2iq::setFreqOffset  (Core/fft_mt_r2iq.cpp:101-109): offset = f / (Fs/2) in [0,1);
+ * quantises the tune bin to a multiple of 4 (truncation toward zero) and returns the residual
+ * (mtunebin/halfFft - offset) * ratio for the fine-tune mixer.  Picked up by the next block. */
+R2IQ_API float r2iq_cuda_set_freq_offset(r2iq_cuda_t h, float offset);
+/* Direct access to mtunebin (Core/fft_mt_r2iq.h:90); must be a multiple of 4 in [0, halfFft). */
+R2IQ_API int r2iq_cuda_set_tunebin(r2iq_cuda_t h, int tunebin);
+R2IQ_API int r2iq_cuda_get_tunebin(r2iq_cuda_t h);
+
+/* r2iqControlClass::updateRand/getRand, setSideband/getSideband  (Core/r2iq.h:24-28). */
+R2IQ_API int r2iq_cuda_set_rand(r2iq_cuda_t h, int on);
+R2IQ_API int r2iq_cuda_get_rand(r2iq_cuda_t h);
+R2IQ_API int r2iq_cuda_set_sideband(r2iq_cuda_t h, int lsb);
+R2IQ_API int r2iq_cuda_get_sideband(r2iq_cuda_t h);
+
+/* fft_mt_r2iq::TurnOn / TurnOff / IsOn  (Core/fft_mt_r2iq.cpp:111-145).  TurnOn latches decimation
+ * and sideband and clears the carried history (a fresh ring starts from zeros here; the reference
+ * reads uninitialised ring memory for the first block, impl.hpp:32).  TurnOff drains outstanding work. */
+R2IQ_API int r2iq_cuda_turn_on(r2iq_cuda_t h);
+R2IQ_API int r2iq_cuda_turn_off(r2iq_cuda_t h);
+R2IQ_API int r2iq_cuda_is_on(r2iq_cuda_t h);
+
+/* Complex output samples per input block at the latched decimation: 32768 >> d. */
+R2IQ_API long r2iq_cuda_out_per_block(r2iq_cuda_t h);
+
+/* The worker loop body (Core/fft_mt_r2iq_impl.hpp:15-151) for n_blocks consecutive blocks held in
+ * HOST memory.  blocks: n_blocks*65536 int16.  history: the halfFft samples preceding blocks[0], or
+ * NULL to continue the stream (history carried from the previous call; zeros after TurnOn).
+ * iq_out: n_blocks*(32768>>d) complex floats, interleaved.  Copies host->device, runs the fused
+ * kernel and copies device->host in pipelined chunks; returns when iq_out is complete.
+ * Pinned host memory (r2iq_cuda_host_alloc) is needed for the copies to overlap. */
+R2IQ_API int r2iq_cuda_process(r2iq_cuda_t h, const int16_t* blocks, long n_blocks, const int16_t* history, float* iq_out);
+
+/* Same transform on DEVICE memory, asynchronously on the caller's stream (cudaStream_t passed as
+ * void*; NULL = the legacy default stream).  d_in points at [halfFft history samples | n_blocks
+ * blocks] contiguous in device memory (4-byte aligned); d_iq_out receives n_blocks*(32768>>d)
+ * complex floats.  No host synchronisation; stream state is not carried. */
+R2IQ_API int r2iq_cuda_process_device(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d_iq_out, void* stream);
+
+/* Block until everything issued through this handle has finished. */
+R2IQ_API int r2iq_cuda_sync(r2iq_cuda_t h);
+
+/* Page-locked host buffers for ring slots / captures (replaces `new T[]` in Core/dsp/ringbuffer.h:166). */
+R2IQ_API void* r2iq_cuda_host_alloc(size_t bytes);
+R2IQ_API int r2iq_cuda_host_free(void* p);
+
+/* convert_float<rand>  (Core/fft_mt_r2iq.h:36-51) on its own: n int16 host samples (n even) ->
+ * n floats, through the same device code the fused kernel uses.  Parity hook for the stage that
+ * must be bit-exact. */
+R2IQ_API int r2iq_cuda_convert(r2iq_cuda_t h, const int16_t* in, long n, int rand, float* out);
+
+R2IQ_API int r2iq_cuda_get_stats(r2iq_cuda_t h, r2iq_cuda_stats* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* R2IQ_CUDA_H */
