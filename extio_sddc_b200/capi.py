@@ -69,6 +69,9 @@ _SIGNATURES = {
     "r2iq_cuda_host_free": (_I, [_VP]),
     "r2iq_cuda_convert": (_I, [_VP, _VP, _L, _I, _VP]),
     "r2iq_cuda_get_stats": (_I, [_VP, ctypes.POINTER(Stats)]),
+    "r2iq_cuda_design_filter": (_I, [_F, _I, _VP, _I]),
+    "r2iq_cuda_kaiser": (_I, [_I, _F, _F, _F, _VP]),
+    "r2iq_cuda_freq_to_tunebin": (_F, [_F, _I, ctypes.POINTER(_I)]),
 }
 
 

@@ -339,9 +339,8 @@ int r2iq_cuda_get_ratio(r2iq_cuda_t h) { return h ? (1 << h->decimate) : R2IQ_E_
 float r2iq_cuda_set_freq_offset(r2iq_cuda_t h, float offset) {
     if (!h) return 0.f;
     // float arithmetic and truncation exactly as the reference (Core/fft_mt_r2iq.cpp:104-106)
-    int tb = int(offset * kHalfFft / 4) * 4;
-    float delta = ((float)tb / kHalfFft) - offset;
-    float ret = delta * (float)(1 << h->decimate);
+    int tb = 0;
+    const float ret = r2iq_cuda_freq_to_tunebin(offset, h->decimate, &tb);
     // The reference stores whatever comes out; bins outside [0, halfFft) would index out of
     // bounds there (offset is documented as [0,1)), so clamp instead of reading garbage.
     if (tb < 0) tb = 0;
@@ -509,6 +508,31 @@ int r2iq_cuda_get_stats(r2iq_cuda_t h, r2iq_cuda_stats* out) {
     if (!h || !out) return fail(R2IQ_E_INVALID, "null argument");
     *out = h->stats;
     return R2IQ_OK;
+}
+
+int r2iq_cuda_design_filter(float gain, int d, float* hw, int n_complex) {
+    if (d < 0 || d >= kNDec || !hw || n_complex != kHalfFft)
+        return fail(R2IQ_E_INVALID, "design_filter: d=%d n_complex=%d (want 0..6, %d)", d, n_complex, kHalfFft);
+    const std::vector<std::complex<float>> H = design_filter_response(gain, d, kFftN);
+    for (int k = 0; k < kHalfFft; k++) {
+        hw[2 * k] = H[k].real();
+        hw[2 * k + 1] = H[k].imag();
+    }
+    return R2IQ_OK;
+}
+
+int r2iq_cuda_kaiser(int num_taps, float astop_db, float f_pass, float f_stop, float* taps) {
+    if (num_taps <= 0 || !taps) return fail(R2IQ_E_INVALID, "kaiser: num_taps must be positive");
+    const std::vector<float> t = kaiser_lowpass(num_taps, astop_db, f_pass, f_stop);
+    memcpy(taps, t.data(), sizeof(float) * (size_t)num_taps);
+    return R2IQ_OK;
+}
+
+float r2iq_cuda_freq_to_tunebin(float offset, int d, int* tunebin) {
+    const int tb = int(offset * kHalfFft / 4) * 4;
+    const float delta = ((float)tb / kHalfFft) - offset;
+    if (tunebin) *tunebin = tb;
+    return delta * (float)(1 << (d < 0 ? 0 : d));
 }
 
 }  // extern "C"

@@ -160,6 +160,26 @@ class CudaR2IQ:
         return out
 
 
+def design_filter(gain: float, d: int) -> np.ndarray:
+    """Host-side filter design of Init for one decimation (device-free): halfFft complex64 bins."""
+    out = np.zeros(2 * HALF_FFT, dtype=np.float32)
+    capi.check(capi.load().r2iq_cuda_design_filter(float(gain), int(d), out.ctypes.data, HALF_FFT))
+    return out.view(np.complex64)
+
+
+def kaiser_taps(num_taps: int, astop_db: float, f_pass: float, f_stop: float) -> np.ndarray:
+    out = np.zeros(int(num_taps), dtype=np.float32)
+    capi.check(capi.load().r2iq_cuda_kaiser(int(num_taps), float(astop_db), float(f_pass), float(f_stop), out.ctypes.data))
+    return out
+
+
+def freq_to_tunebin(offset: float, d: int):
+    """(tunebin, residual) of setFreqOffset without touching an operator (device-free)."""
+    tb = ctypes.c_int(0)
+    r = capi.load().r2iq_cuda_freq_to_tunebin(float(offset), int(d), ctypes.byref(tb))
+    return tb.value, float(r)
+
+
 class PinnedBuffer:
     """Page-locked host buffer (r2iq_cuda_host_alloc) exposed as a numpy array, so the H2D/D2H
     copies inside process() run asynchronously and overlap with the kernels."""

@@ -142,6 +142,16 @@ R2IQ_API int r2iq_cuda_convert(r2iq_cuda_t h, const int16_t* in, long n, int ran
 
 R2IQ_API int r2iq_cuda_get_stats(r2iq_cuda_t h, r2iq_cuda_stats* out);
 
+/* Device-free host logic (usable without a GPU; exercised by the CPU test suite).
+ *  design_filter:  filterHw[d] exactly as r2iq_cuda_create designs it (KaiserWindow + tap placement +
+ *                  gain + spectrum; Core/fir.cpp:48-105, Core/fft_mt_r2iq.cpp:181-205); hw = halfFft complex.
+ *  kaiser:         the Kaiser-windowed sinc taps alone (Core/fir.cpp:48 KaiserWindow, num_taps > 0 form).
+ *  freq_to_tunebin: the quantisation of fft_mt_r2iq::setFreqOffset (Core/fft_mt_r2iq.cpp:101-109);
+ *                  returns the residual and stores the UNCLAMPED tune bin. */
+R2IQ_API int r2iq_cuda_design_filter(float gain, int d, float* hw_interleaved, int n_complex);
+R2IQ_API int r2iq_cuda_kaiser(int num_taps, float astop_db, float f_pass, float f_stop, float* taps);
+R2IQ_API float r2iq_cuda_freq_to_tunebin(float offset, int d, int* tunebin);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,276 @@
+"""GPU suite (-m gpu): the CUDA path, called through the C ABI, against the oracle.
+
+Bars (BASELINE.json north_star): bit-exact through de-randomise/convert; output IQ within
+relative L2 <= 1e-5 and max-abs <= 1e-4 of full scale (32768*gain*1024) of the reference.
+"""
+import ctypes
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, case_input
+from extio_sddc_b200 import CudaR2IQ, PinnedBuffer, capi
+from oracle import r2iq_oracle as orc
+
+pytestmark = pytest.mark.gpu
+
+GAIN = orc.RX888MK2_GAINFACTOR
+REL_L2_TOL = 1e-5          # north_star: relative L2 error <= 1e-5
+MAX_ABS_TOL = 1e-4         # north_star: max abs <= 1e-4 of full scale
+
+
+def check(got, ref, gain, what):
+    e = orc.rel_l2(got, ref)
+    m = float(np.abs(got.astype(np.complex128) - ref.astype(np.complex128)).max()) / orc.full_scale(gain)
+    assert e <= REL_L2_TOL, (what, "rel_l2", e)
+    assert m <= MAX_ABS_TOL, (what, "max_abs/full_scale", m)
+
+
+@pytest.fixture(scope="module")
+def op():
+    r = CudaR2IQ()
+    r.Init(GAIN)
+    yield r
+    r.close()
+
+
+def run(op, x, d, tb, rand=False, lsb=False, history=None):
+    op.setDecimate(d)
+    op.updateRand(rand)
+    op.setSideband(lsb)
+    op.tunebin = tb
+    op.TurnOn()
+    y = op.process(x, history=history)
+    op.TurnOff()
+    return y
+
+
+def test_convert_bit_exact(op):
+    z = np.load(os.path.join(GOLDEN, "convert.npz"))
+    x = z["x"]
+    if x.shape[0] % 2:
+        x = x[:-1]
+    for rnd, key in ((False, "plain"), (True, "rand")):
+        got = op.convert_float(x, rnd)
+        assert np.array_equal(got, z[key][: x.shape[0]]), key
+    # every int16 value, both modes
+    allv = np.arange(-32768, 32768, dtype=np.int32).astype(np.int16)
+    for rnd in (False, True):
+        assert np.array_equal(op.convert_float(allv, rnd), orc.convert_float(allv, rnd))
+
+
+def test_golden_cases(golden_cases):
+    for c in golden_cases["cases"]:
+        r = CudaR2IQ()
+        r.Init(c["gain"])
+        x, h = case_input(c, golden_cases["history"])
+        got = run(r, x, c["d"], c["tunebin"], c["rand"], c["sideband"], history=h)
+        r.close()
+        assert got.shape == c["out"].shape
+        check(got, c["out"], c["gain"], c["name"])
+
+
+@pytest.mark.parametrize("d", range(7))
+def test_parity_matrix(op, d):
+    # config 2 signal (rand on) at the default tune bin, plus edge tune bins with zero-filled bands
+    for tb, rnd, lsb in ((256, True, False), (0, False, False), (1020, True, True), (512, False, True),
+                         (4, True, False), (1024 - (1024 >> d) // 2, False, False), ((1024 >> d) // 2, True, False)):
+        tb = max(0, min(1020, tb)) & ~3
+        x = orc.rx888_blocks(3, d, tb, randomized=rnd, seed=1000 + 7 * d + tb)
+        hist = np.random.default_rng(d).integers(-3000, 3000, 1024).astype(np.int16)
+        got = run(op, x, d, tb, rnd, lsb, history=hist)
+        ref = orc.r2iq(x, d, tb, gain=GAIN, rand=rnd, sideband=lsb, history=hist)
+        check(got, ref, GAIN, (d, tb, rnd, lsb))
+
+
+def test_config1_hf_64msps(op):
+    # BASELINE config 1: synthetic tone 64 Msps, decimation 2 (d=0), default tune and tuned to 5 MHz
+    r = CudaR2IQ()
+    r.Init(orc.BBRF103_GAINFACTOR)
+    x = orc.tone_blocks(4)
+    check(run(r, x, 0, 256), orc.r2iq(x, 0, 256, gain=orc.BBRF103_GAINFACTOR), orc.BBRF103_GAINFACTOR, "tone")
+    x = orc.sine_blocks(4, 5e6, 64e6)
+    r.setDecimate(0)
+    res = r.setFreqOffset(5e6 / 32e6)
+    tb, want_res = orc.set_freq_offset(5e6 / 32e6, 0)
+    assert r.tunebin == tb and res == pytest.approx(want_res, abs=1e-9)
+    r.TurnOn()
+    y = r.process(x)
+    r.TurnOff()
+    check(y, orc.r2iq(x, 0, tb, gain=orc.BBRF103_GAINFACTOR), orc.BBRF103_GAINFACTOR, "sine5m")
+    r.close()
+
+
+def test_config3_vhf_tune_sweep(op):
+    # BASELINE config 3: R828D IF point 4.57 MHz (no inversion), then a retune sweep between batches
+    # over the TuneTest grid of unittest/core_test.cpp:186 plus band-edge points, d = 2 and d = 5
+    offsets = [f / 32e6 for f in np.arange(1e3, 15e6, 1508e3)] + [4.57e6 / 32e6, 0.0, 0.004, 0.97, 0.999]
+    for d in (2, 5):
+        op.setDecimate(d)
+        op.updateRand(False)
+        op.setSideband(False)
+        op.TurnOn()
+        hist = None
+        for i, off in enumerate(offsets):
+            res = op.setFreqOffset(off)            # retune while "streaming"
+            tb, want = orc.set_freq_offset(off, d)
+            assert op.tunebin == tb
+            assert res == pytest.approx(want, abs=1e-9)
+            x = orc.rx888_blocks(1, d, tb, randomized=False, seed=50 + i)
+            got = op.process(x, history=hist if hist is not None else np.zeros(1024, np.int16))
+            ref = orc.r2iq(x, d, tb, gain=GAIN, history=hist)
+            check(got, ref, GAIN, ("sweep", d, off))
+            hist = x[-1024:]
+        op.TurnOff()
+    # one sideband = true case to cover copy<true>
+    x = orc.rx888_blocks(2, 2, 144, randomized=False)
+    check(run(op, x, 2, 144, lsb=True), orc.r2iq(x, 2, 144, gain=GAIN, sideband=True), GAIN, "lsb")
+
+
+def test_streaming_carries_history(op):
+    # one call over N blocks == block-by-block calls with the state carried by the handle
+    x = orc.rx888_blocks(5, 1, 256, randomized=True)
+    whole = run(op, x, 1, 256, rand=True)
+    op.setDecimate(1); op.updateRand(True); op.setSideband(False); op.tunebin = 256
+    op.TurnOn()
+    parts = [op.process(x[b * 65536:(b + 1) * 65536]) for b in range(5)]
+    op.TurnOff()
+    assert np.array_equal(np.concatenate(parts), whole)
+    # TurnOn resets the history to zeros
+    again = run(op, x, 1, 256, rand=True)
+    assert np.array_equal(again, whole)
+
+
+def test_chunked_pipeline_and_ragged_sizes():
+    # chunk size that does not divide the block count; pinned and pageable host buffers
+    r = CudaR2IQ(chunk_blocks=4)
+    r.Init(GAIN)
+    for nb in (1, 3, 4, 5, 11):
+        for d in (0, 3, 6):
+            x = orc.rx888_blocks(nb, d, 256, randomized=True, seed=nb * 10 + d)
+            pin_in = PinnedBuffer(x.shape[0], np.int16)
+            pin_in.array[:] = x
+            pin_out = PinnedBuffer(nb * (32768 >> d), np.complex64)
+            got = run(r, pin_in.array, d, 256, rand=True)
+            r.setDecimate(d); r.TurnOn()
+            got2 = r.process(pin_in.array, out=pin_out.array).copy()
+            r.TurnOff()
+            ref = orc.r2iq(x, d, 256, gain=GAIN, rand=True)
+            check(got, ref, GAIN, ("chunk", nb, d))
+            assert np.array_equal(got, got2)
+            pin_in.free(); pin_out.free()
+    st = r.stats()
+    assert st.kernel_launches > 0 and st.h2d_bytes > 0 and st.d2h_bytes > 0 and st.cc_major == 10
+    r.close()
+
+
+def test_empty_and_error_behaviour():
+    r = CudaR2IQ()
+    r.Init(GAIN)
+    with pytest.raises(capi.R2iqError) as ei:          # process before TurnOn
+        r.process(np.zeros(65536, np.int16))
+    assert ei.value.code == capi.E_STATE
+    r.TurnOn()
+    assert r.process(np.zeros(0, np.int16)).shape == (0,)
+    with pytest.raises(ValueError):
+        r.process(np.zeros(1000, np.int16))
+    with pytest.raises(capi.R2iqError):
+        r.tunebin = 255                                  # not a multiple of 4
+    with pytest.raises(capi.R2iqError):
+        r.setDecimate(7)
+    assert r.IsOn()
+    r.TurnOff()
+    assert not r.IsOn()
+    assert r.getRatio() == 1
+    r.setDecimate(3)
+    assert r.getRatio() == 8
+    # decimation is latched at TurnOn like the reference worker (impl.hpp:3-6)
+    r.TurnOn(); r.setDecimate(1)
+    assert r.out_per_block() == 32768 >> 3
+    r.TurnOff()
+    r.close()
+
+
+def test_zero_and_dc_input(op):
+    y = run(op, np.zeros(2 * 65536, np.int16), 0, 256)
+    assert np.all(y == 0)
+    # DC input tuned away from DC: nothing in band (signal_integrity_test.cpp:367-407 analogue)
+    x = np.full(2 * 65536, 1000, np.int16)
+    y = run(op, x, 2, 512)
+    assert np.abs(y[4096:]).max() < 1e-5 * 1000 * GAIN * 1024
+
+
+def test_custom_filter_upload(op):
+    # host-designed filter uploaded through set_filter (north star: "uploaded once per setDecimate/tune")
+    r = CudaR2IQ()
+    r.Init(GAIN)
+    H = orc.design_filter(GAIN, 2) * np.complex64(0.5)
+    r.set_filter_hw(2, H)
+    assert np.array_equal(r.filter_hw(2), H)
+    x = orc.rx888_blocks(2, 2, 256, randomized=False)
+    got = run(r, x, 2, 256)
+    ref = orc.r2iq(x, 2, 256, gain=GAIN, filter_hw=H)
+    check(got, ref, GAIN * 0.5, "custom filter")
+    r.close()
+
+
+def test_device_resident_path_matches_host_path(op):
+    import torch
+    x = orc.rx888_blocks(6, 0, 256, randomized=True)
+    host = run(op, x, 0, 256, rand=True)
+    dev = torch.device("cuda:0")
+    buf = torch.zeros(1024 + x.shape[0], dtype=torch.int16, device=dev)
+    buf[1024:] = torch.from_numpy(x).to(dev)
+    out = torch.empty(6 * 32768, dtype=torch.complex64, device=dev)
+    op.setDecimate(0); op.updateRand(True); op.setSideband(False); op.tunebin = 256
+    op.TurnOn()
+    op.process_device(buf.data_ptr(), 6, out.data_ptr(), torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    op.TurnOff()
+    assert np.array_equal(out.cpu().numpy(), host)
+
+
+@pytest.mark.parametrize("d", [0, 5])
+def test_full_size_properties(d):
+    """BASELINE config 2 size (8192 blocks, 537 M samples) through size-independent properties:
+    (a) time-slab split with halo == whole capture (what multi-GPU sharding relies on),
+    (b) linearity: r2iq(2x) == 2*r2iq(x) to float rounding,
+    (c) a sampled window agrees with the oracle."""
+    import torch
+    n_blocks = 8192
+    dev = torch.device("cuda:0")
+    g = torch.Generator(device=dev)
+    g.manual_seed(888 + d)
+    x = torch.randint(-4000, 4000, (1024 + n_blocks * 65536,), dtype=torch.int16, device=dev, generator=g)
+    x[:1024] = 0
+    opb = 32768 >> d
+    r = CudaR2IQ()
+    r.Init(GAIN)
+    r.setDecimate(d); r.updateRand(False); r.tunebin = 256
+    r.TurnOn()
+    s = torch.cuda.current_stream().cuda_stream
+    whole = torch.empty(n_blocks * opb, dtype=torch.complex64, device=dev)
+    r.process_device(x.data_ptr(), n_blocks, whole.data_ptr(), s)
+    # (a) two slabs; the second starts at a block boundary and reads its halo from the first
+    half = n_blocks // 2
+    parts = torch.empty_like(whole)
+    r.process_device(x.data_ptr(), half, parts.data_ptr(), s)
+    r.process_device(x.data_ptr() + 2 * half * 65536, n_blocks - half, parts.data_ptr() + 8 * half * opb, s)
+    torch.cuda.synchronize()
+    assert torch.equal(whole, parts)
+    # (b)
+    x2 = x * 2
+    dbl = torch.empty_like(whole)
+    r.process_device(x2.data_ptr(), n_blocks, dbl.data_ptr(), s)
+    torch.cuda.synchronize()
+    err = (torch.linalg.vector_norm(dbl - 2 * whole) / torch.linalg.vector_norm(dbl)).item()
+    assert err < 1e-6, err
+    # (c) blocks [4000, 4003) against the oracle
+    b0 = 4000
+    xin = x[1024 + b0 * 65536: 1024 + (b0 + 3) * 65536].cpu().numpy()
+    hist = x[b0 * 65536: 1024 + b0 * 65536].cpu().numpy()
+    ref = orc.r2iq(xin, d, 256, gain=GAIN, history=hist)
+    check(whole[b0 * opb:(b0 + 3) * opb].cpu().numpy(), ref, GAIN, ("full-size window", d))
+    r.TurnOff()
+    r.close()
