@@ -26,8 +26,12 @@
 
 namespace r2iq {
 
-constexpr int kWarpsPerCta = 8;
+// Small CTAs (4 warps) so that 3 of them fit an SM: 12 resident warps hide the DRAM latency of the
+// 32 loads that open every frame.  A warp never talks to another warp, so CTA size is purely an
+// occupancy knob (registers: 3*128*170 <= 64K; shared memory: 3*68.6 KB <= 227 KB for d >= 1).
+constexpr int kWarpsPerCta = 4;
 constexpr int kThreads = kWarpsPerCta * 32;
+constexpr int kMinCtasPerSm = 3;
 constexpr int kScratch = 32 * 33;   // float2 per warp: 32x32 transposition tile, row pitch 33
 constexpr int kStage = 64 * 17;     // float2 per warp: staged bands of 2^d frames (max over d)
 
@@ -142,7 +146,7 @@ __device__ __forceinline__ void band_rows(const FusedParams& p, const float2 (&v
 }
 
 template <int D>
-__global__ void __launch_bounds__(kThreads) r2iq_fused_kernel(const FusedParams p) {
+__global__ void __launch_bounds__(kThreads, kMinCtasPerSm) r2iq_fused_kernel(const FusedParams p) {
     using G = Geo<D>;
     extern __shared__ float2 smem[];
     const int lane = threadIdx.x & 31;
@@ -270,8 +274,12 @@ static cudaError_t launch_one(const FusedParams& p, int sm_count, cudaStream_t s
 
 template <int D>
 static cudaError_t setup_one() {
-    return cudaFuncSetAttribute(r2iq_fused_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                (int)Geo<D>::SMEM_BYTES);
+    cudaError_t e = cudaFuncSetAttribute(r2iq_fused_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)Geo<D>::SMEM_BYTES);
+    if (e != cudaSuccess) return e;
+    // ask for the largest shared-memory carve-out so that kMinCtasPerSm CTAs are resident
+    return cudaFuncSetAttribute(r2iq_fused_kernel<D>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                cudaSharedmemCarveoutMaxShared);
 }
 
 cudaError_t setup_fused_kernels() {
