@@ -1,0 +1,144 @@
+// dft_regs2.cuh -- the register-resident DFTs of dft_regs.cuh on PACKED fp32x2 lanes (sm_100a).
+//
+// Blackwell adds packed single-precision instructions (PTX add/sub/mul/fma.rn.f32x2, SASS
+// FADD2/FMUL2/FFMA2).  Measured on B200 (tools/ubench/fp32_pipes.cu): a warp-wide FFMA2 retires
+// 64 FMAs and occupies the FMA pipe for two cycles, so the peak FLOP rate equals scalar FFMA but
+// it costs half the ISSUE slots -- the other slot is free for the loads, stores, shuffles and
+// integer work that otherwise compete with the butterflies.  The r2iq kernels therefore run TWO
+// independent frames per warp side by side: every value is a pair (frame A, frame B) in one
+// 64-bit register, every butterfly one packed instruction, and all twiddles (compile-time
+// immediates or per-lane scalars broadcast by the instruction's .F32 operand form) are shared.
+//
+// Negation is written as unpack/negate/repack; ptxas folds it into the operand's negate modifier
+// (verified in SASS: FFMA2 R6, R4.F32x2.HI_LO, 2, -R6.F32x2.HI_LO), so it is free.
+#pragma once
+#include <cuda_runtime.h>
+#include <utility>
+
+#include "dft_regs.cuh"
+
+namespace r2iq {
+
+typedef unsigned long long u64;
+
+__device__ __forceinline__ u64 pk(float lo, float hi) {
+    u64 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void upk(u64 v, float& lo, float& hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ u64 bc(float s) { return pk(s, s); }   // broadcast a scalar to both frames
+__device__ __forceinline__ u64 add2(u64 a, u64 b) {
+    u64 d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+__device__ __forceinline__ u64 sub2(u64 a, u64 b) {
+    u64 d;
+    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+__device__ __forceinline__ u64 mul2(u64 a, u64 b) {
+    u64 d;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+__device__ __forceinline__ u64 fma2(u64 a, u64 b, u64 c) {   // a*b + c
+    u64 d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+__device__ __forceinline__ u64 neg2(u64 a) {
+    float lo, hi;
+    upk(a, lo, hi);
+    return pk(-lo, -hi);
+}
+
+// complex value of two frames: re = (A.re, B.re), im = (A.im, B.im)
+struct c2 {
+    u64 re, im;
+};
+
+// v * w for a per-lane scalar complex w shared by both frames (4 packed ops)
+__device__ __forceinline__ c2 cmul2s(c2 v, float2 w) {
+    c2 r;
+    r.re = fma2(bc(w.x), v.re, mul2(bc(-w.y), v.im));
+    r.im = fma2(bc(w.x), v.im, mul2(bc(w.y), v.re));
+    return r;
+}
+
+// radix-2 DIT butterfly, compile-time twiddle exp(-+2*pi*i*J/LEN), packed version of bfly<>
+template <int J, int LEN, bool INV>
+__device__ __forceinline__ void bfly2(c2& a, c2& b) {
+    constexpr float kInvSqrt2 = 0.70710678118654752440f;
+    if constexpr (J == 0) {
+        c2 t = b;
+        b.re = sub2(a.re, t.re);
+        b.im = sub2(a.im, t.im);
+        a.re = add2(a.re, t.re);
+        a.im = add2(a.im, t.im);
+    } else if constexpr (4 * J == LEN) {
+        // forward w = -i: w*b = (b.im, -b.re); inverse w = +i: w*b = (-b.im, b.re)
+        c2 t = b;
+        if constexpr (INV) {
+            b.re = add2(a.re, t.im);
+            b.im = sub2(a.im, t.re);
+            a.re = sub2(a.re, t.im);
+            a.im = add2(a.im, t.re);
+        } else {
+            b.re = sub2(a.re, t.im);
+            b.im = add2(a.im, t.re);
+            a.re = add2(a.re, t.im);
+            a.im = sub2(a.im, t.re);
+        }
+    } else if constexpr (8 * J == LEN) {
+        u64 tx = INV ? sub2(b.re, b.im) : add2(b.re, b.im);
+        u64 ty = INV ? add2(b.re, b.im) : sub2(b.im, b.re);
+        b.re = fma2(bc(-kInvSqrt2), tx, a.re);
+        b.im = fma2(bc(-kInvSqrt2), ty, a.im);
+        a.re = fma2(bc(kInvSqrt2), tx, a.re);
+        a.im = fma2(bc(kInvSqrt2), ty, a.im);
+    } else if constexpr (8 * J == 3 * LEN) {
+        u64 tx = INV ? add2(b.re, b.im) : sub2(b.im, b.re);
+        u64 ty = INV ? sub2(b.re, b.im) : add2(b.re, b.im);
+        if constexpr (INV) {
+            b.re = fma2(bc(kInvSqrt2), tx, a.re);
+            b.im = fma2(bc(-kInvSqrt2), ty, a.im);
+            a.re = fma2(bc(-kInvSqrt2), tx, a.re);
+            a.im = fma2(bc(kInvSqrt2), ty, a.im);
+        } else {
+            b.re = fma2(bc(-kInvSqrt2), tx, a.re);
+            b.im = fma2(bc(kInvSqrt2), ty, a.im);
+            a.re = fma2(bc(kInvSqrt2), tx, a.re);
+            a.im = fma2(bc(-kInvSqrt2), ty, a.im);
+        }
+    } else {
+        constexpr float wr = (float)cx_cos2pi(J, LEN);
+        constexpr float wi = (float)(INV ? cx_sin2pi(J, LEN) : -cx_sin2pi(J, LEN));
+        u64 ax = fma2(bc(wr), b.re, fma2(bc(-wi), b.im, a.re));
+        u64 ay = fma2(bc(wr), b.im, fma2(bc(wi), b.re, a.im));
+        b.re = fma2(bc(2.0f), a.re, neg2(ax));     // b' = 2a - a'
+        b.im = fma2(bc(2.0f), a.im, neg2(ay));
+        a.re = ax;
+        a.im = ay;
+    }
+}
+
+template <int N, int LEN, bool INV, int... T>
+__device__ __forceinline__ void dit2_stage(c2 (&v)[N], std::integer_sequence<int, T...>) {
+    constexpr int half = LEN / 2;
+    (bfly2<(T % half), LEN, INV>(v[(T / half) * LEN + (T % half)], v[(T / half) * LEN + (T % half) + half]), ...);
+}
+
+// packed counterpart of dit<N, INV>: bit-reversed input order, natural output order, unnormalised
+template <int N, bool INV, int LEN = 2>
+__device__ __forceinline__ void dit2(c2 (&v)[N]) {
+    if constexpr (N >= 2) {
+        dit2_stage<N, LEN, INV>(v, std::make_integer_sequence<int, N / 2>{});
+        if constexpr (LEN < N) dit2<N, INV, LEN * 2>(v);
+    }
+}
+
+}  // namespace r2iq

@@ -10,6 +10,7 @@
 #include <complex>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <mutex>
@@ -42,6 +43,8 @@ constexpr size_t kMaxTableSets = 1024;    // cached (d, tunebin) table sets befo
 struct TableSet {   // device tables for one (decimation, tune bin)
     float2* gk = nullptr;
     float2* gck = nullptr;
+    float2* gp = nullptr;
+    float2* gq = nullptr;
     float2* tw_inv = nullptr;
     int band_lo = 0, band_hi = 0;
 };
@@ -108,6 +111,8 @@ void free_tables(r2iq_cuda_t h) {
     for (auto& kv : h->tables) {
         cudaFree(kv.second.gk);
         cudaFree(kv.second.gck);
+        cudaFree(kv.second.gp);
+        cudaFree(kv.second.gq);
         cudaFree(kv.second.tw_inv);
     }
     h->tables.clear();
@@ -134,7 +139,7 @@ int get_tables(r2iq_cuda_t h, int d, int tunebin, TableSet* out) {
         free_tables(h);
     }
     const int M = kHalfFft >> d;
-    std::vector<float2> gk(kHalfFft), gck(kHalfFft);
+    std::vector<float2> gk(kHalfFft), gck(kHalfFft), gp(kHalfFft), gq(kHalfFft);
     const std::vector<std::complex<float>>& H = h->hw[d];
     TableSet ts;
     ts.band_lo = tunebin - M / 2 < 0 ? 0 : tunebin - M / 2;
@@ -148,9 +153,10 @@ int get_tables(r2iq_cuda_t h, int d, int tunebin, TableSet* out) {
             const std::complex<double> gc = c * hh;
             gk[k] = make_float2((float)hh.real(), (float)hh.imag());
             gck[k] = make_float2((float)gc.real(), (float)gc.imag());
+            gp[k] = make_float2((float)(hh.real() + gc.real()), (float)(hh.imag() + gc.imag()));
+            gq[k] = make_float2((float)(hh.real() - gc.real()), (float)(hh.imag() - gc.imag()));
         } else {
-            gk[k] = make_float2(0.f, 0.f);
-            gck[k] = make_float2(0.f, 0.f);
+            gk[k] = gck[k] = gp[k] = gq[k] = make_float2(0.f, 0.f);
         }
     }
     std::vector<float2> tw(32 * 32);
@@ -173,9 +179,13 @@ int get_tables(r2iq_cuda_t h, int d, int tunebin, TableSet* out) {
     }
     CU(h, cudaMalloc(&ts.gk, sizeof(float2) * kHalfFft));
     CU(h, cudaMalloc(&ts.gck, sizeof(float2) * kHalfFft));
+    CU(h, cudaMalloc(&ts.gp, sizeof(float2) * kHalfFft));
+    CU(h, cudaMalloc(&ts.gq, sizeof(float2) * kHalfFft));
     CU(h, cudaMalloc(&ts.tw_inv, sizeof(float2) * 32 * 32));
     CU(h, cudaMemcpy(ts.gk, gk.data(), sizeof(float2) * kHalfFft, cudaMemcpyHostToDevice));
     CU(h, cudaMemcpy(ts.gck, gck.data(), sizeof(float2) * kHalfFft, cudaMemcpyHostToDevice));
+    CU(h, cudaMemcpy(ts.gp, gp.data(), sizeof(float2) * kHalfFft, cudaMemcpyHostToDevice));
+    CU(h, cudaMemcpy(ts.gq, gq.data(), sizeof(float2) * kHalfFft, cudaMemcpyHostToDevice));
     CU(h, cudaMemcpy(ts.tw_inv, tw.data(), sizeof(float2) * 32 * 32, cudaMemcpyHostToDevice));
     h->tables[key] = ts;
     *out = ts;
@@ -194,6 +204,8 @@ int launch(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d_out, cuda
     p.tw_fwd = h->d_tw_fwd;
     p.gk = ts.gk;
     p.gck = ts.gck;
+    p.gp = ts.gp;
+    p.gq = ts.gq;
     p.tw_inv = ts.tw_inv;
     p.tunebin = h->tunebin;
     p.band_lo = ts.band_lo;
@@ -260,6 +272,7 @@ int r2iq_cuda_create(const r2iq_cuda_config* cfg, r2iq_cuda_t* out) {
         return rc;
     };
     if ((e = cudaSetDevice(dev)) != cudaSuccess) return bail(fail(R2IQ_E_CUDA, "cudaSetDevice: %s", cudaGetErrorString(e)));
+    if (const char* gen = getenv("R2IQ_KERNEL_GEN")) set_kernel_generation(atoi(gen));   // A/B measurements only
     if ((e = setup_fused_kernels()) != cudaSuccess)
         return bail(fail(R2IQ_E_CUDA, "kernel setup: %s", cudaGetErrorString(e)));
     // forward inter-pass twiddles exp(-2 pi i k2 l / 1024)
@@ -453,8 +466,8 @@ int r2iq_cuda_process_device(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, 
     if (rc) return rc;
     if (!h->on) return fail(R2IQ_E_STATE, "process called while the operator is off (call r2iq_cuda_turn_on)");
     if (n_blocks < 0 || (n_blocks > 0 && (!d_in || !d_iq_out))) return fail(R2IQ_E_INVALID, "process_device: bad buffers");
-    if (((uintptr_t)d_in & 3) || ((uintptr_t)d_iq_out & 7))
-        return fail(R2IQ_E_INVALID, "process_device: input must be 4-byte and output 8-byte aligned");
+    if (((uintptr_t)d_in & 15) || ((uintptr_t)d_iq_out & 7))
+        return fail(R2IQ_E_INVALID, "process_device: input must be 16-byte and output 8-byte aligned");
     if (n_blocks == 0) return R2IQ_OK;
     std::lock_guard<std::mutex> lk(h->mu);
     return launch(h, d_in, n_blocks, d_iq_out, (cudaStream_t)stream);

@@ -282,8 +282,12 @@ static cudaError_t setup_one() {
                                 cudaSharedmemCarveoutMaxShared);
 }
 
+static int g_kernel_gen = 0;
+void set_kernel_generation(int gen) { g_kernel_gen = gen; }
+
 cudaError_t setup_fused_kernels() {
     cudaError_t e;
+    if ((e = setup_dual_kernels()) != cudaSuccess) return e;
     if ((e = setup_one<0>()) != cudaSuccess) return e;
     if ((e = setup_one<1>()) != cudaSuccess) return e;
     if ((e = setup_one<2>()) != cudaSuccess) return e;
@@ -295,6 +299,7 @@ cudaError_t setup_fused_kernels() {
 }
 
 cudaError_t launch_fused(int d, const FusedParams& p, int sm_count, cudaStream_t stream) {
+    if (g_kernel_gen != 1 && d == 0) return launch_dual_d0(p, sm_count, stream, g_kernel_gen == 2);
     switch (d) {
         case 0: return launch_one<0>(p, sm_count, stream);
         case 1: return launch_one<1>(p, sm_count, stream);

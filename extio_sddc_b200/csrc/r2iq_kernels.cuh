@@ -21,6 +21,8 @@ struct FusedParams {
     const float2* tw_fwd;       // [32][32]  W_1024^(k2*lane), forward inter-pass twiddles
     const float2* gk;           // [1024]    0.5*H[(k-tunebin) mod 1024] inside the band, else 0
     const float2* gck;          // [1024]    (-i*W_2048^k) * gk[k]
+    const float2* gp;           // [1024]    gk + gck   (dual-frame kernel: Y = gp*a + gq*conj(b))
+    const float2* gq;           // [1024]    gk - gck
     const float2* tw_inv;       // d=0: [32][32] conj(W_1024)^((lane-tunebin)*k2); d>=1: [32][L] conj(W_M)^(n1*k2)
     int tunebin;
     int band_lo, band_hi;       // forward-FFT bins [lo,hi) that feed the inverse transform
@@ -30,6 +32,13 @@ struct FusedParams {
 
 // Launch the fused kernel for decimation index d on `stream`.  Returns cudaGetLastError().
 cudaError_t launch_fused(int d, const FusedParams& p, int sm_count, cudaStream_t stream);
+// Kernel generation selector for A/B measurements (env R2IQ_KERNEL_GEN): 0 = newest kernels (default),
+// 1 = first-generation one-frame-per-warp kernels for every d, 2 = dual-frame kernels with TMA input
+// staging.  All produce results within the parity bar.
+void set_kernel_generation(int gen);
+// second-generation kernels (r2iq_dual.cu): two frames per warp on packed fp32x2 lanes + TMA input
+cudaError_t setup_dual_kernels();
+cudaError_t launch_dual_d0(const FusedParams& p, int sm_count, cudaStream_t stream, bool tma);
 // One-time per-device setup (opt-in shared memory sizes).
 cudaError_t setup_fused_kernels();
 // int16 -> float with optional de-randomisation (the bit-exact stage, exposed for parity tests).

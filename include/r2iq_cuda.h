@@ -124,7 +124,7 @@ R2IQ_API int r2iq_cuda_process(r2iq_cuda_t h, const int16_t* blocks, long n_bloc
 
 /* Same transform on DEVICE memory, asynchronously on the caller's stream (cudaStream_t passed as
  * void*; NULL = the legacy default stream).  d_in points at [halfFft history samples | n_blocks
- * blocks] contiguous in device memory (4-byte aligned); d_iq_out receives n_blocks*(32768>>d)
+ * blocks] contiguous in device memory (16-byte aligned: frames are fetched by TMA bulk copies); d_iq_out receives n_blocks*(32768>>d)
  * complex floats.  No host synchronisation; stream state is not carried. */
 R2IQ_API int r2iq_cuda_process_device(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d_iq_out, void* stream);
 

@@ -18,6 +18,9 @@ from oracle import r2iq_oracle as orc  # noqa: E402
 GAIN = orc.RX888MK2_GAINFACTOR
 
 
+DECIMS = list(range(7))
+
+
 def parity():
     r = CudaR2IQ()
     r.Init(GAIN)
@@ -27,7 +30,7 @@ def parity():
         ok = np.array_equal(r.convert_float(x, rnd), orc.convert_float(x, rnd))
         print(f"convert rand={rnd}: bit-exact={ok}")
     cases = []
-    for d in range(7):
+    for d in DECIMS:
         cases += [(d, 256, True, False), (d, 0, False, False), (d, 1020, True, True), (d, 512, False, True), (d, 144, True, False)]
     for (d, tb, rnd, sb) in cases:
         nb = 3
@@ -46,7 +49,7 @@ def parity():
     return worst
 
 
-def timing(n_blocks):
+def timing(n_blocks, decims=range(7)):
     import torch
     r = CudaR2IQ()
     r.Init(GAIN)
@@ -55,7 +58,7 @@ def timing(n_blocks):
     x = torch.randint(-8000, 8000, (1024 + n_blocks * 65536,), dtype=torch.int16, device=dev, generator=g)
     out = torch.empty(n_blocks * 32768, dtype=torch.complex64, device=dev)
     stream = torch.cuda.current_stream().cuda_stream
-    for d in range(7):
+    for d in decims:
         r.setDecimate(d); r.updateRand(True); r.setSideband(False); r.tunebin = 256
         r.TurnOn()
         for _ in range(3):
@@ -78,7 +81,9 @@ if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--blocks", type=int, default=2048)
     ap.add_argument("--no-parity", action="store_true")
+    ap.add_argument("--decims", default="0,1,2,3,4,5,6")
     a = ap.parse_args()
+    DECIMS[:] = [int(v) for v in a.decims.split(",")]
     if not a.no_parity:
         parity()
-    timing(a.blocks)
+    timing(a.blocks, [int(v) for v in a.decims.split(",")])
