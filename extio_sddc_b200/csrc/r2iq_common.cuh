@@ -1,0 +1,128 @@
+// r2iq_common.cuh -- pieces shared by the one-frame (r2iq_kernels.cu) and dual-frame (r2iq_dual.cu)
+// fused kernels: geometry per decimation, output placement, and the batched backward transform
+// for d >= 1.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "dft_regs.cuh"
+#include "r2iq_kernels.cuh"
+
+namespace r2iq {
+
+constexpr int kScratch = 32 * 33;   // float2 per warp: 32x32 transposition tile, row pitch 33
+constexpr int kStage = 64 * 17;     // float2 per warp: staged bands of 2^d frames (max over d)
+
+template <int D>
+struct Geo {
+    static constexpr int M = kHalfFft >> D;                  // mfft: inverse FFT size
+    static constexpr int ROUNDS = 1 << D;                    // frames a warp runs per unit of work
+    static constexpr int L = (D <= 5) ? (32 >> D) : 1;       // lanes per frame in the inverse transform
+    static constexpr int GS = (D == 6) ? 17 : (M + L);       // staging pitch per frame (bank-conflict free)
+    static constexpr int OUT_PER_BLOCK = (kTransferSamples / 2) >> D;
+    static constexpr int WARP_SMEM = kScratch + (D > 0 ? kStage : 0);   // float2 per warp
+};
+
+__device__ __forceinline__ int brev(int v, int bits) { return (int)(__brev((unsigned)v) >> (32 - bits)); }
+
+// De-randomise (Core/fft_mt_r2iq.h:41-44: `val = input ^ (-2)` when the LSB is set) both int16
+// halves of a word at once, then convert each to float (exact).
+__device__ __forceinline__ float2 unpack_pair(uint32_t w, uint32_t rand_mul) {
+    w ^= (w & 0x00010001u) * rand_mul;
+    return make_float2((float)(short)(w & 0xFFFFu), (float)((int)w >> 16));
+}
+
+struct FrameOut {
+    long long base;   // out[base + idx] receives inverse-FFT sample idx
+    int lo, hi;       // kept range of idx
+};
+
+// Output placement of frame f = block*43 + k (impl.hpp:117-138): k == 0 keeps y[mfft/4, 3mfft/4),
+// k >= 1 keeps y[0, 3mfft/4) at offset mfft/2 + (k-1)*3mfft/4 inside the block's output.
+template <int D>
+__device__ __forceinline__ FrameOut frame_out(long long f) {
+    constexpr int M = Geo<D>::M;
+    long long b = f / kFramesPerBlock;
+    int k = (int)(f - b * kFramesPerBlock);
+    FrameOut o;
+    o.lo = k ? 0 : M / 4;
+    o.hi = 3 * M / 4;
+    o.base = b * (long long)Geo<D>::OUT_PER_BLOCK + (k ? (M / 2 + (k - 1) * (3 * M / 4)) : 0) - o.lo;
+    return o;
+}
+
+__device__ __forceinline__ void store_iq(float2* out, const FrameOut& fo, int idx, float2 v, float imag_sign) {
+    if (idx >= fo.lo && idx < fo.hi) out[fo.base + idx] = make_float2(v.x, v.y * imag_sign);
+}
+
+
+// Backward transforms of the 2^D frames of one unit, whose mfft-bin bands sit in `stage`
+// (frame g at stage + g*GS, bins in inverse-FFT order), 32>>D lanes per frame and 32 points per
+// lane; overlap-save discard, optional conjugate and placement as impl.hpp:117-138.
+// S is a float2[kScratch] transposition tile private to the warp.
+template <int D>
+__device__ __forceinline__ void inverse_batch(const FusedParams& p, long long f0, int lane, float2* S,
+                                              const float2* stage) {
+    using G = Geo<D>;
+    static_assert(D >= 1, "d = 0 keeps its spectrum in registers");
+    __syncwarp();
+    if constexpr (D <= 5) {
+        constexpr int L = G::L;
+        constexpr int NI = 32 / L;
+        constexpr int LB = ilog2(L);
+        const int g = lane / L;
+        const int n = lane % L;
+        float2 t[32];
+#pragma unroll
+        for (int n2 = 0; n2 < 32; n2++) t[brev(n2, 5)] = stage[g * G::GS + n + L * n2];
+        __syncwarp();
+        dit<32, true>(t);                        // pass 1: DFT over n2 within the frame
+        const long long f = f0 + g;
+        const FrameOut fo = frame_out<D>(f);
+        const bool live = f < p.total_frames;
+        if constexpr (L > 1) {
+#pragma unroll
+            for (int k2 = 1; k2 < 32; k2++) t[k2] = cmul(t[k2], __ldg(&p.tw_inv[k2 * L + n]));
+            float2* Sg = S + g * (33 * L);
+#pragma unroll
+            for (int k2 = 0; k2 < 32; k2++) Sg[n * 33 + k2] = t[k2];
+            __syncwarp();
+#pragma unroll
+            for (int i = 0; i < NI; i++) {
+                float2 x[L];
+#pragma unroll
+                for (int n1 = 0; n1 < L; n1++) x[brev(n1, LB)] = Sg[n1 * 33 + n + L * i];
+                dit<L, true>(x);                 // pass 2: DFT over n1
+                if (live) {
+#pragma unroll
+                    for (int k1 = 0; k1 < L; k1++) store_iq(p.out, fo, n + L * i + 32 * k1, x[k1], p.imag_sign);
+                }
+            }
+            __syncwarp();
+        } else {
+            if (live) {
+#pragma unroll
+                for (int k2 = 0; k2 < 32; k2++) store_iq(p.out, fo, k2, t[k2], p.imag_sign);
+            }
+        }
+    } else {
+        // d = 6: mfft = 16, 64 frames per unit, two whole 16-point transforms per lane
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+            const int g = lane + 32 * h;
+            float2 x[16];
+#pragma unroll
+            for (int n = 0; n < 16; n++) x[brev(n, 4)] = stage[g * G::GS + n];
+            dit<16, true>(x);
+            const long long f = f0 + g;
+            if (f < p.total_frames) {
+                const FrameOut fo = frame_out<D>(f);
+#pragma unroll
+                for (int n = 0; n < 16; n++) store_iq(p.out, fo, n, x[n], p.imag_sign);
+            }
+        }
+        __syncwarp();
+    }
+}
+
+}  // namespace r2iq

@@ -16,7 +16,7 @@
 #include <cstdlib>
 
 #include "dft_regs2.cuh"
-#include "r2iq_kernels.cuh"
+#include "r2iq_common.cuh"
 
 namespace r2iq {
 
@@ -31,10 +31,17 @@ constexpr int kDualThreads = kDualWarps * 32;
 //                 16.9 KB per warp, so 12 warps per SM (3 CTAs, 168 registers) hide the load latency.
 constexpr int kTile = 32 * 33;                // elements per plane: 32x32 tile, pitch 33 (conflict-free for 8 B accesses)
 constexpr int kFrameBytes = kFftN * 2;        // 4096 B of int16 per frame
-// per-warp shared memory: transposition tile (two 8-byte planes) [+ two input frames + one mbarrier]
-template <bool kTma>
+// per-warp shared memory: transposition tile (two 8-byte planes; doubles as the float2 tile of the
+// scalar backward transform for d >= 1) [+ staged bands, d >= 1] [+ two input frames + one mbarrier]
+template <int D, bool kTma>
 __host__ __device__ constexpr int warp_bytes() {
-    return kTile * 16 + (kTma ? 2 * kFrameBytes + 16 : 0);
+    return kTile * 16 + (D > 0 ? kStage * 8 : 0) + (kTma ? 2 * kFrameBytes + 16 : 0);
+}
+// resident CTAs per SM the register budget is sized for: d = 0 TMA 2 (255 regs), d = 0 direct 3 (168);
+// d >= 1 keep 2 (shared memory: 4 warps x 25.6 KB per CTA)
+template <int D, bool kTma>
+__host__ __device__ constexpr int min_ctas() {
+    return kDualWarps == 8 ? 1 : ((D == 0 && !kTma) ? 3 : 2) * (4 / kDualWarps);
 }
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -100,58 +107,88 @@ __device__ __forceinline__ void unpack_words(uint32_t wa, uint32_t wb, uint32_t 
     v.im = pk((float)((int)wa >> 16), (float)((int)wb >> 16));
 }
 
-struct FrameOut2 {
-    long long base;
-    int lo;
-    bool live;
-};
-__device__ __forceinline__ FrameOut2 frame_out_d0(long long f, long long total) {
-    constexpr int M = kHalfFft;
-    long long b = f / kFramesPerBlock;
-    int k = (int)(f - b * kFramesPerBlock);
-    FrameOut2 o;
-    o.live = f < total;
-    o.lo = k ? 0 : M / 4;
-    o.base = b * (long long)(kTransferSamples / 2) + (k ? (M / 2 + (k - 1) * (3 * M / 4)) : 0) - o.lo;
-    return o;
+// Packed split/filter of the bin held in register K1 (k = 32*K1 + lane), both frames at once:
+//   Y = P[k]*Z[k] + Q[k]*conj(Z[1024-k]),  P = G + GC, Q = G - GC  (see r2iq_kernels.cu split_filter)
+__device__ __forceinline__ c2 split_filter2(const c2 a, const c2 b, const float2 P, const float2 Q) {
+    c2 y;
+    y.re = fma2(bc(Q.y), b.im, fma2(bc(Q.x), b.re, fma2(bc(-P.y), a.im, mul2(bc(P.x), a.re))));
+    y.im = fma2(bc(Q.y), b.re, fma2(bc(-Q.x), b.im, fma2(bc(P.y), a.re, mul2(bc(P.x), a.im))));
+    return y;
+}
+
+template <int D, int K1>
+__device__ __forceinline__ void band_row2(const FusedParams& p, const c2 (&v)[32], int lane, const u64* S,
+                                          const float2* gp, const float2* gq, float2* stA, float2* stB) {
+    constexpr int M = Geo<D>::M;
+    if (32 * K1 + 31 >= p.band_lo && 32 * K1 < p.band_hi) {      // warp-uniform
+        const int k = 32 * K1 + lane;
+        const c2 b = lds2(S, (kHalfFft - k) & (kHalfFft - 1));
+        const c2 y = split_filter2(v[K1], b, __ldg(gp + 32 * K1), __ldg(gq + 32 * K1));
+        if (k >= p.band_lo && k < p.band_hi) {
+            const int m = (k - p.tunebin) & (M - 1);
+            float ar, br, ai, bi;
+            upk(y.re, ar, br);
+            upk(y.im, ai, bi);
+            stA[m] = make_float2(ar, ai);
+            stB[m] = make_float2(br, bi);
+        }
+    }
+}
+template <int D, int... K1>
+__device__ __forceinline__ void band_rows2(const FusedParams& p, const c2 (&v)[32], int lane, const u64* S,
+                                           const float2* gp, const float2* gq, float2* stA, float2* stB,
+                                           std::integer_sequence<int, K1...>) {
+    (band_row2<D, K1>(p, v, lane, S, gp, gq, stA, stB), ...);
 }
 
 }  // namespace
 
-// d = 0 (decimation 2, mfft = 1024): forward and backward transforms both run packed.
-template <bool kTma>
-__global__ void __launch_bounds__(kDualThreads, kTma ? 2 : 3) r2iq_dual_d0_kernel(const FusedParams p) {
+// One kernel per decimation index D.  A warp walks frame PAIRS (2i, 2i+1); for D >= 1 it stages the
+// filtered bands of 2^D consecutive frames (2^(D-1) pairs) and then runs their backward transforms
+// together (inverse_batch, one-frame lanes); for D = 0 forward and backward both run packed.
+template <int D, bool kTma>
+__global__ void __launch_bounds__(kDualThreads, min_ctas<D, kTma>()) r2iq_dual_kernel(const FusedParams p) {
+    using G = Geo<D>;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
-    constexpr int kWarpBytes = warp_bytes<kTma>();
+    constexpr int kWarpBytes = warp_bytes<D, kTma>();
+    constexpr int kPairs = (D == 0) ? 1 : (G::ROUNDS / 2);      // frame pairs per unit of work
     unsigned char* wbase = smem_raw + (size_t)warp * kWarpBytes;
     u64* S = reinterpret_cast<u64*>(wbase);
-    const uint32_t* inA = reinterpret_cast<const uint32_t*>(wbase + kTile * 16);
+    float2* stage = reinterpret_cast<float2*>(wbase + kTile * 16);
+    unsigned char* in_base = wbase + kTile * 16 + (D > 0 ? kStage * 8 : 0);
+    const uint32_t* inA = reinterpret_cast<const uint32_t*>(in_base);
     const uint32_t* inB = inA + kFrameBytes / 4;
-    const uint32_t mbar = smem_u32(wbase + kTile * 16 + 2 * kFrameBytes);
+    const uint32_t mbar = smem_u32(in_base + 2 * kFrameBytes);
     const uint32_t dstA = smem_u32(inA), dstB = smem_u32(inB);
 
-    const long long n_pairs = (p.total_frames + 1) / 2;
+    const long long last_frame = p.total_frames - 1;
+    const long long n_units = (p.total_frames + 2 * kPairs - 1) / (2 * kPairs);
     const long long stride = (long long)gridDim.x * kDualWarps;
-    long long q = (long long)blockIdx.x * kDualWarps + warp;
+    long long unit = (long long)blockIdx.x * kDualWarps + warp;
 
+    if constexpr (D > 0) {
+        // band bins outside [0, halfFft) are never written and must read as zero (impl.hpp:91-96)
+        for (int i = lane; i < kStage; i += 32) stage[i] = make_float2(0.f, 0.f);
+    }
     if constexpr (kTma) {
         if (lane == 0) {
             mbar_init(mbar, 1);
             asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         }
-        __syncwarp();
     }
-    auto issue = [&](long long pair) {
-        const long long fa = 2 * pair;
-        const long long fb = (fa + 1 < p.total_frames) ? fa + 1 : fa;   // odd tail: B repeats A, never stored
+    __syncwarp();
+    // frames past the end of the capture are clamped for loading and never stored
+    auto issue = [&](long long fa) {
+        const long long a = fa < last_frame ? fa : last_frame;
+        const long long b = fa + 1 < last_frame ? fa + 1 : last_frame;
         mbar_expect_tx(mbar, 2 * kFrameBytes);
-        tma_load_1d(dstA, frame_src(p, fa), kFrameBytes, mbar);
-        tma_load_1d(dstB, frame_src(p, fb), kFrameBytes, mbar);
+        tma_load_1d(dstA, frame_src(p, a), kFrameBytes, mbar);
+        tma_load_1d(dstB, frame_src(p, b), kFrameBytes, mbar);
     };
     if constexpr (kTma) {
-        if (lane == 0 && q < n_pairs) issue(q);
+        if (lane == 0 && unit < n_units) issue(unit * (2 * kPairs));
     }
     uint32_t phase = 0;
 
@@ -161,131 +198,172 @@ __global__ void __launch_bounds__(kDualThreads, kTma ? 2 : 3) r2iq_dual_d0_kerne
     const float2* gq = p.gq + lane;
     const int n1_inv = (lane - p.tunebin) & 31;
 
-    // The loop bound is CTA-uniform and every trip starts with a block barrier: the four warps then
-    // walk the (56 KB, fully unrolled) loop body roughly in step and share instruction-cache lines.
-    for (long long q0 = (long long)blockIdx.x * kDualWarps; q0 < n_pairs; q0 += stride, q += stride) {
-        __syncthreads();
-        const bool idle = q >= n_pairs;           // tail: keep barrier participation uniform, store nothing
-        const long long qq = idle ? n_pairs - 1 : q;
-        c2 v[32];
-        if constexpr (kTma) {
-            if (!idle) {                          // idle warps issued no copy; they chew on stale buffer contents
-                mbar_wait(mbar, phase);
-                phase ^= 1;
+    // The unit loop is CTA-uniform and phase boundaries are CTA barriers (see PHASE_SYNC); warps past
+    // the end of the work list ("idle") keep participating on clamped frames and store nothing.
+    for (long long u0 = (long long)blockIdx.x * kDualWarps; u0 < n_units; u0 += stride, unit += stride) {
+        const bool idle = unit >= n_units;
+        const long long f0 = (idle ? n_units - 1 : unit) * (2 * kPairs);
+#pragma unroll 1
+        for (int r = 0; r < kPairs; r++) {
+            __syncthreads();
+            const long long fa = f0 + 2 * r;
+            c2 v[32];
+            if constexpr (kTma) {
+                if (!idle) {                      // idle warps issued no copy; they chew on stale buffer contents
+                    mbar_wait(mbar, phase);
+                    phase ^= 1;
+                }
+#pragma unroll
+                for (int j = 0; j < 32; j++)
+                    unpack_words(inA[lane + 32 * j], inB[lane + 32 * j], p.rand_mul, v[brev5(j)]);
+                __syncwarp();   // every lane has consumed its words: the buffers may be overwritten
+                if (lane == 0 && !idle) {
+                    if (r + 1 < kPairs) issue(fa + 2);
+                    else if (unit + stride < n_units) issue((unit + stride) * (2 * kPairs));
+                }
+            } else {
+                const long long a = fa < last_frame ? fa : last_frame;
+                const long long b = fa + 1 < last_frame ? fa + 1 : last_frame;
+                const uint32_t* ga = frame_src(p, a) + lane;
+                const uint32_t* gb = frame_src(p, b) + lane;
+                uint32_t wa[32], wb[32];
+#pragma unroll
+                for (int j = 0; j < 32; j++) {
+                    wa[j] = __ldg(ga + 32 * j);
+                    wb[j] = __ldg(gb + 32 * j);
+                }
+#pragma unroll
+                for (int j = 0; j < 32; j++) unpack_words(wa[j], wb[j], p.rand_mul, v[brev5(j)]);
             }
+
+            // ---- forward 1024-point transform of z = x[2n] + i x[2n+1] --------------------------
+            dit2<32, false>(v);
 #pragma unroll
-            for (int j = 0; j < 32; j++) unpack_words(inA[lane + 32 * j], inB[lane + 32 * j], p.rand_mul, v[brev5(j)]);
-            __syncwarp();   // every lane has consumed its words: the buffers may be overwritten
-            if (lane == 0 && q + stride < n_pairs) issue(q + stride);   // idle warps never issued: their barrier would hang
-        } else {
-            const long long fa = 2 * qq;
-            const long long fb = (fa + 1 < p.total_frames) ? fa + 1 : fa;   // odd tail: B repeats A, never stored
-            const uint32_t* ga = frame_src(p, fa) + lane;
-            const uint32_t* gb = frame_src(p, fb) + lane;
-            uint32_t wa[32], wb[32];
+            for (int k2 = 1; k2 < 32; k2++) v[k2] = cmul2s(v[k2], __ldg(twf + 32 * k2));
 #pragma unroll
-            for (int j = 0; j < 32; j++) {
-                wa[j] = __ldg(ga + 32 * j);
-                wb[j] = __ldg(gb + 32 * j);
+            for (int k2 = 0; k2 < 32; k2++) sts2(S, lane * 33 + k2, v[k2]);
+            PHASE_SYNC();
+#pragma unroll
+            for (int n1 = 0; n1 < 32; n1++) v[brev5(n1)] = lds2(S, n1 * 33 + lane);
+            __syncwarp();
+            dit2<32, false>(v);                   // v[k1] = Z[32*k1 + lane]
+
+            // ---- real-FFT split + tune rotation + filter ----------------------------------------
+#pragma unroll
+            for (int k1 = 0; k1 < 32; k1++) sts2(S, 32 * k1 + lane, v[k1]);
+            PHASE_SYNC();
+            if constexpr (D == 0) {
+                c2 t[32];
+#pragma unroll
+                for (int k1 = 0; k1 < 32; k1++) {
+                    const c2 b = lds2(S, (kHalfFft - (32 * k1 + lane)) & (kHalfFft - 1));
+                    // in place, bit-reversed placement for the backward pass
+                    t[brev5(k1)] = split_filter2(v[k1], b, __ldg(gp + 32 * k1), __ldg(gq + 32 * k1));
+                }
+                __syncwarp();
+                // ---- backward 1024-point transform; lane l is residue (l - tunebin) mod 32 -------
+                dit2<32, true>(t);
+#pragma unroll
+                for (int k2 = 1; k2 < 32; k2++) t[k2] = cmul2s(t[k2], __ldg(twi + 32 * k2));
+#pragma unroll
+                for (int k2 = 0; k2 < 32; k2++) sts2(S, n1_inv * 33 + k2, t[k2]);
+                PHASE_SYNC();
+#pragma unroll
+                for (int n = 0; n < 32; n++) t[brev5(n)] = lds2(S, n * 33 + lane);
+                __syncwarp();
+                dit2<32, true>(t);                // t[k1] = y[lane + 32*k1] for both frames
+                // ---- overlap-save discard + placement (impl.hpp:117-138) ------------------------
+                const FrameOut oa = frame_out<0>(fa);
+                const FrameOut ob = frame_out<0>(fa + 1);
+                const bool liveA = !idle && fa <= last_frame;
+                const bool liveB = !idle && fa + 1 <= last_frame;
+#pragma unroll
+                for (int k1 = 0; k1 < 24; k1++) {     // idx >= 768 is always discarded
+                    const int idx = lane + 32 * k1;
+                    float ar, br, ai, bi;
+                    upk(t[k1].re, ar, br);
+                    upk(t[k1].im, ai, bi);
+                    if (liveA && idx >= oa.lo) p.out[oa.base + idx] = make_float2(ar, ai * p.imag_sign);
+                    if (liveB && idx >= ob.lo) p.out[ob.base + idx] = make_float2(br, bi * p.imag_sign);
+                }
+            } else {
+                band_rows2<D>(p, v, lane, S, gp, gq, stage + (2 * r) * G::GS, stage + (2 * r + 1) * G::GS,
+                              std::make_integer_sequence<int, 32>{});
             }
-#pragma unroll
-            for (int j = 0; j < 32; j++) unpack_words(wa[j], wb[j], p.rand_mul, v[brev5(j)]);
         }
-
-        // ---- forward 1024-point transform of z = x[2n] + i x[2n+1] ------------------------------
-        dit2<32, false>(v);
-#pragma unroll
-        for (int k2 = 1; k2 < 32; k2++) v[k2] = cmul2s(v[k2], __ldg(twf + 32 * k2));
-#pragma unroll
-        for (int k2 = 0; k2 < 32; k2++) sts2(S, lane * 33 + k2, v[k2]);
-        PHASE_SYNC();
-#pragma unroll
-        for (int n1 = 0; n1 < 32; n1++) v[brev5(n1)] = lds2(S, n1 * 33 + lane);
-        __syncwarp();
-        dit2<32, false>(v);                       // v[k1] = Z[32*k1 + lane]
-
-        // ---- real-FFT split + tune rotation + filter, in place ---------------------------------
-#pragma unroll
-        for (int k1 = 0; k1 < 32; k1++) sts2(S, 32 * k1 + lane, v[k1]);
-        PHASE_SYNC();
-        c2 t[32];
-#pragma unroll
-        for (int k1 = 0; k1 < 32; k1++) {
-            const c2 a = v[k1];
-            const c2 b = lds2(S, (kHalfFft - (32 * k1 + lane)) & (kHalfFft - 1));
-            const float2 P = __ldg(gp + 32 * k1);
-            const float2 Q = __ldg(gq + 32 * k1);
-            c2 y;
-            y.re = fma2(bc(Q.y), b.im, fma2(bc(Q.x), b.re, fma2(bc(-P.y), a.im, mul2(bc(P.x), a.re))));
-            y.im = fma2(bc(Q.y), b.re, fma2(bc(-Q.x), b.im, fma2(bc(P.y), a.re, mul2(bc(P.x), a.im))));
-            t[brev5(k1)] = y;                     // bit-reversed placement for the backward pass
-        }
-        __syncwarp();
-
-        // ---- backward 1024-point transform; lane l is residue (l - tunebin) mod 32 ---------------
-        dit2<32, true>(t);
-#pragma unroll
-        for (int k2 = 1; k2 < 32; k2++) t[k2] = cmul2s(t[k2], __ldg(twi + 32 * k2));
-#pragma unroll
-        for (int k2 = 0; k2 < 32; k2++) sts2(S, n1_inv * 33 + k2, t[k2]);
-        PHASE_SYNC();
-#pragma unroll
-        for (int n = 0; n < 32; n++) t[brev5(n)] = lds2(S, n * 33 + lane);
-        __syncwarp();
-        dit2<32, true>(t);                        // t[k1] = y[lane + 32*k1] for both frames
-
-        // ---- overlap-save discard + placement (impl.hpp:117-138) --------------------------------
-        const FrameOut2 oa = frame_out_d0(2 * qq, p.total_frames);
-        const FrameOut2 ob = frame_out_d0(2 * qq + 1, p.total_frames);
-#pragma unroll
-        for (int k1 = 0; k1 < 24; k1++) {         // idx >= 768 is always discarded
-            const int idx = lane + 32 * k1;
-            float ar, br, ai, bi;
-            upk(t[k1].re, ar, br);
-            upk(t[k1].im, ai, bi);
-            if (!idle && idx >= oa.lo) p.out[oa.base + idx] = make_float2(ar, ai * p.imag_sign);
-            if (!idle && ob.live && idx >= ob.lo) p.out[ob.base + idx] = make_float2(br, bi * p.imag_sign);
+        if constexpr (D > 0) {
+            __syncthreads();
+            if (!idle) inverse_batch<D>(p, f0, lane, reinterpret_cast<float2*>(S), stage);
         }
     }
 }
 
-template <bool kTma>
+template <int D, bool kTma>
 static cudaError_t setup_dual_one() {
-    cudaError_t e = cudaFuncSetAttribute(r2iq_dual_d0_kernel<kTma>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         kDualWarps * warp_bytes<kTma>());
+    if (kDualWarps * warp_bytes<D, kTma>() > 227 * 1024) return cudaSuccess;   // variant not launchable at this CTA size
+    cudaError_t e = cudaFuncSetAttribute(r2iq_dual_kernel<D, kTma>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         kDualWarps * warp_bytes<D, kTma>());
     if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(r2iq_dual_d0_kernel<kTma>, cudaFuncAttributePreferredSharedMemoryCarveout,
+    return cudaFuncSetAttribute(r2iq_dual_kernel<D, kTma>, cudaFuncAttributePreferredSharedMemoryCarveout,
                                 cudaSharedmemCarveoutMaxShared);
 }
 
-cudaError_t setup_dual_kernels() {
-    cudaError_t e = setup_dual_one<true>();
+template <int D>
+static cudaError_t setup_dual_d() {
+    cudaError_t e = setup_dual_one<D, true>();
     if (e != cudaSuccess) return e;
-    return setup_dual_one<false>();
+    return setup_dual_one<D, false>();
 }
 
-template <bool kTma>
+cudaError_t setup_dual_kernels() {
+    cudaError_t e;
+    if ((e = setup_dual_d<0>()) != cudaSuccess) return e;
+    if ((e = setup_dual_d<1>()) != cudaSuccess) return e;
+    if ((e = setup_dual_d<2>()) != cudaSuccess) return e;
+    if ((e = setup_dual_d<3>()) != cudaSuccess) return e;
+    if ((e = setup_dual_d<4>()) != cudaSuccess) return e;
+    if ((e = setup_dual_d<5>()) != cudaSuccess) return e;
+    if ((e = setup_dual_d<6>()) != cudaSuccess) return e;
+    return cudaSuccess;
+}
+
+template <int D, bool kTma>
 static cudaError_t launch_dual_one(const FusedParams& p, int sm_count, cudaStream_t stream) {
-    constexpr int smem = kDualWarps * warp_bytes<kTma>();
+    constexpr int smem = kDualWarps * warp_bytes<D, kTma>();
+    constexpr int kPairs = (D == 0) ? 1 : (Geo<D>::ROUNDS / 2);
     int ctas_per_sm = 1;
-    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, r2iq_dual_d0_kernel<kTma>, kDualThreads, smem);
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, r2iq_dual_kernel<D, kTma>, kDualThreads, smem);
     if (e != cudaSuccess) return e;
     if (ctas_per_sm < 1) ctas_per_sm = 1;
     if (const char* lim = getenv("R2IQ_CTAS_PER_SM")) {   // occupancy experiments only
         const int v = atoi(lim);
         if (v >= 1 && v < ctas_per_sm) ctas_per_sm = v;
     }
-    const long long n_pairs = (p.total_frames + 1) / 2;
-    long long want = (n_pairs + kDualWarps - 1) / kDualWarps;
+    const long long n_units = (p.total_frames + 2 * kPairs - 1) / (2 * kPairs);
+    long long want = (n_units + kDualWarps - 1) / kDualWarps;
     long long grid = (long long)sm_count * ctas_per_sm;
     if (grid > want) grid = want;
     if (grid < 1) grid = 1;
-    r2iq_dual_d0_kernel<kTma><<<(unsigned)grid, kDualThreads, smem, stream>>>(p);
+    r2iq_dual_kernel<D, kTma><<<(unsigned)grid, kDualThreads, smem, stream>>>(p);
     return cudaGetLastError();
 }
 
-cudaError_t launch_dual_d0(const FusedParams& p, int sm_count, cudaStream_t stream, bool tma) {
-    return tma ? launch_dual_one<true>(p, sm_count, stream) : launch_dual_one<false>(p, sm_count, stream);
+template <int D>
+static cudaError_t launch_dual_d(const FusedParams& p, int sm_count, cudaStream_t stream, bool tma) {
+    return tma ? launch_dual_one<D, true>(p, sm_count, stream) : launch_dual_one<D, false>(p, sm_count, stream);
+}
+
+cudaError_t launch_dual(int d, const FusedParams& p, int sm_count, cudaStream_t stream, bool tma) {
+    switch (d) {
+        case 0: return launch_dual_d<0>(p, sm_count, stream, tma);
+        case 1: return launch_dual_d<1>(p, sm_count, stream, tma);
+        case 2: return launch_dual_d<2>(p, sm_count, stream, tma);
+        case 3: return launch_dual_d<3>(p, sm_count, stream, tma);
+        case 4: return launch_dual_d<4>(p, sm_count, stream, tma);
+        case 5: return launch_dual_d<5>(p, sm_count, stream, tma);
+        case 6: return launch_dual_d<6>(p, sm_count, stream, tma);
+        default: return cudaErrorInvalidValue;
+    }
 }
 
 }  // namespace r2iq

@@ -22,7 +22,7 @@
 // No cuFFT, no tensor cores, no CPU fallback.
 #include "r2iq_kernels.cuh"
 
-#include "dft_regs.cuh"
+#include "r2iq_common.cuh"
 
 namespace r2iq {
 
@@ -32,51 +32,8 @@ namespace r2iq {
 constexpr int kWarpsPerCta = 4;
 constexpr int kThreads = kWarpsPerCta * 32;
 constexpr int kMinCtasPerSm = 3;
-constexpr int kScratch = 32 * 33;   // float2 per warp: 32x32 transposition tile, row pitch 33
-constexpr int kStage = 64 * 17;     // float2 per warp: staged bands of 2^d frames (max over d)
-
 template <int D>
-struct Geo {
-    static constexpr int M = kHalfFft >> D;                  // mfft: inverse FFT size
-    static constexpr int ROUNDS = 1 << D;                    // frames a warp runs per unit of work
-    static constexpr int L = (D <= 5) ? (32 >> D) : 1;       // lanes per frame in the inverse transform
-    static constexpr int GS = (D == 6) ? 17 : (M + L);       // staging pitch per frame (bank-conflict free)
-    static constexpr int OUT_PER_BLOCK = (kTransferSamples / 2) >> D;
-    static constexpr int WARP_SMEM = kScratch + (D > 0 ? kStage : 0);   // float2 per warp
-    static constexpr size_t SMEM_BYTES = (size_t)kWarpsPerCta * WARP_SMEM * sizeof(float2);
-};
-
-__device__ __forceinline__ int brev(int v, int bits) { return (int)(__brev((unsigned)v) >> (32 - bits)); }
-
-// De-randomise (Core/fft_mt_r2iq.h:41-44: `val = input ^ (-2)` when the LSB is set) both int16
-// halves of a word at once, then convert each to float (exact).
-__device__ __forceinline__ float2 unpack_pair(uint32_t w, uint32_t rand_mul) {
-    w ^= (w & 0x00010001u) * rand_mul;
-    return make_float2((float)(short)(w & 0xFFFFu), (float)((int)w >> 16));
-}
-
-struct FrameOut {
-    long long base;   // out[base + idx] receives inverse-FFT sample idx
-    int lo, hi;       // kept range of idx
-};
-
-// Output placement of frame f = block*43 + k (impl.hpp:117-138): k == 0 keeps y[mfft/4, 3mfft/4),
-// k >= 1 keeps y[0, 3mfft/4) at offset mfft/2 + (k-1)*3mfft/4 inside the block's output.
-template <int D>
-__device__ __forceinline__ FrameOut frame_out(long long f) {
-    constexpr int M = Geo<D>::M;
-    long long b = f / kFramesPerBlock;
-    int k = (int)(f - b * kFramesPerBlock);
-    FrameOut o;
-    o.lo = k ? 0 : M / 4;
-    o.hi = 3 * M / 4;
-    o.base = b * (long long)Geo<D>::OUT_PER_BLOCK + (k ? (M / 2 + (k - 1) * (3 * M / 4)) : 0) - o.lo;
-    return o;
-}
-
-__device__ __forceinline__ void store_iq(float2* out, const FrameOut& fo, int idx, float2 v, float imag_sign) {
-    if (idx >= fo.lo && idx < fo.hi) out[fo.base + idx] = make_float2(v.x, v.y * imag_sign);
-}
+constexpr size_t fused_smem_bytes() { return (size_t)kWarpsPerCta * Geo<D>::WARP_SMEM * sizeof(float2); }
 
 // Forward transform of frame f: on return v[k1] = Z[32*k1 + lane], Z = FFT_1024 of the packed frame.
 __device__ __forceinline__ void forward_frame(const FusedParams& p, long long f, int lane, float2* S, float2 (&v)[32]) {
@@ -193,64 +150,7 @@ __global__ void __launch_bounds__(kThreads, kMinCtasPerSm) r2iq_fused_kernel(con
                     band_rows<D>(p, v, lane, stage + r * G::GS, std::make_integer_sequence<int, 32>{});
                 }
             }
-            __syncwarp();
-            if constexpr (D <= 5) {
-                constexpr int L = G::L;
-                constexpr int NI = 32 / L;
-                constexpr int LB = ilog2(L);
-                const int g = lane / L;
-                const int n = lane % L;
-                float2 t[32];
-#pragma unroll
-                for (int n2 = 0; n2 < 32; n2++) t[brev(n2, 5)] = stage[g * G::GS + n + L * n2];
-                __syncwarp();
-                dit<32, true>(t);                        // pass 1: DFT over n2 within the frame
-                const long long f = f0 + g;
-                const FrameOut fo = frame_out<D>(f);
-                const bool live = f < p.total_frames;
-                if constexpr (L > 1) {
-#pragma unroll
-                    for (int k2 = 1; k2 < 32; k2++) t[k2] = cmul(t[k2], __ldg(&p.tw_inv[k2 * L + n]));
-                    float2* Sg = S + g * (33 * L);
-#pragma unroll
-                    for (int k2 = 0; k2 < 32; k2++) Sg[n * 33 + k2] = t[k2];
-                    __syncwarp();
-#pragma unroll
-                    for (int i = 0; i < NI; i++) {
-                        float2 x[L];
-#pragma unroll
-                        for (int n1 = 0; n1 < L; n1++) x[brev(n1, LB)] = Sg[n1 * 33 + n + L * i];
-                        dit<L, true>(x);                 // pass 2: DFT over n1
-                        if (live) {
-#pragma unroll
-                            for (int k1 = 0; k1 < L; k1++) store_iq(p.out, fo, n + L * i + 32 * k1, x[k1], p.imag_sign);
-                        }
-                    }
-                    __syncwarp();
-                } else {
-                    if (live) {
-#pragma unroll
-                        for (int k2 = 0; k2 < 32; k2++) store_iq(p.out, fo, k2, t[k2], p.imag_sign);
-                    }
-                }
-            } else {
-                // d = 6: mfft = 16, 64 frames per unit, two whole 16-point transforms per lane
-#pragma unroll
-                for (int h = 0; h < 2; h++) {
-                    const int g = lane + 32 * h;
-                    float2 x[16];
-#pragma unroll
-                    for (int n = 0; n < 16; n++) x[brev(n, 4)] = stage[g * G::GS + n];
-                    dit<16, true>(x);
-                    const long long f = f0 + g;
-                    if (f < p.total_frames) {
-                        const FrameOut fo = frame_out<D>(f);
-#pragma unroll
-                        for (int n = 0; n < 16; n++) store_iq(p.out, fo, n, x[n], p.imag_sign);
-                    }
-                }
-                __syncwarp();
-            }
+            inverse_batch<D>(p, f0, lane, S, stage);
         }
     }
 }
@@ -260,7 +160,7 @@ static cudaError_t launch_one(const FusedParams& p, int sm_count, cudaStream_t s
     using G = Geo<D>;
     int ctas_per_sm = 1;
     cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, r2iq_fused_kernel<D>, kThreads,
-                                                                 G::SMEM_BYTES);
+                                                                 fused_smem_bytes<D>());
     if (e != cudaSuccess) return e;
     if (ctas_per_sm < 1) ctas_per_sm = 1;
     const long long n_units = (p.total_frames + G::ROUNDS - 1) / G::ROUNDS;
@@ -268,14 +168,14 @@ static cudaError_t launch_one(const FusedParams& p, int sm_count, cudaStream_t s
     long long grid = (long long)sm_count * ctas_per_sm;     // persistent: every CTA strides over units
     if (grid > want) grid = want;
     if (grid < 1) grid = 1;
-    r2iq_fused_kernel<D><<<(unsigned)grid, kThreads, G::SMEM_BYTES, stream>>>(p);
+    r2iq_fused_kernel<D><<<(unsigned)grid, kThreads, fused_smem_bytes<D>(), stream>>>(p);
     return cudaGetLastError();
 }
 
 template <int D>
 static cudaError_t setup_one() {
     cudaError_t e = cudaFuncSetAttribute(r2iq_fused_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         (int)Geo<D>::SMEM_BYTES);
+                                         (int)fused_smem_bytes<D>());
     if (e != cudaSuccess) return e;
     // ask for the largest shared-memory carve-out so that kMinCtasPerSm CTAs are resident
     return cudaFuncSetAttribute(r2iq_fused_kernel<D>, cudaFuncAttributePreferredSharedMemoryCarveout,
@@ -288,6 +188,7 @@ void set_kernel_generation(int gen) { g_kernel_gen = gen; }
 cudaError_t setup_fused_kernels() {
     cudaError_t e;
     if ((e = setup_dual_kernels()) != cudaSuccess) return e;
+    if ((e = setup_dual_d0_kernels()) != cudaSuccess) return e;
     if ((e = setup_one<0>()) != cudaSuccess) return e;
     if ((e = setup_one<1>()) != cudaSuccess) return e;
     if ((e = setup_one<2>()) != cudaSuccess) return e;
@@ -299,7 +200,17 @@ cudaError_t setup_fused_kernels() {
 }
 
 cudaError_t launch_fused(int d, const FusedParams& p, int sm_count, cudaStream_t stream) {
-    if (g_kernel_gen != 1 && d == 0) return launch_dual_d0(p, sm_count, stream, g_kernel_gen == 2);
+    // Kernel choice per decimation, from measurements on B200 (profiles/README.md):
+    //   generation 0 (default): d = 0 specialised dual-frame kernel with TMA-staged input; d = 1 dual-frame
+    //   kernel with direct loads; d >= 2 first-generation one-frame-per-warp kernels (12 warps per SM beat
+    //   8 dual-frame warps once the backward transform is small).
+    //   1: first generation everywhere; 2: generic dual-frame, direct loads; 3: generic dual-frame, TMA.
+    if (g_kernel_gen == 0) {
+        if (d == 0) return launch_dual_d0(p, sm_count, stream, true);
+        if (d == 1) return launch_dual(d, p, sm_count, stream, false);
+    } else if (g_kernel_gen != 1) {
+        return launch_dual(d, p, sm_count, stream, g_kernel_gen == 3);
+    }
     switch (d) {
         case 0: return launch_one<0>(p, sm_count, stream);
         case 1: return launch_one<1>(p, sm_count, stream);

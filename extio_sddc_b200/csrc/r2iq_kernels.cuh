@@ -32,12 +32,15 @@ struct FusedParams {
 
 // Launch the fused kernel for decimation index d on `stream`.  Returns cudaGetLastError().
 cudaError_t launch_fused(int d, const FusedParams& p, int sm_count, cudaStream_t stream);
-// Kernel generation selector for A/B measurements (env R2IQ_KERNEL_GEN): 0 = newest kernels (default),
-// 1 = first-generation one-frame-per-warp kernels for every d, 2 = dual-frame kernels with TMA input
-// staging.  All produce results within the parity bar.
+// Kernel generation selector for A/B measurements (env R2IQ_KERNEL_GEN): 0 = the fastest measured kernel
+// per decimation (default, see launch_fused), 1 = first-generation one-frame-per-warp kernels,
+// 2 = generic dual-frame with direct loads, 3 = generic dual-frame with TMA staging.  All meet the parity bar.
 void set_kernel_generation(int gen);
 // second-generation kernels (r2iq_dual.cu): two frames per warp on packed fp32x2 lanes + TMA input
 cudaError_t setup_dual_kernels();
+cudaError_t launch_dual(int d, const FusedParams& p, int sm_count, cudaStream_t stream, bool tma);
+// specialised d = 0 dual-frame kernel (r2iq_dual_d0.cu)
+cudaError_t setup_dual_d0_kernels();
 cudaError_t launch_dual_d0(const FusedParams& p, int sm_count, cudaStream_t stream, bool tma);
 // One-time per-device setup (opt-in shared memory sizes).
 cudaError_t setup_fused_kernels();
