@@ -191,20 +191,24 @@ def run_reference(args, rank: int, world: int):
 # ------------------------------------------------------------------------------------------------
 # our arm
 # ------------------------------------------------------------------------------------------------
-def synth_capture(torch, dev, n_blocks: int, seed: int):
+def synth_capture(torch, dev, n_blocks: int, seed: int, first_block: int = 0):
     """Synthetic RX-888 capture generated on the device: three tones (one in every decimation's pass-band
     around the tune bin, two out of band) + uniform noise, rounded to int16, then passed through the ADC
-    randomizer (x ^= 0xFFFE when the LSB is set).  Layout: [halfFft halo zeros | n_blocks blocks]."""
+    randomizer (x ^= 0xFFFE when the LSB is set).  Layout: [halfFft halo | n_blocks blocks]; this rank's
+    slab starts at block `first_block` of the global capture (tones are phase-continuous in the global
+    sample index); the halo holds the 1024 samples before the slab, zeros for the slab that starts at 0."""
     n = n_blocks * SAMPLES_PER_BLOCK
     buf = torch.zeros(1024 + n, dtype=torch.int16, device=dev)
     g = torch.Generator(device=dev)
     g.manual_seed(seed)
     chunk = 1 << 24
+    origin = first_block * SAMPLES_PER_BLOCK
     f_tune = TUNEBIN / 2048.0
     tones = ((8000.0, f_tune + 0.1 / 256, 0.0), (4000.0, (f_tune + 0.23) % 0.5, 0.7), (4000.0, (f_tune + 0.37) % 0.5, 1.9))
-    for s in range(0, n, chunk):
+    lo = -1024 if first_block > 0 else 0
+    for s in range(lo, n, chunk):
         m = min(chunk, n - s)
-        t = torch.arange(s, s + m, device=dev, dtype=torch.float64)
+        t = torch.arange(origin + s, origin + s + m, device=dev, dtype=torch.float64)
         x = (torch.rand(m, device=dev, generator=g, dtype=torch.float32) * 1024.0 - 512.0).to(torch.float64)
         for a, f, ph in tones:
             x += a * torch.sin(2.0 * torch.pi * ((t * f) % 1.0) + ph)
@@ -230,7 +234,7 @@ def run_ours(args, rank: int, local_rank: int, world: int):
 
     n_blocks = args.blocks
     samples_per_launch = n_blocks * SAMPLES_PER_BLOCK
-    x = synth_capture(torch, dev, n_blocks, seed=888 + rank)
+    x = synth_capture(torch, dev, n_blocks, seed=888 + rank, first_block=rank * n_blocks)
     out = torch.empty(n_blocks * 32768, dtype=torch.complex64, device=dev)
     op = CudaR2IQ(device=local_rank)
     op.Init(GAIN)
@@ -296,7 +300,8 @@ def run_ours(args, rank: int, local_rank: int, world: int):
                       "alg_bytes_per_sample": bytes_per_sample(d), "achieved_gbs": round(gbs, 1),
                       "hbm_frac": round(gbs / peak, 4)})
     dom = max(per_d, key=lambda r: r["kernel_ms"])
-    roofline = {"bound": "hbm", "kernel": f"r2iq_fused_kernel<{dom['d']}> (decimation {dom['decimation']})",
+    names = {0: "r2iq_dual_d0_kernel<tma>", 1: "r2iq_dual_kernel<1,direct>"}
+    roofline = {"bound": "hbm", "kernel": f"{names.get(dom['d'], 'r2iq_fused_kernel<%d>' % dom['d'])} (decimation {dom['decimation']})",
                 "achieved": dom["achieved_gbs"], "peak": peak, "unit": "GB/s", "frac": round(dom["achieved_gbs"] / peak, 4),
                 "traffic": ncu_traffic(dom["d"]), "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": samples_per_launch * bytes_per_sample(dom["d"]),
@@ -356,6 +361,9 @@ def run_ours(args, rank: int, local_rank: int, world: int):
     gather = None
     if world > 1:
         gather = []
+        warm = torch.zeros(1024, dtype=torch.float32, device=dev)      # bring the NCCL communicator up untimed
+        dist.gather(warm, [torch.empty_like(warm) for _ in range(world)] if rank == 0 else None, dst=0)
+        torch.cuda.synchronize()
         for d in (DECIMS[-1], DECIMS[0]):
             n_out = n_blocks * (32768 >> d)
             op.setDecimate(d)
