@@ -385,6 +385,39 @@ def run_ours(args, rank: int, local_rank: int, world: int):
                            "gathered_bytes": int(n_out * 8 * (world - 1))})
             del dst
 
+    # ---- config 4: 64-channel channelizer at d = 5, channels sharded over the ranks ---------------------
+    channelizer = None
+    if not args.no_channelizer:
+        from extio_sddc_b200 import shard
+        all_bins = shard.channel_tunebins(64)
+        mine = [all_bins[c] for c in shard.channel_shards(64, world)[rank]]
+        cd = 5
+        cout = torch.empty(len(mine) * n_blocks * (32768 >> cd), dtype=torch.complex64, device=dev)
+        op.setDecimate(cd)
+        op.TurnOn()
+        for _ in range(2):
+            op.process_channels_device(x.data_ptr(), n_blocks, mine, cout.data_ptr(), stream)
+        barrier()
+        torch.cuda.synchronize()
+        c0 = torch.cuda.Event(enable_timing=True)
+        c1 = torch.cuda.Event(enable_timing=True)
+        c0.record()
+        reps = 5
+        for _ in range(reps):
+            op.process_channels_device(x.data_ptr(), n_blocks, mine, cout.data_ptr(), stream)
+        c1.record()
+        torch.cuda.synchronize()
+        cms = c0.elapsed_time(c1) / reps
+        if world > 1:
+            t = torch.tensor([cms], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            cms = float(t.item())
+        channelizer = {"channels": 64, "channels_per_gpu": len(mine), "d": cd, "decimation": 64, "ms": round(cms, 3),
+                       "input_gsamples_s": round(samples_per_launch / (cms * 1e-3) / 1e9, 2),
+                       "channel_gsamples_s": round(64 * samples_per_launch / (cms * 1e-3) / 1e9, 1),
+                       "note": "every rank reads the same capture; one forward FFT per frame shared by its channels"}
+        del cout
+
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         try:
@@ -414,6 +447,8 @@ def run_ours(args, rank: int, local_rank: int, world: int):
             line["e2e"] = e2e
         if gather is not None:
             line["gather"] = gather
+        if channelizer is not None:
+            line["channelizer"] = channelizer
         if cpu_baseline is not None:
             line["cpu_baseline"] = cpu_baseline
         print(json.dumps(line))
@@ -434,6 +469,7 @@ def main():
     ap.add_argument("--ref-blocks", type=int, default=2048, help="blocks per instance per decimation for the CPU arm")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-channelizer", action="store_true")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3

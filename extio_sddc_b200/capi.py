@@ -64,6 +64,8 @@ _SIGNATURES = {
     "r2iq_cuda_out_per_block": (_L, [_VP]),
     "r2iq_cuda_process": (_I, [_VP, _VP, _L, _VP, _VP]),
     "r2iq_cuda_process_device": (_I, [_VP, _VP, _L, _VP, _VP]),
+    "r2iq_cuda_process_channels": (_I, [_VP, _VP, _L, _VP, _VP, _I, _VP]),
+    "r2iq_cuda_process_channels_device": (_I, [_VP, _VP, _L, _VP, _I, _VP, _VP]),
     "r2iq_cuda_sync": (_I, [_VP]),
     "r2iq_cuda_host_alloc": (_VP, [ctypes.c_size_t]),
     "r2iq_cuda_host_free": (_I, [_VP]),

@@ -82,6 +82,9 @@ struct r2iq_cuda_s {
     uint64_t hw_version[kNDec] = {0};
     float2* d_tw_fwd = nullptr;
     std::map<long long, TableSet> tables;          // key = version<<20 | d<<12 | tunebin... see table_key
+    std::map<long long, float2*> gh_tables;        // channelizer: 0.5*H_d in inverse-FFT bin order, key = version<<4 | d
+    std::map<std::vector<int>, int*> chan_lists;   // channelizer: device copies of tune-bin lists
+    float2* d_ctab = nullptr;                      // channelizer: -i * W_2048^k
     Slot slots[kSlots];
     int16_t* carry = nullptr;                      // pinned: last halfFft samples of the stream
     bool carry_valid = false;
@@ -105,6 +108,13 @@ int check_handle(r2iq_cuda_t h) {
     if (!h) return fail(R2IQ_E_INVALID, "null handle");
     if (h->poisoned) return fail(R2IQ_E_CUDA, "handle is unusable after an earlier CUDA error: %s", g_err);
     return R2IQ_OK;
+}
+
+void free_channel_tables(r2iq_cuda_t h) {
+    for (auto& kv : h->gh_tables) cudaFree(kv.second);
+    for (auto& kv : h->chan_lists) cudaFree(kv.second);
+    h->gh_tables.clear();
+    h->chan_lists.clear();
 }
 
 void free_tables(r2iq_cuda_t h) {
@@ -218,6 +228,75 @@ int launch(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d_out, cuda
     return R2IQ_OK;
 }
 
+// Channelizer launch: per-d filter table in inverse-FFT bin order + the tune-bin list on the device.
+int launch_channels_impl(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, const int* tunebins, int n_channels,
+                         float* d_out, cudaStream_t stream) {
+    const int d = h->latched_decimate;
+    if (d < 1) return fail(R2IQ_E_INVALID, "the channelizer needs decimation index >= 1 (latched: %d)", d);
+    for (int c = 0; c < n_channels; c++)
+        if (tunebins[c] < 0 || tunebins[c] >= kHalfFft || (tunebins[c] & 3))
+            return fail(R2IQ_E_INVALID, "channel %d: tune bin %d must be a multiple of 4 in [0,%d)", c, tunebins[c], kHalfFft);
+    const int M = kHalfFft >> d;
+    TableSet ts;   // for tw_inv (independent of the tune bin when d >= 1)
+    int rc = get_tables(h, d, 0, &ts);
+    if (rc != R2IQ_OK) return rc;
+    if (!h->d_ctab) {
+        std::vector<float2> c(kHalfFft);
+        for (int k = 0; k < kHalfFft; k++) {
+            const double th = 2.0 * kPiD * (double)k / (double)kFftN;
+            c[k] = make_float2((float)-sin(th), (float)-cos(th));
+        }
+        CU(h, cudaMalloc(&h->d_ctab, sizeof(float2) * kHalfFft));
+        CU(h, cudaMemcpy(h->d_ctab, c.data(), sizeof(float2) * kHalfFft, cudaMemcpyHostToDevice));
+    }
+    const long long gkey = ((long long)h->hw_version[d] << 4) | d;
+    float2* gh = nullptr;
+    auto git = h->gh_tables.find(gkey);
+    if (git != h->gh_tables.end()) gh = git->second;
+    else {
+        std::vector<float2> g(M);
+        for (int m = 0; m < M; m++) {
+            const int s = m < M / 2 ? m : m - M;
+            const std::complex<float> hh = h->hw[d][(s + kHalfFft) % kHalfFft];
+            g[m] = make_float2(0.5f * hh.real(), 0.5f * hh.imag());
+        }
+        CU(h, cudaMalloc(&gh, sizeof(float2) * M));
+        CU(h, cudaMemcpy(gh, g.data(), sizeof(float2) * M, cudaMemcpyHostToDevice));
+        h->gh_tables[gkey] = gh;
+    }
+    std::vector<int> key(tunebins, tunebins + n_channels);
+    int* d_list = nullptr;
+    auto lit = h->chan_lists.find(key);
+    if (lit != h->chan_lists.end()) d_list = lit->second;
+    else {
+        if (h->chan_lists.size() >= 256) {
+            CU(h, cudaDeviceSynchronize());
+            for (auto& kv : h->chan_lists) cudaFree(kv.second);
+            h->chan_lists.clear();
+        }
+        CU(h, cudaMalloc(&d_list, sizeof(int) * n_channels));
+        CU(h, cudaMemcpy(d_list, tunebins, sizeof(int) * n_channels, cudaMemcpyHostToDevice));
+        h->chan_lists[key] = d_list;
+    }
+    ChannelParams p;
+    p.in_words = (const uint32_t*)d_in;
+    p.out = (float2*)d_out;
+    p.out_stride = (long long)n_blocks * ((kTransferSamples / 2) >> d);
+    p.total_frames = (long long)n_blocks * kFramesPerBlock;
+    p.tw_fwd = h->d_tw_fwd;
+    p.ctab = h->d_ctab;
+    p.gh = gh;
+    p.tw_inv = ts.tw_inv;
+    p.tunebins = d_list;
+    p.n_channels = n_channels;
+    p.rand_mul = h->rand_on ? 0xFFFEu : 0u;
+    p.imag_sign = h->latched_sideband ? -1.0f : 1.0f;
+    CU(h, launch_channels(d, p, h->sm_count, stream));
+    h->stats.kernel_launches++;
+    h->stats.blocks_processed += (uint64_t)n_blocks;
+    return R2IQ_OK;
+}
+
 int ensure_slots(r2iq_cuda_t h) {
     for (int i = 0; i < kSlots; i++) {
         Slot& s = h->slots[i];
@@ -273,6 +352,8 @@ int r2iq_cuda_create(const r2iq_cuda_config* cfg, r2iq_cuda_t* out) {
     };
     if ((e = cudaSetDevice(dev)) != cudaSuccess) return bail(fail(R2IQ_E_CUDA, "cudaSetDevice: %s", cudaGetErrorString(e)));
     if (const char* gen = getenv("R2IQ_KERNEL_GEN")) set_kernel_generation(atoi(gen));   // A/B measurements only
+    if ((e = setup_channel_kernels()) != cudaSuccess)
+        return bail(fail(R2IQ_E_CUDA, "channelizer kernel setup: %s", cudaGetErrorString(e)));
     if ((e = setup_fused_kernels()) != cudaSuccess)
         return bail(fail(R2IQ_E_CUDA, "kernel setup: %s", cudaGetErrorString(e)));
     // forward inter-pass twiddles exp(-2 pi i k2 l / 1024)
@@ -301,6 +382,8 @@ int r2iq_cuda_destroy(r2iq_cuda_t h) {
     cudaSetDevice(h->device);
     cudaDeviceSynchronize();
     free_tables(h);
+    free_channel_tables(h);
+    cudaFree(h->d_ctab);
     for (int i = 0; i < kSlots; i++) {
         Slot& s = h->slots[i];
         if (s.stream) cudaStreamDestroy(s.stream);
@@ -471,6 +554,58 @@ int r2iq_cuda_process_device(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, 
     if (n_blocks == 0) return R2IQ_OK;
     std::lock_guard<std::mutex> lk(h->mu);
     return launch(h, d_in, n_blocks, d_iq_out, (cudaStream_t)stream);
+}
+
+int r2iq_cuda_process_channels_device(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, const int* tunebins,
+                                      int n_channels, float* d_iq_out, void* stream) {
+    int rc = check_handle(h);
+    if (rc) return rc;
+    if (!h->on) return fail(R2IQ_E_STATE, "process called while the operator is off (call r2iq_cuda_turn_on)");
+    if (n_blocks < 0 || n_channels < 0 || ((n_blocks > 0 && n_channels > 0) && (!d_in || !d_iq_out || !tunebins)))
+        return fail(R2IQ_E_INVALID, "process_channels_device: bad arguments");
+    if (((uintptr_t)d_in & 15) || ((uintptr_t)d_iq_out & 7))
+        return fail(R2IQ_E_INVALID, "process_channels_device: input must be 16-byte and output 8-byte aligned");
+    if (n_blocks == 0 || n_channels == 0) return R2IQ_OK;
+    std::lock_guard<std::mutex> lk(h->mu);
+    CU(h, cudaSetDevice(h->device));
+    return launch_channels_impl(h, d_in, n_blocks, tunebins, n_channels, d_iq_out, (cudaStream_t)stream);
+}
+
+int r2iq_cuda_process_channels(r2iq_cuda_t h, const int16_t* blocks, long n_blocks, const int16_t* history,
+                               const int* tunebins, int n_channels, float* iq_out) {
+    int rc = check_handle(h);
+    if (rc) return rc;
+    if (!h->on) return fail(R2IQ_E_STATE, "process called while the operator is off (call r2iq_cuda_turn_on)");
+    if (n_blocks < 0 || n_channels < 0 || ((n_blocks > 0 && n_channels > 0) && (!blocks || !iq_out || !tunebins)))
+        return fail(R2IQ_E_INVALID, "process_channels: bad arguments");
+    if (n_blocks == 0 || n_channels == 0) return R2IQ_OK;
+    std::lock_guard<std::mutex> lk(h->mu);
+    CU(h, cudaSetDevice(h->device));
+    const int d = h->latched_decimate;
+    const size_t per_ch = (size_t)n_blocks * ((kTransferSamples / 2) >> d);
+    int16_t* d_in = nullptr;
+    float* d_out = nullptr;
+    CU(h, cudaMalloc(&d_in, sizeof(int16_t) * ((size_t)kHalfFft + (size_t)n_blocks * kTransferSamples)));
+    cudaError_t e = cudaMalloc(&d_out, sizeof(float) * 2 * per_ch * (size_t)n_channels);
+    if (e != cudaSuccess) {
+        cudaFree(d_in);
+        return fail(R2IQ_E_NOMEM, "cudaMalloc(channel output): %s", cudaGetErrorString(e));
+    }
+    if (history) CU(h, cudaMemcpyAsync(d_in, history, sizeof(int16_t) * kHalfFft, cudaMemcpyHostToDevice, h->util_stream));
+    else CU(h, cudaMemsetAsync(d_in, 0, sizeof(int16_t) * kHalfFft, h->util_stream));
+    CU(h, cudaMemcpyAsync(d_in + kHalfFft, blocks, sizeof(int16_t) * (size_t)n_blocks * kTransferSamples,
+                          cudaMemcpyHostToDevice, h->util_stream));
+    rc = launch_channels_impl(h, d_in, n_blocks, tunebins, n_channels, d_out, h->util_stream);
+    if (rc == R2IQ_OK) {
+        CU(h, cudaMemcpyAsync(iq_out, d_out, sizeof(float) * 2 * per_ch * (size_t)n_channels, cudaMemcpyDeviceToHost,
+                              h->util_stream));
+        h->stats.h2d_bytes += sizeof(int16_t) * ((size_t)kHalfFft + (size_t)n_blocks * kTransferSamples);
+        h->stats.d2h_bytes += sizeof(float) * 2 * per_ch * (size_t)n_channels;
+    }
+    CU(h, cudaStreamSynchronize(h->util_stream));
+    cudaFree(d_in);
+    cudaFree(d_out);
+    return rc;
 }
 
 int r2iq_cuda_sync(r2iq_cuda_t h) {

@@ -56,13 +56,21 @@ __device__ __forceinline__ void store_iq(float2* out, const FrameOut& fo, int id
 }
 
 
-// Backward transforms of the 2^D frames of one unit, whose mfft-bin bands sit in `stage`
-// (frame g at stage + g*GS, bins in inverse-FFT order), 32>>D lanes per frame and 32 points per
-// lane; overlap-save discard, optional conjugate and placement as impl.hpp:117-138.
+// Where the backward transform of staged band g goes: output pointer, kept range and liveness.
+struct Placement {
+    float2* out;
+    FrameOut fo;
+    bool live;
+};
+
+// Backward transforms of 2^D staged bands (band g at stage + g*GS, bins in inverse-FFT order), 32>>D
+// lanes per band and 32 points per lane; overlap-save discard, optional conjugate and placement as
+// impl.hpp:117-138.  `place(g)` says where band g goes: consecutive frames of one channel in the
+// fused kernels, one frame of consecutive channels in the channelizer.
 // S is a float2[kScratch] transposition tile private to the warp.
-template <int D>
-__device__ __forceinline__ void inverse_batch(const FusedParams& p, long long f0, int lane, float2* S,
-                                              const float2* stage) {
+template <int D, typename PlaceFn>
+__device__ __forceinline__ void inverse_bands(int lane, float2* S, const float2* stage, const float2* tw_inv,
+                                              float imag_sign, PlaceFn place) {
     using G = Geo<D>;
     static_assert(D >= 1, "d = 0 keeps its spectrum in registers");
     __syncwarp();
@@ -76,13 +84,11 @@ __device__ __forceinline__ void inverse_batch(const FusedParams& p, long long f0
 #pragma unroll
         for (int n2 = 0; n2 < 32; n2++) t[brev(n2, 5)] = stage[g * G::GS + n + L * n2];
         __syncwarp();
-        dit<32, true>(t);                        // pass 1: DFT over n2 within the frame
-        const long long f = f0 + g;
-        const FrameOut fo = frame_out<D>(f);
-        const bool live = f < p.total_frames;
+        dit<32, true>(t);                        // pass 1: DFT over n2 within the band
+        const Placement pl = place(g);
         if constexpr (L > 1) {
 #pragma unroll
-            for (int k2 = 1; k2 < 32; k2++) t[k2] = cmul(t[k2], __ldg(&p.tw_inv[k2 * L + n]));
+            for (int k2 = 1; k2 < 32; k2++) t[k2] = cmul(t[k2], __ldg(&tw_inv[k2 * L + n]));
             float2* Sg = S + g * (33 * L);
 #pragma unroll
             for (int k2 = 0; k2 < 32; k2++) Sg[n * 33 + k2] = t[k2];
@@ -93,20 +99,20 @@ __device__ __forceinline__ void inverse_batch(const FusedParams& p, long long f0
 #pragma unroll
                 for (int n1 = 0; n1 < L; n1++) x[brev(n1, LB)] = Sg[n1 * 33 + n + L * i];
                 dit<L, true>(x);                 // pass 2: DFT over n1
-                if (live) {
+                if (pl.live) {
 #pragma unroll
-                    for (int k1 = 0; k1 < L; k1++) store_iq(p.out, fo, n + L * i + 32 * k1, x[k1], p.imag_sign);
+                    for (int k1 = 0; k1 < L; k1++) store_iq(pl.out, pl.fo, n + L * i + 32 * k1, x[k1], imag_sign);
                 }
             }
             __syncwarp();
         } else {
-            if (live) {
+            if (pl.live) {
 #pragma unroll
-                for (int k2 = 0; k2 < 32; k2++) store_iq(p.out, fo, k2, t[k2], p.imag_sign);
+                for (int k2 = 0; k2 < 32; k2++) store_iq(pl.out, pl.fo, k2, t[k2], imag_sign);
             }
         }
     } else {
-        // d = 6: mfft = 16, 64 frames per unit, two whole 16-point transforms per lane
+        // d = 6: mfft = 16, 64 bands per unit, two whole 16-point transforms per lane
 #pragma unroll
         for (int h = 0; h < 2; h++) {
             const int g = lane + 32 * h;
@@ -114,15 +120,27 @@ __device__ __forceinline__ void inverse_batch(const FusedParams& p, long long f0
 #pragma unroll
             for (int n = 0; n < 16; n++) x[brev(n, 4)] = stage[g * G::GS + n];
             dit<16, true>(x);
-            const long long f = f0 + g;
-            if (f < p.total_frames) {
-                const FrameOut fo = frame_out<D>(f);
+            const Placement pl = place(g);
+            if (pl.live) {
 #pragma unroll
-                for (int n = 0; n < 16; n++) store_iq(p.out, fo, n, x[n], p.imag_sign);
+                for (int n = 0; n < 16; n++) store_iq(pl.out, pl.fo, n, x[n], imag_sign);
             }
         }
         __syncwarp();
     }
+}
+
+// The fused kernels' use: band g is frame f0 + g of the one tuned channel.
+template <int D>
+__device__ __forceinline__ void inverse_batch(const FusedParams& p, long long f0, int lane, float2* S,
+                                              const float2* stage) {
+    inverse_bands<D>(lane, S, stage, p.tw_inv, p.imag_sign, [&](int g) {
+        Placement pl;
+        pl.out = p.out;
+        pl.fo = frame_out<D>(f0 + g);
+        pl.live = f0 + g < p.total_frames;
+        return pl;
+    });
 }
 
 }  // namespace r2iq

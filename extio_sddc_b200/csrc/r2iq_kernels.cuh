@@ -30,6 +30,24 @@ struct FusedParams {
     float imag_sign;            // -1 when sideband inversion (copy<true>) is requested, else +1
 };
 
+// Channelizer (r2iq_channels.cu): n_channels tuned channels from one input stream, d >= 1.
+struct ChannelParams {
+    const uint32_t* in_words;   // as FusedParams
+    float2* out;                // channel c writes out[c*out_stride + ...], n_blocks*(32768>>d) complex each
+    long long out_stride;       // complex samples between channels
+    long long total_frames;
+    const float2* tw_fwd;
+    const float2* ctab;         // [1024]  -i * W_2048^k  (odd-part twiddle of the real-FFT split)
+    const float2* gh;           // [mfft]  0.5 * H_d at inverse-FFT bin m (lower half m, upper half m - mfft)
+    const float2* tw_inv;       // [32][L] as FusedParams for d >= 1
+    const int* tunebins;        // [n_channels] device array, multiples of 4 in [0, halfFft)
+    int n_channels;
+    uint32_t rand_mul;
+    float imag_sign;
+};
+cudaError_t setup_channel_kernels();
+cudaError_t launch_channels(int d, const ChannelParams& p, int sm_count, cudaStream_t stream);
+
 // Launch the fused kernel for decimation index d on `stream`.  Returns cudaGetLastError().
 cudaError_t launch_fused(int d, const FusedParams& p, int sm_count, cudaStream_t stream);
 // Kernel generation selector for A/B measurements (env R2IQ_KERNEL_GEN): 0 = the fastest measured kernel

@@ -152,6 +152,30 @@ class CudaR2IQ:
         capi.check(self._lib.r2iq_cuda_process_device(self._handle(), ctypes.c_void_p(d_in_ptr), int(n_blocks),
                                                       ctypes.c_void_p(d_out_ptr), ctypes.c_void_p(stream_ptr)))
 
+    def process_channels(self, blocks: np.ndarray, tunebins, history: np.ndarray | None = None) -> np.ndarray:
+        """Channelizer: every tune bin in ``tunebins`` from one pass over ``blocks`` (latched d >= 1).
+        Returns complex64 [n_channels, n_blocks*(32768>>d)]; row c equals a separate operator tuned to
+        ``tunebins[c]``."""
+        blocks = np.ascontiguousarray(blocks, dtype=np.int16).reshape(-1)
+        if blocks.shape[0] % TRANSFER_SAMPLES:
+            raise ValueError("input must be a whole number of 65536-sample blocks")
+        n_blocks = blocks.shape[0] // TRANSFER_SAMPLES
+        tb = np.ascontiguousarray(tunebins, dtype=np.int32)
+        out = np.empty((tb.shape[0], n_blocks * self.out_per_block()), dtype=np.complex64)
+        hist_p = None
+        if history is not None:
+            history = np.ascontiguousarray(history, dtype=np.int16)
+            hist_p = history.ctypes.data
+        capi.check(self._lib.r2iq_cuda_process_channels(self._handle(), blocks.ctypes.data, n_blocks, hist_p,
+                                                        tb.ctypes.data, tb.shape[0], out.ctypes.data))
+        return out
+
+    def process_channels_device(self, d_in_ptr: int, n_blocks: int, tunebins, d_out_ptr: int, stream_ptr: int = 0) -> None:
+        tb = np.ascontiguousarray(tunebins, dtype=np.int32)
+        capi.check(self._lib.r2iq_cuda_process_channels_device(self._handle(), ctypes.c_void_p(d_in_ptr), int(n_blocks),
+                                                               tb.ctypes.data, tb.shape[0], ctypes.c_void_p(d_out_ptr),
+                                                               ctypes.c_void_p(stream_ptr)))
+
     def convert_float(self, x: np.ndarray, rand: bool) -> np.ndarray:
         """convert_float<rand> (Core/fft_mt_r2iq.h:36-51) through the device code path."""
         x = np.ascontiguousarray(x, dtype=np.int16).reshape(-1)

@@ -128,6 +128,19 @@ R2IQ_API int r2iq_cuda_process(r2iq_cuda_t h, const int16_t* blocks, long n_bloc
  * complex floats.  No host synchronisation; stream state is not carried. */
 R2IQ_API int r2iq_cuda_process_device(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d_iq_out, void* stream);
 
+/* Wideband channelizer: n_channels tuned channels from ONE input stream in a single pass (the forward
+ * FFT of every frame is computed once and shared).  Channel c is tuned to tunebins[c] (multiples of 4 in
+ * [0, halfFft), the value setFreqOffset would store in mtunebin) and receives exactly the stream a
+ * separate fft_mt_r2iq tuned there would produce (Core/fft_mt_r2iq_impl.hpp:76-138) at the latched
+ * decimation d >= 1, with the current rand / sideband settings.  iq_out is channel-major:
+ * channel c occupies [c*n_blocks*(32768>>d), (c+1)*n_blocks*(32768>>d)) complex floats.
+ * Host-buffer form: history as r2iq_cuda_process (NULL = zeros; no state is carried).
+ * Device form: d_in = [halfFft history | blocks] (16-byte aligned), asynchronous on `stream`. */
+R2IQ_API int r2iq_cuda_process_channels(r2iq_cuda_t h, const int16_t* blocks, long n_blocks, const int16_t* history,
+                                        const int* tunebins, int n_channels, float* iq_out);
+R2IQ_API int r2iq_cuda_process_channels_device(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, const int* tunebins,
+                                               int n_channels, float* d_iq_out, void* stream);
+
 /* Block until everything issued through this handle has finished. */
 R2IQ_API int r2iq_cuda_sync(r2iq_cuda_t h);
 

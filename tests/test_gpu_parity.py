@@ -274,3 +274,33 @@ def test_full_size_properties(d):
     check(whole[b0 * opb:(b0 + 3) * opb].cpu().numpy(), ref, GAIN, ("full-size window", d))
     r.TurnOff()
     r.close()
+
+
+def test_config4_channelizer(op):
+    """BASELINE config 4: many tuned DDC channels from one stream.  Every channel must equal an
+    independent reference run tuned to that bin (64 channels at d = 5; a subset at d = 3, 1 and 6;
+    edge channels whose bands leave [0, halfFft) included)."""
+    from extio_sddc_b200 import shard
+    x = orc.rx888_blocks(2, 5, 256, randomized=True, seed=4)
+    hist = np.random.default_rng(4).integers(-2000, 2000, 1024).astype(np.int16)
+    for d, bins in ((5, shard.channel_tunebins(64)), (3, [0, 4, 60, 256, 1020] + shard.channel_tunebins(64)[::8]),
+                    (1, [0, 256, 768, 1020]), (6, shard.channel_tunebins(64) + [0, 1020] * 3)):
+        op.setDecimate(d); op.updateRand(True); op.setSideband(False)
+        op.TurnOn()
+        got = op.process_channels(x, bins, history=hist)
+        op.TurnOff()
+        assert got.shape == (len(bins), 2 * (32768 >> d))
+        for c, tb in enumerate(bins):
+            ref = orc.r2iq(x, d, tb, gain=GAIN, rand=True, history=hist)
+            check(got[c], ref, GAIN, ("channelizer", d, tb))
+    # must agree with the single-channel kernels too, and refuse d = 0
+    op.setDecimate(5); op.tunebin = 264
+    single = run(op, x, 5, 264, rand=True, history=hist)
+    op.setDecimate(5); op.TurnOn()
+    multi = op.process_channels(x, [264], history=hist)[0]
+    op.TurnOff()
+    assert orc.rel_l2(multi, single) < 1e-6
+    op.setDecimate(0); op.TurnOn()
+    with pytest.raises(capi.R2iqError):
+        op.process_channels(x, [256])
+    op.TurnOff()
