@@ -92,7 +92,7 @@ __global__ void __launch_bounds__(kChThreads, 2) r2iq_channels_kernel(const Chan
                 }
                 stage[j * G::GS + m] = y;
             }
-            inverse_bands<D>(lane, S, stage, p.tw_inv, p.imag_sign, [&](int g) {
+            inverse_bands<D, true>(lane, S, stage, p.tw_inv, p.imag_sign, [&](int g) {
                 Placement pl;
                 pl.out = p.out + (long long)(c0 + g) * p.out_stride;
                 pl.fo = fo;

@@ -63,12 +63,48 @@ struct Placement {
     bool live;
 };
 
+// Coalesced output for the small transforms (d >= 5), one band per lane: lane g deposits the kept samples
+// of its band (value(idx), idx in [lo, hi)) and the band's destination in shared memory; the warp then
+// writes all 32 bands as runs of consecutive lanes.  `vals` needs 32*(KEEP+1) float2, `S` 32*16 bytes.
+template <int D, typename ValueFn>
+__device__ __forceinline__ void staged_store(int lane, float2* S, float2* vals, const Placement& pl, float imag_sign,
+                                             ValueFn value) {
+    constexpr int M = Geo<D>::M;
+    constexpr int KEEP = 3 * M / 4;          // 24 (d = 5) or 12 (d = 6); frame 0 of a block keeps M/2 of them
+    constexpr int PITCH = KEEP + 1;          // odd: conflict-free deposits
+    float2** dst = reinterpret_cast<float2**>(S);
+    int* keep = reinterpret_cast<int*>(S + 32);
+    __syncwarp();
+    dst[lane] = pl.out + pl.fo.base + pl.fo.lo;
+    keep[lane] = pl.live ? (pl.fo.hi - pl.fo.lo) : 0;
+#pragma unroll
+    for (int r = 0; r < KEEP; r++) {
+        // frame 0 of a block keeps [M/4, 3M/4): its r-th kept sample is idx M/4 + r; others keep [0, 3M/4)
+        const float2 a = value(r);
+        const float2 b = value(r + M / 4);
+        const float2 v = pl.fo.lo ? b : a;
+        vals[lane * PITCH + r] = make_float2(v.x, v.y * imag_sign);
+    }
+    __syncwarp();
+#pragma unroll
+    for (int it = 0; it < KEEP; it++) {
+        const int item = it * 32 + lane;
+        const int band = item / KEEP;
+        const int r = item - band * KEEP;
+        if (r < keep[band]) dst[band][r] = vals[band * PITCH + r];
+    }
+    __syncwarp();
+}
+
 // Backward transforms of 2^D staged bands (band g at stage + g*GS, bins in inverse-FFT order), 32>>D
 // lanes per band and 32 points per lane; overlap-save discard, optional conjugate and placement as
 // impl.hpp:117-138.  `place(g)` says where band g goes: consecutive frames of one channel in the
 // fused kernels, one frame of consecutive channels in the channelizer.
 // S is a float2[kScratch] transposition tile private to the warp.
-template <int D, typename PlaceFn>
+// kStaged selects the coalescing output path for d >= 5 (measured: it wins when bands are far apart in
+// memory -- the channelizer, 3.95 -> 1.71 ms for 64 channels -- and loses ~13 % when they are consecutive
+// frames of one channel, whose 8-byte stores already land in adjacent sectors).
+template <int D, bool kStaged = false, typename PlaceFn>
 __device__ __forceinline__ void inverse_bands(int lane, float2* S, const float2* stage, const float2* tw_inv,
                                               float imag_sign, PlaceFn place) {
     using G = Geo<D>;
@@ -106,27 +142,38 @@ __device__ __forceinline__ void inverse_bands(int lane, float2* S, const float2*
             }
             __syncwarp();
         } else {
-            if (pl.live) {
+            // d = 5: lane g holds all 32 samples of band g.  Writing them straight out would issue 8-byte
+            // stores 192 bytes apart (one 32-byte sector transaction per lane); instead the kept samples go
+            // through shared memory and leave as runs of consecutive lanes (full sectors).
+            if constexpr (kStaged) {
+                staged_store<D>(lane, S, const_cast<float2*>(stage), pl, imag_sign, [&](int idx) { return t[idx]; });
+            } else if (pl.live) {
 #pragma unroll
                 for (int k2 = 0; k2 < 32; k2++) store_iq(pl.out, pl.fo, k2, t[k2], imag_sign);
             }
         }
     } else {
         // d = 6: mfft = 16, 64 bands per unit, two whole 16-point transforms per lane
+        float2 x0[16], x1[16];
 #pragma unroll
-        for (int h = 0; h < 2; h++) {
-            const int g = lane + 32 * h;
-            float2 x[16];
-#pragma unroll
-            for (int n = 0; n < 16; n++) x[brev(n, 4)] = stage[g * G::GS + n];
-            dit<16, true>(x);
-            const Placement pl = place(g);
-            if (pl.live) {
-#pragma unroll
-                for (int n = 0; n < 16; n++) store_iq(pl.out, pl.fo, n, x[n], imag_sign);
-            }
+        for (int n = 0; n < 16; n++) {
+            x0[brev(n, 4)] = stage[lane * G::GS + n];
+            x1[brev(n, 4)] = stage[(lane + 32) * G::GS + n];
         }
         __syncwarp();
+        dit<16, true>(x0);
+        dit<16, true>(x1);
+        if constexpr (kStaged) {
+            staged_store<D>(lane, S, const_cast<float2*>(stage), place(lane), imag_sign, [&](int idx) { return x0[idx]; });
+            staged_store<D>(lane, S, const_cast<float2*>(stage), place(lane + 32), imag_sign, [&](int idx) { return x1[idx]; });
+        } else {
+            const Placement p0 = place(lane), p1 = place(lane + 32);
+#pragma unroll
+            for (int n = 0; n < 16; n++) {
+                if (p0.live) store_iq(p0.out, p0.fo, n, x0[n], imag_sign);
+                if (p1.live) store_iq(p1.out, p1.fo, n, x1[n], imag_sign);
+            }
+        }
     }
 }
 
