@@ -46,6 +46,7 @@ struct TableSet {   // device tables for one (decimation, tune bin)
     float2* gp = nullptr;
     float2* gq = nullptr;
     float2* tw_inv = nullptr;
+    float2* tw_aux = nullptr;
     int band_lo = 0, band_hi = 0;
 };
 
@@ -124,6 +125,7 @@ void free_tables(r2iq_cuda_t h) {
         cudaFree(kv.second.gp);
         cudaFree(kv.second.gq);
         cudaFree(kv.second.tw_inv);
+        cudaFree(kv.second.tw_aux);
     }
     h->tables.clear();
 }
@@ -187,6 +189,16 @@ int get_tables(r2iq_cuda_t h, int d, int tunebin, TableSet* out) {
                 tw[k2 * L + n1] = make_float2((float)cos(th), (float)sin(th));
             }
     }
+    if (d == 1) {   // d = 1 dual-frame kernel: 512 = 16 x 32 backward decomposition, twiddle exp(+2 pi i lane k2 / 512)
+        std::vector<float2> ta(16 * 32);
+        for (int k2 = 0; k2 < 16; k2++)
+            for (int l = 0; l < 32; l++) {
+                const double th = 2.0 * kPiD * (double)((l * k2) % 512) / 512.0;
+                ta[k2 * 32 + l] = make_float2((float)cos(th), (float)sin(th));
+            }
+        CU(h, cudaMalloc(&ts.tw_aux, sizeof(float2) * 16 * 32));
+        CU(h, cudaMemcpy(ts.tw_aux, ta.data(), sizeof(float2) * 16 * 32, cudaMemcpyHostToDevice));
+    }
     CU(h, cudaMalloc(&ts.gk, sizeof(float2) * kHalfFft));
     CU(h, cudaMalloc(&ts.gck, sizeof(float2) * kHalfFft));
     CU(h, cudaMalloc(&ts.gp, sizeof(float2) * kHalfFft));
@@ -217,6 +229,7 @@ int launch(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d_out, cuda
     p.gp = ts.gp;
     p.gq = ts.gq;
     p.tw_inv = ts.tw_inv;
+    p.tw_aux = ts.tw_aux;
     p.tunebin = h->tunebin;
     p.band_lo = ts.band_lo;
     p.band_hi = ts.band_hi;

@@ -104,7 +104,9 @@ __device__ __forceinline__ void staged_store(int lane, float2* S, float2* vals, 
 // kStaged selects the coalescing output path for d >= 5 (measured: it wins when bands are far apart in
 // memory -- the channelizer, 3.95 -> 1.71 ms for 64 channels -- and loses ~13 % when they are consecutive
 // frames of one channel, whose 8-byte stores already land in adjacent sectors).
-template <int D, bool kStaged = false, typename PlaceFn>
+// NB (a power of two <= 2^D) is the number of bands actually staged: with NB < 2^D the lane groups
+// beyond NB recompute band (g mod NB) and store nothing.
+template <int D, bool kStaged = false, int NB = (1 << D), typename PlaceFn>
 __device__ __forceinline__ void inverse_bands(int lane, float2* S, const float2* stage, const float2* tw_inv,
                                               float imag_sign, PlaceFn place) {
     using G = Geo<D>;
@@ -118,10 +120,11 @@ __device__ __forceinline__ void inverse_bands(int lane, float2* S, const float2*
         const int n = lane % L;
         float2 t[32];
 #pragma unroll
-        for (int n2 = 0; n2 < 32; n2++) t[brev(n2, 5)] = stage[g * G::GS + n + L * n2];
+        for (int n2 = 0; n2 < 32; n2++) t[brev(n2, 5)] = stage[(g & (NB - 1)) * G::GS + n + L * n2];
         __syncwarp();
         dit<32, true>(t);                        // pass 1: DFT over n2 within the band
-        const Placement pl = place(g);
+        Placement pl = place(g);
+        pl.live = pl.live && g < NB;
         if constexpr (L > 1) {
 #pragma unroll
             for (int k2 = 1; k2 < 32; k2++) t[k2] = cmul(t[k2], __ldg(&tw_inv[k2 * L + n]));
@@ -157,8 +160,8 @@ __device__ __forceinline__ void inverse_bands(int lane, float2* S, const float2*
         float2 x0[16], x1[16];
 #pragma unroll
         for (int n = 0; n < 16; n++) {
-            x0[brev(n, 4)] = stage[lane * G::GS + n];
-            x1[brev(n, 4)] = stage[(lane + 32) * G::GS + n];
+            x0[brev(n, 4)] = stage[(lane & (NB - 1)) * G::GS + n];
+            x1[brev(n, 4)] = stage[((lane + 32) & (NB - 1)) * G::GS + n];
         }
         __syncwarp();
         dit<16, true>(x0);
@@ -170,8 +173,8 @@ __device__ __forceinline__ void inverse_bands(int lane, float2* S, const float2*
             const Placement p0 = place(lane), p1 = place(lane + 32);
 #pragma unroll
             for (int n = 0; n < 16; n++) {
-                if (p0.live) store_iq(p0.out, p0.fo, n, x0[n], imag_sign);
-                if (p1.live) store_iq(p1.out, p1.fo, n, x1[n], imag_sign);
+                if (p0.live && lane < NB) store_iq(p0.out, p0.fo, n, x0[n], imag_sign);
+                if (p1.live && lane + 32 < NB) store_iq(p1.out, p1.fo, n, x1[n], imag_sign);
             }
         }
     }

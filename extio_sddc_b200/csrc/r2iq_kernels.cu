@@ -31,12 +31,28 @@ namespace r2iq {
 // occupancy knob (registers: 3*128*170 <= 64K; shared memory: 3*68.6 KB <= 227 KB for d >= 1).
 constexpr int kWarpsPerCta = 4;
 constexpr int kThreads = kWarpsPerCta * 32;
-constexpr int kMinCtasPerSm = 3;
+// d = 2, 5, 6: a unit of work is HALF the 2^d frames one backward batch could hold.  The backward
+// transform then runs with half its lane groups idle, but staging shrinks to 4.3 KB per warp and the
+// kernel fits 128 registers, so FOUR CTAs = 16 warps are resident per SM instead of 12.  Measured
+// (Gsamples/s, 12 -> 16 warps): d=2 474 -> 501, d=5 683 -> 739, d=6 639 -> 726; d=3 591 -> 573 and
+// d=4 656 -> 639 lose (their idle backward lanes cost more than the extra warps hide), d=1 is even:
+// those keep full units and 3 CTAs.  d = 0 needs 165 registers: 3 CTAs.
 template <int D>
-constexpr size_t fused_smem_bytes() { return (size_t)kWarpsPerCta * Geo<D>::WARP_SMEM * sizeof(float2); }
+__host__ __device__ constexpr bool half_units() { return D == 2 || D == 5 || D == 6; }
+template <int D>
+__host__ __device__ constexpr int unit_frames() { return D == 0 ? 1 : (half_units<D>() ? (1 << (D - 1)) : (1 << D)); }
+template <int D>
+__host__ __device__ constexpr int min_ctas_v1() { return half_units<D>() ? 4 : 3; }
+template <int D>
+__host__ __device__ constexpr int warp_smem_v1() { return kScratch + (D == 0 ? 0 : unit_frames<D>() * Geo<D>::GS); }   // float2
+template <int D>
+constexpr size_t fused_smem_bytes() { return (size_t)kWarpsPerCta * warp_smem_v1<D>() * sizeof(float2); }
 
 // Forward transform of frame f: on return v[k1] = Z[32*k1 + lane], Z = FFT_1024 of the packed frame.
-__device__ __forceinline__ void forward_frame(const FusedParams& p, long long f, int lane, float2* S, float2 (&v)[32]) {
+// `f_next` (>= 0) is the frame this warp will run after f: its 4 KB are requested into L2 now, one
+// 128-byte line per lane, so that its loads find them there (L2 hit instead of a DRAM round trip).
+__device__ __forceinline__ void forward_frame(const FusedParams& p, long long f, long long f_next, int lane, float2* S,
+                                              float2 (&v)[32]) {
     const long long b = f / kFramesPerBlock;
     const int k = (int)(f - b * kFramesPerBlock);
     // frame k of block b starts k*1536 samples into [halo | block b]  (impl.hpp:88)
@@ -44,6 +60,12 @@ __device__ __forceinline__ void forward_frame(const FusedParams& p, long long f,
     uint32_t w[32];
 #pragma unroll
     for (int j = 0; j < 32; j++) w[j] = __ldg(src + 32 * j);
+    if (f_next >= 0 && f_next < p.total_frames) {
+        const long long bn = f_next / kFramesPerBlock;
+        const int kn = (int)(f_next - bn * kFramesPerBlock);
+        const uint32_t* nxt = p.in_words + bn * (kTransferSamples / 2) + kn * (kHop / 2) + 32 * lane;
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(nxt));
+    }
 #pragma unroll
     for (int j = 0; j < 32; j++) v[brev(j, 5)] = unpack_pair(w[j], p.rand_mul);
     dit<32, false>(v);                                  // pass 1: DFT over n2, lane = n1
@@ -103,28 +125,29 @@ __device__ __forceinline__ void band_rows(const FusedParams& p, const float2 (&v
 }
 
 template <int D>
-__global__ void __launch_bounds__(kThreads, kMinCtasPerSm) r2iq_fused_kernel(const FusedParams p) {
+__global__ void __launch_bounds__(kThreads, min_ctas_v1<D>()) r2iq_fused_kernel(const FusedParams p) {
     using G = Geo<D>;
     extern __shared__ float2 smem[];
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
-    float2* S = smem + warp * G::WARP_SMEM;
+    constexpr int UNIT = unit_frames<D>();
+    float2* S = smem + warp * warp_smem_v1<D>();
     float2* stage = S + kScratch;
 
     if constexpr (D > 0) {
         // bins of the band that fall outside [0, halfFft) are never written: they must read as
         // zero (the memset calls of impl.hpp:91-96)
-        for (int i = lane; i < kStage; i += 32) stage[i] = make_float2(0.f, 0.f);
+        for (int i = lane; i < UNIT * G::GS; i += 32) stage[i] = make_float2(0.f, 0.f);
         __syncwarp();
     }
 
-    const long long n_units = (p.total_frames + G::ROUNDS - 1) / G::ROUNDS;
+    const long long n_units = (p.total_frames + UNIT - 1) / UNIT;
     for (long long unit = (long long)blockIdx.x * kWarpsPerCta + warp; unit < n_units;
          unit += (long long)gridDim.x * kWarpsPerCta) {
-        const long long f0 = unit * G::ROUNDS;
+        const long long f0 = unit * UNIT;
         if constexpr (D == 0) {
             float2 v[32], t[32];
-            forward_frame(p, f0, lane, S, v);
+            forward_frame(p, f0, (unit + (long long)gridDim.x * kWarpsPerCta) * UNIT, lane, S, v);
             band_d0<D>(p, v, lane, t, std::make_integer_sequence<int, 32>{});
             // backward pass 1 over the register index; lane l is residue (l - tunebin) mod 32
             dit<32, true>(t);
@@ -142,15 +165,22 @@ __global__ void __launch_bounds__(kThreads, kMinCtasPerSm) r2iq_fused_kernel(con
 #pragma unroll
             for (int k1 = 0; k1 < 32; k1++) store_iq(p.out, fo, lane + 32 * k1, t[k1], p.imag_sign);
         } else {
-            for (int r = 0; r < G::ROUNDS; r++) {
+            for (int r = 0; r < UNIT; r++) {
                 const long long f = f0 + r;
                 if (f < p.total_frames) {                // warp-uniform
                     float2 v[32];
-                    forward_frame(p, f, lane, S, v);
+                    forward_frame(p, f, r + 1 < UNIT ? f + 1 : (unit + (long long)gridDim.x * kWarpsPerCta) * UNIT,
+                                  lane, S, v);
                     band_rows<D>(p, v, lane, stage + r * G::GS, std::make_integer_sequence<int, 32>{});
                 }
             }
-            inverse_batch<D>(p, f0, lane, S, stage);
+            inverse_bands<D, false, UNIT>(lane, S, stage, p.tw_inv, p.imag_sign, [&](int g) {
+                Placement pl;
+                pl.out = p.out;
+                pl.fo = frame_out<D>(f0 + g);
+                pl.live = f0 + g < p.total_frames;
+                return pl;
+            });
         }
     }
 }
@@ -163,7 +193,7 @@ static cudaError_t launch_one(const FusedParams& p, int sm_count, cudaStream_t s
                                                                  fused_smem_bytes<D>());
     if (e != cudaSuccess) return e;
     if (ctas_per_sm < 1) ctas_per_sm = 1;
-    const long long n_units = (p.total_frames + G::ROUNDS - 1) / G::ROUNDS;
+    const long long n_units = (p.total_frames + unit_frames<D>() - 1) / unit_frames<D>();
     long long want = (n_units + kWarpsPerCta - 1) / kWarpsPerCta;
     long long grid = (long long)sm_count * ctas_per_sm;     // persistent: every CTA strides over units
     if (grid > want) grid = want;
@@ -189,6 +219,7 @@ cudaError_t setup_fused_kernels() {
     cudaError_t e;
     if ((e = setup_dual_kernels()) != cudaSuccess) return e;
     if ((e = setup_dual_d0_kernels()) != cudaSuccess) return e;
+    if ((e = setup_dual_d1_kernels()) != cudaSuccess) return e;
     if ((e = setup_one<0>()) != cudaSuccess) return e;
     if ((e = setup_one<1>()) != cudaSuccess) return e;
     if ((e = setup_one<2>()) != cudaSuccess) return e;
@@ -207,7 +238,7 @@ cudaError_t launch_fused(int d, const FusedParams& p, int sm_count, cudaStream_t
     //   1: first generation everywhere; 2: generic dual-frame, direct loads; 3: generic dual-frame, TMA.
     if (g_kernel_gen == 0) {
         if (d == 0) return launch_dual_d0(p, sm_count, stream, true);
-        if (d == 1) return launch_dual(d, p, sm_count, stream, false);
+        if (d == 1) return launch_dual_d1(p, sm_count, stream, true);
     } else if (g_kernel_gen != 1) {
         return launch_dual(d, p, sm_count, stream, g_kernel_gen == 3);
     }

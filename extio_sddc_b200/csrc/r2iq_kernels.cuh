@@ -24,6 +24,7 @@ struct FusedParams {
     const float2* gp;           // [1024]    gk + gck   (dual-frame kernel: Y = gp*a + gq*conj(b))
     const float2* gq;           // [1024]    gk - gck
     const float2* tw_inv;       // d=0: [32][32] conj(W_1024)^((lane-tunebin)*k2); d>=1: [32][L] conj(W_M)^(n1*k2)
+    const float2* tw_aux;       // d=1 dual-frame kernel: [16][32] exp(+2 pi i lane k2 / 512); else null
     int tunebin;
     int band_lo, band_hi;       // forward-FFT bins [lo,hi) that feed the inverse transform
     uint32_t rand_mul;          // 0xFFFE when the ADC randomizer is on, else 0
@@ -57,6 +58,9 @@ void set_kernel_generation(int gen);
 // second-generation kernels (r2iq_dual.cu): two frames per warp on packed fp32x2 lanes + TMA input
 cudaError_t setup_dual_kernels();
 cudaError_t launch_dual(int d, const FusedParams& p, int sm_count, cudaStream_t stream, bool tma);
+// specialised d = 1 dual-frame kernel (r2iq_dual_d1.cu)
+cudaError_t setup_dual_d1_kernels();
+cudaError_t launch_dual_d1(const FusedParams& p, int sm_count, cudaStream_t stream, bool tma);
 // specialised d = 0 dual-frame kernel (r2iq_dual_d0.cu)
 cudaError_t setup_dual_d0_kernels();
 cudaError_t launch_dual_d0(const FusedParams& p, int sm_count, cudaStream_t stream, bool tma);
