@@ -189,15 +189,23 @@ int get_tables(r2iq_cuda_t h, int d, int tunebin, TableSet* out) {
                 tw[k2 * L + n1] = make_float2((float)cos(th), (float)sin(th));
             }
     }
-    if (d == 1) {   // d = 1 dual-frame kernel: 512 = 16 x 32 backward decomposition, twiddle exp(+2 pi i lane k2 / 512)
-        std::vector<float2> ta(16 * 32);
-        for (int k2 = 0; k2 < 16; k2++)
+    if (d >= 1 && d <= 5) {
+        // dual-frame kernels, backward transform mfft = 32*R on 32 lanes: pass-1 twiddles exp(+2 pi i lane k2 / mfft)
+        // (k2 < R), then the pass-2 weights exp(+2 pi i (lane % G) n1 / 32), G = 32/R
+        const int R = 32 >> d, G = 32 / R;
+        std::vector<float2> ta((size_t)(R + 32) * 32);
+        for (int k2 = 0; k2 < R; k2++)
             for (int l = 0; l < 32; l++) {
-                const double th = 2.0 * kPiD * (double)((l * k2) % 512) / 512.0;
+                const double th = 2.0 * kPiD * (double)((l * k2) % M) / (double)M;
                 ta[k2 * 32 + l] = make_float2((float)cos(th), (float)sin(th));
             }
-        CU(h, cudaMalloc(&ts.tw_aux, sizeof(float2) * 16 * 32));
-        CU(h, cudaMemcpy(ts.tw_aux, ta.data(), sizeof(float2) * 16 * 32, cudaMemcpyHostToDevice));
+        for (int n1 = 0; n1 < 32; n1++)
+            for (int l = 0; l < 32; l++) {
+                const double th = 2.0 * kPiD * (double)(((l % G) * n1) % 32) / 32.0;
+                ta[(R + n1) * 32 + l] = make_float2((float)cos(th), (float)sin(th));
+            }
+        CU(h, cudaMalloc(&ts.tw_aux, sizeof(float2) * ta.size()));
+        CU(h, cudaMemcpy(ts.tw_aux, ta.data(), sizeof(float2) * ta.size(), cudaMemcpyHostToDevice));
     }
     CU(h, cudaMalloc(&ts.gk, sizeof(float2) * kHalfFft));
     CU(h, cudaMalloc(&ts.gck, sizeof(float2) * kHalfFft));

@@ -1,0 +1,320 @@
+// r2iq_dual_dn.cu -- dual-frame kernels for d = 2..5 (mfft = 256..32), generalising r2iq_dual_d1.cu.
+//
+// Forward transform as in the d = 0 / d = 1 kernels (two frames per warp on packed fp32x2 lanes, input
+// staged by TMA).  With R = mfft/32 = 32 >> d band bins per lane:
+//   * band cut from the natural-order spectrum in shared memory, in backward-transform order
+//     (m = lane + 32*j, j < R), filtered in registers -- no staging buffer, no second launch phase;
+//   * backward transform of size mfft = 32 * R on all 32 lanes, both frames packed:
+//       n = lane + 32*n2, k = k2 + R*k1.   Pass 1: radix-R register DFT over n2, twiddle w_M^(lane*k2).
+//       Pass 2 needs R 32-point DFTs from 32 lanes, G = 32/R lanes each: lane (k2, h) computes the
+//       outputs k1 = h + G*q, q < R:  u_j = sum_r x[j + R*r] * w_32^(h*(j + R*r)), a 32-term
+//       multiply-accumulate with per-lane weights from a 32x32 table, then a radix-R register DFT
+//       over j.  Output index k = k2 + R*h + 32*q: every store instruction covers 32 consecutive samples.
+// d = 6 (mfft = 16 < 32 lanes) stays with the first-generation kernel.
+#include <cstdlib>
+
+#include "dft_regs2.cuh"
+#include "r2iq_kernels.cuh"
+
+namespace r2iq {
+
+namespace {
+
+constexpr int kDualWarps = 4;                 // warps per CTA
+constexpr int kDualThreads = kDualWarps * 32;
+// Input staging is a template switch so both variants stay measurable (profiles/README.md):
+//   kTma = true : next pair of frames prefetched global->shared by TMA bulk copies; 25.1 KB of shared
+//                 memory per warp, so 8 warps per SM (2 CTAs, 255 registers).
+//   kTma = false: frames read straight into registers (32 coalesced 128-byte requests per frame);
+//                 16.9 KB per warp, so 12 warps per SM (3 CTAs, 168 registers) hide the load latency.
+constexpr int kTile = 32 * 33;                // elements per plane: 32x32 tile, pitch 33 (conflict-free for 8 B accesses)
+constexpr int kFrameBytes = kFftN * 2;        // 4096 B of int16 per frame
+// per-warp shared memory: transposition tile (two 8-byte planes) [+ two input frames + one mbarrier]
+template <bool kTma>
+__host__ __device__ constexpr int warp_bytes() {
+    return kTile * 16 + (kTma ? 2 * kFrameBytes + 16 : 0);
+}
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t mbar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(mbar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t mbar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t mbar, uint32_t parity) {
+    uint32_t done;
+    do {
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+            "selp.u32 %0, 1, 0, p;\n"
+            "}\n"
+            : "=r"(done)
+            : "r"(mbar), "r"(parity)
+            : "memory");
+    } while (!done);
+}
+// TMA 1-D bulk copy global -> shared, completion signalled on the mbarrier (SASS: UBLKCP)
+__device__ __forceinline__ void tma_load_1d(uint32_t dst, const void* src, uint32_t bytes, uint32_t mbar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+                 "l"(src), "r"(bytes), "r"(mbar)
+                 : "memory");
+}
+
+__device__ __forceinline__ const uint32_t* frame_src(const FusedParams& p, long long f) {
+    const long long b = f / kFramesPerBlock;
+    const int k = (int)(f - b * kFramesPerBlock);
+    return p.in_words + b * (kTransferSamples / 2) + k * (kHop / 2);
+}
+
+// Phase boundaries double as CTA barriers (a superset of the __syncwarp the data hazard needs): they
+// keep the warps of a CTA within one phase of each other in the 50 KB unrolled loop body, so that
+// instruction-cache lines fetched by one warp are still resident for the others.
+#define PHASE_SYNC() __syncthreads()
+
+__device__ __forceinline__ int brev5(int v) { return (int)(__brev((unsigned)v) >> 27); }
+__device__ __forceinline__ int brev_n(int v, int bits) { return bits == 0 ? 0 : (int)(__brev((unsigned)v) >> (32 - bits)); }
+
+// Shared-memory exchanges use two 64-bit planes (re pairs, im pairs) rather than one 128-bit element:
+// a v2.b64 access needs re and im in four consecutive registers, and ptxas paid ~400 MOVs per
+// iteration to arrange that; plane accesses have no such constraint and stay conflict-free at pitch 33.
+__device__ __forceinline__ void sts2(u64* S, int idx, c2 v) {
+    S[idx] = v.re;
+    S[kTile + idx] = v.im;
+}
+__device__ __forceinline__ c2 lds2(const u64* S, int idx) {
+    c2 v;
+    v.re = S[idx];
+    v.im = S[kTile + idx];
+    return v;
+}
+
+__device__ __forceinline__ void unpack_words(uint32_t wa, uint32_t wb, uint32_t rand_mul, c2& v) {
+    wa ^= (wa & 0x00010001u) * rand_mul;    // de-randomise both int16 halves (Core/fft_mt_r2iq.h:41-44)
+    wb ^= (wb & 0x00010001u) * rand_mul;
+    v.re = pk((float)(short)(wa & 0xFFFFu), (float)(short)(wb & 0xFFFFu));
+    v.im = pk((float)((int)wa >> 16), (float)((int)wb >> 16));
+}
+
+struct FrameOut2 {
+    long long base;
+    int lo;
+    bool live;
+};
+template <int D>
+__device__ __forceinline__ FrameOut2 frame_out_dn(long long f, long long total) {
+    constexpr int M = kHalfFft >> D;
+    long long b = f / kFramesPerBlock;
+    int k = (int)(f - b * kFramesPerBlock);
+    FrameOut2 o;
+    o.live = f < total;
+    o.lo = k ? 0 : M / 4;
+    o.base = b * (long long)((kTransferSamples / 2) >> D) + (k ? (M / 2 + (k - 1) * (3 * M / 4)) : 0) - o.lo;
+    return o;
+}
+
+}  // namespace
+
+// forward and backward transforms both run packed; D = 2..5
+template <int D, bool kTma>
+__global__ void __launch_bounds__(kDualThreads, 2) r2iq_dual_dn_kernel(const FusedParams p) {
+    constexpr int M = kHalfFft >> D;
+    constexpr int R = 32 >> D;            // band bins per lane = size of the register DFTs
+    constexpr int G = 32 / R;             // lanes sharing one 32-point DFT in pass 2
+    constexpr int RB = ilog2(R);
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    constexpr int kWarpBytes = warp_bytes<kTma>();
+    unsigned char* wbase = smem_raw + (size_t)warp * kWarpBytes;
+    u64* S = reinterpret_cast<u64*>(wbase);
+    const uint32_t* inA = reinterpret_cast<const uint32_t*>(wbase + kTile * 16);
+    const uint32_t* inB = inA + kFrameBytes / 4;
+    const uint32_t mbar = smem_u32(wbase + kTile * 16 + 2 * kFrameBytes);
+    const uint32_t dstA = smem_u32(inA), dstB = smem_u32(inB);
+
+    const long long n_pairs = (p.total_frames + 1) / 2;
+    const long long stride = (long long)gridDim.x * kDualWarps;
+    long long q = (long long)blockIdx.x * kDualWarps + warp;
+
+    if constexpr (kTma) {
+        if (lane == 0) {
+            mbar_init(mbar, 1);
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+        __syncwarp();
+    }
+    auto issue = [&](long long pair) {
+        const long long fa = 2 * pair;
+        const long long fb = (fa + 1 < p.total_frames) ? fa + 1 : fa;   // odd tail: B repeats A, never stored
+        mbar_expect_tx(mbar, 2 * kFrameBytes);
+        tma_load_1d(dstA, frame_src(p, fa), kFrameBytes, mbar);
+        tma_load_1d(dstB, frame_src(p, fb), kFrameBytes, mbar);
+    };
+    if constexpr (kTma) {
+        if (lane == 0 && q < n_pairs) issue(q);
+    }
+    uint32_t phase = 0;
+
+    const float2* twf = p.tw_fwd + lane;
+    const float2* twi = p.tw_aux + lane;            // [R][32]  exp(+2 pi i lane k2 / M)
+    const float2* tw2 = p.tw_aux + R * 32 + lane;   // [32][32] exp(+2 pi i (lane % G) n1 / 32)
+
+    // The loop bound is CTA-uniform and every trip starts with a block barrier: the four warps then
+    // walk the (56 KB, fully unrolled) loop body roughly in step and share instruction-cache lines.
+    for (long long q0 = (long long)blockIdx.x * kDualWarps; q0 < n_pairs; q0 += stride, q += stride) {
+        __syncthreads();
+        const bool idle = q >= n_pairs;           // tail: keep barrier participation uniform, store nothing
+        const long long qq = idle ? n_pairs - 1 : q;
+        c2 v[32];
+        if constexpr (kTma) {
+            if (!idle) {                          // idle warps issued no copy; they chew on stale buffer contents
+                mbar_wait(mbar, phase);
+                phase ^= 1;
+            }
+#pragma unroll
+            for (int j = 0; j < 32; j++) unpack_words(inA[lane + 32 * j], inB[lane + 32 * j], p.rand_mul, v[brev5(j)]);
+            __syncwarp();   // every lane has consumed its words: the buffers may be overwritten
+            if (lane == 0 && q + stride < n_pairs) issue(q + stride);   // idle warps never issued: their barrier would hang
+        } else {
+            const long long fa = 2 * qq;
+            const long long fb = (fa + 1 < p.total_frames) ? fa + 1 : fa;   // odd tail: B repeats A, never stored
+            const uint32_t* ga = frame_src(p, fa) + lane;
+            const uint32_t* gb = frame_src(p, fb) + lane;
+            uint32_t wa[32], wb[32];
+#pragma unroll
+            for (int j = 0; j < 32; j++) {
+                wa[j] = __ldg(ga + 32 * j);
+                wb[j] = __ldg(gb + 32 * j);
+            }
+#pragma unroll
+            for (int j = 0; j < 32; j++) unpack_words(wa[j], wb[j], p.rand_mul, v[brev5(j)]);
+        }
+
+        // ---- forward 1024-point transform of z = x[2n] + i x[2n+1] ------------------------------
+        dit2<32, false>(v);
+#pragma unroll
+        for (int k2 = 1; k2 < 32; k2++) v[k2] = cmul2s(v[k2], __ldg(twf + 32 * k2));
+#pragma unroll
+        for (int k2 = 0; k2 < 32; k2++) sts2(S, lane * 33 + k2, v[k2]);
+        PHASE_SYNC();
+#pragma unroll
+        for (int n1 = 0; n1 < 32; n1++) v[brev5(n1)] = lds2(S, n1 * 33 + lane);
+        __syncwarp();
+        dit2<32, false>(v);                       // v[k1] = Z[32*k1 + lane]
+
+        // ---- spectrum to shared memory in natural order -------------------------------------------
+#pragma unroll
+        for (int k1 = 0; k1 < 32; k1++) sts2(S, 32 * k1 + lane, v[k1]);
+        PHASE_SYNC();
+        // ---- band cut in backward-transform order: m = lane + 32*j, bin k = tunebin + s(m) --------
+        c2 y[R];
+#pragma unroll
+        for (int j = 0; j < R; j++) {
+            const int m = lane + 32 * j;
+            const int s = m < M / 2 ? m : m - M;                     // upper half of the band is below the tune bin
+            const int kk = (p.tunebin + s) & (kHalfFft - 1);         // wrapped bins meet P = Q = 0: zero fill
+            const c2 a = lds2(S, kk);
+            const c2 b = lds2(S, (kHalfFft - kk) & (kHalfFft - 1));
+            const float2 P = __ldg(p.gp + kk);
+            const float2 Q = __ldg(p.gq + kk);
+            c2 r;
+            r.re = fma2(bc(Q.y), b.im, fma2(bc(Q.x), b.re, fma2(bc(-P.y), a.im, mul2(bc(P.x), a.re))));
+            r.im = fma2(bc(Q.y), b.re, fma2(bc(-Q.x), b.im, fma2(bc(P.y), a.re, mul2(bc(P.x), a.im))));
+            y[brev_n(j, RB)] = r;                                    // bit-reversed placement
+        }
+        PHASE_SYNC();   // every lane is done with the spectrum: the tile is free for the transposition
+
+        // ---- backward mfft-point transform: n = lane + 32*n2, k = k2 + R*k1 ------------------------
+        dit2<R, true>(y);                         // pass 1 over n2
+#pragma unroll
+        for (int k2 = 1; k2 < R; k2++) y[k2] = cmul2s(y[k2], __ldg(twi + 32 * k2));   // exp(+2 pi i lane k2 / M)
+#pragma unroll
+        for (int k2 = 0; k2 < R; k2++) sts2(S, lane * (R + 1) + k2, y[k2]);
+        PHASE_SYNC();
+        const int k2p = lane / G;                 // which 32-point DFT this lane works on
+        const int h = lane % G;                   // it computes outputs k1 = h + G*q
+        c2 t[R];
+#pragma unroll
+        for (int n1 = 0; n1 < 32; n1++) {         // u_j = sum_r x[j + R*r] * exp(+2 pi i h (j + R*r) / 32)
+            const c2 x = lds2(S, n1 * (R + 1) + k2p);
+            const float2 w = __ldg(tw2 + 32 * n1);
+            const int j = n1 % R;
+            c2& u = t[brev_n(j, RB)];
+            if (n1 < R) {
+                u.re = fma2(bc(w.x), x.re, mul2(bc(-w.y), x.im));
+                u.im = fma2(bc(w.x), x.im, mul2(bc(w.y), x.re));
+            } else {
+                u.re = fma2(bc(w.x), x.re, fma2(bc(-w.y), x.im, u.re));
+                u.im = fma2(bc(w.x), x.im, fma2(bc(w.y), x.re, u.im));
+            }
+        }
+        __syncwarp();
+        dit2<R, true>(t);                         // t[q] = y_out[k2p + R*h + 32*q] for both frames
+
+        // ---- overlap-save discard + placement (impl.hpp:117-138) --------------------------------
+        const FrameOut2 oa = frame_out_dn<D>(2 * qq, p.total_frames);
+        const FrameOut2 ob = frame_out_dn<D>(2 * qq + 1, p.total_frames);
+        const int idx0 = k2p + R * h;
+#pragma unroll
+        for (int q4 = 0; q4 < R; q4++) {
+            const int idx = idx0 + 32 * q4;
+            float ar, br, ai, bi;
+            upk(t[q4].re, ar, br);
+            upk(t[q4].im, ai, bi);
+            if (!idle && idx >= oa.lo && idx < 3 * M / 4) p.out[oa.base + idx] = make_float2(ar, ai * p.imag_sign);
+            if (!idle && ob.live && idx >= ob.lo && idx < 3 * M / 4) p.out[ob.base + idx] = make_float2(br, bi * p.imag_sign);
+        }
+    }
+}
+
+template <int D, bool kTma>
+static cudaError_t setup_dual_one() {
+    cudaError_t e = cudaFuncSetAttribute(r2iq_dual_dn_kernel<D, kTma>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         kDualWarps * warp_bytes<kTma>());
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(r2iq_dual_dn_kernel<D, kTma>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                cudaSharedmemCarveoutMaxShared);
+}
+
+cudaError_t setup_dual_dn_kernels() {
+    cudaError_t e;
+    if ((e = setup_dual_one<1, true>()) != cudaSuccess) return e;
+    if ((e = setup_dual_one<2, true>()) != cudaSuccess) return e;
+    if ((e = setup_dual_one<3, true>()) != cudaSuccess) return e;
+    if ((e = setup_dual_one<4, true>()) != cudaSuccess) return e;
+    if ((e = setup_dual_one<5, true>()) != cudaSuccess) return e;
+    return cudaSuccess;
+}
+
+template <int D, bool kTma>
+static cudaError_t launch_dual_one(const FusedParams& p, int sm_count, cudaStream_t stream) {
+    constexpr int smem = kDualWarps * warp_bytes<kTma>();
+    int ctas_per_sm = 1;
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, r2iq_dual_dn_kernel<D, kTma>, kDualThreads, smem);
+    if (e != cudaSuccess) return e;
+    if (ctas_per_sm < 1) ctas_per_sm = 1;
+    const long long n_pairs = (p.total_frames + 1) / 2;
+    long long want = (n_pairs + kDualWarps - 1) / kDualWarps;
+    long long grid = (long long)sm_count * ctas_per_sm;
+    if (grid > want) grid = want;
+    if (grid < 1) grid = 1;
+    r2iq_dual_dn_kernel<D, kTma><<<(unsigned)grid, kDualThreads, smem, stream>>>(p);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_dual_dn(int d, const FusedParams& p, int sm_count, cudaStream_t stream) {
+    switch (d) {
+        case 1: return launch_dual_one<1, true>(p, sm_count, stream);
+        case 2: return launch_dual_one<2, true>(p, sm_count, stream);
+        case 3: return launch_dual_one<3, true>(p, sm_count, stream);
+        case 4: return launch_dual_one<4, true>(p, sm_count, stream);
+        case 5: return launch_dual_one<5, true>(p, sm_count, stream);
+        default: return cudaErrorInvalidValue;
+    }
+}
+
+}  // namespace r2iq

@@ -220,6 +220,7 @@ cudaError_t setup_fused_kernels() {
     if ((e = setup_dual_kernels()) != cudaSuccess) return e;
     if ((e = setup_dual_d0_kernels()) != cudaSuccess) return e;
     if ((e = setup_dual_d1_kernels()) != cudaSuccess) return e;
+    if ((e = setup_dual_dn_kernels()) != cudaSuccess) return e;
     if ((e = setup_one<0>()) != cudaSuccess) return e;
     if ((e = setup_one<1>()) != cudaSuccess) return e;
     if ((e = setup_one<2>()) != cudaSuccess) return e;
@@ -232,13 +233,15 @@ cudaError_t setup_fused_kernels() {
 
 cudaError_t launch_fused(int d, const FusedParams& p, int sm_count, cudaStream_t stream) {
     // Kernel choice per decimation, from measurements on B200 (profiles/README.md):
-    //   generation 0 (default): d = 0 specialised dual-frame kernel with TMA-staged input; d = 1 dual-frame
-    //   kernel with direct loads; d >= 2 first-generation one-frame-per-warp kernels (12 warps per SM beat
-    //   8 dual-frame warps once the backward transform is small).
-    //   1: first generation everywhere; 2: generic dual-frame, direct loads; 3: generic dual-frame, TMA.
-    if (g_kernel_gen == 0) {
+    //   generation 0 (default): dual-frame packed-fp32x2 kernels with TMA-staged input -- specialised for
+    //   d = 0 and d = 1, the generic R = 32>>d member for d = 2..5; d = 6 (mfft 16 < 32 lanes) runs the
+    //   first-generation one-frame-per-warp kernel.
+    //   1: first generation everywhere; 2: first dual-frame family (scalar backward batch), direct loads;
+    //   3: the same with TMA; 4: generic packed-backward kernel also for d = 1.
+    if (g_kernel_gen == 0 || g_kernel_gen == 4) {
         if (d == 0) return launch_dual_d0(p, sm_count, stream, true);
-        if (d == 1) return launch_dual_d1(p, sm_count, stream, true);
+        if (d == 1 && g_kernel_gen == 0) return launch_dual_d1(p, sm_count, stream, true);
+        if (d <= 5) return launch_dual_dn(d, p, sm_count, stream);
     } else if (g_kernel_gen != 1) {
         return launch_dual(d, p, sm_count, stream, g_kernel_gen == 3);
     }

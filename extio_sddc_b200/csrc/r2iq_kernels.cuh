@@ -24,7 +24,8 @@ struct FusedParams {
     const float2* gp;           // [1024]    gk + gck   (dual-frame kernel: Y = gp*a + gq*conj(b))
     const float2* gq;           // [1024]    gk - gck
     const float2* tw_inv;       // d=0: [32][32] conj(W_1024)^((lane-tunebin)*k2); d>=1: [32][L] conj(W_M)^(n1*k2)
-    const float2* tw_aux;       // d=1 dual-frame kernel: [16][32] exp(+2 pi i lane k2 / 512); else null
+    const float2* tw_aux;       // d=1..5 dual-frame kernels: [R][32] exp(+2 pi i lane k2 / mfft), R = 32>>d, then
+                                // [32][32] exp(+2 pi i (lane % (32/R)) n1 / 32); else null
     int tunebin;
     int band_lo, band_hi;       // forward-FFT bins [lo,hi) that feed the inverse transform
     uint32_t rand_mul;          // 0xFFFE when the ADC randomizer is on, else 0
@@ -52,12 +53,15 @@ cudaError_t launch_channels(int d, const ChannelParams& p, int sm_count, cudaStr
 // Launch the fused kernel for decimation index d on `stream`.  Returns cudaGetLastError().
 cudaError_t launch_fused(int d, const FusedParams& p, int sm_count, cudaStream_t stream);
 // Kernel generation selector for A/B measurements (env R2IQ_KERNEL_GEN): 0 = the fastest measured kernel
-// per decimation (default, see launch_fused), 1 = first-generation one-frame-per-warp kernels,
-// 2 = generic dual-frame with direct loads, 3 = generic dual-frame with TMA staging.  All meet the parity bar.
+// per decimation (default, see launch_fused); 1..4 = older or alternative families kept for comparison.
+// All meet the parity bar.
 void set_kernel_generation(int gen);
 // second-generation kernels (r2iq_dual.cu): two frames per warp on packed fp32x2 lanes + TMA input
 cudaError_t setup_dual_kernels();
 cudaError_t launch_dual(int d, const FusedParams& p, int sm_count, cudaStream_t stream, bool tma);
+// dual-frame kernels with packed backward transform for d = 1..5 (r2iq_dual_dn.cu)
+cudaError_t setup_dual_dn_kernels();
+cudaError_t launch_dual_dn(int d, const FusedParams& p, int sm_count, cudaStream_t stream);
 // specialised d = 1 dual-frame kernel (r2iq_dual_d1.cu)
 cudaError_t setup_dual_d1_kernels();
 cudaError_t launch_dual_d1(const FusedParams& p, int sm_count, cudaStream_t stream, bool tma);
