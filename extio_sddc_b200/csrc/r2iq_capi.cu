@@ -48,6 +48,7 @@ struct TableSet {   // device tables for one (decimation, tune bin)
     float2* tw_inv = nullptr;
     float2* tw_aux = nullptr;
     int band_lo = 0, band_hi = 0;
+    uint32_t row_mask = 0xFFFFFFFFu;
 };
 
 struct Slot {
@@ -156,6 +157,12 @@ int get_tables(r2iq_cuda_t h, int d, int tunebin, TableSet* out) {
     TableSet ts;
     ts.band_lo = tunebin - M / 2 < 0 ? 0 : tunebin - M / 2;
     ts.band_hi = tunebin + M / 2 > kHalfFft ? kHalfFft : tunebin + M / 2;
+    ts.row_mask = 0;   // rows the band cut of the dual-frame kernels reads (wrapped bins and mirrors included)
+    for (int s = -M / 2; s < M / 2; s++) {
+        const int kk = (tunebin + s) & (kHalfFft - 1);
+        ts.row_mask |= 1u << (kk >> 5);
+        ts.row_mask |= 1u << (((kHalfFft - kk) & (kHalfFft - 1)) >> 5);
+    }
     for (int k = 0; k < kHalfFft; k++) {
         const int s = k - tunebin;
         if (s >= -M / 2 && s < M / 2) {
@@ -241,6 +248,7 @@ int launch(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d_out, cuda
     p.tunebin = h->tunebin;
     p.band_lo = ts.band_lo;
     p.band_hi = ts.band_hi;
+    p.row_mask = ts.row_mask;
     p.rand_mul = h->rand_on ? 0xFFFEu : 0u;
     p.imag_sign = h->latched_sideband ? -1.0f : 1.0f;
     CU(h, launch_fused(d, p, h->sm_count, stream));

@@ -89,14 +89,21 @@ __device__ __forceinline__ int brev5(int v) { return (int)(__brev((unsigned)v) >
 // Shared-memory exchanges use two 64-bit planes (re pairs, im pairs) rather than one 128-bit element:
 // a v2.b64 access needs re and im in four consecutive registers, and ptxas paid ~400 MOVs per
 // iteration to arrange that; plane accesses have no such constraint and stay conflict-free at pitch 33.
+// (Stored as float2 halves: a plain 64-bit store of the packed register makes ptxas copy the pair into a
+// scratch pair first -- two MOVs per STS.64 and a serialising dependency; float2 stores use it in place.)
 __device__ __forceinline__ void sts2(u64* S, int idx, c2 v) {
-    S[idx] = v.re;
-    S[kTile + idx] = v.im;
+    float a, b, c, d;
+    upk(v.re, a, b);
+    upk(v.im, c, d);
+    reinterpret_cast<float2*>(S)[idx] = make_float2(a, b);
+    reinterpret_cast<float2*>(S)[kTile + idx] = make_float2(c, d);
 }
 __device__ __forceinline__ c2 lds2(const u64* S, int idx) {
+    const float2 r = reinterpret_cast<const float2*>(S)[idx];
+    const float2 i = reinterpret_cast<const float2*>(S)[kTile + idx];
     c2 v;
-    v.re = S[idx];
-    v.im = S[kTile + idx];
+    v.re = pk(r.x, r.y);
+    v.im = pk(i.x, i.y);
     return v;
 }
 

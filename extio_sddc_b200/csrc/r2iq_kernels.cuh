@@ -28,6 +28,7 @@ struct FusedParams {
                                 // [32][32] exp(+2 pi i (lane % (32/R)) n1 / 32); else null
     int tunebin;
     int band_lo, band_hi;       // forward-FFT bins [lo,hi) that feed the inverse transform
+    uint32_t row_mask;          // bit k1 set: spectrum row [32*k1, 32*k1+32) holds a band bin or the mirror of one
     uint32_t rand_mul;          // 0xFFFE when the ADC randomizer is on, else 0
     float imag_sign;            // -1 when sideband inversion (copy<true>) is requested, else +1
 };
