@@ -159,7 +159,7 @@ def run_reference(args, rank: int, world: int):
         return 0
     from oracle import ref_lib
     if not ref_lib.available(2048) and not ref_lib.build():
-        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref is not built and /root/reference is absent"}))
+        _emit({"impl": "reference", "unavailable": "oracle/_ref is not built and /root/reference is absent"})
         return 0
     cores = pick_instances()
     blocks = args.ref_blocks
@@ -184,7 +184,7 @@ def run_reference(args, rank: int, world: int):
             "cpu_baseline": {"value": round(value, 4), "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample},
             "e2e": {"value": round(value, 4), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "per_decimation": detail, "gpu_launches": 0}
-    print(json.dumps(line))
+    _emit(line)
     return 0
 
 
@@ -451,13 +451,26 @@ def run_ours(args, rank: int, local_rank: int, world: int):
             line["channelizer"] = channelizer
         if cpu_baseline is not None:
             line["cpu_baseline"] = cpu_baseline
-        print(json.dumps(line))
+        _emit(line)
     if world > 1:
         dist.destroy_process_group()
     return 0
 
 
+def _emit(line: dict) -> None:
+    """Print the ONE JSON line on the real stdout (see main(): fd 1 is parked on stderr while the run is
+    in progress so that library banners -- NCCL prints its version on stdout -- cannot precede it)."""
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
+
+
+_REAL_STDOUT = 1
+
+
 def main():
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
