@@ -1,5 +1,8 @@
-// r2iq_dual.cu -- second-generation fused r2iq kernels: TWO frames per warp on packed fp32x2 lanes,
-// input frames prefetched into shared memory by TMA bulk copies (cp.async.bulk + mbarrier).
+// r2iq_dual.cu -- FIRST dual-frame family (kept for A/B measurements, R2IQ_KERNEL_GEN=2/3; the default
+// kernels are r2iq_dual_d0.cu, r2iq_dual_d1.cu and r2iq_dual_dn.cu, which also pack the backward transform):
+// TWO frames per warp on packed fp32x2 lanes, input frames optionally prefetched into shared memory by TMA
+// bulk copies (cp.async.bulk + mbarrier); for d >= 1 the bands are staged and transformed back by the
+// scalar inverse_batch of the first-generation kernels.
 //
 // Same mathematics and the same warp-per-frame decomposition as r2iq_kernels.cu (radix-32 register
 // passes, one padded shared-memory transposition per 1024-point transform), but every register
@@ -9,7 +12,7 @@
 //   * the real-FFT mirror bin Z[1024-k] is fetched through shared memory (Z is written once in
 //     natural order, 16 bytes per bin for the two frames) instead of by warp shuffle, which lets the
 //     split/filter step  Y = P[k]*Z[k] + Q[k]*conj(Z[1024-k])  run IN PLACE in the registers;
-//   * 128-bit shared accesses (both frames of a bin) halve the LDS/STS count per frame;
+//   * shared-memory exchanges move both frames of a bin (two 8-byte planes, re pairs and im pairs);
 //   * the next pair of frames is in flight (TMA -> smem) while the current pair is transformed, so
 //     8 resident warps per SM (255 registers each) are enough to cover DRAM latency.
 // Reference lines replaced: Core/fft_mt_r2iq_impl.hpp:40-54,84-138 (see r2iq_kernels.cu).

@@ -74,16 +74,17 @@ def gather_to_rank0(local, sizes: Sequence[int], rank: int, world: int, group=No
     import torch.distributed as dist
     if world == 1:
         return local
+    # one grouped exchange (ncclGroupStart/End under NCCL): all peers' transfers are in flight together,
+    # rank 0's NVLink ingest is the only serial resource
     if rank == 0:
-        parts = [local]
-        for src in range(1, world):
-            buf = torch.empty(sizes[src], dtype=local.dtype, device=local.device)
-            if sizes[src]:
-                dist.recv(buf, src=src, group=group)
-            parts.append(buf)
+        parts = [local] + [torch.empty(sizes[src], dtype=local.dtype, device=local.device) for src in range(1, world)]
+        ops = [dist.P2POp(dist.irecv, parts[src], src, group) for src in range(1, world) if sizes[src]]
+        for req in (dist.batch_isend_irecv(ops) if ops else []):
+            req.wait()
         return torch.cat(parts)
     if sizes[rank]:
-        dist.send(local, dst=0, group=group)
+        for req in dist.batch_isend_irecv([dist.P2POp(dist.isend, local, 0, group)]):
+            req.wait()
     return None
 
 
