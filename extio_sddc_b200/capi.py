@@ -66,6 +66,7 @@ _SIGNATURES = {
     "r2iq_cuda_process_device": (_I, [_VP, _VP, _L, _VP, _VP]),
     "r2iq_cuda_process_channels": (_I, [_VP, _VP, _L, _VP, _VP, _I, _VP]),
     "r2iq_cuda_process_channels_device": (_I, [_VP, _VP, _L, _VP, _I, _VP, _VP]),
+    "r2iq_cuda_set_fine_tune": (_F, [_VP, _F]),
     "r2iq_cuda_sync": (_I, [_VP]),
     "r2iq_cuda_host_alloc": (_VP, [ctypes.c_size_t]),
     "r2iq_cuda_host_free": (_I, [_VP]),

@@ -56,7 +56,23 @@ struct Slot {
     cudaEvent_t done = nullptr;
     int16_t* d_in = nullptr;     // [halfFft | chunk_blocks * 65536]
     float* d_out = nullptr;      // chunk_blocks * 32768 complex (sized for d = 0)
+    float* d_starts = nullptr;   // fine-tune NCO: start phasors of the chunk's 128-sample blocks
+    size_t starts_cap = 0;       // capacity of d_starts in 128-sample blocks
     bool busy = false;
+};
+
+// Host side of the fine-tune NCO: the state and small table of shift_limited_unroll_C_sse_init
+// (Core/pffft/pf_mixer.cpp:750-787) and the once-per-128-samples recurrence of
+// shift_limited_unroll_C_sse_inp_c (:840-853), in the same single-precision operations.
+struct NcoState {
+    bool on = false;
+    float fc = 0.f;
+    float tab[33][2];       // phasor of 4*(g+1) phase increments, g = 0..32 (dinterl_trig)
+    float cs[4], sn[4];     // phase_state_i / phase_state_q
+    float* d_tab = nullptr;
+    float* d_starts = nullptr;   // device-path scratch (caller's stream keeps launches ordered)
+    size_t starts_cap = 0;
+    std::vector<float> h_starts;
 };
 
 }  // namespace
@@ -91,6 +107,8 @@ struct r2iq_cuda_s {
     int16_t* carry = nullptr;                      // pinned: last halfFft samples of the stream
     bool carry_valid = false;
     cudaStream_t util_stream = nullptr;
+
+    NcoState nco;
 
     r2iq_cuda_stats stats{};
 };
@@ -229,7 +247,72 @@ int get_tables(r2iq_cuda_t h, int d, int tunebin, TableSet* out) {
     return R2IQ_OK;
 }
 
-int launch(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d_out, cudaStream_t stream) {
+void nco_init(NcoState& s, float relative_freq) {
+    const float PI_F = 3.14159265358979323846f;             // PI as the reference's float arithmetic sees it
+    const float inc = 2 * relative_freq * PI_F;
+    float myphase = 0.0F;
+    for (int g = 0; g < 33; g++) {
+        for (int k = 0; k < 4; k++) {
+            myphase += inc;
+            while (myphase > PI_F) myphase -= 2 * PI_F;
+            while (myphase < -PI_F) myphase += 2 * PI_F;
+        }
+        s.tab[g][0] = cosf(myphase);
+        s.tab[g][1] = sinf(myphase);
+    }
+    myphase = 0.0F;                                          // phase_start_rad = 0 (RadioHandler.cpp:295)
+    for (int i = 0; i < 4; i++) {
+        s.cs[i] = cosf(myphase);
+        s.sn[i] = sinf(myphase);
+        myphase += inc;
+        while (myphase > PI_F) myphase -= 2 * PI_F;
+        while (myphase < -PI_F) myphase += 2 * PI_F;
+    }
+    s.fc = relative_freq;
+}
+
+// Start phasors of the next n128 blocks of 128 samples into s.h_starts ([block][lane] (cos, sin)); advances the state.
+void nco_advance(NcoState& s, size_t n128) {
+    s.h_starts.resize(n128 * 8);
+    const volatile float tc = s.tab[31][0], ts = s.tab[31][1];   // after 32 groups vals = table[31] * starts
+    for (size_t b = 0; b < n128; b++) {
+        for (int j = 0; j < 4; j++) {
+            s.h_starts[b * 8 + 2 * j] = s.cs[j];
+            s.h_starts[b * 8 + 2 * j + 1] = s.sn[j];
+            // volatile temporaries keep every product separately rounded (no contraction, as the SSE code)
+            volatile float a = tc * s.cs[j], bb = ts * s.sn[j], cc = ts * s.cs[j], dd = tc * s.sn[j];
+            volatile float cv = a - bb, sv = cc + dd;
+            volatile float m1 = cv * cv, m2 = sv * sv;
+            volatile float mag = sqrtf(m1 + m2);
+            s.cs[j] = cv / mag;
+            s.sn[j] = sv / mag;
+        }
+    }
+}
+
+// Apply the fine-tune NCO to the n_out complex samples a launch just produced (same stream).
+int nco_stage(r2iq_cuda_t h, float* d_out, size_t n_out, float** d_starts, size_t* cap, cudaStream_t stream) {
+    NcoState& s = h->nco;
+    if (!s.on || n_out == 0) return R2IQ_OK;
+    if (n_out % 128) return fail(R2IQ_E_INVALID, "fine-tune mixer needs a multiple of 128 output samples per call");
+    const size_t n128 = n_out / 128;
+    if (*cap < n128) {
+        if (*d_starts) {
+            CU(h, cudaStreamSynchronize(stream));
+            cudaFree(*d_starts);
+        }
+        CU(h, cudaMalloc(d_starts, sizeof(float) * 8 * n128));
+        *cap = n128;
+    }
+    nco_advance(s, n128);
+    // pageable source: the call returns once the data sits in the driver's staging buffer, so h_starts may be reused
+    CU(h, cudaMemcpyAsync(*d_starts, s.h_starts.data(), sizeof(float) * 8 * n128, cudaMemcpyHostToDevice, stream));
+    CU(h, launch_nco_mix(d_out, (long long)n_out, *d_starts, s.d_tab, stream));
+    return R2IQ_OK;
+}
+
+int launch(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d_out, cudaStream_t stream, float** nco_starts,
+           size_t* nco_cap) {
     TableSet ts;
     const int d = h->latched_decimate;
     int rc = get_tables(h, d, h->tunebin, &ts);
@@ -254,7 +337,7 @@ int launch(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d_out, cuda
     CU(h, launch_fused(d, p, h->sm_count, stream));
     h->stats.kernel_launches++;
     h->stats.blocks_processed += (uint64_t)n_blocks;
-    return R2IQ_OK;
+    return nco_stage(h, d_out, (size_t)n_blocks * (size_t)((kTransferSamples / 2) >> d), nco_starts, nco_cap, stream);
 }
 
 // Channelizer launch: per-d filter table in inverse-FFT bin order + the tune-bin list on the device.
@@ -419,7 +502,10 @@ int r2iq_cuda_destroy(r2iq_cuda_t h) {
         if (s.done) cudaEventDestroy(s.done);
         cudaFree(s.d_in);
         cudaFree(s.d_out);
+        cudaFree(s.d_starts);
     }
+    cudaFree(h->nco.d_tab);
+    cudaFree(h->nco.d_starts);
     if (h->util_stream) cudaStreamDestroy(h->util_stream);
     cudaFree(h->d_tw_fwd);
     if (h->carry) cudaFreeHost(h->carry);
@@ -497,6 +583,29 @@ int r2iq_cuda_set_sideband(r2iq_cuda_t h, int lsb) {
 }
 int r2iq_cuda_get_sideband(r2iq_cuda_t h) { return h ? (int)h->sideband : R2IQ_E_INVALID; }
 
+float r2iq_cuda_set_fine_tune(r2iq_cuda_t h, float fc) {
+    if (!h || h->poisoned) return 0.f;
+    std::lock_guard<std::mutex> lk(h->mu);
+    NcoState& s = h->nco;
+    if (fc == 0.0f) {                 // RadioHandler.cpp:33: the mixer is skipped when fc == 0
+        s.on = false;
+        s.fc = 0.f;
+        return 0.f;
+    }
+    if (s.on && s.fc == fc) return fc;   // RadioHandler.cpp:292: the state restarts only when fc changes
+    nco_init(s, fc);
+    if (!s.d_tab && cudaMalloc(&s.d_tab, sizeof(float) * 66) != cudaSuccess) return 0.f;
+    // ordered after everything already queued: the table may still be read by launches in flight
+    if (cudaDeviceSynchronize() != cudaSuccess ||
+        cudaMemcpy(s.d_tab, &s.tab[0][0], sizeof(float) * 66, cudaMemcpyHostToDevice) != cudaSuccess) {
+        h->poisoned = true;
+        fail(R2IQ_E_CUDA, "fine-tune table upload failed");
+        return 0.f;
+    }
+    s.on = true;
+    return fc;
+}
+
 int r2iq_cuda_turn_on(r2iq_cuda_t h) {
     int rc = check_handle(h);
     if (rc) return rc;
@@ -551,7 +660,7 @@ int r2iq_cuda_process(r2iq_cuda_t h, const int16_t* blocks, long n_blocks, const
                                   cudaMemcpyHostToDevice, s.stream));
         }
         h->stats.h2d_bytes += sizeof(int16_t) * ((size_t)kHalfFft + (size_t)nb * kTransferSamples);
-        if ((rc = launch(h, s.d_in, nb, s.d_out, s.stream)) != R2IQ_OK) return rc;
+        if ((rc = launch(h, s.d_in, nb, s.d_out, s.stream, &s.d_starts, &s.starts_cap)) != R2IQ_OK) return rc;
         const size_t out_bytes = sizeof(float) * 2 * (size_t)nb * out_per_block;
         CU(h, cudaMemcpyAsync(iq_out + 2 * (size_t)done * out_per_block, s.d_out, out_bytes, cudaMemcpyDeviceToHost,
                               s.stream));
@@ -582,7 +691,7 @@ int r2iq_cuda_process_device(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, 
         return fail(R2IQ_E_INVALID, "process_device: input must be 16-byte and output 8-byte aligned");
     if (n_blocks == 0) return R2IQ_OK;
     std::lock_guard<std::mutex> lk(h->mu);
-    return launch(h, d_in, n_blocks, d_iq_out, (cudaStream_t)stream);
+    return launch(h, d_in, n_blocks, d_iq_out, (cudaStream_t)stream, &h->nco.d_starts, &h->nco.starts_cap);
 }
 
 int r2iq_cuda_process_channels_device(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, const int* tunebins,

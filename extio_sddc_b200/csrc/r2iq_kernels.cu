@@ -258,6 +258,43 @@ cudaError_t launch_fused(int d, const FusedParams& p, int sm_count, cudaStream_t
 }
 
 // ---------------------------------------------------------------------------------------------
+// Residual fine-tune mixer: the complex NCO RadioHandlerClass applies to every output
+// slot right after the operator (Core/RadioHandler.cpp:33-37 -> shift_limited_unroll_C_sse_inp_c,
+// Core/pffft/pf_mixer.cpp:791-856).  The reference advances four start phasors once per 128 samples
+// (multiply by a table entry, renormalise) and derives the phasor of sample group g inside the block as
+// table[g-1] * start; `starts` holds the start phasors of every 128-sample block of this launch (the
+// sequential recurrence is run on the host, r2iq_capi.cu), so every sample is independent here.  Products
+// are formed with separately rounded multiplies and add/sub exactly like the reference's SSE code (its
+// function clones carry no FMA target, Core/pffft/fmv.h:9): the result is bit-identical to the CPU mixer.
+// ---------------------------------------------------------------------------------------------
+__global__ void nco_mix_kernel(float2* __restrict__ iq, long long n, const float2* __restrict__ starts,
+                               const float2* __restrict__ tab) {
+    long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (; i < n; i += stride) {
+        const float2 s = __ldg(&starts[(i >> 7) * 4 + (i & 3)]);
+        const int g = (int)((i & 127) >> 2);
+        float2 ph = s;
+        if (g) {
+            const float2 t = __ldg(&tab[g - 1]);
+            ph.x = __fsub_rn(__fmul_rn(t.x, s.x), __fmul_rn(t.y, s.y));
+            ph.y = __fadd_rn(__fmul_rn(t.y, s.x), __fmul_rn(t.x, s.y));
+        }
+        const float2 v = iq[i];
+        iq[i] = make_float2(__fsub_rn(__fmul_rn(v.x, ph.x), __fmul_rn(v.y, ph.y)),
+                            __fadd_rn(__fmul_rn(v.y, ph.x), __fmul_rn(v.x, ph.y)));
+    }
+}
+
+cudaError_t launch_nco_mix(float* iq, long long n_complex, const float* starts, const float* tab, cudaStream_t stream) {
+    if (n_complex <= 0) return cudaSuccess;
+    long long blocks = (n_complex + 255) / 256;
+    if (blocks > 148 * 32) blocks = 148 * 32;
+    nco_mix_kernel<<<(unsigned)blocks, 256, 0, stream>>>((float2*)iq, n_complex, (const float2*)starts, (const float2*)tab);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------
 // the bit-exact stage on its own (parity hook): convert_float<rand> of Core/fft_mt_r2iq.h:36-51
 // ---------------------------------------------------------------------------------------------
 __global__ void convert_kernel(const uint32_t* __restrict__ in, float2* __restrict__ out, long long n_words,

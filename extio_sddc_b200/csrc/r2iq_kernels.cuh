@@ -71,6 +71,8 @@ cudaError_t setup_dual_d0_kernels();
 cudaError_t launch_dual_d0(const FusedParams& p, int sm_count, cudaStream_t stream, bool tma);
 // One-time per-device setup (opt-in shared memory sizes).
 cudaError_t setup_fused_kernels();
+// Fine-tune NCO applied in place to n_complex output samples (see nco_mix_kernel).
+cudaError_t launch_nco_mix(float* iq, long long n_complex, const float* starts, const float* tab, cudaStream_t stream);
 // int16 -> float with optional de-randomisation (the bit-exact stage, exposed for parity tests).
 cudaError_t launch_convert(const int16_t* in, float* out, long long n, int rand, cudaStream_t stream);
 

@@ -10,8 +10,9 @@ constexpr int kBlock = R2IQ_TRANSFER_SAMPLES;        // int16 samples per input 
 constexpr int kSlotComplex = R2IQ_TRANSFER_SAMPLES / 2;   // complex samples per output slot (EXT_BLOCKLEN)
 }
 
-cuda_r2iq::cuda_r2iq(int device, int slots_per_batch)
-    : r2iqControlClass(), device_(device), slots_per_batch_(slots_per_batch < 1 ? 1 : slots_per_batch) {}
+cuda_r2iq::cuda_r2iq(int device, int slots_per_batch, bool fuse_fine_tune)
+    : r2iqControlClass(), device_(device), slots_per_batch_(slots_per_batch < 1 ? 1 : slots_per_batch),
+      fuse_fine_tune_(fuse_fine_tune) {}
 
 cuda_r2iq::~cuda_r2iq() {
     if (run_.load()) TurnOff();
@@ -46,7 +47,10 @@ void cuda_r2iq::Init(float gain, ringbuffer<int16_t>* input, ringbuffer<float>* 
 float cuda_r2iq::setFreqOffset(float offset) {
     if (!handle_) return 0.0f;
     r2iq_cuda_set_decimate(handle_, mdecimation);   // the residual scales with getRatio()
-    return r2iq_cuda_set_freq_offset(handle_, offset);
+    const float residual = r2iq_cuda_set_freq_offset(handle_, offset);
+    if (!fuse_fine_tune_) return residual;
+    r2iq_cuda_set_fine_tune(handle_, residual);      // same restart rule as RadioHandler.cpp:292-297
+    return 0.0f;
 }
 
 // fft_mt_r2iq::TurnOn (Core/fft_mt_r2iq.cpp:111-129)

@@ -23,7 +23,10 @@
 
 class cuda_r2iq : public r2iqControlClass {
 public:
-    explicit cuda_r2iq(int device = -1, int slots_per_batch = 1);
+    // fuse_fine_tune: run RadioHandlerClass's residual mixer (Core/RadioHandler.cpp:33-37) on the GPU too.
+    // setFreqOffset then hands the residual to the device NCO and returns 0, so the caller's `fc` stays 0
+    // and its CPU mixer is skipped (RadioHandler.cpp:33 `if (fc != 0.0f)`); the stream is bit-identical.
+    explicit cuda_r2iq(int device = -1, int slots_per_batch = 1, bool fuse_fine_tune = false);
     ~cuda_r2iq() override;
 
     void Init(float gain, ringbuffer<int16_t>* input, ringbuffer<float>* obuffers) override;
@@ -41,6 +44,7 @@ private:
 
     int device_;
     int slots_per_batch_;
+    bool fuse_fine_tune_;
     r2iq_cuda_t handle_ = nullptr;
     ringbuffer<int16_t>* in_ = nullptr;
     ringbuffer<float>* out_ = nullptr;

@@ -94,6 +94,11 @@ class CudaR2IQ:
         """fft_mt_r2iq::setFreqOffset (Core/fft_mt_r2iq.cpp:101-109); returns the fine-tune residual."""
         return float(self._lib.r2iq_cuda_set_freq_offset(self._handle(), float(offset)))
 
+    def setFineTune(self, fc: float) -> float:  # noqa: N802
+        """The residual mixer RadioHandlerClass applies after the operator (RadioHandler.cpp:33-37,292-297),
+        run on the device instead: ``fc`` is what :meth:`setFreqOffset` returned; 0 switches it off."""
+        return float(self._lib.r2iq_cuda_set_fine_tune(self._handle(), float(fc)))
+
     # -- extras the reference keeps private ---------------------------------------------------
     @property
     def tunebin(self) -> int:

@@ -141,6 +141,16 @@ R2IQ_API int r2iq_cuda_process_channels(r2iq_cuda_t h, const int16_t* blocks, lo
 R2IQ_API int r2iq_cuda_process_channels_device(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, const int* tunebins,
                                                int n_channels, float* d_iq_out, void* stream);
 
+/* Residual fine-tune mixer on the device.  RadioHandlerClass::TuneLO keeps the value
+ * returned by setFreqOffset as `fc`, restarts the NCO with shift_limited_unroll_C_sse_init(fc, 0) when it
+ * changes, and OnDataPacket rotates every output slot with shift_limited_unroll_C_sse_inp_c when fc != 0
+ * (Core/RadioHandler.cpp:33-37,287-297; Core/pffft/pf_mixer.cpp:750-856).  This call is that init: from the
+ * next processed block on, every output sample of r2iq_cuda_process / r2iq_cuda_process_device is multiplied
+ * by the same phasor sequence, bit-identical to the CPU mixer (phase continues across calls; fc = 0 switches
+ * it off; the same fc again leaves the running phase alone).  Returns fc, or 0 when switched off / on error.
+ * Not applied by the channelizer entry points. */
+R2IQ_API float r2iq_cuda_set_fine_tune(r2iq_cuda_t h, float fc);
+
 /* Block until everything issued through this handle has finished. */
 R2IQ_API int r2iq_cuda_sync(r2iq_cuda_t h);
 

@@ -31,7 +31,7 @@ def lib_path(fftn: int) -> str:
 def build(force: bool = False) -> bool:
     """Run ``make ref`` when the reference tree is present (this container).  On the GPU box the
     prebuilt libraries travel with the snapshot and /root/reference does not exist."""
-    have = all(os.path.exists(lib_path(n)) for n in (2048, 8192))
+    have = all(os.path.exists(lib_path(n)) for n in (2048, 8192)) and mixer_available()
     if os.path.isdir(os.path.join(REFERENCE_ROOT, "Core")) and (force or not have):
         subprocess.run(["make", "-C", _HERE, "ref"], check=True, stdout=subprocess.DEVNULL)
         have = True
@@ -141,6 +141,21 @@ class RefLib:
         sps = self.lib.refr2iq_bench(blocks.ctypes.data, n_distinct, warm_blocks, timed_blocks, gain, d, tunebin,
                                      int(rand), int(sideband), VARIANTS[variant], instances, ctypes.byref(sec))
         return float(sps), float(sec.value)
+
+
+def mixer_available() -> bool:
+    return os.path.exists(os.path.join(REF_DIR, "libref_mixer.so"))
+
+
+def mixer_apply(iq: np.ndarray, fc: float, slot: int = 32768) -> np.ndarray:
+    """The reference's fine-tune mixer over a complex64 stream, slot by slot with carried state, as
+    RadioHandlerClass::OnDataPacket does (Core/RadioHandler.cpp:28-37)."""
+    lib = ctypes.CDLL(os.path.join(REF_DIR, "libref_mixer.so"))
+    lib.refmix_apply.argtypes = [ctypes.c_float, ctypes.c_void_p, ctypes.c_long, ctypes.c_long]
+    lib.refmix_apply.restype = None
+    out = np.array(iq, dtype=np.complex64, copy=True)
+    lib.refmix_apply(fc, out.ctypes.data, out.shape[0], slot)
+    return out
 
 
 def get(fftn: int = 2048) -> RefLib:

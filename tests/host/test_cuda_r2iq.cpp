@@ -127,6 +127,23 @@ int main() {
         op.TurnOff();
     }
     printf("start/stop cycles done\n");
+    {   // fused fine-tune: setFreqOffset returns 0 to the caller and the device applies the residual NCO
+        cuda_r2iq fused(-1, 1, true);
+        fused.Init(gain, &in, &out);
+        fused.updateRand(false);
+        const float r = fused.setFreqOffset(0.2503f);
+        CHECK(r == 0.0f);
+        std::vector<float> a = stream(fused, in, out, 1, 32, false);
+        op.setFreqOffset(0.2503f);
+        std::vector<float> b = stream(op, in, out, 1, 32, false);
+        op.setFreqOffset(0.25f);
+        CHECK(a.size() == b.size());
+        double ea = 0, eb = 0, diff = 0;
+        for (size_t i = 0; i < a.size(); i++) { ea += (double)a[i] * a[i]; eb += (double)b[i] * b[i]; diff += (double)(a[i] - b[i]) * (a[i] - b[i]); }
+        CHECK(fabs(ea - eb) < 1e-4 * eb);   // a pure rotation keeps the energy ...
+        CHECK(diff > 1e-3 * eb);            // ... but changes the samples
+        printf("fused fine-tune mixer: energy kept (%.6g vs %.6g), samples rotated\n", ea, eb);
+    }
     r2iq_cuda_destroy(h);
     printf(failures ? "FAILED %d\n" : "ALL PASS\n", failures);
     return failures ? 1 : 0;

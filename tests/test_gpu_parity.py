@@ -304,3 +304,30 @@ def test_config4_channelizer(op):
     with pytest.raises(capi.R2iqError):
         op.process_channels(x, [256])
     op.TurnOff()
+
+
+def test_fine_tune_mixer_bit_exact(op):
+    """Next row: the residual NCO mixer RadioHandlerClass applies after the operator, run on
+    the device.  Applied to the same IQ, the device result must equal the reference's own mixer
+    (Core/pffft/pf_mixer.cpp compiled in place) BIT FOR BIT, with the phase carried across calls."""
+    from oracle import ref_lib
+    if not ref_lib.mixer_available():
+        pytest.skip("oracle/_ref/libref_mixer.so not built")
+    x = orc.rx888_blocks(6, 1, 256, randomized=True, seed=77)
+    for d, off in ((0, 0.2503), (1, 0.1431), (4, 0.6002)):
+        op.setDecimate(d); op.updateRand(True); op.setSideband(False)
+        fc = op.setFreqOffset(off)                    # residual after tune-bin quantisation
+        assert fc != 0.0
+        op.setFineTune(0.0)
+        op.TurnOn()
+        plain = op.process(x)
+        op.TurnOff()
+        assert op.setFineTune(fc) == pytest.approx(fc)
+        op.TurnOn()
+        mixed = np.concatenate([op.process(x[: 2 * 65536]), op.process(x[2 * 65536:])])   # phase carries over
+        op.TurnOff()
+        op.setFineTune(0.0)
+        want = ref_lib.mixer_apply(plain, fc, slot=32768)
+        assert np.array_equal(mixed.view(np.uint32), want.view(np.uint32)), (d, off)
+        assert not np.array_equal(mixed, plain)
+    op.tunebin = 256
