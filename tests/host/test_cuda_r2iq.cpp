@@ -24,17 +24,21 @@ static void make_block(std::vector<int16_t>& v, long first_sample) {
 }
 
 // feed n_blocks through the rings, return everything the operator published
+// `prebuilt` (optional): 16 pre-generated blocks cycled by memcpy, like fx3handler_benchmark
+// (unittest/benchmark_test.cpp:78-107), so that the producer is not the bottleneck of a throughput check.
 static std::vector<float> stream(cuda_r2iq& op, ringbuffer<int16_t>& in, ringbuffer<float>& out, int d, int n_blocks,
-                                 bool retune) {
+                                 bool retune, const std::vector<int16_t>* prebuilt = nullptr) {
     op.setDecimate(d);
     op.TurnOn();
     CHECK(op.IsOn());
     std::thread prod([&] {
         std::vector<int16_t> blk(R2IQ_TRANSFER_SAMPLES);
         for (int b = 0; b < n_blocks; b++) {
-            make_block(blk, (long)b * R2IQ_TRANSFER_SAMPLES);
+            const int16_t* src = blk.data();
+            if (prebuilt) src = prebuilt->data() + (size_t)(b % 16) * R2IQ_TRANSFER_SAMPLES;
+            else make_block(blk, (long)b * R2IQ_TRANSFER_SAMPLES);
             int16_t* p = in.getWritePtr();
-            memcpy(p, blk.data(), sizeof(int16_t) * R2IQ_TRANSFER_SAMPLES);
+            memcpy(p, src, sizeof(int16_t) * R2IQ_TRANSFER_SAMPLES);
             in.WriteDone();
         }
     });
@@ -101,6 +105,22 @@ int main() {
         for (float v : got) e += (double)v * v;
         CHECK(e > 0);
         printf("d=%d: %zu complex through the rings, identical to the direct call, %llu batches\n", d, got.size() / 2, op.batches());
+    }
+    {   // real-time margin of the live path: one launch per output slot, pageable ring slots, two PCIe copies
+        std::vector<int16_t> pre((size_t)16 * R2IQ_TRANSFER_SAMPLES), one(R2IQ_TRANSFER_SAMPLES);
+        for (int b = 0; b < 16; b++) {
+            make_block(one, (long)b * R2IQ_TRANSFER_SAMPLES);
+            memcpy(pre.data() + (size_t)b * R2IQ_TRANSFER_SAMPLES, one.data(), sizeof(int16_t) * R2IQ_TRANSFER_SAMPLES);
+        }
+        for (int d : {0, 5}) {
+            const int n_blocks = 4096;
+            auto t0 = std::chrono::steady_clock::now();
+            std::vector<float> got = stream(op, in, out, d, n_blocks, false, &pre);
+            double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+            double msps = (double)n_blocks * R2IQ_TRANSFER_SAMPLES / sec / 1e6;
+            printf("live path d=%d: %.0f Msps through the rings (RX-888 full rate is 128 Msps)\n", d, msps);
+            CHECK(msps > 128.0);
+        }
     }
     {   // retune while streaming
         std::vector<float> got = stream(op, in, out, 2, 128, true);

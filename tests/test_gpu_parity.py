@@ -331,3 +331,34 @@ def test_fine_tune_mixer_bit_exact(op):
         assert np.array_equal(mixed.view(np.uint32), want.view(np.uint32)), (d, off)
         assert not np.array_equal(mixed, plain)
     op.tunebin = 256
+
+
+@pytest.mark.parametrize("gen", ["1", "2", "3", "4"])
+def test_alternative_kernel_generations_meet_the_bar(gen):
+    """The kernel families kept in-tree for A/B measurements (env R2IQ_KERNEL_GEN, r2iq_kernels.cu
+    launch_fused) must meet the same parity bar as the default selection."""
+    import subprocess
+    import sys
+    code = r'''
+import sys, numpy as np
+sys.path.insert(0, %r)
+from extio_sddc_b200 import CudaR2IQ
+from oracle import r2iq_oracle as orc
+G = orc.RX888MK2_GAINFACTOR
+r = CudaR2IQ(); r.Init(G)
+worst = 0.0
+for d in range(7):
+    for tb, rnd, lsb in ((256, True, False), (0, False, True), (1020, True, False), (148, False, False)):
+        x = orc.rx888_blocks(3, d, tb, randomized=rnd, seed=31 + d)
+        h = np.random.default_rng(d).integers(-3000, 3000, 1024).astype(np.int16)
+        r.setDecimate(d); r.updateRand(rnd); r.setSideband(lsb); r.tunebin = tb; r.TurnOn()
+        got = r.process(x, history=h); r.TurnOff()
+        ref = orc.r2iq(x, d, tb, gain=G, rand=rnd, sideband=lsb, history=h)
+        e = orc.rel_l2(got, ref); m = float(np.abs(got - ref).max()) / orc.full_scale(G)
+        assert e <= 1e-5 and m <= 1e-4, (d, tb, e, m)
+        worst = max(worst, e)
+print("worst", worst)
+''' % (os.path.dirname(os.path.dirname(os.path.abspath(__file__))),)
+    env = dict(os.environ, R2IQ_KERNEL_GEN=gen)
+    r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "worst" in r.stdout, r.stdout + r.stderr
