@@ -424,11 +424,13 @@ def run_ours(args, rank: int, local_rank: int, world: int):
             cores = pick_instances()
             v, sec, detail, backend = reference_sweep(args.ref_blocks, cores)
             v1, sec1, _, _ = reference_sweep(max(256, args.ref_blocks // 2), 1)
+            v2, _, _, _ = reference_sweep(max(256, args.ref_blocks // 2), 1, variant="avx2")
             cpu_baseline = {"value": round(v, 4), "unit": UNIT, "cores": cores, "kind": "reference",
                             "sample": (f"oracle/_ref (unmodified fft_mt_r2iq loop over the fftw3 shim; {backend}): {cores} "
                                        f"independent operator instances x {args.ref_blocks} blocks per decimation, "
                                        f"same sweep d=0..5, {sec:.1f} s of CPU time window"),
-                            "single_instance_as_shipped": round(v1, 4), "per_decimation": detail}
+                            "single_instance_as_shipped": round(v1, 4),        # cpuid dispatcher's pick (avx512 TU on this host)
+                            "single_instance_forced_avx2_intrinsics": round(v2, 4), "per_decimation": detail}
         except Exception as ex:  # the baseline is reported, never required for the GPU arm
             cpu_baseline = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": f"unavailable: {ex}"}
 
