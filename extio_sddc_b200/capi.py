@@ -23,7 +23,8 @@ E_INVALID, E_CUDA, E_NOMEM, E_STATE, E_NODEVICE = -1, -2, -3, -4, -5
 
 
 class Config(ctypes.Structure):
-    _fields_ = [("device", ctypes.c_int), ("gain", ctypes.c_float), ("chunk_blocks", ctypes.c_int)]
+    _fields_ = [("device", ctypes.c_int), ("gain", ctypes.c_float), ("chunk_blocks", ctypes.c_int),
+                ("fftn", ctypes.c_int)]
 
 
 class Stats(ctypes.Structure):
@@ -72,6 +73,7 @@ _SIGNATURES = {
     "r2iq_cuda_host_free": (_I, [_VP]),
     "r2iq_cuda_convert": (_I, [_VP, _VP, _L, _I, _VP]),
     "r2iq_cuda_get_stats": (_I, [_VP, ctypes.POINTER(Stats)]),
+    "r2iq_cuda_get_fftn": (_I, [_VP]),
     "r2iq_cuda_design_filter": (_I, [_F, _I, _VP, _I]),
     "r2iq_cuda_kaiser": (_I, [_I, _F, _F, _F, _VP]),
     "r2iq_cuda_freq_to_tunebin": (_F, [_F, _I, ctypes.POINTER(_I)]),

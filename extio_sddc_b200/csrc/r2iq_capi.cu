@@ -85,6 +85,8 @@ struct r2iq_cuda_s {
     int chunk_blocks = kDefaultChunkBlocks;
 
     // control state (r2iqControlClass members, Core/r2iq.h:38-47; mtunebin, Core/fft_mt_r2iq.h:90)
+    int fftn = kFftN;             // FFTN_R_ADC of this operator: 2048 (north star) or 8192 (reference as shipped)
+    int half = kHalfFft;          // halfFft
     int decimate = 0;
     int tunebin = kHalfFft / 4;
     bool rand_on = false;
@@ -103,6 +105,11 @@ struct r2iq_cuda_s {
     std::map<long long, float2*> gh_tables;        // channelizer: 0.5*H_d in inverse-FFT bin order, key = version<<4 | d
     std::map<std::vector<int>, int*> chan_lists;   // channelizer: device copies of tune-bin lists
     float2* d_ctab = nullptr;                      // channelizer: -i * W_2048^k
+    // FFTN 8192 family (r2iq_wide.cu)
+    float2* d_twq = nullptr;                       // [3][1024] W_4096^(q n)
+    float2* d_wctab = nullptr;                     // [2049] -i * W_8192^p
+    struct WideSet { float2* g = nullptr; float2* tw_r = nullptr; };
+    std::map<long long, WideSet> wide_tables;      // per (filter version, d, tunebin)
     Slot slots[kSlots];
     int16_t* carry = nullptr;                      // pinned: last halfFft samples of the stream
     bool carry_valid = false;
@@ -128,6 +135,24 @@ int check_handle(r2iq_cuda_t h) {
     if (!h) return fail(R2IQ_E_INVALID, "null handle");
     if (h->poisoned) return fail(R2IQ_E_CUDA, "handle is unusable after an earlier CUDA error: %s", g_err);
     return R2IQ_OK;
+}
+
+// Twiddles of the R = M/32 register scheme for an M-point backward transform on 32 lanes (r2iq_dual_dn.cu,
+// r2iq_wide.cu): [R][32] exp(+2 pi i lane k2 / M), then [32][32] exp(+2 pi i (lane % G) n1 / 32), G = 32/R.
+std::vector<float2> build_tw_aux(int M) {
+    const int R = M / 32, G = 32 / R;
+    std::vector<float2> ta((size_t)(R + 32) * 32);
+    for (int k2 = 0; k2 < R; k2++)
+        for (int l = 0; l < 32; l++) {
+            const double th = 2.0 * kPiD * (double)((l * k2) % M) / (double)M;
+            ta[k2 * 32 + l] = make_float2((float)cos(th), (float)sin(th));
+        }
+    for (int n1 = 0; n1 < 32; n1++)
+        for (int l = 0; l < 32; l++) {
+            const double th = 2.0 * kPiD * (double)(((l % G) * n1) % 32) / 32.0;
+            ta[(R + n1) * 32 + l] = make_float2((float)cos(th), (float)sin(th));
+        }
+    return ta;
 }
 
 void free_channel_tables(r2iq_cuda_t h) {
@@ -217,18 +242,7 @@ int get_tables(r2iq_cuda_t h, int d, int tunebin, TableSet* out) {
     if (d >= 1 && d <= 5) {
         // dual-frame kernels, backward transform mfft = 32*R on 32 lanes: pass-1 twiddles exp(+2 pi i lane k2 / mfft)
         // (k2 < R), then the pass-2 weights exp(+2 pi i (lane % G) n1 / 32), G = 32/R
-        const int R = 32 >> d, G = 32 / R;
-        std::vector<float2> ta((size_t)(R + 32) * 32);
-        for (int k2 = 0; k2 < R; k2++)
-            for (int l = 0; l < 32; l++) {
-                const double th = 2.0 * kPiD * (double)((l * k2) % M) / (double)M;
-                ta[k2 * 32 + l] = make_float2((float)cos(th), (float)sin(th));
-            }
-        for (int n1 = 0; n1 < 32; n1++)
-            for (int l = 0; l < 32; l++) {
-                const double th = 2.0 * kPiD * (double)(((l % G) * n1) % 32) / 32.0;
-                ta[(R + n1) * 32 + l] = make_float2((float)cos(th), (float)sin(th));
-            }
+        const std::vector<float2> ta = build_tw_aux(M);
         CU(h, cudaMalloc(&ts.tw_aux, sizeof(float2) * ta.size()));
         CU(h, cudaMemcpy(ts.tw_aux, ta.data(), sizeof(float2) * ta.size(), cudaMemcpyHostToDevice));
     }
@@ -311,8 +325,84 @@ int nco_stage(r2iq_cuda_t h, float* d_out, size_t n_out, float** d_starts, size_
     return R2IQ_OK;
 }
 
+// FFTN 8192: static twiddles once per handle, filter gains (and small-transform twiddles) per (d, tune bin).
+int launch_wide_impl(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d_out, cudaStream_t stream) {
+    const int d = h->latched_decimate;
+    const int HF = 4096, M = HF >> d;
+    if (!h->d_twq) {
+        std::vector<float2> tq(3 * 1024), ct(2049);
+        for (int q = 1; q <= 3; q++)
+            for (int n = 0; n < 1024; n++) {
+                const double th = -2.0 * kPiD * (double)((q * n) % 4096) / 4096.0;
+                tq[(q - 1) * 1024 + n] = make_float2((float)cos(th), (float)sin(th));
+            }
+        for (int k = 0; k <= 2048; k++) {
+            const double th = 2.0 * kPiD * (double)k / 8192.0;
+            ct[k] = make_float2((float)-sin(th), (float)-cos(th));      // -i * exp(-i th)
+        }
+        CU(h, cudaMalloc(&h->d_twq, sizeof(float2) * tq.size()));
+        CU(h, cudaMalloc(&h->d_wctab, sizeof(float2) * ct.size()));
+        CU(h, cudaMemcpy(h->d_twq, tq.data(), sizeof(float2) * tq.size(), cudaMemcpyHostToDevice));
+        CU(h, cudaMemcpy(h->d_wctab, ct.data(), sizeof(float2) * ct.size(), cudaMemcpyHostToDevice));
+    }
+    const long long key = ((long long)h->hw_version[d] << 20) | ((long long)d << 16) | (long long)h->tunebin;
+    r2iq_cuda_s::WideSet ws;
+    auto it = h->wide_tables.find(key);
+    if (it != h->wide_tables.end()) ws = it->second;
+    else {
+        if (h->wide_tables.size() >= kMaxTableSets) {
+            CU(h, cudaDeviceSynchronize());
+            for (auto& kv : h->wide_tables) {
+                cudaFree(kv.second.g);
+                cudaFree(kv.second.tw_r);
+            }
+            h->wide_tables.clear();
+        }
+        std::vector<float2> g(HF);
+        for (int k = 0; k < HF; k++) {
+            const int s = k - h->tunebin;
+            if (s >= -M / 2 && s < M / 2) {
+                const std::complex<float> hh = h->hw[d][(s + HF) % HF];
+                g[k] = make_float2(0.5f * hh.real(), 0.5f * hh.imag());
+            } else {
+                g[k] = make_float2(0.f, 0.f);
+            }
+        }
+        CU(h, cudaMalloc(&ws.g, sizeof(float2) * HF));
+        CU(h, cudaMemcpy(ws.g, g.data(), sizeof(float2) * HF, cudaMemcpyHostToDevice));
+        if (d >= 2) {
+            const std::vector<float2> ta = build_tw_aux(M);
+            CU(h, cudaMalloc(&ws.tw_r, sizeof(float2) * ta.size()));
+            CU(h, cudaMemcpy(ws.tw_r, ta.data(), sizeof(float2) * ta.size(), cudaMemcpyHostToDevice));
+        }
+        h->wide_tables[key] = ws;
+    }
+    WideParams p;
+    p.in_words = (const uint32_t*)d_in;
+    p.out = (float2*)d_out;
+    p.total_frames = (long long)n_blocks * 11;
+    p.tw1024 = h->d_tw_fwd;
+    p.twq = h->d_twq;
+    p.ctab = h->d_wctab;
+    p.g = ws.g;
+    p.tw_r = ws.tw_r;
+    p.tunebin = h->tunebin;
+    p.rand_mul = h->rand_on ? 0xFFFEu : 0u;
+    p.imag_sign = h->latched_sideband ? -1.0f : 1.0f;
+    CU(h, launch_wide(d, p, h->sm_count, stream));
+    return R2IQ_OK;
+}
+
 int launch(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d_out, cudaStream_t stream, float** nco_starts,
            size_t* nco_cap) {
+    if (h->fftn == 8192) {
+        int rc = launch_wide_impl(h, d_in, n_blocks, d_out, stream);
+        if (rc != R2IQ_OK) return rc;
+        h->stats.kernel_launches++;
+        h->stats.blocks_processed += (uint64_t)n_blocks;
+        return nco_stage(h, d_out, (size_t)n_blocks * (size_t)((kTransferSamples / 2) >> h->latched_decimate), nco_starts,
+                         nco_cap, stream);
+    }
     TableSet ts;
     const int d = h->latched_decimate;
     int rc = get_tables(h, d, h->tunebin, &ts);
@@ -344,6 +434,7 @@ int launch(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d_out, cuda
 int launch_channels_impl(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, const int* tunebins, int n_channels,
                          float* d_out, cudaStream_t stream) {
     const int d = h->latched_decimate;
+    if (h->fftn != kFftN) return fail(R2IQ_E_INVALID, "the channelizer is built for FFTN %d only", kFftN);
     if (d < 1) return fail(R2IQ_E_INVALID, "the channelizer needs decimation index >= 1 (latched: %d)", d);
     for (int c = 0; c < n_channels; c++)
         if (tunebins[c] < 0 || tunebins[c] >= kHalfFft || (tunebins[c] & 3))
@@ -415,7 +506,7 @@ int ensure_slots(r2iq_cuda_t h) {
         if (s.d_in) continue;
         CU(h, cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
         CU(h, cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
-        CU(h, cudaMalloc(&s.d_in, sizeof(int16_t) * ((size_t)kHalfFft + (size_t)h->chunk_blocks * kTransferSamples)));
+        CU(h, cudaMalloc(&s.d_in, sizeof(int16_t) * ((size_t)h->half + (size_t)h->chunk_blocks * kTransferSamples)));
         CU(h, cudaMalloc(&s.d_out, sizeof(float) * 2 * (size_t)h->chunk_blocks * (kTransferSamples / 2)));
     }
     return R2IQ_OK;
@@ -447,6 +538,8 @@ int r2iq_cuda_create(const r2iq_cuda_config* cfg, r2iq_cuda_t* out) {
     if (prop.major != 10)
         return fail(R2IQ_E_NODEVICE, "device %d is sm_%d%d; kernels are built for sm_100a only", dev, prop.major,
                     prop.minor);
+    if (cfg->fftn != 0 && cfg->fftn != 2048 && cfg->fftn != 8192)
+        return fail(R2IQ_E_INVALID, "fftn %d: kernels exist for FFTN_R_ADC 2048 and 8192", cfg->fftn);
     r2iq_cuda_s* h = new (std::nothrow) r2iq_cuda_s();
     if (!h) return fail(R2IQ_E_NOMEM, "out of host memory");
     h->device = dev;
@@ -454,6 +547,9 @@ int r2iq_cuda_create(const r2iq_cuda_config* cfg, r2iq_cuda_t* out) {
     h->cc_major = prop.major;
     h->cc_minor = prop.minor;
     h->gain = cfg->gain;
+    h->fftn = cfg->fftn == 0 ? kFftN : cfg->fftn;
+    h->half = h->fftn / 2;
+    h->tunebin = h->half / 4;     // constructor default mtunebin = halfFft / 4 (Core/fft_mt_r2iq.cpp:43)
     h->chunk_blocks = cfg->chunk_blocks > 0 ? cfg->chunk_blocks : kDefaultChunkBlocks;
     h->stats.sm_count = h->sm_count;
     h->stats.cc_major = prop.major;
@@ -468,6 +564,8 @@ int r2iq_cuda_create(const r2iq_cuda_config* cfg, r2iq_cuda_t* out) {
         return bail(fail(R2IQ_E_CUDA, "channelizer kernel setup: %s", cudaGetErrorString(e)));
     if ((e = setup_fused_kernels()) != cudaSuccess)
         return bail(fail(R2IQ_E_CUDA, "kernel setup: %s", cudaGetErrorString(e)));
+    if ((e = setup_wide_kernels()) != cudaSuccess)
+        return bail(fail(R2IQ_E_CUDA, "FFTN 8192 kernel setup: %s", cudaGetErrorString(e)));
     // forward inter-pass twiddles exp(-2 pi i k2 l / 1024)
     std::vector<float2> tw(32 * 32);
     for (int k2 = 0; k2 < 32; k2++)
@@ -477,12 +575,12 @@ int r2iq_cuda_create(const r2iq_cuda_config* cfg, r2iq_cuda_t* out) {
         }
     if ((e = cudaMalloc(&h->d_tw_fwd, sizeof(float2) * 32 * 32)) != cudaSuccess ||
         (e = cudaMemcpy(h->d_tw_fwd, tw.data(), sizeof(float2) * 32 * 32, cudaMemcpyHostToDevice)) != cudaSuccess ||
-        (e = cudaMallocHost(&h->carry, sizeof(int16_t) * kHalfFft)) != cudaSuccess ||
+        (e = cudaMallocHost(&h->carry, sizeof(int16_t) * h->half)) != cudaSuccess ||
         (e = cudaStreamCreateWithFlags(&h->util_stream, cudaStreamNonBlocking)) != cudaSuccess)
         return bail(fail(R2IQ_E_CUDA, "device setup: %s", cudaGetErrorString(e)));
-    memset(h->carry, 0, sizeof(int16_t) * kHalfFft);
+    memset(h->carry, 0, sizeof(int16_t) * h->half);
     for (int d = 0; d < kNDec; d++) {
-        h->hw[d] = design_filter_response(h->gain, d, kFftN);
+        h->hw[d] = design_filter_response(h->gain, d, h->fftn);
         h->hw_version[d] = 1;
     }
     *out = h;
@@ -496,6 +594,12 @@ int r2iq_cuda_destroy(r2iq_cuda_t h) {
     free_tables(h);
     free_channel_tables(h);
     cudaFree(h->d_ctab);
+    for (auto& kv : h->wide_tables) {
+        cudaFree(kv.second.g);
+        cudaFree(kv.second.tw_r);
+    }
+    cudaFree(h->d_twq);
+    cudaFree(h->d_wctab);
     for (int i = 0; i < kSlots; i++) {
         Slot& s = h->slots[i];
         if (s.stream) cudaStreamDestroy(s.stream);
@@ -516,10 +620,10 @@ int r2iq_cuda_destroy(r2iq_cuda_t h) {
 int r2iq_cuda_set_filter(r2iq_cuda_t h, int d, const float* hw, int n_complex) {
     int rc = check_handle(h);
     if (rc) return rc;
-    if (d < 0 || d >= kNDec || !hw || n_complex != kHalfFft)
-        return fail(R2IQ_E_INVALID, "set_filter: d=%d n_complex=%d (want 0..6, %d)", d, n_complex, kHalfFft);
+    if (d < 0 || d >= kNDec || !hw || n_complex != h->half)
+        return fail(R2IQ_E_INVALID, "set_filter: d=%d n_complex=%d (want 0..6, %d)", d, n_complex, h->half);
     std::lock_guard<std::mutex> lk(h->mu);
-    for (int k = 0; k < kHalfFft; k++) h->hw[d][k] = std::complex<float>(hw[2 * k], hw[2 * k + 1]);
+    for (int k = 0; k < h->half; k++) h->hw[d][k] = std::complex<float>(hw[2 * k], hw[2 * k + 1]);
     h->hw_version[d]++;   // cached tables of older versions are simply never looked up again
     return R2IQ_OK;
 }
@@ -527,10 +631,10 @@ int r2iq_cuda_set_filter(r2iq_cuda_t h, int d, const float* hw, int n_complex) {
 int r2iq_cuda_get_filter(r2iq_cuda_t h, int d, float* hw, int n_complex) {
     int rc = check_handle(h);
     if (rc) return rc;
-    if (d < 0 || d >= kNDec || !hw || n_complex != kHalfFft)
-        return fail(R2IQ_E_INVALID, "get_filter: d=%d n_complex=%d (want 0..6, %d)", d, n_complex, kHalfFft);
+    if (d < 0 || d >= kNDec || !hw || n_complex != h->half)
+        return fail(R2IQ_E_INVALID, "get_filter: d=%d n_complex=%d (want 0..6, %d)", d, n_complex, h->half);
     std::lock_guard<std::mutex> lk(h->mu);
-    for (int k = 0; k < kHalfFft; k++) {
+    for (int k = 0; k < h->half; k++) {
         hw[2 * k] = h->hw[d][k].real();
         hw[2 * k + 1] = h->hw[d][k].imag();
     }
@@ -550,12 +654,13 @@ int r2iq_cuda_get_ratio(r2iq_cuda_t h) { return h ? (1 << h->decimate) : R2IQ_E_
 float r2iq_cuda_set_freq_offset(r2iq_cuda_t h, float offset) {
     if (!h) return 0.f;
     // float arithmetic and truncation exactly as the reference (Core/fft_mt_r2iq.cpp:104-106)
-    int tb = 0;
-    const float ret = r2iq_cuda_freq_to_tunebin(offset, h->decimate, &tb);
+    // float arithmetic and truncation of Core/fft_mt_r2iq.cpp:104-106 with this operator's halfFft
+    int tb = int(offset * h->half / 4) * 4;
+    const float ret = (((float)tb / h->half) - offset) * (float)(1 << h->decimate);
     // The reference stores whatever comes out; bins outside [0, halfFft) would index out of
     // bounds there (offset is documented as [0,1)), so clamp instead of reading garbage.
     if (tb < 0) tb = 0;
-    if (tb > kHalfFft - 4) tb = kHalfFft - 4;
+    if (tb > h->half - 4) tb = h->half - 4;
     h->tunebin = tb;
     return ret;
 }
@@ -563,8 +668,8 @@ float r2iq_cuda_set_freq_offset(r2iq_cuda_t h, float offset) {
 int r2iq_cuda_set_tunebin(r2iq_cuda_t h, int tunebin) {
     int rc = check_handle(h);
     if (rc) return rc;
-    if (tunebin < 0 || tunebin >= kHalfFft || (tunebin & 3))
-        return fail(R2IQ_E_INVALID, "tune bin %d must be a multiple of 4 in [0,%d)", tunebin, kHalfFft);
+    if (tunebin < 0 || tunebin >= h->half || (tunebin & 3))
+        return fail(R2IQ_E_INVALID, "tune bin %d must be a multiple of 4 in [0,%d)", tunebin, h->half);
     h->tunebin = tunebin;
     return R2IQ_OK;
 }
@@ -612,7 +717,7 @@ int r2iq_cuda_turn_on(r2iq_cuda_t h) {
     std::lock_guard<std::mutex> lk(h->mu);
     h->latched_decimate = h->decimate;
     h->latched_sideband = h->sideband;
-    memset(h->carry, 0, sizeof(int16_t) * kHalfFft);
+    memset(h->carry, 0, sizeof(int16_t) * h->half);
     h->carry_valid = false;
     h->on = true;
     return R2IQ_OK;
@@ -639,7 +744,7 @@ int r2iq_cuda_process(r2iq_cuda_t h, const int16_t* blocks, long n_blocks, const
     if ((rc = ensure_slots(h)) != R2IQ_OK) return rc;
     const int d = h->latched_decimate;
     const size_t out_per_block = (size_t)((kTransferSamples / 2) >> d);
-    if (history) memcpy(h->carry, history, sizeof(int16_t) * kHalfFft);
+    if (history) memcpy(h->carry, history, sizeof(int16_t) * h->half);
     long done = 0;
     int si = 0;
     while (done < n_blocks) {
@@ -650,16 +755,16 @@ int r2iq_cuda_process(r2iq_cuda_t h, const int16_t* blocks, long n_blocks, const
         }
         const long nb = (n_blocks - done) < h->chunk_blocks ? (n_blocks - done) : h->chunk_blocks;
         if (done == 0) {
-            CU(h, cudaMemcpyAsync(s.d_in, h->carry, sizeof(int16_t) * kHalfFft, cudaMemcpyHostToDevice, s.stream));
-            CU(h, cudaMemcpyAsync(s.d_in + kHalfFft, blocks, sizeof(int16_t) * (size_t)nb * kTransferSamples,
+            CU(h, cudaMemcpyAsync(s.d_in, h->carry, sizeof(int16_t) * h->half, cudaMemcpyHostToDevice, s.stream));
+            CU(h, cudaMemcpyAsync(s.d_in + h->half, blocks, sizeof(int16_t) * (size_t)nb * kTransferSamples,
                                   cudaMemcpyHostToDevice, s.stream));
         } else {
             // history of this chunk = tail of the previous block, contiguous in the caller's buffer
-            CU(h, cudaMemcpyAsync(s.d_in, blocks + (size_t)done * kTransferSamples - kHalfFft,
-                                  sizeof(int16_t) * ((size_t)kHalfFft + (size_t)nb * kTransferSamples),
+            CU(h, cudaMemcpyAsync(s.d_in, blocks + (size_t)done * kTransferSamples - h->half,
+                                  sizeof(int16_t) * ((size_t)h->half + (size_t)nb * kTransferSamples),
                                   cudaMemcpyHostToDevice, s.stream));
         }
-        h->stats.h2d_bytes += sizeof(int16_t) * ((size_t)kHalfFft + (size_t)nb * kTransferSamples);
+        h->stats.h2d_bytes += sizeof(int16_t) * ((size_t)h->half + (size_t)nb * kTransferSamples);
         if ((rc = launch(h, s.d_in, nb, s.d_out, s.stream, &s.d_starts, &s.starts_cap)) != R2IQ_OK) return rc;
         const size_t out_bytes = sizeof(float) * 2 * (size_t)nb * out_per_block;
         CU(h, cudaMemcpyAsync(iq_out + 2 * (size_t)done * out_per_block, s.d_out, out_bytes, cudaMemcpyDeviceToHost,
@@ -677,7 +782,7 @@ int r2iq_cuda_process(r2iq_cuda_t h, const int16_t* blocks, long n_blocks, const
             h->slots[i].busy = false;
         }
     }
-    memcpy(h->carry, blocks + (size_t)n_blocks * kTransferSamples - kHalfFft, sizeof(int16_t) * kHalfFft);
+    memcpy(h->carry, blocks + (size_t)n_blocks * kTransferSamples - h->half, sizeof(int16_t) * h->half);
     h->carry_valid = true;
     return R2IQ_OK;
 }
@@ -717,6 +822,7 @@ int r2iq_cuda_process_channels(r2iq_cuda_t h, const int16_t* blocks, long n_bloc
     if (n_blocks < 0 || n_channels < 0 || ((n_blocks > 0 && n_channels > 0) && (!blocks || !iq_out || !tunebins)))
         return fail(R2IQ_E_INVALID, "process_channels: bad arguments");
     if (n_blocks == 0 || n_channels == 0) return R2IQ_OK;
+    if (h->fftn != kFftN) return fail(R2IQ_E_INVALID, "the channelizer is built for FFTN %d only", kFftN);
     std::lock_guard<std::mutex> lk(h->mu);
     CU(h, cudaSetDevice(h->device));
     const int d = h->latched_decimate;
@@ -789,6 +895,8 @@ int r2iq_cuda_convert(r2iq_cuda_t h, const int16_t* in, long n, int rand, float*
     cudaFree(d_out);
     return R2IQ_OK;
 }
+
+int r2iq_cuda_get_fftn(r2iq_cuda_t h) { return h ? h->fftn : R2IQ_E_INVALID; }
 
 int r2iq_cuda_get_stats(r2iq_cuda_t h, r2iq_cuda_stats* out) {
     if (!h || !out) return fail(R2IQ_E_INVALID, "null argument");

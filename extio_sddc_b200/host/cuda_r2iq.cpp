@@ -2,6 +2,9 @@
 #include <string>
 
 #include "cuda_r2iq.h"
+#ifdef R2IQ_USE_REFERENCE_HEADERS
+#include "config.h"
+#endif
 
 #include <cstring>
 
@@ -29,7 +32,10 @@ void cuda_r2iq::Init(float gain, ringbuffer<int16_t>* input, ringbuffer<float>* 
         r2iq_cuda_destroy(handle_);
         handle_ = nullptr;
     }
-    r2iq_cuda_config cfg;
+    r2iq_cuda_config cfg = {};
+#ifdef R2IQ_USE_REFERENCE_HEADERS
+    cfg.fftn = FFTN_R_ADC;       // inside the reference tree: whatever Core/config.h:49 says (8192 as shipped)
+#endif
     cfg.device = device_;
     cfg.gain = gain;
     cfg.chunk_blocks = 0;

@@ -26,11 +26,13 @@ HALF_FFT = capi.HALF_FFT
 class CudaR2IQ:
     """``fft_mt_r2iq`` on a B200."""
 
-    def __init__(self, device: int = -1, chunk_blocks: int = 0):
+    def __init__(self, device: int = -1, chunk_blocks: int = 0, fftn: int = 2048):
         self._lib = capi.load()
         self._h = ctypes.c_void_p(None)
         self._device = device
         self._chunk_blocks = chunk_blocks
+        self.fftn = int(fftn)              # FFTN_R_ADC: 2048 (north star) or 8192 (reference as shipped)
+        self.half_fft = self.fftn // 2
 
     # -- lifecycle ---------------------------------------------------------------------------
     def Init(self, gain: float, input=None, obuffers=None) -> None:  # noqa: N802 (reference naming)
@@ -38,7 +40,7 @@ class CudaR2IQ:
         buffers of the reference signature; the Python mirror has none and ignores them."""
         if self._h:
             self.close()
-        cfg = capi.Config(self._device, float(gain), int(self._chunk_blocks))
+        cfg = capi.Config(self._device, float(gain), int(self._chunk_blocks), self.fftn)
         h = ctypes.c_void_p(None)
         capi.check(self._lib.r2iq_cuda_create(ctypes.byref(cfg), ctypes.byref(h)))
         self._h = h
@@ -109,8 +111,8 @@ class CudaR2IQ:
         capi.check(self._lib.r2iq_cuda_set_tunebin(self._handle(), int(tb)))
 
     def filter_hw(self, d: int) -> np.ndarray:
-        out = np.zeros(2 * HALF_FFT, dtype=np.float32)
-        capi.check(self._lib.r2iq_cuda_get_filter(self._handle(), int(d), out.ctypes.data, HALF_FFT))
+        out = np.zeros(2 * self.half_fft, dtype=np.float32)
+        capi.check(self._lib.r2iq_cuda_get_filter(self._handle(), int(d), out.ctypes.data, self.half_fft))
         return out.view(np.complex64)
 
     def set_filter_hw(self, d: int, hw: np.ndarray) -> None:
@@ -144,8 +146,8 @@ class CudaR2IQ:
         hist_p = None
         if history is not None:
             history = np.ascontiguousarray(history, dtype=np.int16)
-            if history.shape[0] != HALF_FFT:
-                raise ValueError(f"history must hold {HALF_FFT} samples")
+            if history.shape[0] != self.half_fft:
+                raise ValueError(f"history must hold {self.half_fft} samples")
             hist_p = history.ctypes.data
         capi.check(self._lib.r2iq_cuda_process(self._handle(), blocks.ctypes.data, n_blocks, hist_p,
                                                out.ctypes.data if n_out else None))

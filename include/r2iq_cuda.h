@@ -54,6 +54,9 @@ typedef struct r2iq_cuda_config {
     int device;            /* CUDA device ordinal; -1 = current device */
     float gain;            /* RadioHardware::getGain(), the `gain` argument of fft_mt_r2iq::Init */
     int chunk_blocks;      /* host-buffer path: blocks per pipelined H2D/compute/D2H chunk; 0 = default (256) */
+    int fftn;              /* FFTN_R_ADC (Core/config.h:49): 0 or 2048 = north-star size, 8192 = the value the reference
+                              tree ships with.  halfFft = fftn/2 sets history length, filter length (halfFft complex bins,
+                              halfFft/4+1 taps) and the tune-bin range; the channelizer exists for 2048 only. */
 } r2iq_cuda_config;
 
 typedef struct r2iq_cuda_stats {
@@ -164,6 +167,8 @@ R2IQ_API int r2iq_cuda_host_free(void* p);
 R2IQ_API int r2iq_cuda_convert(r2iq_cuda_t h, const int16_t* in, long n, int rand, float* out);
 
 R2IQ_API int r2iq_cuda_get_stats(r2iq_cuda_t h, r2iq_cuda_stats* out);
+/* FFTN_R_ADC this operator was created with (2048 or 8192). */
+R2IQ_API int r2iq_cuda_get_fftn(r2iq_cuda_t h);
 
 /* Device-free host logic (usable without a GPU; exercised by the CPU test suite).
  *  design_filter:  filterHw[d] exactly as r2iq_cuda_create designs it (KaiserWindow + tap placement +

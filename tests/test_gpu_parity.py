@@ -362,3 +362,36 @@ print("worst", worst)
     env = dict(os.environ, R2IQ_KERNEL_GEN=gen)
     r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "worst" in r.stdout, r.stdout + r.stderr
+
+
+@pytest.mark.parametrize("d", range(7))
+def test_fftn8192_reference_as_shipped(d):
+    """FFTN_R_ADC = 8192 is what the reference tree ships (Core/config.h:49): halfFft 4096, 11 frames per
+    block, 1025 taps, mfft = 4096 >> d.  Same bars as the 2048 family, against the oracle at FFTN 8192."""
+    r = CudaR2IQ(fftn=8192)
+    r.Init(GAIN)
+    assert r.filter_hw(d).shape[0] == 4096
+    assert orc.rel_l2(r.filter_hw(d), orc.design_filter(GAIN, d, 8192)) < 1e-6
+    for tb, rnd, lsb in ((1024, True, False), (0, False, False), (4092, True, True), (2048, False, True), (584, True, False),
+                         (4096 - (4096 >> d) // 2, False, False)):
+        tb = max(0, min(4092, tb)) & ~3
+        x = orc.rx888_blocks(3, d, tb, fftn=8192, randomized=rnd, seed=8192 + 7 * d + tb)
+        hist = np.random.default_rng(d).integers(-3000, 3000, 4096).astype(np.int16)
+        r.setDecimate(d); r.updateRand(rnd); r.setSideband(lsb); r.tunebin = tb
+        r.TurnOn()
+        got = r.process(x, history=hist)
+        r.TurnOff()
+        ref = orc.r2iq(x, d, tb, gain=GAIN, rand=rnd, sideband=lsb, fftn=8192, history=hist)
+        check(got, ref, GAIN, ("fftn8192", d, tb, rnd, lsb))
+    # setFreqOffset quantises on halfFft = 4096 (VHF IF point: bin 584, SURVEY.md 8d)
+    r.setDecimate(2)
+    res = r.setFreqOffset(4.57e6 / 32e6)
+    tbw, want = orc.set_freq_offset(4.57e6 / 32e6, 2, 8192)
+    assert r.tunebin == tbw == 584 and res == pytest.approx(want, abs=1e-9)
+    # streaming: block-by-block with carried 4096-sample history == one call
+    x = orc.rx888_blocks(4, d, 1024, fftn=8192, randomized=True)
+    r.setDecimate(d); r.updateRand(True); r.setSideband(False); r.tunebin = 1024
+    r.TurnOn(); whole = r.process(x); r.TurnOff()
+    r.TurnOn(); parts = np.concatenate([r.process(x[b * 65536:(b + 1) * 65536]) for b in range(4)]); r.TurnOff()
+    assert np.array_equal(parts, whole)
+    r.close()
