@@ -94,7 +94,7 @@ __global__ void __launch_bounds__(kWThreads, 1) r2iq_wide_kernel(const WideParam
         const int kf = (int)(f - b * kWFrames);
         const uint32_t* src = p.in_words + b * (kTransferSamples / 2) + kf * kWHopWords + lane;
         float2 v[32];
-#pragma unroll 4
+#pragma unroll 8
         for (int j = 0; j < 32; j++) {
             const int n = lane + 32 * j;
             const float2 z0 = unpack_pair(__ldg(src + 32 * j), p.rand_mul);
@@ -125,7 +125,7 @@ __global__ void __launch_bounds__(kWThreads, 1) r2iq_wide_kernel(const WideParam
         __syncwarp();
 
         // ---------------- real-FFT split + filter, in place on mirror pairs ------------------------------
-#pragma unroll 2
+#pragma unroll 5
         for (int i = 0; i <= 64; i++) {
             const int pp = i < 64 ? lane + 32 * i : 2048;
             if (i < 64 || lane == 0) {
@@ -150,7 +150,7 @@ __global__ void __launch_bounds__(kWThreads, 1) r2iq_wide_kernel(const WideParam
         const FrameOut fo = wide_frame_out<D>(f);
         if constexpr (D <= 1) {
             constexpr int A = M / 1024;                              // 4 or 2 interleaved 1024-point transforms
-#pragma unroll 2
+#pragma unroll 4
             for (int i = 0; i < 32; i++) {
                 const int n = lane + 32 * i;
                 if constexpr (A == 4) {

@@ -49,17 +49,17 @@ def parity():
     return worst
 
 
-def timing(n_blocks, decims=range(7)):
+def timing(n_blocks, decims=range(7), fftn=2048):
     import torch
-    r = CudaR2IQ()
+    r = CudaR2IQ(fftn=fftn)
     r.Init(GAIN)
     dev = torch.device("cuda:0")
     g = torch.Generator(device=dev); g.manual_seed(1)
-    x = torch.randint(-8000, 8000, (1024 + n_blocks * 65536,), dtype=torch.int16, device=dev, generator=g)
+    x = torch.randint(-8000, 8000, (fftn // 2 + n_blocks * 65536,), dtype=torch.int16, device=dev, generator=g)
     out = torch.empty(n_blocks * 32768, dtype=torch.complex64, device=dev)
     stream = torch.cuda.current_stream().cuda_stream
     for d in decims:
-        r.setDecimate(d); r.updateRand(True); r.setSideband(False); r.tunebin = 256
+        r.setDecimate(d); r.updateRand(True); r.setSideband(False); r.tunebin = fftn // 8
         r.TurnOn()
         for _ in range(3):
             r.process_device(x.data_ptr(), n_blocks, out.data_ptr(), stream)
@@ -82,8 +82,9 @@ if __name__ == "__main__":
     ap.add_argument("--blocks", type=int, default=2048)
     ap.add_argument("--no-parity", action="store_true")
     ap.add_argument("--decims", default="0,1,2,3,4,5,6")
+    ap.add_argument("--fftn", type=int, default=2048)
     a = ap.parse_args()
     DECIMS[:] = [int(v) for v in a.decims.split(",")]
     if not a.no_parity:
         parity()
-    timing(a.blocks, [int(v) for v in a.decims.split(",")])
+    timing(a.blocks, [int(v) for v in a.decims.split(",")], a.fftn)
