@@ -223,6 +223,7 @@ static cudaError_t setup_w() {
 
 cudaError_t setup_wide_kernels() {
     cudaError_t e;
+    if ((e = setup_wide4_kernels()) != cudaSuccess) return e;
     if ((e = setup_w<0>()) != cudaSuccess) return e;
     if ((e = setup_w<1>()) != cudaSuccess) return e;
     if ((e = setup_w<2>()) != cudaSuccess) return e;
@@ -245,6 +246,7 @@ static cudaError_t launch_w(const WideParams& p, int sm_count, cudaStream_t stre
 }
 
 cudaError_t launch_wide(int d, const WideParams& p, int sm_count, cudaStream_t stream) {
+    if (kernel_generation() != 1) return launch_wide4(d, p, sm_count, stream);
     switch (d) {
         case 0: return launch_w<0>(p, sm_count, stream);
         case 1: return launch_w<1>(p, sm_count, stream);
