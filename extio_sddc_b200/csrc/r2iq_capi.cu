@@ -108,7 +108,7 @@ struct r2iq_cuda_s {
     // FFTN 8192 family (r2iq_wide.cu)
     float2* d_twq = nullptr;                       // [3][1024] W_4096^(q n)
     float2* d_wctab = nullptr;                     // [2049] -i * W_8192^p
-    struct WideSet { float2* g = nullptr; float2* tw_r = nullptr; float2* tw_sub = nullptr; };
+    struct WideSet { float2* g = nullptr; float2* tw_sub = nullptr; };
     std::map<long long, WideSet> wide_tables;      // per (filter version, d, tunebin)
     Slot slots[kSlots];
     int16_t* carry = nullptr;                      // pinned: last halfFft samples of the stream
@@ -354,7 +354,6 @@ int launch_wide_impl(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d
             CU(h, cudaDeviceSynchronize());
             for (auto& kv : h->wide_tables) {
                 cudaFree(kv.second.g);
-                cudaFree(kv.second.tw_r);
                 cudaFree(kv.second.tw_sub);
             }
             h->wide_tables.clear();
@@ -371,11 +370,6 @@ int launch_wide_impl(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d
         }
         CU(h, cudaMalloc(&ws.g, sizeof(float2) * HF));
         CU(h, cudaMemcpy(ws.g, g.data(), sizeof(float2) * HF, cudaMemcpyHostToDevice));
-        if (d >= 2) {
-            const std::vector<float2> ta = build_tw_aux(M);
-            CU(h, cudaMalloc(&ws.tw_r, sizeof(float2) * ta.size()));
-            CU(h, cudaMemcpy(ws.tw_r, ta.data(), sizeof(float2) * ta.size(), cudaMemcpyHostToDevice));
-        }
         if (d >= 1) {
             const std::vector<float2> ta = build_tw_aux(d == 6 ? M : M / 4);
             CU(h, cudaMalloc(&ws.tw_sub, sizeof(float2) * ta.size()));
@@ -391,7 +385,6 @@ int launch_wide_impl(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d
     p.twq = h->d_twq;
     p.ctab = h->d_wctab;
     p.g = ws.g;
-    p.tw_r = ws.tw_r;
     p.tw_sub = ws.tw_sub;
     p.tunebin = h->tunebin;
     p.rand_mul = h->rand_on ? 0xFFFEu : 0u;
@@ -603,7 +596,6 @@ int r2iq_cuda_destroy(r2iq_cuda_t h) {
     cudaFree(h->d_ctab);
     for (auto& kv : h->wide_tables) {
         cudaFree(kv.second.g);
-        cudaFree(kv.second.tw_r);
         cudaFree(kv.second.tw_sub);
     }
     cudaFree(h->d_twq);

@@ -214,7 +214,6 @@ static cudaError_t setup_one() {
 
 static int g_kernel_gen = 0;
 void set_kernel_generation(int gen) { g_kernel_gen = gen; }
-int kernel_generation() { return g_kernel_gen; }
 
 cudaError_t setup_fused_kernels() {
     cudaError_t e;

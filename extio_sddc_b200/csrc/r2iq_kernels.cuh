@@ -51,7 +51,7 @@ struct ChannelParams {
 cudaError_t setup_channel_kernels();
 cudaError_t launch_channels(int d, const ChannelParams& p, int sm_count, cudaStream_t stream);
 
-// FFTN = 8192 family (r2iq_wide.cu): halfFft 4096, 11 frames per block, hop 6144 samples.
+// FFTN = 8192 family (r2iq_wide.cu): halfFft 4096, 11 frames per block, hop 6144 samples; four warps per frame.
 struct WideParams {
     const uint32_t* in_words;   // [2048 halo words | n_blocks * 32768 words]
     float2* out;                // n_blocks * (32768 >> d) complex
@@ -60,19 +60,14 @@ struct WideParams {
     const float2* twq;          // [3][1024] W_4096^(q*n), q = 1..3
     const float2* ctab;         // [2049]    -i * W_8192^p
     const float2* g;            // [4096]    0.5 * H_d[(k - tunebin) mod 4096] inside the band, else 0
-    const float2* tw_r;         // d >= 2: [R][32] exp(+2 pi i lane k2 / mfft), then [32][32] exp(+2 pi i (lane % (32/R)) n1 / 32)
-    const float2* tw_sub;       // four-warp kernel (r2iq_wide4.cu): the same two tables for the per-plane size
-                                // mfft/4 (d = 1..5) or for mfft = 64 (d = 6)
+    const float2* tw_sub;       // d >= 1: [R][32] exp(+2 pi i lane k2 / S), then [32][32] exp(+2 pi i (lane % (32/R)) n1 / 32),
+                                // R = S/32, S = the per-plane size mfft/4 (d = 1..5) or mfft = 64 (d = 6)
     int tunebin;
     uint32_t rand_mul;
     float imag_sign;
 };
 cudaError_t setup_wide_kernels();
-cudaError_t launch_wide(int d, const WideParams& p, int sm_count, cudaStream_t stream);   // dispatches on the generation
-// second-generation wide kernel: four warps per frame (r2iq_wide4.cu); generation 1 keeps the one-warp kernel
-cudaError_t setup_wide4_kernels();
-cudaError_t launch_wide4(int d, const WideParams& p, int sm_count, cudaStream_t stream);
-int kernel_generation();
+cudaError_t launch_wide(int d, const WideParams& p, int sm_count, cudaStream_t stream);
 
 // Launch the fused kernel for decimation index d on `stream`.  Returns cudaGetLastError().
 cudaError_t launch_fused(int d, const FusedParams& p, int sm_count, cudaStream_t stream);

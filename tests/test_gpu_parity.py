@@ -395,3 +395,42 @@ def test_fftn8192_reference_as_shipped(d):
     r.TurnOn(); parts = np.concatenate([r.process(x[b * 65536:(b + 1) * 65536]) for b in range(4)]); r.TurnOff()
     assert np.array_equal(parts, whole)
     r.close()
+
+
+@pytest.mark.parametrize("d", [0, 4])
+def test_fftn8192_full_size_properties(d):
+    """FFTN 8192 at BASELINE config 2 size (8192 blocks): time slabs with a 4096-sample halo == the whole
+    capture (bit-exact), linearity, and a sampled window against the oracle."""
+    import torch
+    n_blocks, half_fft, tb = 8192, 4096, 1024
+    dev = torch.device("cuda:0")
+    g = torch.Generator(device=dev)
+    g.manual_seed(8192 + d)
+    x = torch.randint(-4000, 4000, (half_fft + n_blocks * 65536,), dtype=torch.int16, device=dev, generator=g)
+    opb = 32768 >> d
+    r = CudaR2IQ(fftn=8192)
+    r.Init(GAIN)
+    r.setDecimate(d); r.updateRand(False); r.tunebin = tb
+    r.TurnOn()
+    s = torch.cuda.current_stream().cuda_stream
+    whole = torch.empty(n_blocks * opb, dtype=torch.complex64, device=dev)
+    r.process_device(x.data_ptr(), n_blocks, whole.data_ptr(), s)
+    cut = 3000
+    parts = torch.empty_like(whole)
+    r.process_device(x.data_ptr(), cut, parts.data_ptr(), s)
+    r.process_device(x.data_ptr() + 2 * cut * 65536, n_blocks - cut, parts.data_ptr() + 8 * cut * opb, s)
+    torch.cuda.synchronize()
+    assert torch.equal(whole, parts)
+    dbl = torch.empty_like(whole)
+    x2 = x * 2
+    r.process_device(x2.data_ptr(), n_blocks, dbl.data_ptr(), s)
+    torch.cuda.synchronize()
+    err = (torch.linalg.vector_norm(dbl - 2 * whole) / torch.linalg.vector_norm(dbl)).item()
+    assert err < 1e-6, err
+    b0 = 5000
+    xin = x[half_fft + b0 * 65536: half_fft + (b0 + 2) * 65536].cpu().numpy()
+    hist = x[b0 * 65536: half_fft + b0 * 65536].cpu().numpy()
+    ref = orc.r2iq(xin, d, tb, gain=GAIN, fftn=8192, history=hist)
+    check(whole[b0 * opb:(b0 + 2) * opb].cpu().numpy(), ref, GAIN, ("fftn8192 full-size window", d))
+    r.TurnOff()
+    r.close()
