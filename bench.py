@@ -121,18 +121,19 @@ def cpu_signal(n_blocks: int):
     return orc.rx888_blocks(n_blocks, 0, TUNEBIN, randomized=True, seed=888)
 
 
-def reference_sweep(blocks_per_instance: int, instances: int, variant: str = "dispatch", warm: int = 64):
+def reference_sweep(blocks_per_instance: int, instances: int, variant: str = "dispatch", warm: int = 64, fftn: int = 2048):
     """One bounded sample of the workload on the host cores: for every decimation of the sweep, each of
     `instances` independent reference operators processes `blocks_per_instance` blocks (saturated input
     ring, like unittest/benchmark_test.cpp:78-142).  Returns (Gsamples/s over the sweep, seconds, detail)."""
     from oracle import ref_lib
-    R = ref_lib.get(2048)
+    R = ref_lib.get(fftn)
+    tunebin = TUNEBIN * (fftn // 2048)
     backend = "MKL DFTI float32 (torch libtorch_cpu.so)" if R.set_fft_backend(ref_lib.BACKEND_MKL) == 0 else \
         "portable float64 FFT (MKL unavailable)"
     sig = cpu_signal(16)
     tot_s, tot_t, detail = 0.0, 0.0, []
     for d in DECIMS:
-        sps, sec = R.bench(sig, d, TUNEBIN, warm_blocks=warm, timed_blocks=blocks_per_instance, gain=GAIN, rand=True,
+        sps, sec = R.bench(sig, d, tunebin, warm_blocks=warm, timed_blocks=blocks_per_instance, gain=GAIN, rand=True,
                            variant=variant, instances=instances)
         n = sps * sec
         tot_s += n
@@ -418,6 +419,42 @@ def run_ours(args, rank: int, local_rank: int, world: int):
                        "note": "every rank reads the same capture; one forward FFT per frame shared by its channels"}
         del cout
 
+    # ---- FFTN 8192 (the reference tree as shipped, Core/config.h:49): the same sweep on the wide kernel family ----
+    wide = None
+    if not args.no_fftn8192:
+        wop = CudaR2IQ(device=local_rank, fftn=8192)
+        wop.Init(GAIN)
+        wop.updateRand(True)
+        wop.tunebin = TUNEBIN * 4
+        wblocks = n_blocks - 1                       # the first 4096 samples of the capture serve as the halo
+        wper = []
+        wtot = 0.0
+        for d in DECIMS:
+            wop.setDecimate(d)
+            wop.TurnOn()
+            for _ in range(2):
+                wop.process_device(x.data_ptr(), wblocks, out.data_ptr(), stream)
+            barrier()
+            torch.cuda.synchronize()
+            w0 = torch.cuda.Event(enable_timing=True)
+            w1 = torch.cuda.Event(enable_timing=True)
+            w0.record()
+            for _ in range(3):
+                wop.process_device(x.data_ptr(), wblocks, out.data_ptr(), stream)
+            w1.record()
+            torch.cuda.synchronize()
+            wms = w0.elapsed_time(w1) / 3
+            if world > 1:
+                t = torch.tensor([wms], dtype=torch.float64, device=dev)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                wms = float(t.item())
+            wtot += wms
+            wper.append({"d": d, "ms": round(wms, 4), "gsamples_s": round(world * wblocks * 65536 / (wms * 1e-3) / 1e9, 1)})
+            wop.TurnOff()
+        wide = {"fftn": 8192, "value": round(world * len(DECIMS) * wblocks * 65536 / (wtot * 1e-3) / 1e9, 1), "unit": UNIT,
+                "per_decimation": wper, "note": "same capture and sweep on a handle created with fftn = 8192 (halfFft 4096)"}
+        wop.close()
+
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         try:
@@ -431,6 +468,9 @@ def run_ours(args, rank: int, local_rank: int, world: int):
                                        f"same sweep d=0..5, {sec:.1f} s of CPU time window"),
                             "single_instance_as_shipped": round(v1, 4),        # cpuid dispatcher's pick (avx512 TU on this host)
                             "single_instance_forced_avx2_intrinsics": round(v2, 4), "per_decimation": detail}
+            if wide is not None:
+                v8, _, _, _ = reference_sweep(max(256, args.ref_blocks // 4), cores, fftn=8192)
+                wide["cpu_reference_gsamples_s"] = round(v8, 4)        # oracle/_ref built at FFTN_R_ADC 8192, same cores
         except Exception as ex:  # the baseline is reported, never required for the GPU arm
             cpu_baseline = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": f"unavailable: {ex}"}
 
@@ -451,6 +491,8 @@ def run_ours(args, rank: int, local_rank: int, world: int):
             line["gather"] = gather
         if channelizer is not None:
             line["channelizer"] = channelizer
+        if wide is not None:
+            line["fftn8192"] = wide
         if cpu_baseline is not None:
             line["cpu_baseline"] = cpu_baseline
         _emit(line)
@@ -485,6 +527,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-channelizer", action="store_true")
+    ap.add_argument("--no-fftn8192", action="store_true")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3
