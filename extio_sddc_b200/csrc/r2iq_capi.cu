@@ -517,7 +517,7 @@ int ensure_slots(r2iq_cuda_t h) {
 extern "C" {
 
 const char* r2iq_cuda_last_error(void) { return g_err; }
-const char* r2iq_cuda_version(void) { return "r2iq-b200 0.1 sm_100a fftn=2048"; }
+const char* r2iq_cuda_version(void) { return "r2iq-b200 0.1 sm_100a fftn=2048,8192"; }
 
 int r2iq_cuda_create(const r2iq_cuda_config* cfg, r2iq_cuda_t* out) {
     if (!cfg || !out) return fail(R2IQ_E_INVALID, "null argument");

@@ -70,7 +70,7 @@ typedef struct r2iq_cuda_stats {
 
 /* Thread-local description of the last failure on this thread. */
 R2IQ_API const char* r2iq_cuda_last_error(void);
-/* Library / kernel build identification, e.g. "r2iq-b200 0.1 sm_100a fftn=2048". */
+/* Library / kernel build identification, e.g. "r2iq-b200 0.1 sm_100a fftn=2048,8192". */
 R2IQ_API const char* r2iq_cuda_version(void);
 
 /* fft_mt_r2iq::fft_mt_r2iq() + fft_mt_r2iq::Init(gain, in, out)  (Core/fft_mt_r2iq.cpp:39-49,147-227).
