@@ -16,7 +16,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIB_DIR = os.path.join(HERE, "lib")
 LIB_PATH = os.path.join(LIB_DIR, "libr2iq_cuda.so")
 SOURCES = ["r2iq_kernels.cu", "r2iq_dual.cu", "r2iq_dual_d0.cu", "r2iq_dual_d1.cu", "r2iq_dual_dn.cu", "r2iq_channels.cu", "r2iq_wide.cu", "r2iq_capi.cu", "fir_design.cpp"]
-HEADERS = ["r2iq_kernels.cuh", "dft_regs.cuh", "dft_regs2.cuh", "r2iq_common.cuh", "fir_design.h", os.path.join("..", "..", "include", "r2iq_cuda.h")]
+HEADERS = ["r2iq_kernels.cuh", "dft_regs.cuh", "dft_regs2.cuh", "r2iq_common.cuh", "work_dispenser.cuh", "fir_design.h", os.path.join("..", "..", "include", "r2iq_cuda.h")]
 ARCH_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a"]
 NVCC_FLAGS = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden",
               "--cudart", "static"]

@@ -69,6 +69,39 @@ __device__ __forceinline__ c2 cmul2s(c2 v, float2 w) {
     return r;
 }
 
+// v[k] *= w^k, k = 1..31, for a per-lane complex w shared by both frames -- the inter-pass twiddles of a
+// 32 x 32 decomposition.  `tab` points at this lane's column of a [32][32] table whose row k holds w^k; only
+// rows 1, 2, 16 and 17 are loaded (4 instead of 31 loads: the L1 data pipe, not the FMA pipe, is the busier
+// unit, and the table rows no longer evict the filter tables from L1).  The other powers come from the packed
+// recurrence (w^(2j+2), w^(2j+3)) = (w^(2j), w^(2j+1)) * w^2, seven steps from each loaded pair, so no power is
+// more than 7 roundings away from a table value.
+__device__ __forceinline__ void twiddle_powers32(c2 (&v)[32], const float2* tab) {
+    const float2 w1 = __ldg(tab + 32 * 1);
+    const float2 w2 = __ldg(tab + 32 * 2);
+    const float2 w16 = __ldg(tab + 32 * 16);
+    const float2 w17 = __ldg(tab + 32 * 17);
+    const u64 cr = bc(w2.x), ci = bc(w2.y), cni = bc(-w2.y);
+#pragma unroll
+    for (int half = 0; half < 2; half++) {
+        u64 pr = half ? pk(w16.x, w17.x) : pk(1.0f, w1.x);   // (re w^(2j), re w^(2j+1))
+        u64 pi = half ? pk(w16.y, w17.y) : pk(0.0f, w1.y);
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            const int k = 16 * half + 2 * j;
+            float r0, r1, i0, i1;
+            upk(pr, r0, r1);
+            upk(pi, i0, i1);
+            if (k > 0) v[k] = cmul2s(v[k], make_float2(r0, i0));
+            v[k + 1] = cmul2s(v[k + 1], make_float2(r1, i1));
+            if (j < 7) {
+                const u64 nr = fma2(cr, pr, mul2(cni, pi));
+                pi = fma2(cr, pi, mul2(ci, pr));
+                pr = nr;
+            }
+        }
+    }
+}
+
 // radix-2 DIT butterfly, compile-time twiddle exp(-+2*pi*i*J/LEN), packed version of bfly<>
 template <int J, int LEN, bool INV>
 __device__ __forceinline__ void bfly2(c2& a, c2& b) {

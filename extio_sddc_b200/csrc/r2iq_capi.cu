@@ -101,6 +101,7 @@ struct r2iq_cuda_s {
     std::vector<std::complex<float>> hw[kNDec];   // filterHw[d], host copy
     uint64_t hw_version[kNDec] = {0};
     float2* d_tw_fwd = nullptr;
+    unsigned long long* d_work_counter = nullptr;   // frame-pair dispenser of the dual-frame kernels
     std::map<long long, TableSet> tables;          // key = version<<20 | d<<12 | tunebin... see table_key
     std::map<long long, float2*> gh_tables;        // channelizer: 0.5*H_d in inverse-FFT bin order, key = version<<4 | d
     std::map<std::vector<int>, int*> chan_lists;   // channelizer: device copies of tune-bin lists
@@ -389,6 +390,7 @@ int launch_wide_impl(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d
     p.tunebin = h->tunebin;
     p.rand_mul = h->rand_on ? 0xFFFEu : 0u;
     p.imag_sign = h->latched_sideband ? -1.0f : 1.0f;
+    p.work_counter = h->d_work_counter;
     CU(h, launch_wide(d, p, h->sm_count, stream));
     return R2IQ_OK;
 }
@@ -424,6 +426,7 @@ int launch(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d_out, cuda
     p.row_mask = ts.row_mask;
     p.rand_mul = h->rand_on ? 0xFFFEu : 0u;
     p.imag_sign = h->latched_sideband ? -1.0f : 1.0f;
+    p.work_counter = h->d_work_counter;
     CU(h, launch_fused(d, p, h->sm_count, stream));
     h->stats.kernel_launches++;
     h->stats.blocks_processed += (uint64_t)n_blocks;
@@ -494,6 +497,7 @@ int launch_channels_impl(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, cons
     p.n_channels = n_channels;
     p.rand_mul = h->rand_on ? 0xFFFEu : 0u;
     p.imag_sign = h->latched_sideband ? -1.0f : 1.0f;
+    p.work_counter = h->d_work_counter;
     CU(h, launch_channels(d, p, h->sm_count, stream));
     h->stats.kernel_launches++;
     h->stats.blocks_processed += (uint64_t)n_blocks;
@@ -573,7 +577,9 @@ int r2iq_cuda_create(const r2iq_cuda_config* cfg, r2iq_cuda_t* out) {
             const double th = -2.0 * kPiD * (double)(k2 * l) / (double)kHalfFft;
             tw[k2 * 32 + l] = make_float2((float)cos(th), (float)sin(th));
         }
-    if ((e = cudaMalloc(&h->d_tw_fwd, sizeof(float2) * 32 * 32)) != cudaSuccess ||
+    if ((e = cudaMalloc(&h->d_work_counter, sizeof(unsigned long long))) != cudaSuccess ||
+        (e = cudaMemset(h->d_work_counter, 0, sizeof(unsigned long long))) != cudaSuccess ||
+        (e = cudaMalloc(&h->d_tw_fwd, sizeof(float2) * 32 * 32)) != cudaSuccess ||
         (e = cudaMemcpy(h->d_tw_fwd, tw.data(), sizeof(float2) * 32 * 32, cudaMemcpyHostToDevice)) != cudaSuccess ||
         (e = cudaMallocHost(&h->carry, sizeof(int16_t) * h->half)) != cudaSuccess ||
         (e = cudaStreamCreateWithFlags(&h->util_stream, cudaStreamNonBlocking)) != cudaSuccess)
@@ -612,6 +618,7 @@ int r2iq_cuda_destroy(r2iq_cuda_t h) {
     cudaFree(h->nco.d_starts);
     if (h->util_stream) cudaStreamDestroy(h->util_stream);
     cudaFree(h->d_tw_fwd);
+    cudaFree(h->d_work_counter);
     if (h->carry) cudaFreeHost(h->carry);
     delete h;
     return R2IQ_OK;

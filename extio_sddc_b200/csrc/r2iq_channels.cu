@@ -9,6 +9,7 @@
 // the stream a separate operator tuned to that bin would produce.
 // Output is channel-major: channel c writes out[c*out_stride + ...].
 #include "r2iq_common.cuh"
+#include "work_dispenser.cuh"
 
 namespace r2iq {
 
@@ -46,6 +47,7 @@ __device__ __forceinline__ void forward_frame_ch(const ChannelParams& p, long lo
 
 template <int D>
 __global__ void __launch_bounds__(kChThreads, 2) r2iq_channels_kernel(const ChannelParams p) {
+    constexpr bool kDyn = true;   // frames from the device-wide counter (work_dispenser.cuh); warps run free
     using G = Geo<D>;
     constexpr int M = G::M;
     constexpr int GROUP = G::ROUNDS;     // channels transformed back together
@@ -56,8 +58,11 @@ __global__ void __launch_bounds__(kChThreads, 2) r2iq_channels_kernel(const Chan
     float2* stage = S + kScratch;
     float2* Z = stage + kStage;
 
-    for (long long f = (long long)blockIdx.x * kChWarps + warp; f < p.total_frames;
-         f += (long long)gridDim.x * kChWarps) {
+    PairDispenser<kDyn, true, kChWarps> work;
+    work.init(p.work_counter, nullptr, lane, warp);
+    for (; work.more(p.total_frames); work.advance()) {
+        work.top(p.work_counter, nullptr);
+        const long long f = work.cur(warp);
         {
             float2 v[32];
             forward_frame_ch(p, f, lane, S, v);
@@ -135,6 +140,8 @@ static cudaError_t launch_ch(const ChannelParams& p, int sm_count, cudaStream_t 
     long long grid = (long long)sm_count * ctas;
     if (grid > want) grid = want;
     if (grid < 1) grid = 1;
+    e = cudaMemsetAsync(p.work_counter, 0, sizeof(unsigned long long), stream);
+    if (e != cudaSuccess) return e;
     r2iq_channels_kernel<D><<<(unsigned)grid, kChThreads, smem, stream>>>(p);
     return cudaGetLastError();
 }

@@ -23,6 +23,7 @@
 
 #include "dft_regs2.cuh"
 #include "r2iq_kernels.cuh"
+#include "work_dispenser.cuh"
 
 namespace r2iq {
 
@@ -38,9 +39,12 @@ constexpr int kDualThreads = kDualWarps * 32;
 constexpr int kTile = 32 * 33;                // elements per plane: 32x32 tile, pitch 33 (conflict-free for 8 B accesses)
 constexpr int kFrameBytes = kFftN * 2;        // 4096 B of int16 per frame
 // per-warp shared memory: transposition tile (two 8-byte planes) [+ two input frames + one mbarrier]
-template <bool kTma>
+//   kStage = 2 : TMA bulk copies land IN the transposition tile, which is idle between the last read of the
+//                 backward transposition and the next forward one; 16.9 KB per warp, 12 warps per SM
+//                 (3 CTAs, 168 registers) with TMA-staged input.
+template <int kStage>
 __host__ __device__ constexpr int warp_bytes() {
-    return kTile * 16 + (kTma ? 2 * kFrameBytes + 16 : 0);
+    return kTile * 16 + (kStage == 1 ? 2 * kFrameBytes : 0) + (kStage ? 16 : 0);
 }
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -81,9 +85,15 @@ __device__ __forceinline__ const uint32_t* frame_src(const FusedParams& p, long 
 // Phase boundaries double as CTA barriers (a superset of the __syncwarp the data hazard needs): they
 // keep the warps of a CTA within one phase of each other in the 50 KB unrolled loop body, so that
 // instruction-cache lines fetched by one warp are still resident for the others.
-#define PHASE_SYNC() __syncthreads()
+// Variant bit 1 (kFree) replaces them by warp-level fences: the warps of a CTA then run unsynchronised.
+#define PHASE_SYNC()                           \
+    do {                                       \
+        if constexpr (kFree) __syncwarp();     \
+        else __syncthreads();                  \
+    } while (0)
 
 __device__ __forceinline__ int brev5(int v) { return (int)(__brev((unsigned)v) >> 27); }
+__device__ __forceinline__ float flip(float x, uint32_t sgn) { return __uint_as_float(__float_as_uint(x) ^ sgn); }
 
 // Shared-memory exchanges use two 64-bit planes (re pairs, im pairs) rather than one 128-bit element:
 // a v2.b64 access needs re and im in four consecutive registers, and ptxas paid ~400 MOVs per
@@ -132,22 +142,27 @@ __device__ __forceinline__ FrameOut2 frame_out_d0(long long f, long long total) 
 }  // namespace
 
 // d = 0 (decimation 2, mfft = 1024): forward and backward transforms both run packed.
-template <bool kTma>
-__global__ void __launch_bounds__(kDualThreads, kTma ? 2 : 3) r2iq_dual_d0_kernel(const FusedParams p) {
+// kVar (measurement variants, env R2IQ_VARIANT): bit 0 = frame pairs handed out by an atomic counter instead of a
+// fixed stride (evens out SM-to-SM speed differences at the tail); bit 1 = no block barriers (warps run free).
+template <int kStage, int kVar = 0>
+__global__ void __launch_bounds__(kDualThreads, kStage == 1 ? 2 : 3) r2iq_dual_d0_kernel(const FusedParams p) {
+    constexpr bool kTma = kStage != 0;
+    constexpr bool kDyn = (kVar & 1) != 0;
+    constexpr bool kFree = (kVar & 2) != 0;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
-    constexpr int kWarpBytes = warp_bytes<kTma>();
+    constexpr int kWarpBytes = warp_bytes<kStage>();
     unsigned char* wbase = smem_raw + (size_t)warp * kWarpBytes;
     u64* S = reinterpret_cast<u64*>(wbase);
-    const uint32_t* inA = reinterpret_cast<const uint32_t*>(wbase + kTile * 16);
-    const uint32_t* inB = inA + kFrameBytes / 4;
-    const uint32_t mbar = smem_u32(wbase + kTile * 16 + 2 * kFrameBytes);
+    // kStage 1: two frame buffers behind the tile; kStage 2: frame A at the head of the re plane, frame B at the
+    // head of the im plane of the tile itself
+    const uint32_t* inA = reinterpret_cast<const uint32_t*>(wbase + (kStage == 2 ? 0 : kTile * 16));
+    const uint32_t* inB = kStage == 2 ? reinterpret_cast<const uint32_t*>(wbase + kTile * 8) : inA + kFrameBytes / 4;
+    const uint32_t mbar = smem_u32(wbase + kTile * 16 + (kStage == 1 ? 2 * kFrameBytes : 0));
     const uint32_t dstA = smem_u32(inA), dstB = smem_u32(inB);
 
     const long long n_pairs = (p.total_frames + 1) / 2;
-    const long long stride = (long long)gridDim.x * kDualWarps;
-    long long q = (long long)blockIdx.x * kDualWarps + warp;
 
     if constexpr (kTma) {
         if (lane == 0) {
@@ -163,6 +178,11 @@ __global__ void __launch_bounds__(kDualThreads, kTma ? 2 : 3) r2iq_dual_d0_kerne
         tma_load_1d(dstA, frame_src(p, fa), kFrameBytes, mbar);
         tma_load_1d(dstB, frame_src(p, fb), kFrameBytes, mbar);
     };
+    // frame pairs from the device-wide counter (kDyn) or by fixed stride; see work_dispenser.cuh
+    __shared__ long long s_base[3];
+    PairDispenser<kDyn, kFree, kDualWarps> work;
+    work.init(p.work_counter, s_base, lane, warp);
+    long long q = work.cur(warp);
     if constexpr (kTma) {
         if (lane == 0 && q < n_pairs) issue(q);
     }
@@ -173,11 +193,15 @@ __global__ void __launch_bounds__(kDualThreads, kTma ? 2 : 3) r2iq_dual_d0_kerne
     const float2* gp = p.gp + lane;
     const float2* gq = p.gq + lane;
     const int n1_inv = (lane - p.tunebin) & 31;
+    // sideband inversion (copy<true>, Core/fft_mt_r2iq.h:63-81) as a sign-bit flip: same bits as the multiply by
+    // -1, on the integer pipe, and no constant-bank load in the store epilogue
+    const uint32_t sgn = __float_as_uint(p.imag_sign) & 0x80000000u;
 
     // The loop bound is CTA-uniform and every trip starts with a block barrier: the four warps then
     // walk the (56 KB, fully unrolled) loop body roughly in step and share instruction-cache lines.
-    for (long long q0 = (long long)blockIdx.x * kDualWarps; q0 < n_pairs; q0 += stride, q += stride) {
-        __syncthreads();
+    while (work.more(n_pairs)) {
+        work.top(p.work_counter, s_base);
+        const long long qn = work.next(warp);
         const bool idle = q >= n_pairs;           // tail: keep barrier participation uniform, store nothing
         const long long qq = idle ? n_pairs - 1 : q;
         c2 v[32];
@@ -189,7 +213,9 @@ __global__ void __launch_bounds__(kDualThreads, kTma ? 2 : 3) r2iq_dual_d0_kerne
 #pragma unroll
             for (int j = 0; j < 32; j++) unpack_words(inA[lane + 32 * j], inB[lane + 32 * j], p.rand_mul, v[brev5(j)]);
             __syncwarp();   // every lane has consumed its words: the buffers may be overwritten
-            if (lane == 0 && q + stride < n_pairs) issue(q + stride);   // idle warps never issued: their barrier would hang
+            if constexpr (kStage == 1) {
+                if (lane == 0 && qn < n_pairs) issue(qn);   // idle warps never issue: nobody would consume the copy
+            }
         } else {
             const long long fa = 2 * qq;
             const long long fb = (fa + 1 < p.total_frames) ? fa + 1 : fa;   // odd tail: B repeats A, never stored
@@ -207,8 +233,12 @@ __global__ void __launch_bounds__(kDualThreads, kTma ? 2 : 3) r2iq_dual_d0_kerne
 
         // ---- forward 1024-point transform of z = x[2n] + i x[2n+1] ------------------------------
         dit2<32, false>(v);
+        if constexpr (kVar & 8) {
+            twiddle_powers32(v, twf);
+        } else {
 #pragma unroll
-        for (int k2 = 1; k2 < 32; k2++) v[k2] = cmul2s(v[k2], __ldg(twf + 32 * k2));
+            for (int k2 = 1; k2 < 32; k2++) v[k2] = cmul2s(v[k2], __ldg(twf + 32 * k2));
+        }
 #pragma unroll
         for (int k2 = 0; k2 < 32; k2++) sts2(S, lane * 33 + k2, v[k2]);
         PHASE_SYNC();
@@ -219,7 +249,8 @@ __global__ void __launch_bounds__(kDualThreads, kTma ? 2 : 3) r2iq_dual_d0_kerne
 
         // ---- real-FFT split + tune rotation + filter, in place ---------------------------------
 #pragma unroll
-        for (int k1 = 0; k1 < 32; k1++) sts2(S, 32 * k1 + lane, v[k1]);
+        for (int k1 = 0; k1 < 32; k1++)
+            sts2(S, 32 * k1 + lane, v[k1]);
         PHASE_SYNC();
         c2 t[32];
 #pragma unroll
@@ -237,14 +268,26 @@ __global__ void __launch_bounds__(kDualThreads, kTma ? 2 : 3) r2iq_dual_d0_kerne
 
         // ---- backward 1024-point transform; lane l is residue (l - tunebin) mod 32 ---------------
         dit2<32, true>(t);
+        if constexpr (kVar & 8) {
+            twiddle_powers32(t, twi);
+        } else {
 #pragma unroll
-        for (int k2 = 1; k2 < 32; k2++) t[k2] = cmul2s(t[k2], __ldg(twi + 32 * k2));
+            for (int k2 = 1; k2 < 32; k2++) t[k2] = cmul2s(t[k2], __ldg(twi + 32 * k2));
+        }
 #pragma unroll
         for (int k2 = 0; k2 < 32; k2++) sts2(S, n1_inv * 33 + k2, t[k2]);
         PHASE_SYNC();
 #pragma unroll
         for (int n = 0; n < 32; n++) t[brev5(n)] = lds2(S, n * 33 + lane);
         __syncwarp();
+        if constexpr (kStage == 2) {
+            // the tile has been read for the last time in this trip: the next pair of frames lands in it while the
+            // last radix-32 pass and the stores run (generic-proxy reads ordered before the async-proxy writes)
+            if (lane == 0 && qn < n_pairs) {
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                issue(qn);
+            }
+        }
         dit2<32, true>(t);                        // t[k1] = y[lane + 32*k1] for both frames
 
         // ---- overlap-save discard + placement (impl.hpp:117-138) --------------------------------
@@ -256,32 +299,43 @@ __global__ void __launch_bounds__(kDualThreads, kTma ? 2 : 3) r2iq_dual_d0_kerne
             float ar, br, ai, bi;
             upk(t[k1].re, ar, br);
             upk(t[k1].im, ai, bi);
-            if (!idle && idx >= oa.lo) p.out[oa.base + idx] = make_float2(ar, ai * p.imag_sign);
-            if (!idle && ob.live && idx >= ob.lo) p.out[ob.base + idx] = make_float2(br, bi * p.imag_sign);
+            if (!idle && idx >= oa.lo) p.out[oa.base + idx] = make_float2(ar, flip(ai, sgn));
+            if (!idle && ob.live && idx >= ob.lo) p.out[ob.base + idx] = make_float2(br, flip(bi, sgn));
         }
+        work.advance();
+        q = qn;
     }
 }
 
-template <bool kTma>
+template <int kStage, int kVar>
 static cudaError_t setup_dual_one() {
-    cudaError_t e = cudaFuncSetAttribute(r2iq_dual_d0_kernel<kTma>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         kDualWarps * warp_bytes<kTma>());
+    cudaError_t e = cudaFuncSetAttribute(r2iq_dual_d0_kernel<kStage, kVar>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         kDualWarps * warp_bytes<kStage>());
     if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(r2iq_dual_d0_kernel<kTma>, cudaFuncAttributePreferredSharedMemoryCarveout,
+    return cudaFuncSetAttribute(r2iq_dual_d0_kernel<kStage, kVar>, cudaFuncAttributePreferredSharedMemoryCarveout,
                                 cudaSharedmemCarveoutMaxShared);
 }
 
 cudaError_t setup_dual_d0_kernels() {
-    cudaError_t e = setup_dual_one<true>();
-    if (e != cudaSuccess) return e;
-    return setup_dual_one<false>();
+    cudaError_t e;
+    if ((e = setup_dual_one<1, 0>()) != cudaSuccess) return e;
+    if ((e = setup_dual_one<1, 1>()) != cudaSuccess) return e;
+    if ((e = setup_dual_one<1, 2>()) != cudaSuccess) return e;
+    if ((e = setup_dual_one<1, 3>()) != cudaSuccess) return e;
+    if ((e = setup_dual_one<1, 8>()) != cudaSuccess) return e;
+    if ((e = setup_dual_one<1, 9>()) != cudaSuccess) return e;
+    if ((e = setup_dual_one<2, 0>()) != cudaSuccess) return e;
+    if ((e = setup_dual_one<2, 1>()) != cudaSuccess) return e;
+    if ((e = setup_dual_one<2, 2>()) != cudaSuccess) return e;
+    if ((e = setup_dual_one<2, 3>()) != cudaSuccess) return e;
+    return setup_dual_one<0, 0>();
 }
 
-template <bool kTma>
+template <int kStage, int kVar>
 static cudaError_t launch_dual_one(const FusedParams& p, int sm_count, cudaStream_t stream) {
-    constexpr int smem = kDualWarps * warp_bytes<kTma>();
+    constexpr int smem = kDualWarps * warp_bytes<kStage>();
     int ctas_per_sm = 1;
-    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, r2iq_dual_d0_kernel<kTma>, kDualThreads, smem);
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, r2iq_dual_d0_kernel<kStage, kVar>, kDualThreads, smem);
     if (e != cudaSuccess) return e;
     if (ctas_per_sm < 1) ctas_per_sm = 1;
     if (const char* lim = getenv("R2IQ_CTAS_PER_SM")) {   // occupancy experiments only
@@ -293,12 +347,33 @@ static cudaError_t launch_dual_one(const FusedParams& p, int sm_count, cudaStrea
     long long grid = (long long)sm_count * ctas_per_sm;
     if (grid > want) grid = want;
     if (grid < 1) grid = 1;
-    r2iq_dual_d0_kernel<kTma><<<(unsigned)grid, kDualThreads, smem, stream>>>(p);
+    if constexpr (kVar & 1) {
+        e = cudaMemsetAsync(p.work_counter, 0, sizeof(unsigned long long), stream);
+        if (e != cudaSuccess) return e;
+    }
+    r2iq_dual_d0_kernel<kStage, kVar><<<(unsigned)grid, kDualThreads, smem, stream>>>(p);
     return cudaGetLastError();
 }
 
+template <int kStage>
+static cudaError_t launch_dual_var(const FusedParams& p, int sm_count, cudaStream_t stream) {
+    switch (kernel_variant() & 3) {
+        case 1: return launch_dual_one<kStage, 1>(p, sm_count, stream);
+        case 2: return launch_dual_one<kStage, 2>(p, sm_count, stream);
+        case 3: return launch_dual_one<kStage, 3>(p, sm_count, stream);
+        default: return launch_dual_one<kStage, 0>(p, sm_count, stream);
+    }
+}
+
 cudaError_t launch_dual_d0(const FusedParams& p, int sm_count, cudaStream_t stream, bool tma) {
-    return tma ? launch_dual_one<true>(p, sm_count, stream) : launch_dual_one<false>(p, sm_count, stream);
+    if (!tma) return launch_dual_one<0, 0>(p, sm_count, stream);
+    switch (kernel_variant()) {   // bit 3: inter-pass twiddles from the packed power recurrence
+        case 8: return launch_dual_one<1, 8>(p, sm_count, stream);
+        case 9: return launch_dual_one<1, 9>(p, sm_count, stream);
+        default: break;
+    }
+    if (kernel_variant() & 4) return launch_dual_var<2>(p, sm_count, stream);   // bit 2: input lands in the tile, 12 warps per SM
+    return launch_dual_var<1>(p, sm_count, stream);
 }
 
 }  // namespace r2iq

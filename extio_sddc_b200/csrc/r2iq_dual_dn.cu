@@ -15,6 +15,7 @@
 
 #include "dft_regs2.cuh"
 #include "r2iq_kernels.cuh"
+#include "work_dispenser.cuh"
 
 namespace r2iq {
 
@@ -73,7 +74,12 @@ __device__ __forceinline__ const uint32_t* frame_src(const FusedParams& p, long 
 // Phase boundaries double as CTA barriers (a superset of the __syncwarp the data hazard needs): they
 // keep the warps of a CTA within one phase of each other in the 50 KB unrolled loop body, so that
 // instruction-cache lines fetched by one warp are still resident for the others.
-#define PHASE_SYNC() __syncthreads()
+// Variant bit 1 (kFree) replaces them by warp-level fences: the warps of a CTA then run unsynchronised.
+#define PHASE_SYNC()                           \
+    do {                                       \
+        if constexpr (kFree) __syncwarp();     \
+        else __syncthreads();                  \
+    } while (0)
 
 __device__ __forceinline__ int brev5(int v) { return (int)(__brev((unsigned)v) >> 27); }
 __device__ __forceinline__ int brev_n(int v, int bits) { return bits == 0 ? 0 : (int)(__brev((unsigned)v) >> (32 - bits)); }
@@ -126,8 +132,12 @@ __device__ __forceinline__ FrameOut2 frame_out_dn(long long f, long long total) 
 }  // namespace
 
 // forward and backward transforms both run packed; D = 2..5
-template <int D, bool kTma>
+// kVar (measurement variants, env R2IQ_VARIANT): bit 0 = frame pairs handed out by an atomic counter instead of a
+// fixed stride (evens out SM-to-SM speed differences at the tail); bit 1 = no block barriers (warps run free).
+template <int D, bool kTma, int kVar = 0>
 __global__ void __launch_bounds__(kDualThreads, 2) r2iq_dual_dn_kernel(const FusedParams p) {
+    constexpr bool kDyn = (kVar & 1) != 0;
+    constexpr bool kFree = (kVar & 2) != 0;
     constexpr int M = kHalfFft >> D;
     constexpr int R = 32 >> D;            // band bins per lane = size of the register DFTs
     constexpr int G = 32 / R;             // lanes sharing one 32-point DFT in pass 2
@@ -144,8 +154,6 @@ __global__ void __launch_bounds__(kDualThreads, 2) r2iq_dual_dn_kernel(const Fus
     const uint32_t dstA = smem_u32(inA), dstB = smem_u32(inB);
 
     const long long n_pairs = (p.total_frames + 1) / 2;
-    const long long stride = (long long)gridDim.x * kDualWarps;
-    long long q = (long long)blockIdx.x * kDualWarps + warp;
 
     if constexpr (kTma) {
         if (lane == 0) {
@@ -161,6 +169,11 @@ __global__ void __launch_bounds__(kDualThreads, 2) r2iq_dual_dn_kernel(const Fus
         tma_load_1d(dstA, frame_src(p, fa), kFrameBytes, mbar);
         tma_load_1d(dstB, frame_src(p, fb), kFrameBytes, mbar);
     };
+    // frame pairs from the device-wide counter (kDyn) or by fixed stride; see work_dispenser.cuh
+    __shared__ long long s_base[3];
+    PairDispenser<kDyn, kFree, kDualWarps> work;
+    work.init(p.work_counter, s_base, lane, warp);
+    long long q = work.cur(warp);
     if constexpr (kTma) {
         if (lane == 0 && q < n_pairs) issue(q);
     }
@@ -172,8 +185,9 @@ __global__ void __launch_bounds__(kDualThreads, 2) r2iq_dual_dn_kernel(const Fus
 
     // The loop bound is CTA-uniform and every trip starts with a block barrier: the four warps then
     // walk the (56 KB, fully unrolled) loop body roughly in step and share instruction-cache lines.
-    for (long long q0 = (long long)blockIdx.x * kDualWarps; q0 < n_pairs; q0 += stride, q += stride) {
-        __syncthreads();
+    while (work.more(n_pairs)) {
+        work.top(p.work_counter, s_base);
+        const long long qn = work.next(warp);
         const bool idle = q >= n_pairs;           // tail: keep barrier participation uniform, store nothing
         const long long qq = idle ? n_pairs - 1 : q;
         c2 v[32];
@@ -185,7 +199,7 @@ __global__ void __launch_bounds__(kDualThreads, 2) r2iq_dual_dn_kernel(const Fus
 #pragma unroll
             for (int j = 0; j < 32; j++) unpack_words(inA[lane + 32 * j], inB[lane + 32 * j], p.rand_mul, v[brev5(j)]);
             __syncwarp();   // every lane has consumed its words: the buffers may be overwritten
-            if (lane == 0 && q + stride < n_pairs) issue(q + stride);   // idle warps never issued: their barrier would hang
+            if (lane == 0 && qn < n_pairs) issue(qn);   // idle warps never issue: nobody would consume the copy
         } else {
             const long long fa = 2 * qq;
             const long long fb = (fa + 1 < p.total_frames) ? fa + 1 : fa;   // odd tail: B repeats A, never stored
@@ -276,51 +290,79 @@ __global__ void __launch_bounds__(kDualThreads, 2) r2iq_dual_dn_kernel(const Fus
             if (!idle && idx >= oa.lo && idx < 3 * M / 4) p.out[oa.base + idx] = make_float2(ar, ai * p.imag_sign);
             if (!idle && ob.live && idx >= ob.lo && idx < 3 * M / 4) p.out[ob.base + idx] = make_float2(br, bi * p.imag_sign);
         }
+        work.advance();
+        q = qn;
     }
 }
 
-template <int D, bool kTma>
+template <int D, int kVar>
 static cudaError_t setup_dual_one() {
-    cudaError_t e = cudaFuncSetAttribute(r2iq_dual_dn_kernel<D, kTma>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         kDualWarps * warp_bytes<kTma>());
+    cudaError_t e = cudaFuncSetAttribute(r2iq_dual_dn_kernel<D, true, kVar>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         kDualWarps * warp_bytes<true>());
     if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(r2iq_dual_dn_kernel<D, kTma>, cudaFuncAttributePreferredSharedMemoryCarveout,
+    return cudaFuncSetAttribute(r2iq_dual_dn_kernel<D, true, kVar>, cudaFuncAttributePreferredSharedMemoryCarveout,
                                 cudaSharedmemCarveoutMaxShared);
+}
+
+template <int D>
+static cudaError_t setup_dual_all() {
+    cudaError_t e;
+    if ((e = setup_dual_one<D, 0>()) != cudaSuccess) return e;
+    if ((e = setup_dual_one<D, 1>()) != cudaSuccess) return e;
+    if ((e = setup_dual_one<D, 2>()) != cudaSuccess) return e;
+    return setup_dual_one<D, 3>();
 }
 
 cudaError_t setup_dual_dn_kernels() {
     cudaError_t e;
-    if ((e = setup_dual_one<1, true>()) != cudaSuccess) return e;
-    if ((e = setup_dual_one<2, true>()) != cudaSuccess) return e;
-    if ((e = setup_dual_one<3, true>()) != cudaSuccess) return e;
-    if ((e = setup_dual_one<4, true>()) != cudaSuccess) return e;
-    if ((e = setup_dual_one<5, true>()) != cudaSuccess) return e;
-    return cudaSuccess;
+    if ((e = setup_dual_all<1>()) != cudaSuccess) return e;
+    if ((e = setup_dual_all<2>()) != cudaSuccess) return e;
+    if ((e = setup_dual_all<3>()) != cudaSuccess) return e;
+    if ((e = setup_dual_all<4>()) != cudaSuccess) return e;
+    return setup_dual_all<5>();
 }
 
-template <int D, bool kTma>
+template <int D, int kVar>
 static cudaError_t launch_dual_one(const FusedParams& p, int sm_count, cudaStream_t stream) {
-    constexpr int smem = kDualWarps * warp_bytes<kTma>();
+    constexpr int smem = kDualWarps * warp_bytes<true>();
     int ctas_per_sm = 1;
-    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, r2iq_dual_dn_kernel<D, kTma>, kDualThreads, smem);
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, r2iq_dual_dn_kernel<D, true, kVar>, kDualThreads, smem);
     if (e != cudaSuccess) return e;
     if (ctas_per_sm < 1) ctas_per_sm = 1;
+    if (const char* lim = getenv("R2IQ_CTAS_PER_SM")) {   // occupancy experiments only
+        const int v = atoi(lim);
+        if (v >= 1 && v < ctas_per_sm) ctas_per_sm = v;
+    }
     const long long n_pairs = (p.total_frames + 1) / 2;
     long long want = (n_pairs + kDualWarps - 1) / kDualWarps;
     long long grid = (long long)sm_count * ctas_per_sm;
     if (grid > want) grid = want;
     if (grid < 1) grid = 1;
-    r2iq_dual_dn_kernel<D, kTma><<<(unsigned)grid, kDualThreads, smem, stream>>>(p);
+    if constexpr (kVar & 1) {
+        e = cudaMemsetAsync(p.work_counter, 0, sizeof(unsigned long long), stream);
+        if (e != cudaSuccess) return e;
+    }
+    r2iq_dual_dn_kernel<D, true, kVar><<<(unsigned)grid, kDualThreads, smem, stream>>>(p);
     return cudaGetLastError();
+}
+
+template <int D>
+static cudaError_t launch_dual_var(const FusedParams& p, int sm_count, cudaStream_t stream) {
+    switch (kernel_variant() & 3) {
+        case 1: return launch_dual_one<D, 1>(p, sm_count, stream);
+        case 2: return launch_dual_one<D, 2>(p, sm_count, stream);
+        case 3: return launch_dual_one<D, 3>(p, sm_count, stream);
+        default: return launch_dual_one<D, 0>(p, sm_count, stream);
+    }
 }
 
 cudaError_t launch_dual_dn(int d, const FusedParams& p, int sm_count, cudaStream_t stream) {
     switch (d) {
-        case 1: return launch_dual_one<1, true>(p, sm_count, stream);
-        case 2: return launch_dual_one<2, true>(p, sm_count, stream);
-        case 3: return launch_dual_one<3, true>(p, sm_count, stream);
-        case 4: return launch_dual_one<4, true>(p, sm_count, stream);
-        case 5: return launch_dual_one<5, true>(p, sm_count, stream);
+        case 1: return launch_dual_var<1>(p, sm_count, stream);
+        case 2: return launch_dual_var<2>(p, sm_count, stream);
+        case 3: return launch_dual_var<3>(p, sm_count, stream);
+        case 4: return launch_dual_var<4>(p, sm_count, stream);
+        case 5: return launch_dual_var<5>(p, sm_count, stream);
         default: return cudaErrorInvalidValue;
     }
 }

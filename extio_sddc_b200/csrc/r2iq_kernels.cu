@@ -22,7 +22,10 @@
 // No cuFFT, no tensor cores, no CPU fallback.
 #include "r2iq_kernels.cuh"
 
+#include <cstdlib>
+
 #include "r2iq_common.cuh"
+#include "work_dispenser.cuh"
 
 namespace r2iq {
 
@@ -124,7 +127,8 @@ __device__ __forceinline__ void band_rows(const FusedParams& p, const float2 (&v
     (band_row<D, K1>(p, v, lane, stage), ...);
 }
 
-template <int D>
+// kDyn: units of work from the device-wide counter instead of a fixed stride (work_dispenser.cuh)
+template <int D, bool kDyn = false>
 __global__ void __launch_bounds__(kThreads, min_ctas_v1<D>()) r2iq_fused_kernel(const FusedParams p) {
     using G = Geo<D>;
     extern __shared__ float2 smem[];
@@ -142,12 +146,16 @@ __global__ void __launch_bounds__(kThreads, min_ctas_v1<D>()) r2iq_fused_kernel(
     }
 
     const long long n_units = (p.total_frames + UNIT - 1) / UNIT;
-    for (long long unit = (long long)blockIdx.x * kWarpsPerCta + warp; unit < n_units;
-         unit += (long long)gridDim.x * kWarpsPerCta) {
+    PairDispenser<kDyn, true, kWarpsPerCta> work;          // warps run free: one unit per grab
+    work.init(p.work_counter, nullptr, lane, warp);
+    for (; work.more(n_units); work.advance()) {
+        work.top(p.work_counter, nullptr);
+        const long long unit = work.cur(warp);
+        const long long next_unit = work.next(warp);       // its first frame is prefetched into L2
         const long long f0 = unit * UNIT;
         if constexpr (D == 0) {
             float2 v[32], t[32];
-            forward_frame(p, f0, (unit + (long long)gridDim.x * kWarpsPerCta) * UNIT, lane, S, v);
+            forward_frame(p, f0, next_unit * UNIT, lane, S, v);
             band_d0<D>(p, v, lane, t, std::make_integer_sequence<int, 32>{});
             // backward pass 1 over the register index; lane l is residue (l - tunebin) mod 32
             dit<32, true>(t);
@@ -169,7 +177,7 @@ __global__ void __launch_bounds__(kThreads, min_ctas_v1<D>()) r2iq_fused_kernel(
                 const long long f = f0 + r;
                 if (f < p.total_frames) {                // warp-uniform
                     float2 v[32];
-                    forward_frame(p, f, r + 1 < UNIT ? f + 1 : (unit + (long long)gridDim.x * kWarpsPerCta) * UNIT,
+                    forward_frame(p, f, r + 1 < UNIT ? f + 1 : next_unit * UNIT,
                                   lane, S, v);
                     band_rows<D>(p, v, lane, stage + r * G::GS, std::make_integer_sequence<int, 32>{});
                 }
@@ -185,11 +193,18 @@ __global__ void __launch_bounds__(kThreads, min_ctas_v1<D>()) r2iq_fused_kernel(
     }
 }
 
-template <int D>
-static cudaError_t launch_one(const FusedParams& p, int sm_count, cudaStream_t stream) {
-    using G = Geo<D>;
+static int g_kernel_gen = 0;
+void set_kernel_generation(int gen) { g_kernel_gen = gen; }
+int kernel_variant() {
+    // default 1: dynamic work distribution, lock-step CTAs (the fastest measured combination)
+    const char* v = getenv("R2IQ_VARIANT");
+    return v ? atoi(v) : 1;
+}
+
+template <int D, bool kDyn>
+static cudaError_t launch_one_v(const FusedParams& p, int sm_count, cudaStream_t stream) {
     int ctas_per_sm = 1;
-    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, r2iq_fused_kernel<D>, kThreads,
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, r2iq_fused_kernel<D, kDyn>, kThreads,
                                                                  fused_smem_bytes<D>());
     if (e != cudaSuccess) return e;
     if (ctas_per_sm < 1) ctas_per_sm = 1;
@@ -198,23 +213,33 @@ static cudaError_t launch_one(const FusedParams& p, int sm_count, cudaStream_t s
     long long grid = (long long)sm_count * ctas_per_sm;     // persistent: every CTA strides over units
     if (grid > want) grid = want;
     if (grid < 1) grid = 1;
-    r2iq_fused_kernel<D><<<(unsigned)grid, kThreads, fused_smem_bytes<D>(), stream>>>(p);
+    if constexpr (kDyn) {
+        e = cudaMemsetAsync(p.work_counter, 0, sizeof(unsigned long long), stream);
+        if (e != cudaSuccess) return e;
+    }
+    r2iq_fused_kernel<D, kDyn><<<(unsigned)grid, kThreads, fused_smem_bytes<D>(), stream>>>(p);
     return cudaGetLastError();
 }
-
 template <int D>
-static cudaError_t setup_one() {
-    cudaError_t e = cudaFuncSetAttribute(r2iq_fused_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+static cudaError_t launch_one(const FusedParams& p, int sm_count, cudaStream_t stream) {
+    return (kernel_variant() & 1) ? launch_one_v<D, true>(p, sm_count, stream) : launch_one_v<D, false>(p, sm_count, stream);
+}
+
+template <int D, bool kDyn>
+static cudaError_t setup_one_v() {
+    cudaError_t e = cudaFuncSetAttribute(r2iq_fused_kernel<D, kDyn>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)fused_smem_bytes<D>());
     if (e != cudaSuccess) return e;
     // ask for the largest shared-memory carve-out so that kMinCtasPerSm CTAs are resident
-    return cudaFuncSetAttribute(r2iq_fused_kernel<D>, cudaFuncAttributePreferredSharedMemoryCarveout,
+    return cudaFuncSetAttribute(r2iq_fused_kernel<D, kDyn>, cudaFuncAttributePreferredSharedMemoryCarveout,
                                 cudaSharedmemCarveoutMaxShared);
 }
-
-static int g_kernel_gen = 0;
-void set_kernel_generation(int gen) { g_kernel_gen = gen; }
-
+template <int D>
+static cudaError_t setup_one() {
+    cudaError_t e = setup_one_v<D, false>();
+    if (e != cudaSuccess) return e;
+    return setup_one_v<D, true>();
+}
 cudaError_t setup_fused_kernels() {
     cudaError_t e;
     if ((e = setup_dual_kernels()) != cudaSuccess) return e;

@@ -31,7 +31,11 @@ struct FusedParams {
     uint32_t row_mask;          // bit k1 set: spectrum row [32*k1, 32*k1+32) holds a band bin or the mirror of one
     uint32_t rand_mul;          // 0xFFFE when the ADC randomizer is on, else 0
     float imag_sign;            // -1 when sideband inversion (copy<true>) is requested, else +1
+    unsigned long long* work_counter;   // device counter handing out frame pairs (dynamic work distribution)
 };
+// Measurement variants of the dual-frame kernels (env R2IQ_VARIANT, read at every launch): bit 0 = dynamic
+// work distribution, bit 1 = no block barriers between phases.
+int kernel_variant();
 
 // Channelizer (r2iq_channels.cu): n_channels tuned channels from one input stream, d >= 1.
 struct ChannelParams {
@@ -47,6 +51,7 @@ struct ChannelParams {
     int n_channels;
     uint32_t rand_mul;
     float imag_sign;
+    unsigned long long* work_counter;   // as FusedParams
 };
 cudaError_t setup_channel_kernels();
 cudaError_t launch_channels(int d, const ChannelParams& p, int sm_count, cudaStream_t stream);
@@ -65,6 +70,7 @@ struct WideParams {
     int tunebin;
     uint32_t rand_mul;
     float imag_sign;
+    unsigned long long* work_counter;   // as FusedParams
 };
 cudaError_t setup_wide_kernels();
 cudaError_t launch_wide(int d, const WideParams& p, int sm_count, cudaStream_t stream);

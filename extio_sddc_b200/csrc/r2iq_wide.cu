@@ -19,6 +19,7 @@
 //             planes and writes y[n' + (mfft/4) a] for a = 0..2 (a = 3 is always in the discarded quarter).
 //   d = 6     mfft = 64 is too small to split: warp 0 transforms the band alone.
 #include "r2iq_common.cuh"
+#include "work_dispenser.cuh"
 
 namespace r2iq {
 
@@ -82,7 +83,8 @@ __device__ __forceinline__ FrameOut quad_frame_out(long long f) {
 
 }  // namespace
 
-template <int D>
+// kDyn: frames from the device-wide counter instead of a fixed stride (work_dispenser.cuh; one frame per CTA)
+template <int D, bool kDyn = false>
 __global__ void __launch_bounds__(kQThreads, kQCtasPerSm) r2iq_wide_kernel(const WideParams p) {
     constexpr int M = kQHalf >> D;
     extern __shared__ float2 Z[];
@@ -93,7 +95,12 @@ __global__ void __launch_bounds__(kQThreads, kQCtasPerSm) r2iq_wide_kernel(const
     const int tb = p.tunebin;
     const int tb4 = tb >> 2;
 
-    for (long long f = blockIdx.x; f < p.total_frames; f += gridDim.x) {
+    __shared__ long long s_base[3];
+    PairDispenser<kDyn, false, 1> work;
+    work.init(p.work_counter, s_base, lane, warp);
+    for (; work.more(p.total_frames); work.advance()) {
+        work.top(p.work_counter, s_base);
+        const long long f = work.cur(0);
         // ---------------- stage A: radix-4 DIF over the four quarters of the frame ---------------------------
         const long long b = f / kQFrames;
         const int kf = (int)(f - b * kQFrames);
@@ -260,12 +267,18 @@ __global__ void __launch_bounds__(kQThreads, kQCtasPerSm) r2iq_wide_kernel(const
     }
 }
 
+template <int D, bool kDyn>
+static cudaError_t setup_qv() {
+    cudaError_t e = cudaFuncSetAttribute(r2iq_wide_kernel<D, kDyn>, cudaFuncAttributeMaxDynamicSharedMemorySize, kQSmemBytes);
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(r2iq_wide_kernel<D, kDyn>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                cudaSharedmemCarveoutMaxShared);
+}
 template <int D>
 static cudaError_t setup_q() {
-    cudaError_t e = cudaFuncSetAttribute(r2iq_wide_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, kQSmemBytes);
+    cudaError_t e = setup_qv<D, false>();
     if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(r2iq_wide_kernel<D>, cudaFuncAttributePreferredSharedMemoryCarveout,
-                                cudaSharedmemCarveoutMaxShared);
+    return setup_qv<D, true>();
 }
 
 cudaError_t setup_wide_kernels() {
@@ -280,13 +293,21 @@ cudaError_t setup_wide_kernels() {
     return cudaSuccess;
 }
 
-template <int D>
-static cudaError_t launch_q(const WideParams& p, int sm_count, cudaStream_t stream) {
+template <int D, bool kDyn>
+static cudaError_t launch_qv(const WideParams& p, int sm_count, cudaStream_t stream) {
     long long grid = (long long)sm_count * kQCtasPerSm;
     if (grid > p.total_frames) grid = p.total_frames;
     if (grid < 1) grid = 1;
-    r2iq_wide_kernel<D><<<(unsigned)grid, kQThreads, kQSmemBytes, stream>>>(p);
+    if constexpr (kDyn) {
+        cudaError_t e = cudaMemsetAsync(p.work_counter, 0, sizeof(unsigned long long), stream);
+        if (e != cudaSuccess) return e;
+    }
+    r2iq_wide_kernel<D, kDyn><<<(unsigned)grid, kQThreads, kQSmemBytes, stream>>>(p);
     return cudaGetLastError();
+}
+template <int D>
+static cudaError_t launch_q(const WideParams& p, int sm_count, cudaStream_t stream) {
+    return (kernel_variant() & 1) ? launch_qv<D, true>(p, sm_count, stream) : launch_qv<D, false>(p, sm_count, stream);
 }
 
 cudaError_t launch_wide(int d, const WideParams& p, int sm_count, cudaStream_t stream) {
