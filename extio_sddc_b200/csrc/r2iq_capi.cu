@@ -101,7 +101,13 @@ struct r2iq_cuda_s {
     std::vector<std::complex<float>> hw[kNDec];   // filterHw[d], host copy
     uint64_t hw_version[kNDec] = {0};
     float2* d_tw_fwd = nullptr;
-    unsigned long long* d_work_counter = nullptr;   // frame-pair dispenser of the dual-frame kernels
+    // Work dispensers of the persistent kernels (work_dispenser.cuh).  Launches of one handle may be in flight on
+    // several streams at once (the slots of the host pipeline), so every launch takes the next counter of a ring;
+    // the ring is longer than the number of kernels a device can run concurrently.
+    static constexpr unsigned kCounterRing = 256;
+    unsigned long long* d_work_counter = nullptr;
+    unsigned counter_next = 0;
+    unsigned long long* next_counter() { return d_work_counter + (counter_next++ % kCounterRing); }
     std::map<long long, TableSet> tables;          // key = version<<20 | d<<12 | tunebin... see table_key
     std::map<long long, float2*> gh_tables;        // channelizer: 0.5*H_d in inverse-FFT bin order, key = version<<4 | d
     std::map<std::vector<int>, int*> chan_lists;   // channelizer: device copies of tune-bin lists
@@ -390,7 +396,7 @@ int launch_wide_impl(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d
     p.tunebin = h->tunebin;
     p.rand_mul = h->rand_on ? 0xFFFEu : 0u;
     p.imag_sign = h->latched_sideband ? -1.0f : 1.0f;
-    p.work_counter = h->d_work_counter;
+    p.work_counter = h->next_counter();
     CU(h, launch_wide(d, p, h->sm_count, stream));
     return R2IQ_OK;
 }
@@ -426,7 +432,7 @@ int launch(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d_out, cuda
     p.row_mask = ts.row_mask;
     p.rand_mul = h->rand_on ? 0xFFFEu : 0u;
     p.imag_sign = h->latched_sideband ? -1.0f : 1.0f;
-    p.work_counter = h->d_work_counter;
+    p.work_counter = h->next_counter();
     CU(h, launch_fused(d, p, h->sm_count, stream));
     h->stats.kernel_launches++;
     h->stats.blocks_processed += (uint64_t)n_blocks;
@@ -497,7 +503,7 @@ int launch_channels_impl(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, cons
     p.n_channels = n_channels;
     p.rand_mul = h->rand_on ? 0xFFFEu : 0u;
     p.imag_sign = h->latched_sideband ? -1.0f : 1.0f;
-    p.work_counter = h->d_work_counter;
+    p.work_counter = h->next_counter();
     CU(h, launch_channels(d, p, h->sm_count, stream));
     h->stats.kernel_launches++;
     h->stats.blocks_processed += (uint64_t)n_blocks;
@@ -577,8 +583,8 @@ int r2iq_cuda_create(const r2iq_cuda_config* cfg, r2iq_cuda_t* out) {
             const double th = -2.0 * kPiD * (double)(k2 * l) / (double)kHalfFft;
             tw[k2 * 32 + l] = make_float2((float)cos(th), (float)sin(th));
         }
-    if ((e = cudaMalloc(&h->d_work_counter, sizeof(unsigned long long))) != cudaSuccess ||
-        (e = cudaMemset(h->d_work_counter, 0, sizeof(unsigned long long))) != cudaSuccess ||
+    if ((e = cudaMalloc(&h->d_work_counter, sizeof(unsigned long long) * r2iq_cuda_s::kCounterRing)) != cudaSuccess ||
+        (e = cudaMemset(h->d_work_counter, 0, sizeof(unsigned long long) * r2iq_cuda_s::kCounterRing)) != cudaSuccess ||
         (e = cudaMalloc(&h->d_tw_fwd, sizeof(float2) * 32 * 32)) != cudaSuccess ||
         (e = cudaMemcpy(h->d_tw_fwd, tw.data(), sizeof(float2) * 32 * 32, cudaMemcpyHostToDevice)) != cudaSuccess ||
         (e = cudaMallocHost(&h->carry, sizeof(int16_t) * h->half)) != cudaSuccess ||

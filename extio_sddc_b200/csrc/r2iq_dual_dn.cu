@@ -31,10 +31,13 @@ constexpr int kDualThreads = kDualWarps * 32;
 constexpr int kTile = 32 * 33;                // elements per plane: 32x32 tile, pitch 33 (conflict-free for 8 B accesses)
 constexpr int kFrameBytes = kFftN * 2;        // 4096 B of int16 per frame
 // per-warp shared memory: transposition tile (two 8-byte planes) [+ two input frames + one mbarrier]
-template <bool kTma>
+//   kStage = 2 : TMA bulk copies land IN the transposition tile, in the part the (small) backward transposition
+//                 does not use, as soon as the band has been cut; 16.9 KB per warp, 12 warps per SM.
+template <int kStage>
 __host__ __device__ constexpr int warp_bytes() {
-    return kTile * 16 + (kTma ? 2 * kFrameBytes + 16 : 0);
+    return kTile * 16 + (kStage == 1 ? 2 * kFrameBytes : 0) + (kStage ? 16 : 0);
 }
+constexpr int kLandOff = kTile * 8 - kFrameBytes;   // 4352: a frame at the tail of each 8448-byte plane
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -134,8 +137,10 @@ __device__ __forceinline__ FrameOut2 frame_out_dn(long long f, long long total) 
 // forward and backward transforms both run packed; D = 2..5
 // kVar (measurement variants, env R2IQ_VARIANT): bit 0 = frame pairs handed out by an atomic counter instead of a
 // fixed stride (evens out SM-to-SM speed differences at the tail); bit 1 = no block barriers (warps run free).
-template <int D, bool kTma, int kVar = 0>
-__global__ void __launch_bounds__(kDualThreads, 2) r2iq_dual_dn_kernel(const FusedParams p) {
+template <int D, int kStage, int kVar = 0>
+__global__ void __launch_bounds__(kDualThreads, kStage == 2 ? 3 : 2) r2iq_dual_dn_kernel(const FusedParams p) {
+    constexpr bool kTma = kStage != 0;
+    static_assert(kStage != 2 || 32 * ((32 >> D) + 1) * 8 <= kLandOff, "backward transposition overlaps the landing zone");
     constexpr bool kDyn = (kVar & 1) != 0;
     constexpr bool kFree = (kVar & 2) != 0;
     constexpr int M = kHalfFft >> D;
@@ -145,12 +150,12 @@ __global__ void __launch_bounds__(kDualThreads, 2) r2iq_dual_dn_kernel(const Fus
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
-    constexpr int kWarpBytes = warp_bytes<kTma>();
+    constexpr int kWarpBytes = warp_bytes<kStage>();
     unsigned char* wbase = smem_raw + (size_t)warp * kWarpBytes;
     u64* S = reinterpret_cast<u64*>(wbase);
-    const uint32_t* inA = reinterpret_cast<const uint32_t*>(wbase + kTile * 16);
-    const uint32_t* inB = inA + kFrameBytes / 4;
-    const uint32_t mbar = smem_u32(wbase + kTile * 16 + 2 * kFrameBytes);
+    const uint32_t* inA = reinterpret_cast<const uint32_t*>(wbase + (kStage == 2 ? kLandOff : kTile * 16));
+    const uint32_t* inB = kStage == 2 ? reinterpret_cast<const uint32_t*>(wbase + kTile * 8 + kLandOff) : inA + kFrameBytes / 4;
+    const uint32_t mbar = smem_u32(wbase + kTile * 16 + (kStage == 1 ? 2 * kFrameBytes : 0));
     const uint32_t dstA = smem_u32(inA), dstB = smem_u32(inB);
 
     const long long n_pairs = (p.total_frames + 1) / 2;
@@ -199,7 +204,9 @@ __global__ void __launch_bounds__(kDualThreads, 2) r2iq_dual_dn_kernel(const Fus
 #pragma unroll
             for (int j = 0; j < 32; j++) unpack_words(inA[lane + 32 * j], inB[lane + 32 * j], p.rand_mul, v[brev5(j)]);
             __syncwarp();   // every lane has consumed its words: the buffers may be overwritten
-            if (lane == 0 && qn < n_pairs) issue(qn);   // idle warps never issue: nobody would consume the copy
+            if constexpr (kStage == 1) {
+                if (lane == 0 && qn < n_pairs) issue(qn);   // idle warps never issue: nobody would consume the copy
+            }
         } else {
             const long long fa = 2 * qq;
             const long long fb = (fa + 1 < p.total_frames) ? fa + 1 : fa;   // odd tail: B repeats A, never stored
@@ -249,6 +256,13 @@ __global__ void __launch_bounds__(kDualThreads, 2) r2iq_dual_dn_kernel(const Fus
             y[brev_n(j, RB)] = r;                                    // bit-reversed placement
         }
         PHASE_SYNC();   // every lane is done with the spectrum: the tile is free for the transposition
+        if constexpr (kStage == 2) {
+            // ... and its tail for the next pair of frames (generic-proxy reads ordered before the async-proxy writes)
+            if (lane == 0 && qn < n_pairs) {
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                issue(qn);
+            }
+        }
 
         // ---- backward mfft-point transform: n = lane + 32*n2, k = k2 + R*k1 ------------------------
         dit2<R, true>(y);                         // pass 1 over n2
@@ -295,12 +309,12 @@ __global__ void __launch_bounds__(kDualThreads, 2) r2iq_dual_dn_kernel(const Fus
     }
 }
 
-template <int D, int kVar>
+template <int D, int kVar, int kStage = 1>
 static cudaError_t setup_dual_one() {
-    cudaError_t e = cudaFuncSetAttribute(r2iq_dual_dn_kernel<D, true, kVar>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         kDualWarps * warp_bytes<true>());
+    cudaError_t e = cudaFuncSetAttribute(r2iq_dual_dn_kernel<D, kStage, kVar>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         kDualWarps * warp_bytes<kStage>());
     if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(r2iq_dual_dn_kernel<D, true, kVar>, cudaFuncAttributePreferredSharedMemoryCarveout,
+    return cudaFuncSetAttribute(r2iq_dual_dn_kernel<D, kStage, kVar>, cudaFuncAttributePreferredSharedMemoryCarveout,
                                 cudaSharedmemCarveoutMaxShared);
 }
 
@@ -310,6 +324,8 @@ static cudaError_t setup_dual_all() {
     if ((e = setup_dual_one<D, 0>()) != cudaSuccess) return e;
     if ((e = setup_dual_one<D, 1>()) != cudaSuccess) return e;
     if ((e = setup_dual_one<D, 2>()) != cudaSuccess) return e;
+    if ((e = setup_dual_one<D, 1, 2>()) != cudaSuccess) return e;
+    if ((e = setup_dual_one<D, 3, 2>()) != cudaSuccess) return e;
     return setup_dual_one<D, 3>();
 }
 
@@ -322,11 +338,11 @@ cudaError_t setup_dual_dn_kernels() {
     return setup_dual_all<5>();
 }
 
-template <int D, int kVar>
+template <int D, int kVar, int kStage = 1>
 static cudaError_t launch_dual_one(const FusedParams& p, int sm_count, cudaStream_t stream) {
-    constexpr int smem = kDualWarps * warp_bytes<true>();
+    constexpr int smem = kDualWarps * warp_bytes<kStage>();
     int ctas_per_sm = 1;
-    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, r2iq_dual_dn_kernel<D, true, kVar>, kDualThreads, smem);
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, r2iq_dual_dn_kernel<D, kStage, kVar>, kDualThreads, smem);
     if (e != cudaSuccess) return e;
     if (ctas_per_sm < 1) ctas_per_sm = 1;
     if (const char* lim = getenv("R2IQ_CTAS_PER_SM")) {   // occupancy experiments only
@@ -342,17 +358,21 @@ static cudaError_t launch_dual_one(const FusedParams& p, int sm_count, cudaStrea
         e = cudaMemsetAsync(p.work_counter, 0, sizeof(unsigned long long), stream);
         if (e != cudaSuccess) return e;
     }
-    r2iq_dual_dn_kernel<D, true, kVar><<<(unsigned)grid, kDualThreads, smem, stream>>>(p);
+    r2iq_dual_dn_kernel<D, kStage, kVar><<<(unsigned)grid, kDualThreads, smem, stream>>>(p);
     return cudaGetLastError();
 }
 
 template <int D>
 static cudaError_t launch_dual_var(const FusedParams& p, int sm_count, cudaStream_t stream) {
-    switch (kernel_variant() & 3) {
+    // default 7 (measured on B200, 8192 blocks): 12 free-running warps per SM + dynamic distribution give
+    // 760 / 869 / 929 / 968 Gsamples/s at d = 2..5, the 8-warp lock-step form (variant 1) 710 / 791 / 858 / 878
+    switch (kernel_variant(7)) {
+        case 0: return launch_dual_one<D, 0>(p, sm_count, stream);
         case 1: return launch_dual_one<D, 1>(p, sm_count, stream);
         case 2: return launch_dual_one<D, 2>(p, sm_count, stream);
         case 3: return launch_dual_one<D, 3>(p, sm_count, stream);
-        default: return launch_dual_one<D, 0>(p, sm_count, stream);
+        case 5: return launch_dual_one<D, 1, 2>(p, sm_count, stream);
+        default: return launch_dual_one<D, 3, 2>(p, sm_count, stream);
     }
 }
 

@@ -195,10 +195,10 @@ __global__ void __launch_bounds__(kThreads, min_ctas_v1<D>()) r2iq_fused_kernel(
 
 static int g_kernel_gen = 0;
 void set_kernel_generation(int gen) { g_kernel_gen = gen; }
-int kernel_variant() {
-    // default 1: dynamic work distribution, lock-step CTAs (the fastest measured combination)
+int kernel_variant(int dflt) {
+    // unset: every kernel family runs its fastest measured combination (`dflt`)
     const char* v = getenv("R2IQ_VARIANT");
-    return v ? atoi(v) : 1;
+    return v ? atoi(v) : dflt;
 }
 
 template <int D, bool kDyn>

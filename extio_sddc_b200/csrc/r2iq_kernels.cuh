@@ -33,9 +33,13 @@ struct FusedParams {
     float imag_sign;            // -1 when sideband inversion (copy<true>) is requested, else +1
     unsigned long long* work_counter;   // device counter handing out frame pairs (dynamic work distribution)
 };
-// Measurement variants of the dual-frame kernels (env R2IQ_VARIANT, read at every launch): bit 0 = dynamic
-// work distribution, bit 1 = no block barriers between phases.
-int kernel_variant();
+// Measurement variants of the persistent kernels (env R2IQ_VARIANT, read at every launch): bit 0 = dynamic work
+// distribution (work_dispenser.cuh), bit 1 = no block barriers between phases (warps run free), bit 2 = TMA
+// input lands in the transposition tile itself (12 instead of 8 warps per SM; d = 0 and d >= 2 kernels), bit 3 =
+// inter-pass twiddles from a packed power recurrence instead of table loads (d = 0 kernel).  Without the
+// variable every family runs its fastest measured combination: 1 for d = 0 and d = 1, 7 for d = 2..5, bit 0 for
+// the one-frame, FFTN 8192 and channelizer kernels.
+int kernel_variant(int dflt = 1);
 
 // Channelizer (r2iq_channels.cu): n_channels tuned channels from one input stream, d >= 1.
 struct ChannelParams {

@@ -333,6 +333,62 @@ def test_fine_tune_mixer_bit_exact(op):
     op.tunebin = 256
 
 
+def test_chunks_in_flight_on_several_streams_do_not_share_work_counters():
+    """The host-buffer path keeps three chunks in flight on three streams; the persistent kernels hand out
+    their frame pairs through a device counter (work_dispenser.cuh).  Two launches sharing one counter would
+    skip frames: run a many-chunk capture repeatedly and require the one-launch result bit for bit."""
+    import torch
+    d, nb = 5, 96
+    x = orc.rx888_blocks(nb, d, 256, randomized=True, seed=77)
+    r = CudaR2IQ(chunk_blocks=2)
+    r.Init(GAIN)
+    r.setDecimate(d); r.updateRand(True); r.tunebin = 256; r.TurnOn()
+    dev = torch.device("cuda:0")
+    xin = torch.from_numpy(np.concatenate([np.zeros(1024, np.int16), x])).to(dev)
+    out = torch.empty(nb * (32768 >> d), dtype=torch.complex64, device=dev)
+    r.process_device(xin.data_ptr(), nb, out.data_ptr(), torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    want = out.cpu().numpy()
+    r.TurnOff()
+    for _ in range(20):
+        r.TurnOn()
+        got = r.process(x)
+        r.TurnOff()
+        assert np.array_equal(got, want)
+    r.close()
+
+
+@pytest.mark.parametrize("variant", ["0", "1", "2", "3", "5", "7", "9"])
+def test_measurement_variants_meet_the_bar(variant):
+    """Every work-distribution / staging variant kept behind R2IQ_VARIANT (r2iq_kernels.cuh) meets the parity bar,
+    on the device path and through the pipelined host path."""
+    import subprocess
+    import sys
+    code = r'''
+import sys, numpy as np
+sys.path.insert(0, %r)
+from extio_sddc_b200 import CudaR2IQ
+from oracle import r2iq_oracle as orc
+G = orc.RX888MK2_GAINFACTOR
+r = CudaR2IQ(chunk_blocks=2); r.Init(G)
+worst = 0.0
+for d in range(7):
+    for tb, rnd, lsb, nb in ((256, True, False, 5), (0, False, True, 1), (1020, True, False, 2)):
+        x = orc.rx888_blocks(nb, d, tb, randomized=rnd, seed=31 + d)
+        h = np.random.default_rng(d).integers(-3000, 3000, 1024).astype(np.int16)
+        r.setDecimate(d); r.updateRand(rnd); r.setSideband(lsb); r.tunebin = tb; r.TurnOn()
+        got = r.process(x, history=h); r.TurnOff()
+        ref = orc.r2iq(x, d, tb, gain=G, rand=rnd, sideband=lsb, history=h)
+        e = orc.rel_l2(got, ref); m = float(np.abs(got - ref).max()) / orc.full_scale(G)
+        assert e <= 1e-5 and m <= 1e-4, (d, tb, e, m)
+        worst = max(worst, e)
+print("worst", worst)
+''' % (os.path.dirname(os.path.dirname(os.path.abspath(__file__))),)
+    env = dict(os.environ, R2IQ_VARIANT=variant)
+    r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "worst" in r.stdout, r.stdout + r.stderr
+
+
 @pytest.mark.parametrize("gen", ["1", "2", "3", "4"])
 def test_alternative_kernel_generations_meet_the_bar(gen):
     """The kernel families kept in-tree for A/B measurements (env R2IQ_KERNEL_GEN, r2iq_kernels.cu
