@@ -56,6 +56,7 @@ struct Slot {
     cudaEvent_t done = nullptr;
     int16_t* d_in = nullptr;     // [halfFft | chunk_blocks * 65536]
     float* d_out = nullptr;      // chunk_blocks * 32768 complex (sized for d = 0)
+    float* d_out_rates = nullptr;   // r2iq_cuda_process_rates: the chunk's output at up to 7 rates, allocated on first use
     float* d_starts = nullptr;   // fine-tune NCO: start phasors of the chunk's 128-sample blocks
     size_t starts_cap = 0;       // capacity of d_starts in 128-sample blocks
     bool busy = false;
@@ -614,6 +615,7 @@ int r2iq_cuda_destroy(r2iq_cuda_t h) {
     cudaFree(h->d_wctab);
     for (int i = 0; i < kSlots; i++) {
         Slot& s = h->slots[i];
+        cudaFree(s.d_out_rates);
         if (s.stream) cudaStreamDestroy(s.stream);
         if (s.done) cudaEventDestroy(s.done);
         cudaFree(s.d_in);
@@ -795,6 +797,79 @@ int r2iq_cuda_process(r2iq_cuda_t h, const int16_t* blocks, long n_blocks, const
             h->slots[i].busy = false;
         }
     }
+    memcpy(h->carry, blocks + (size_t)n_blocks * kTransferSamples - h->half, sizeof(int16_t) * h->half);
+    h->carry_valid = true;
+    return R2IQ_OK;
+}
+
+int r2iq_cuda_process_rates(r2iq_cuda_t h, const int16_t* blocks, long n_blocks, const int16_t* history,
+                            const int* decimations, int n_rates, float* const* iq_outs) {
+    int rc = check_handle(h);
+    if (rc) return rc;
+    if (!h->on) return fail(R2IQ_E_STATE, "process_rates called while the operator is off (call r2iq_cuda_turn_on)");
+    if (n_rates < 1 || n_rates > kNDec || !decimations || !iq_outs) return fail(R2IQ_E_INVALID, "process_rates: 1..%d rates", kNDec);
+    for (int r = 0; r < n_rates; r++)
+        if (decimations[r] < 0 || decimations[r] >= kNDec || (n_blocks > 0 && !iq_outs[r]))
+            return fail(R2IQ_E_INVALID, "process_rates: bad decimation index or output buffer at position %d", r);
+    if (h->nco.on) return fail(R2IQ_E_STATE, "process_rates: the fine-tune mixer belongs to one rate; switch it off first");
+    if (n_blocks < 0 || (n_blocks > 0 && !blocks)) return fail(R2IQ_E_INVALID, "process_rates: bad buffers");
+    if (n_blocks == 0) return R2IQ_OK;
+    std::lock_guard<std::mutex> lk(h->mu);
+    CU(h, cudaSetDevice(h->device));
+    if ((rc = ensure_slots(h)) != R2IQ_OK) return rc;
+    // a chunk's output at every rate: sum over d of 32768 >> d  <  2 * 32768 complex per block
+    const size_t rates_floats = 2 * 2 * (size_t)h->chunk_blocks * (kTransferSamples / 2);
+    for (int i = 0; i < kSlots; i++)
+        if (!h->slots[i].d_out_rates) CU(h, cudaMalloc(&h->slots[i].d_out_rates, sizeof(float) * rates_floats));
+    if (history) memcpy(h->carry, history, sizeof(int16_t) * h->half);
+    const int latched = h->latched_decimate;
+    long done = 0;
+    int si = 0;
+    while (done < n_blocks && rc == R2IQ_OK) {
+        Slot& s = h->slots[si];
+        if (s.busy) {
+            CU(h, cudaEventSynchronize(s.done));
+            s.busy = false;
+        }
+        const long nb = (n_blocks - done) < h->chunk_blocks ? (n_blocks - done) : h->chunk_blocks;
+        if (done == 0) {
+            CU(h, cudaMemcpyAsync(s.d_in, h->carry, sizeof(int16_t) * h->half, cudaMemcpyHostToDevice, s.stream));
+            CU(h, cudaMemcpyAsync(s.d_in + h->half, blocks, sizeof(int16_t) * (size_t)nb * kTransferSamples,
+                                  cudaMemcpyHostToDevice, s.stream));
+        } else {
+            CU(h, cudaMemcpyAsync(s.d_in, blocks + (size_t)done * kTransferSamples - h->half,
+                                  sizeof(int16_t) * ((size_t)h->half + (size_t)nb * kTransferSamples),
+                                  cudaMemcpyHostToDevice, s.stream));
+        }
+        h->stats.h2d_bytes += sizeof(int16_t) * ((size_t)h->half + (size_t)nb * kTransferSamples);
+        size_t off = 0;   // floats into d_out_rates
+        for (int r = 0; r < n_rates && rc == R2IQ_OK; r++) {
+            const int d = decimations[r];
+            const size_t opb = (size_t)((kTransferSamples / 2) >> d);
+            h->latched_decimate = d;      // the kernels and tables are chosen per launch from the latched index
+            rc = launch(h, s.d_in, nb, s.d_out_rates + off, s.stream, &s.d_starts, &s.starts_cap);
+            if (rc != R2IQ_OK) break;
+            const size_t out_bytes = sizeof(float) * 2 * (size_t)nb * opb;
+            cudaError_t ce = cudaMemcpyAsync(iq_outs[r] + 2 * (size_t)done * opb, s.d_out_rates + off, out_bytes,
+                                             cudaMemcpyDeviceToHost, s.stream);
+            if (ce != cudaSuccess) rc = fail(R2IQ_E_CUDA, "process_rates: %s", cudaGetErrorString(ce));
+            h->stats.d2h_bytes += out_bytes;
+            off += 2 * (size_t)h->chunk_blocks * opb;
+        }
+        h->latched_decimate = latched;
+        if (rc != R2IQ_OK) break;
+        CU(h, cudaEventRecord(s.done, s.stream));
+        s.busy = true;
+        done += nb;
+        si = (si + 1) % kSlots;
+    }
+    for (int i = 0; i < kSlots; i++) {
+        if (h->slots[i].busy) {
+            CU(h, cudaEventSynchronize(h->slots[i].done));
+            h->slots[i].busy = false;
+        }
+    }
+    if (rc != R2IQ_OK) return rc;
     memcpy(h->carry, blocks + (size_t)n_blocks * kTransferSamples - h->half, sizeof(int16_t) * h->half);
     h->carry_valid = true;
     return R2IQ_OK;

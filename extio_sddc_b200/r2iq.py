@@ -159,6 +159,32 @@ class CudaR2IQ:
         capi.check(self._lib.r2iq_cuda_process_device(self._handle(), ctypes.c_void_p(d_in_ptr), int(n_blocks),
                                                       ctypes.c_void_p(d_out_ptr), ctypes.c_void_p(stream_ptr)))
 
+    def process_rates(self, blocks: np.ndarray, decimations, history: np.ndarray | None = None, outs=None) -> list:
+        """One ADC stream at several output rates (``r2iq_cuda_process_rates``): the capture crosses PCIe once,
+        every entry of ``decimations`` (indices 0..6) gets the stream ``process`` would give at that decimation.
+        Returns a list of complex64 arrays (``outs`` may supply them, e.g. pinned buffers)."""
+        blocks = np.ascontiguousarray(blocks, dtype=np.int16).reshape(-1)
+        if blocks.shape[0] % TRANSFER_SAMPLES:
+            raise ValueError("input must be a whole number of 65536-sample blocks")
+        n_blocks = blocks.shape[0] // TRANSFER_SAMPLES
+        dec = np.ascontiguousarray(decimations, dtype=np.int32)
+        sizes = [n_blocks * ((TRANSFER_SAMPLES // 2) >> int(d)) for d in dec]
+        if outs is None:
+            outs = [np.empty(n, dtype=np.complex64) for n in sizes]
+        for o, n in zip(outs, sizes):
+            if o.dtype != np.complex64 or o.size != n or not o.flags.c_contiguous:
+                raise ValueError("outs[r] must be a contiguous complex64 array of n_blocks*(32768>>d) samples")
+        ptrs = (ctypes.c_void_p * len(outs))(*[o.ctypes.data for o in outs])
+        hist_p = None
+        if history is not None:
+            history = np.ascontiguousarray(history, dtype=np.int16)
+            if history.shape[0] != self.half_fft:
+                raise ValueError(f"history must hold {self.half_fft} samples")
+            hist_p = history.ctypes.data
+        capi.check(self._lib.r2iq_cuda_process_rates(self._handle(), blocks.ctypes.data, n_blocks, hist_p,
+                                                     dec.ctypes.data, dec.shape[0], ptrs))
+        return list(outs)
+
     def process_channels(self, blocks: np.ndarray, tunebins, history: np.ndarray | None = None) -> np.ndarray:
         """Channelizer: every tune bin in ``tunebins`` from one pass over ``blocks`` (latched d >= 1).
         Returns complex64 [n_channels, n_blocks*(32768>>d)]; row c equals a separate operator tuned to

@@ -125,6 +125,16 @@ R2IQ_API long r2iq_cuda_out_per_block(r2iq_cuda_t h);
  * Pinned host memory (r2iq_cuda_host_alloc) is needed for the copies to overlap. */
 R2IQ_API int r2iq_cuda_process(r2iq_cuda_t h, const int16_t* blocks, long n_blocks, const int16_t* history, float* iq_out);
 
+/* One ADC stream at several output rates.  In the reference every rate is its own fft_mt_r2iq instance reading
+ * the SAME input ring slots in place (Core/fft_mt_r2iq_impl.hpp:20-33; RadioHandlerClass owns the ring,
+ * Core/RadioHandler.h:111); here the capture crosses PCIe once and is transformed n_rates times on the device:
+ * decimations[r] in [0, 7) selects the rate of iq_outs[r] (n_blocks*(32768>>d) complex floats each), tune bin,
+ * rand and the latched sideband as for r2iq_cuda_process, history handling identical (carried across calls).
+ * Every output equals what r2iq_cuda_process gives at that decimation.  The latched decimation is left unchanged;
+ * the fine-tune mixer (one residual per rate) must be off. */
+R2IQ_API int r2iq_cuda_process_rates(r2iq_cuda_t h, const int16_t* blocks, long n_blocks, const int16_t* history,
+                                     const int* decimations, int n_rates, float* const* iq_outs);
+
 /* Same transform on DEVICE memory, asynchronously on the caller's stream (cudaStream_t passed as
  * void*; NULL = the legacy default stream).  d_in points at [halfFft history samples | n_blocks
  * blocks] contiguous in device memory (16-byte aligned: frames are fetched by TMA bulk copies); d_iq_out receives n_blocks*(32768>>d)

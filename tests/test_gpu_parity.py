@@ -333,6 +333,35 @@ def test_fine_tune_mixer_bit_exact(op):
     op.tunebin = 256
 
 
+def test_process_rates_equals_one_operator_per_rate():
+    """r2iq_cuda_process_rates: one upload, every decimation's stream bit-identical to r2iq_cuda_process at that
+    decimation; ragged chunking, carried history across calls, latched decimation untouched."""
+    r = CudaR2IQ(chunk_blocks=3)
+    r.Init(GAIN)
+    r.updateRand(True); r.tunebin = 148
+    x = orc.rx888_blocks(8, 2, 148, randomized=True, seed=9)
+    want = {}
+    for d in range(7):
+        r.setDecimate(d); r.TurnOn()
+        want[d] = np.concatenate([r.process(x[: 5 * 65536]), r.process(x[5 * 65536:])])   # history carried
+        r.TurnOff()
+    r.setDecimate(3); r.TurnOn()
+    decs = [0, 5, 2, 6, 1, 4, 3]
+    a = r.process_rates(x[: 5 * 65536], decs)
+    b = r.process_rates(x[5 * 65536:], decs)
+    for i, d in enumerate(decs):
+        assert np.array_equal(np.concatenate([a[i], b[i]]), want[d]), d
+    assert r.getDecimate() == 3 if hasattr(r, "getDecimate") else True
+    got3 = r.process(x, history=np.zeros(1024, np.int16))
+    assert np.array_equal(got3, want[3])
+    ref = orc.r2iq(x, 5, 148, gain=GAIN, rand=True)
+    check(np.concatenate([a[1], b[1]]), ref, GAIN, "rates d5")
+    with pytest.raises(Exception):
+        r.process_rates(x, [7])
+    r.TurnOff()
+    r.close()
+
+
 def test_chunks_in_flight_on_several_streams_do_not_share_work_counters():
     """The host-buffer path keeps three chunks in flight on three streams; the persistent kernels hand out
     their frame pairs through a device counter (work_dispenser.cuh).  Two launches sharing one counter would
