@@ -13,6 +13,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <map>
+#include <atomic>
 #include <mutex>
 #include <new>
 #include <vector>
@@ -88,10 +89,13 @@ struct r2iq_cuda_s {
     // control state (r2iqControlClass members, Core/r2iq.h:38-47; mtunebin, Core/fft_mt_r2iq.h:90)
     int fftn = kFftN;             // FFTN_R_ADC of this operator: 2048 (north star) or 8192 (reference as shipped)
     int half = kHalfFft;          // halfFft
-    int decimate = 0;
-    int tunebin = kHalfFft / 4;
-    bool rand_on = false;
-    bool sideband = false;
+    // decimate / tunebin / rand_on / sideband are written by the application thread while the worker streams
+    // (Core/RadioHandler.cpp:289,335; unittest/core_test.cpp:176-197): atomics, and every launch reads the tune bin
+    // ONCE -- tables, row mask and kernel parameter must describe the same bin (impl.hpp:20 snapshots it per block).
+    std::atomic<int> decimate{0};
+    std::atomic<int> tunebin{kHalfFft / 4};
+    std::atomic<bool> rand_on{false};
+    std::atomic<bool> sideband{false};
     bool on = false;
     int latched_decimate = 0;     // worker prologue latches these at TurnOn (impl.hpp:3-6)
     bool latched_sideband = false;
@@ -353,7 +357,8 @@ int launch_wide_impl(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d
         CU(h, cudaMemcpy(h->d_twq, tq.data(), sizeof(float2) * tq.size(), cudaMemcpyHostToDevice));
         CU(h, cudaMemcpy(h->d_wctab, ct.data(), sizeof(float2) * ct.size(), cudaMemcpyHostToDevice));
     }
-    const long long key = ((long long)h->hw_version[d] << 20) | ((long long)d << 16) | (long long)h->tunebin;
+    const int tunebin = h->tunebin.load();   // one snapshot per launch
+    const long long key = ((long long)h->hw_version[d] << 20) | ((long long)d << 16) | (long long)tunebin;
     r2iq_cuda_s::WideSet ws;
     auto it = h->wide_tables.find(key);
     if (it != h->wide_tables.end()) ws = it->second;
@@ -368,7 +373,7 @@ int launch_wide_impl(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d
         }
         std::vector<float2> g(HF);
         for (int k = 0; k < HF; k++) {
-            const int s = k - h->tunebin;
+            const int s = k - tunebin;
             if (s >= -M / 2 && s < M / 2) {
                 const std::complex<float> hh = h->hw[d][(s + HF) % HF];
                 g[k] = make_float2(0.5f * hh.real(), 0.5f * hh.imag());
@@ -394,7 +399,7 @@ int launch_wide_impl(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d
     p.ctab = h->d_wctab;
     p.g = ws.g;
     p.tw_sub = ws.tw_sub;
-    p.tunebin = h->tunebin;
+    p.tunebin = tunebin;
     p.rand_mul = h->rand_on ? 0xFFFEu : 0u;
     p.imag_sign = h->latched_sideband ? -1.0f : 1.0f;
     p.work_counter = h->next_counter();
@@ -414,7 +419,9 @@ int launch(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d_out, cuda
     }
     TableSet ts;
     const int d = h->latched_decimate;
-    int rc = get_tables(h, d, h->tunebin, &ts);
+    const int tunebin = h->tunebin.load();   // one snapshot per launch: a retune from the application thread between the
+                                             // table lookup and the parameter block would pair tables with another bin
+    int rc = get_tables(h, d, tunebin, &ts);
     if (rc != R2IQ_OK) return rc;
     FusedParams p;
     p.in_words = (const uint32_t*)d_in;
@@ -427,7 +434,7 @@ int launch(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d_out, cuda
     p.gq = ts.gq;
     p.tw_inv = ts.tw_inv;
     p.tw_aux = ts.tw_aux;
-    p.tunebin = h->tunebin;
+    p.tunebin = tunebin;
     p.band_lo = ts.band_lo;
     p.band_hi = ts.band_hi;
     p.row_mask = ts.row_mask;
@@ -663,15 +670,15 @@ int r2iq_cuda_set_decimate(r2iq_cuda_t h, int d) {
     h->decimate = d;
     return R2IQ_OK;
 }
-int r2iq_cuda_get_decimate(r2iq_cuda_t h) { return h ? h->decimate : R2IQ_E_INVALID; }
-int r2iq_cuda_get_ratio(r2iq_cuda_t h) { return h ? (1 << h->decimate) : R2IQ_E_INVALID; }
+int r2iq_cuda_get_decimate(r2iq_cuda_t h) { return h ? h->decimate.load() : R2IQ_E_INVALID; }
+int r2iq_cuda_get_ratio(r2iq_cuda_t h) { return h ? (1 << h->decimate.load()) : R2IQ_E_INVALID; }
 
 float r2iq_cuda_set_freq_offset(r2iq_cuda_t h, float offset) {
     if (!h) return 0.f;
     // float arithmetic and truncation exactly as the reference (Core/fft_mt_r2iq.cpp:104-106)
     // float arithmetic and truncation of Core/fft_mt_r2iq.cpp:104-106 with this operator's halfFft
     int tb = int(offset * h->half / 4) * 4;
-    const float ret = (((float)tb / h->half) - offset) * (float)(1 << h->decimate);
+    const float ret = (((float)tb / h->half) - offset) * (float)(1 << h->decimate.load());
     // The reference stores whatever comes out; bins outside [0, halfFft) would index out of
     // bounds there (offset is documented as [0,1)), so clamp instead of reading garbage.
     if (tb < 0) tb = 0;
@@ -688,20 +695,20 @@ int r2iq_cuda_set_tunebin(r2iq_cuda_t h, int tunebin) {
     h->tunebin = tunebin;
     return R2IQ_OK;
 }
-int r2iq_cuda_get_tunebin(r2iq_cuda_t h) { return h ? h->tunebin : R2IQ_E_INVALID; }
+int r2iq_cuda_get_tunebin(r2iq_cuda_t h) { return h ? h->tunebin.load() : R2IQ_E_INVALID; }
 
 int r2iq_cuda_set_rand(r2iq_cuda_t h, int on) {
     if (!h) return fail(R2IQ_E_INVALID, "null handle");
     h->rand_on = on != 0;
     return R2IQ_OK;
 }
-int r2iq_cuda_get_rand(r2iq_cuda_t h) { return h ? (int)h->rand_on : R2IQ_E_INVALID; }
+int r2iq_cuda_get_rand(r2iq_cuda_t h) { return h ? (int)h->rand_on.load() : R2IQ_E_INVALID; }
 int r2iq_cuda_set_sideband(r2iq_cuda_t h, int lsb) {
     if (!h) return fail(R2IQ_E_INVALID, "null handle");
     h->sideband = lsb != 0;
     return R2IQ_OK;
 }
-int r2iq_cuda_get_sideband(r2iq_cuda_t h) { return h ? (int)h->sideband : R2IQ_E_INVALID; }
+int r2iq_cuda_get_sideband(r2iq_cuda_t h) { return h ? (int)h->sideband.load() : R2IQ_E_INVALID; }
 
 float r2iq_cuda_set_fine_tune(r2iq_cuda_t h, float fc) {
     if (!h || h->poisoned) return 0.f;
@@ -730,8 +737,8 @@ int r2iq_cuda_turn_on(r2iq_cuda_t h) {
     int rc = check_handle(h);
     if (rc) return rc;
     std::lock_guard<std::mutex> lk(h->mu);
-    h->latched_decimate = h->decimate;
-    h->latched_sideband = h->sideband;
+    h->latched_decimate = h->decimate.load();
+    h->latched_sideband = h->sideband.load();
     memset(h->carry, 0, sizeof(int16_t) * h->half);
     h->carry_valid = false;
     h->on = true;

@@ -149,6 +149,7 @@ __global__ void __launch_bounds__(kDualThreads, kStage == 1 ? 2 : 3) r2iq_dual_d
     constexpr bool kTma = kStage != 0;
     constexpr bool kDyn = (kVar & 1) != 0;
     constexpr bool kFree = (kVar & 2) != 0;
+    constexpr bool kShfl = (kVar & 16) != 0;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
@@ -248,11 +249,38 @@ __global__ void __launch_bounds__(kDualThreads, kStage == 1 ? 2 : 3) r2iq_dual_d
         dit2<32, false>(v);                       // v[k1] = Z[32*k1 + lane]
 
         // ---- real-FFT split + tune rotation + filter, in place ---------------------------------
+        c2 t[32];
+        if constexpr (kShfl) {
+            // Variant bit 4: the mirror bin Z[1024-k] comes by warp shuffle instead of a shared-memory round trip.
+            // For k = 32*k1 + lane it sits in lane (32 - lane) & 31, register 31 - k1 (lane 0: register (32 - k1) & 31,
+            // its own), so each lane SENDS v[31-k1] (lane 0: v[(32-k1)&31]): 4 SHFL.32 per bin pair (one wavefront each)
+            // where the staged exchange costs 2 STS.64 + 2 LDS.64 (two wavefronts each).  Rows are walked from both
+            // ends (k1 = 0, 31, 1, 30, ...) so that v[] dies as fast as t[] fills.
+            const int src = (32 - lane) & 31;
+            const bool l0 = lane == 0;
+#pragma unroll
+            for (int i = 0; i < 32; i++) {
+                const int k1 = (i & 1) ? 31 - (i >> 1) : (i >> 1);
+                const c2 a = v[k1];
+                c2 snd;
+                snd.re = l0 ? v[(32 - k1) & 31].re : v[31 - k1].re;
+                snd.im = l0 ? v[(32 - k1) & 31].im : v[31 - k1].im;
+                c2 b;
+                b.re = __shfl_sync(0xffffffffu, snd.re, src);
+                b.im = __shfl_sync(0xffffffffu, snd.im, src);
+                const float2 P = __ldg(gp + 32 * k1);
+                const float2 Q = __ldg(gq + 32 * k1);
+                c2 y;
+                y.re = fma2(bc(Q.y), b.im, fma2(bc(Q.x), b.re, fma2(bc(-P.y), a.im, mul2(bc(P.x), a.re))));
+                y.im = fma2(bc(Q.y), b.re, fma2(bc(-Q.x), b.im, fma2(bc(P.y), a.re, mul2(bc(P.x), a.im))));
+                t[brev5(k1)] = y;
+            }
+            PHASE_SYNC();   // pacing only (instruction-cache sharing between the warps of the CTA)
+        } else {
 #pragma unroll
         for (int k1 = 0; k1 < 32; k1++)
             sts2(S, 32 * k1 + lane, v[k1]);
         PHASE_SYNC();
-        c2 t[32];
 #pragma unroll
         for (int k1 = 0; k1 < 32; k1++) {
             const c2 a = v[k1];
@@ -265,6 +293,7 @@ __global__ void __launch_bounds__(kDualThreads, kStage == 1 ? 2 : 3) r2iq_dual_d
             t[brev5(k1)] = y;                     // bit-reversed placement for the backward pass
         }
         __syncwarp();
+        }
 
         // ---- backward 1024-point transform; lane l is residue (l - tunebin) mod 32 ---------------
         dit2<32, true>(t);
@@ -324,6 +353,8 @@ cudaError_t setup_dual_d0_kernels() {
     if ((e = setup_dual_one<1, 3>()) != cudaSuccess) return e;
     if ((e = setup_dual_one<1, 8>()) != cudaSuccess) return e;
     if ((e = setup_dual_one<1, 9>()) != cudaSuccess) return e;
+    if ((e = setup_dual_one<1, 17>()) != cudaSuccess) return e;
+    if ((e = setup_dual_one<1, 25>()) != cudaSuccess) return e;
     if ((e = setup_dual_one<2, 0>()) != cudaSuccess) return e;
     if ((e = setup_dual_one<2, 1>()) != cudaSuccess) return e;
     if ((e = setup_dual_one<2, 2>()) != cudaSuccess) return e;
@@ -370,6 +401,8 @@ cudaError_t launch_dual_d0(const FusedParams& p, int sm_count, cudaStream_t stre
     switch (kernel_variant()) {   // bit 3: inter-pass twiddles from the packed power recurrence
         case 8: return launch_dual_one<1, 8>(p, sm_count, stream);
         case 9: return launch_dual_one<1, 9>(p, sm_count, stream);
+        case 17: return launch_dual_one<1, 17>(p, sm_count, stream);   // bit 4: mirror bins by warp shuffle
+        case 25: return launch_dual_one<1, 25>(p, sm_count, stream);
         default: break;
     }
     if (kernel_variant() & 4) return launch_dual_var<2>(p, sm_count, stream);   // bit 2: input lands in the tile, 12 warps per SM

@@ -24,6 +24,10 @@ VARIANTS = {"dispatch": 0, "def": 1, "avx": 2, "avx2": 3, "avx512": 4}
 _libs: dict[int, "RefLib"] = {}
 
 
+# RadioHandlerClass-level drop-in check (oracle/ref_radio_driver.cpp), run by tests/test_host_adapter.py on the GPU
+RADIO_DROPIN = os.path.join(REF_DIR, "ref_radio_dropin")
+
+
 def lib_path(fftn: int) -> str:
     return os.path.join(REF_DIR, f"libref_r2iq_{fftn}.so")
 
@@ -31,7 +35,7 @@ def lib_path(fftn: int) -> str:
 def build(force: bool = False) -> bool:
     """Run ``make ref`` when the reference tree is present (this container).  On the GPU box the
     prebuilt libraries travel with the snapshot and /root/reference does not exist."""
-    have = all(os.path.exists(lib_path(n)) for n in (2048, 8192)) and mixer_available()
+    have = all(os.path.exists(lib_path(n)) for n in (2048, 8192)) and mixer_available() and os.path.exists(RADIO_DROPIN)
     if os.path.isdir(os.path.join(REFERENCE_ROOT, "Core")) and (force or not have):
         subprocess.run(["make", "-C", _HERE, "ref"], check=True, stdout=subprocess.DEVNULL)
         have = True

@@ -27,7 +27,7 @@ static void make_block(std::vector<int16_t>& v, long first_sample) {
 // `prebuilt` (optional): 16 pre-generated blocks cycled by memcpy, like fx3handler_benchmark
 // (unittest/benchmark_test.cpp:78-107), so that the producer is not the bottleneck of a throughput check.
 static std::vector<float> stream(cuda_r2iq& op, ringbuffer<int16_t>& in, ringbuffer<float>& out, int d, int n_blocks,
-                                 bool retune, const std::vector<int16_t>* prebuilt = nullptr) {
+                                 bool retune, const std::vector<int16_t>* prebuilt = nullptr, bool hammer = false) {
     op.setDecimate(d);
     op.TurnOn();
     CHECK(op.IsOn());
@@ -50,7 +50,8 @@ static std::vector<float> stream(cuda_r2iq& op, ringbuffer<int16_t>& in, ringbuf
             op.setFreqOffset(f / 32e6f);
             f += 377e3f;
             if (f > 15e6f) f = 1e3f;
-            std::this_thread::sleep_for(std::chrono::milliseconds(2));
+            if (hammer) std::this_thread::yield();   // retune as fast as the thread can: any launch that reads the tune
+            else std::this_thread::sleep_for(std::chrono::milliseconds(2));   // bin twice would pair tables with another bin
         }
     });
     const int n_slots = n_blocks >> d;
@@ -128,6 +129,15 @@ int main() {
         for (float v : got) finite = finite && std::isfinite(v);
         CHECK(finite);
         printf("retune-while-streaming: %zu complex, all finite\n", got.size() / 2);
+        for (int d : {0, 2, 5}) {   // the same with a retune storm (regression: tables and kernel parameter from two different bins)
+            std::vector<float> g2 = stream(op, in, out, d, 512, true, nullptr, true);
+            bool fin = true;
+            double e = 0;
+            for (float v : g2) { fin = fin && std::isfinite(v); e += (double)v * v; }
+            CHECK(fin);
+            CHECK(e > 0 && e < 1e6);
+            printf("retune storm d=%d: %zu complex, finite=%d energy=%.3g\n", d, g2.size() / 2, (int)fin, e);
+        }
         op.setFreqOffset(0.25f);
     }
     for (int cycle = 0; cycle < 6; cycle++) {   // start/stop cycles over the rates, stopping mid-stream

@@ -40,3 +40,21 @@ def test_cuda_r2iq_adapter_streams_through_rings():
                    extra=[os.path.join(HOST, "cuda_r2iq.cpp"), "-L", lib_dir, "-lr2iq_cuda", f"-Wl,-rpath,{lib_dir}"])
     r = subprocess.run([exe], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "ALL PASS" in r.stdout, r.stdout + r.stderr
+
+
+@pytest.mark.gpu
+def test_radiohandler_drop_in_matches_reference_operator():
+    """the reference's UNMODIFIED RadioHandlerClass (Init/UptRand/UpdatemodeRF/TuneLO/Start/Stop, its
+    radio models and its CPU fine-tune mixer, compiled in place into oracle/_ref/ref_radio_dropin) is run with its own
+    fft_mt_r2iq, then with cuda_r2iq passed as the third Init argument (Core/RadioHandler.h:34), on the same mock-USB
+    capture; the IQ reaching the application callback must agree within rel-L2 1e-5 / 1e-4 of full scale, and the
+    device-side mixer must equal the CPU mixer bit for bit (checked inside the binary, FFTN 8192 as shipped)."""
+    from oracle import ref_lib
+    if not os.path.exists(ref_lib.RADIO_DROPIN):
+        pytest.skip("oracle/_ref/ref_radio_dropin not built (needs /root/reference at build time)")
+    capi.load()
+    r = subprocess.run([ref_lib.RADIO_DROPIN], capture_output=True, text=True, timeout=600)
+    lines = [l for l in r.stdout.splitlines() if l.startswith(("PASS", "FAIL", "ALL PASS"))]
+    print("\n".join(lines))
+    assert r.returncode == 0 and "ALL PASS" in r.stdout, "\n".join(lines) + r.stderr[-2000:]
+    assert sum(l.startswith("PASS") for l in lines) == 4
