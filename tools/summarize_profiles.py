@@ -37,6 +37,13 @@ with open(os.path.join(dst, f"{tag}_launch_shares.txt"), "w") as f:
     f.write(f"# share of summed kernel time over the profiled command ({len(out) - 1} launches, {total / 1000:.2f} ms)\n")
     for s, k, v in share[:25]:
         f.write(f"{100 * s:6.2f}%  {v / 1000:9.3f} ms  {k}\n")
+    # the timed step of bench.py is the FFTN 2048 sweep alone (the FFTN 8192 sweep is a separate section of the line)
+    head = {k: v for k, v in tot.items() if "wide" not in k}
+    ht = sum(head.values())
+    if head and ht < total:
+        f.write(f"# shares within the headline step (FFTN 2048 kernels only, {ht / 1000:.2f} ms)\n")
+        for v, k in sorted(((v, k) for k, v in head.items()), reverse=True):
+            f.write(f"{100 * v / ht:6.2f}%  {v / 1000:9.3f} ms  {k}\n")
 
 # ---- per-kernel metrics from the full capture ------------------------------------------------------
 rep = os.path.join(src, f"{tag}_full.ncu-rep")
