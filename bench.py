@@ -224,7 +224,7 @@ def run_ours(args, rank: int, local_rank: int, world: int):
     import numpy as np
     import torch
     import torch.distributed as dist
-    from extio_sddc_b200 import CudaR2IQ, PinnedBuffer
+    from extio_sddc_b200 import CudaR2IQ, PinnedBuffer, capi
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the r2iq backend has no CPU path (use --impl reference for the CPU arm)")
@@ -311,8 +311,8 @@ def run_ours(args, rank: int, local_rank: int, world: int):
     # ---- e2e: same sweep through the host-buffer C-ABI call, pinned host memory -------------------
     e2e = None
     if not args.no_e2e:
-        hin = PinnedBuffer(samples_per_launch, np.int16)
-        hout = PinnedBuffer(n_blocks * 32768, np.complex64)
+        hin = PinnedBuffer(samples_per_launch, np.int16, device=local_rank)
+        hout = PinnedBuffer(n_blocks * 32768, np.complex64, device=local_rank)
         torch.cuda.synchronize()
         hin.array[:] = x[1024:].cpu().numpy()
         eop = CudaR2IQ(device=local_rank, chunk_blocks=args.chunk_blocks)
@@ -332,7 +332,7 @@ def run_ours(args, rank: int, local_rank: int, world: int):
                 acc += float(y[0].real)                   # touch the result on the host
             return acc
 
-        houts = [PinnedBuffer(n_blocks * (32768 >> d), np.complex64) for d in DECIMS]
+        houts = [PinnedBuffer(n_blocks * (32768 >> d), np.complex64, device=local_rank) for d in DECIMS]
 
         def e2e_step_rates():
             # the same sweep through r2iq_cuda_process_rates: the capture crosses PCIe once (the reference's
@@ -367,6 +367,7 @@ def run_ours(args, rank: int, local_rank: int, world: int):
         e2e = timed(e2e_step_rates)
         e2e["api"] = ("r2iq_cuda_process_rates (C ABI, pinned host buffers, chunked pipeline): one H2D of the capture, "
                       "six decimations on the device, every IQ stream copied back")
+        e2e["host_numa_node"] = int(capi.load().r2iq_cuda_device_numa_node(local_rank))   # rank 0's; -1 = default placement
         e2e["per_operator"] = timed(e2e_step_per_operator)
         e2e["per_operator"]["api"] = ("r2iq_cuda_process once per decimation (one operator per rate): the capture is "
                                       "copied to the device six times")

@@ -71,6 +71,8 @@ _SIGNATURES = {
     "r2iq_cuda_set_fine_tune": (_F, [_VP, _F]),
     "r2iq_cuda_sync": (_I, [_VP]),
     "r2iq_cuda_host_alloc": (_VP, [ctypes.c_size_t]),
+    "r2iq_cuda_host_alloc_on": (_VP, [ctypes.c_size_t, _I]),
+    "r2iq_cuda_device_numa_node": (_I, [_I]),
     "r2iq_cuda_host_free": (_I, [_VP]),
     "r2iq_cuda_convert": (_I, [_VP, _VP, _L, _I, _VP]),
     "r2iq_cuda_get_stats": (_I, [_VP, ctypes.POINTER(Stats)]),

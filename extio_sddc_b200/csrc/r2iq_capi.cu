@@ -14,6 +14,8 @@
 #include <cstring>
 #include <map>
 #include <atomic>
+#include <sys/syscall.h>
+#include <unistd.h>
 #include <mutex>
 #include <new>
 #include <vector>
@@ -955,15 +957,58 @@ int r2iq_cuda_sync(r2iq_cuda_t h) {
     return R2IQ_OK;
 }
 
-void* r2iq_cuda_host_alloc(size_t bytes) {
+// ---- NUMA placement of page-locked buffers ---------------------------------------------------------------------
+// A pinned buffer is what the GPU's copy engines read and write over PCIe.  On a two-socket 8-GPU box a buffer that
+// sits on the other socket makes every copy cross the socket interconnect, and with all ranks allocating from the
+// socket their launcher happened to start on, the copies of all GPUs share one memory controller set.  The pages
+// are therefore placed on the NUMA node the GPU's PCIe root port belongs to (sysfs numa_node of its bus id) by
+// setting the calling thread's memory policy to "preferred: that node" around cudaMallocHost (raw set_mempolicy
+// syscalls: libnuma is not assumed).  Every failure (no sysfs entry, node -1, syscall filtered) degrades to the
+// default first-touch placement.  R2IQ_NUMA=0 switches it off (A/B measurement).
+namespace {
+int device_numa_node_impl(int device) {
+    if (const char* v = getenv("R2IQ_NUMA")) {
+        if (atoi(v) == 0) return -1;
+    }
+    if (device < 0 && cudaGetDevice(&device) != cudaSuccess) return -1;
+    char bus[32] = {0};
+    if (cudaDeviceGetPCIBusId(bus, (int)sizeof(bus), device) != cudaSuccess) return -1;
+    for (char* c = bus; *c; ++c)
+        if (*c >= 'A' && *c <= 'Z') *c = (char)(*c - 'A' + 'a');
+    char path[128];
+    snprintf(path, sizeof(path), "/sys/bus/pci/devices/%s/numa_node", bus);
+    FILE* f = fopen(path, "r");
+    if (!f) return -1;
+    int node = -1;
+    if (fscanf(f, "%d", &node) != 1) node = -1;
+    fclose(f);
+    return (node >= 0 && node < 1024) ? node : -1;
+}
+constexpr int kMpolDefault = 0, kMpolPreferred = 1;
+constexpr unsigned long kMaskWords = 1024 / (8 * sizeof(unsigned long));
+}  // namespace
+
+int r2iq_cuda_device_numa_node(int device) { return device_numa_node_impl(device); }
+
+void* r2iq_cuda_host_alloc_on(size_t bytes, int device) {
+    const int node = device_numa_node_impl(device);
+    int old_mode = kMpolDefault;
+    unsigned long old_mask[kMaskWords] = {0}, mask[kMaskWords] = {0};
+    bool policy_set = false;
+    if (node >= 0 && syscall(SYS_get_mempolicy, &old_mode, old_mask, 1024UL, nullptr, 0UL) == 0) {
+        mask[node / (8 * sizeof(unsigned long))] = 1UL << (node % (8 * sizeof(unsigned long)));
+        policy_set = syscall(SYS_set_mempolicy, kMpolPreferred, mask, 1024UL) == 0;
+    }
     void* p = nullptr;
     cudaError_t e = cudaMallocHost(&p, bytes ? bytes : 1);
+    if (policy_set) syscall(SYS_set_mempolicy, old_mode, old_mode == kMpolDefault ? nullptr : old_mask, old_mode == kMpolDefault ? 0UL : 1024UL);
     if (e != cudaSuccess) {
         fail(R2IQ_E_NOMEM, "cudaMallocHost(%zu): %s", bytes, cudaGetErrorString(e));
         return nullptr;
     }
     return p;
 }
+void* r2iq_cuda_host_alloc(size_t bytes) { return r2iq_cuda_host_alloc_on(bytes, -1); }
 int r2iq_cuda_host_free(void* p) {
     if (!p) return R2IQ_OK;
     cudaError_t e = cudaFreeHost(p);

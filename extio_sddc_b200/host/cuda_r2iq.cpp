@@ -45,8 +45,8 @@ void cuda_r2iq::Init(float gain, ringbuffer<int16_t>* input, ringbuffer<float>* 
         return;
     }
     const size_t max_blocks = (size_t)slots_per_batch_ << (NDECIDX - 1);
-    if (!stage_in_) stage_in_ = (int16_t*)r2iq_cuda_host_alloc(sizeof(int16_t) * max_blocks * kBlock);
-    if (!stage_out_) stage_out_ = (float*)r2iq_cuda_host_alloc(sizeof(float) * 2 * (size_t)slots_per_batch_ * kSlotComplex);
+    if (!stage_in_) stage_in_ = (int16_t*)r2iq_cuda_host_alloc_on(sizeof(int16_t) * max_blocks * kBlock, device_);
+    if (!stage_out_) stage_out_ = (float*)r2iq_cuda_host_alloc_on(sizeof(float) * 2 * (size_t)slots_per_batch_ * kSlotComplex, device_);
     if (!stage_in_ || !stage_out_) error_ = r2iq_cuda_last_error();
 }
 

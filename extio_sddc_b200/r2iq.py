@@ -241,11 +241,12 @@ class PinnedBuffer:
     """Page-locked host buffer (r2iq_cuda_host_alloc) exposed as a numpy array, so the H2D/D2H
     copies inside process() run asynchronously and overlap with the kernels."""
 
-    def __init__(self, n: int, dtype):
+    def __init__(self, n: int, dtype, device: int = -1):
+        # device: the GPU whose copy engines will use the buffer; its pages go to that GPU's NUMA node
         self._lib = capi.load()
         dt = np.dtype(dtype)
         self.nbytes = int(n) * dt.itemsize
-        self._ptr = self._lib.r2iq_cuda_host_alloc(self.nbytes)
+        self._ptr = self._lib.r2iq_cuda_host_alloc_on(self.nbytes, int(device))
         if not self._ptr:
             raise capi.R2iqError(capi.E_NOMEM, capi.last_error())
         buf = (ctypes.c_char * self.nbytes).from_address(self._ptr)

@@ -169,6 +169,13 @@ R2IQ_API int r2iq_cuda_sync(r2iq_cuda_t h);
 
 /* Page-locked host buffers for ring slots / captures (replaces `new T[]` in Core/dsp/ringbuffer.h:166). */
 R2IQ_API void* r2iq_cuda_host_alloc(size_t bytes);
+/* The same, placed on the NUMA node of `device`'s PCIe root port (device < 0: the current device), so that the
+ * copy engines of each GPU of a multi-socket box read and write socket-local memory -- the ingest side of the path
+ * (Core/arch/linux/FX3handler.cpp:93-147 copies every USB frame into such a slot).  Falls back to the default
+ * placement when the node is unknown; r2iq_cuda_host_alloc(bytes) == r2iq_cuda_host_alloc_on(bytes, -1). */
+R2IQ_API void* r2iq_cuda_host_alloc_on(size_t bytes, int device);
+/* NUMA node of a device's PCIe root port, -1 when unknown or switched off (R2IQ_NUMA=0). */
+R2IQ_API int r2iq_cuda_device_numa_node(int device);
 R2IQ_API int r2iq_cuda_host_free(void* p);
 
 /* convert_float<rand>  (Core/fft_mt_r2iq.h:36-51) on its own: n int16 host samples (n even) ->

@@ -108,3 +108,17 @@ def test_product_never_imports_oracle():
                     text = f.read()
                 assert "oracle" not in text.replace("r2iq_oracle", "oracle") or "import oracle" not in text, fn
                 assert "from oracle" not in text and "import oracle" not in text and "oracle/" not in text, fn
+
+
+def test_numa_helpers_degrade_without_device(monkeypatch):
+    """r2iq_cuda_device_numa_node / r2iq_cuda_host_alloc_on never guess: no device (or R2IQ_NUMA=0) -> node -1, and a
+    failed page-locked allocation is an error with a message, not a pageable buffer."""
+    import torch
+    lib = capi.load()
+    monkeypatch.setenv("R2IQ_NUMA", "0")
+    assert lib.r2iq_cuda_device_numa_node(0) == -1
+    monkeypatch.delenv("R2IQ_NUMA")
+    if not torch.cuda.is_available():
+        assert lib.r2iq_cuda_device_numa_node(0) == -1
+        assert not lib.r2iq_cuda_host_alloc_on(4096, 0)
+        assert "cudaMallocHost" in capi.last_error()
