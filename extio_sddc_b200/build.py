@@ -58,5 +58,23 @@ def build(force: bool = False, verbose: bool = False) -> str:
     return LIB_PATH
 
 
+HOST = os.path.join(HERE, "host")
+BIN_DIR = os.path.join(HERE, "bin")
+REPLAY_PATH = os.path.join(BIN_DIR, "r2iq_replay")
+
+
+def build_tools(force: bool = False) -> str:
+    """Host-side tools over the C ABI (g++ only): bin/r2iq_replay, the capture-file replayer (host/r2iq_replay.cpp)."""
+    srcs = [os.path.join(HOST, "r2iq_replay.cpp"), os.path.join(HOST, "wav_capture.cpp")]
+    deps = srcs + [os.path.join(HOST, "wav_capture.h"), LIB_PATH]
+    if not force and os.path.exists(REPLAY_PATH) and all(os.path.getmtime(d) <= os.path.getmtime(REPLAY_PATH) for d in deps):
+        return REPLAY_PATH
+    os.makedirs(BIN_DIR, exist_ok=True)
+    subprocess.run(["g++", "-std=c++17", "-O2", "-I", os.path.join(HERE, "..", "include"), "-I", HOST, *srcs,
+                    "-L", LIB_DIR, "-lr2iq_cuda", "-Wl,-rpath,$ORIGIN/../lib", "-o", REPLAY_PATH], check=True)
+    return REPLAY_PATH
+
+
 if __name__ == "__main__":
     print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    print(build_tools(force="--force" in sys.argv))

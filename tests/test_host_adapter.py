@@ -58,3 +58,85 @@ def test_radiohandler_drop_in_matches_reference_operator():
     print("\n".join(lines))
     assert r.returncode == 0 and "ALL PASS" in r.stdout, "\n".join(lines) + r.stderr[-2000:]
     assert sum(l.startswith("PASS") for l in lines) == 4
+
+
+# ---- capture file format: libsddc/wavehdr.h + wavewrite.c ---------------------------------------
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+WAV_SRC = os.path.join(HOST, "wav_capture.cpp")
+
+
+def test_wav_capture_matches_reference_writer():
+    """Reader/writer of the reference's RIFF/auxi capture format against files written by libsddc/wavewrite.c itself
+    (tests/golden/ref_capture*.wav): fields recovered, re-packed header byte-identical, round trip, unfinalised file."""
+    exe = _compile(os.path.join(ROOT, "tests", "host", "test_wav_capture.cpp"), os.path.join(OUT, "test_wav_capture"), extra=[WAV_SRC])
+    r = subprocess.run([exe, GOLDEN, OUT], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0 and "ALL PASS" in r.stdout, r.stdout + r.stderr
+
+
+def _build_replay():
+    capi.load()
+    lib_dir = os.path.dirname(capi.LIB_PATH)
+    return _compile(os.path.join(HOST, "r2iq_replay.cpp"), os.path.join(OUT, "r2iq_replay"),
+                    extra=[WAV_SRC, "-L", lib_dir, "-lr2iq_cuda", f"-Wl,-rpath,{lib_dir}"])
+
+
+def _write_capture(path, samples):
+    """A capture as the reference records it: the 120-byte header the reference's writer produced (golden file) with
+    the two size fields set for this payload, then raw little-endian int16."""
+    import struct
+    hdr = bytearray(open(os.path.join(GOLDEN, "ref_capture.wav"), "rb").read(120))
+    nbytes = samples.size * 2
+    hdr[4:8] = struct.pack("<I", 112 + nbytes)
+    hdr[116:120] = struct.pack("<I", nbytes)
+    with open(path, "wb") as f:
+        f.write(hdr)
+        f.write(samples.astype("<i2").tobytes())
+
+
+def test_replay_tool_has_no_cpu_path():
+    import numpy as np
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present: covered by test_replay_capture_matches_oracle")
+    exe = _build_replay()
+    cap = os.path.join(OUT, "replay_nogpu.wav")
+    _write_capture(cap, np.zeros(65536, dtype=np.int16))
+    r = subprocess.run([exe, cap, os.path.join(OUT, "replay_nogpu_out.wav"), "--decimate", "0"], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 1 and "no CPU path" in r.stderr, r.stdout + r.stderr
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("d,tune_hz,tunebin,rand", [(0, None, 256, False), (3, 9.0e6, 144, True), (5, 9.0e6, 144, True)])
+def test_replay_capture_matches_oracle(d, tune_hz, tunebin, rand):
+    """A recorded 128 Msps capture (reference header, 20 transfers + a partial one that must be dropped) replayed in
+    batches through r2iq_replay equals one oracle pass over the same transfers; the IQ file carries the rate and
+    tuned frequency in the reference's own container."""
+    import struct
+    import numpy as np
+    from oracle import r2iq_oracle as orc
+    exe = _build_replay()
+    gain = orc.RX888MK2_GAINFACTOR
+    nb = 20
+    x = orc.rx888_blocks(nb, d, tunebin, randomized=rand, seed=77 + d).reshape(-1)
+    cap = os.path.join(OUT, f"replay_d{d}.wav")
+    out = os.path.join(OUT, f"replay_d{d}_iq.wav")
+    _write_capture(cap, np.concatenate([x, np.arange(1000, dtype=np.int16)]))
+    cmd = [exe, cap, out, "--decimate", str(d), "--batch-blocks", "8"] + (["--rand"] if rand else [])
+    if tune_hz is not None:
+        cmd += ["--tune-hz", repr(tune_hz)]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    raw = open(out, "rb").read()
+    assert raw[:4] == b"RIFF" and raw[8:12] == b"WAVE" and raw[36:40] == b"auxi" and raw[112:116] == b"data"
+    tag, ch, rate = struct.unpack("<HHI", raw[20:28])
+    bits, = struct.unpack("<H", raw[34:36])
+    center, adrate = struct.unpack("<II", raw[76:84])
+    nbytes, = struct.unpack("<I", raw[116:120])
+    assert (tag, ch, bits) == (3, 2, 32) and rate == 128000000 // (2 << d) and adrate == 128000000
+    assert center == (int(tune_hz) if tune_hz else 0)
+    got = np.frombuffer(raw[120:120 + nbytes], dtype=np.complex64)
+    ref = orc.r2iq(x.reshape(nb, 65536), d, tunebin, gain=gain, rand=rand)
+    assert got.shape == ref.shape == (nb * (32768 >> d),)
+    err = orc.rel_l2(got, ref)
+    mx = float(np.abs(got - ref).max()) / orc.full_scale(gain)
+    assert err <= 1e-5 and mx <= 1e-4, (err, mx)   # north-star tolerance
