@@ -519,3 +519,37 @@ def test_fftn8192_full_size_properties(d):
     check(whole[b0 * opb:(b0 + 2) * opb].cpu().numpy(), ref, GAIN, ("fftn8192 full-size window", d))
     r.TurnOff()
     r.close()
+
+
+@pytest.mark.parametrize("fftn", [2048, 8192])
+def test_kernels_write_exactly_their_output_range(fftn):
+    """compute-sanitizer is closed on this GPU pool, so the out-of-bounds-write check is our own: the IQ buffer sits
+    between two guard regions filled with a NaN bit pattern, the input buffer is exactly halo + blocks long, and for
+    every decimation, edge tune bins, odd block counts (odd frame totals: the second frame of the last pair is
+    computed but must never be stored) every guard word must survive and every output sample must be written."""
+    import torch
+    dev = torch.device("cuda:0")
+    half = fftn // 2
+    guard = 1 << 16                                           # complex samples either side
+    r = CudaR2IQ(fftn=fftn)
+    r.Init(GAIN)
+    pattern = torch.tensor([0x7FC0DEAD], dtype=torch.int32, device=dev)
+    stream = torch.cuda.current_stream().cuda_stream
+    for nb in (1, 3):
+        x = orc.rx888_blocks(nb, 0, half // 4, randomized=True, seed=nb)
+        buf = torch.zeros(half + x.shape[0], dtype=torch.int16, device=dev)
+        buf[half:] = torch.from_numpy(x).to(dev)
+        for d in range(7):
+            n_out = nb * (32768 >> d)
+            for tb in (0, half // 4, half - 4):
+                raw = pattern.repeat(2 * (n_out + 2 * guard))  # int32 view of [guard | out | guard] complex64
+                out = raw[2 * guard: 2 * (guard + n_out)]
+                r.setDecimate(d); r.updateRand(True); r.setSideband(False); r.tunebin = tb
+                r.TurnOn()
+                r.process_device(buf.data_ptr(), nb, out.data_ptr(), stream)
+                torch.cuda.synchronize()
+                r.TurnOff()
+                assert bool((raw[: 2 * guard] == 0x7FC0DEAD).all()), (fftn, d, tb, nb, "write below the output range")
+                assert bool((raw[2 * (guard + n_out):] == 0x7FC0DEAD).all()), (fftn, d, tb, nb, "write above the output range")
+                assert not bool((out == 0x7FC0DEAD).any()), (fftn, d, tb, nb, "output sample never written")
+    r.close()
