@@ -15,6 +15,9 @@
 #include <map>
 #include <atomic>
 #include <sys/syscall.h>
+#if defined(__SSE2__)
+#include <emmintrin.h>
+#endif
 #include <unistd.h>
 #include <mutex>
 #include <new>
@@ -300,8 +303,28 @@ void nco_init(NcoState& s, float relative_freq) {
 }
 
 // Start phasors of the next n128 blocks of 128 samples into s.h_starts ([block][lane] (cos, sin)); advances the state.
+// This recurrence is inherently sequential (every step renormalises the previous one) and is what bounds the mixer
+// in bulk use: ~2.1 M steps per 8192-block launch at d = 0.  The four lanes are the reference's own SSE lanes
+// (Core/pffft/pf_mixer.cpp:791-856), so the x86 path runs them as one __m128 chain -- mulps/subps/addps/sqrtps/divps
+// are correctly rounded and never contracted, i.e. the same bits as the scalar form below.
 void nco_advance(NcoState& s, size_t n128) {
     s.h_starts.resize(n128 * 8);
+#if defined(__SSE2__)
+    const __m128 tc = _mm_set1_ps(s.tab[31][0]), ts = _mm_set1_ps(s.tab[31][1]);   // after 32 groups vals = table[31] * starts
+    __m128 cs = _mm_loadu_ps(s.cs), sn = _mm_loadu_ps(s.sn);
+    float* dst = s.h_starts.data();
+    for (size_t b = 0; b < n128; b++, dst += 8) {
+        _mm_storeu_ps(dst, _mm_unpacklo_ps(cs, sn));        // (c0, s0, c1, s1)
+        _mm_storeu_ps(dst + 4, _mm_unpackhi_ps(cs, sn));    // (c2, s2, c3, s3)
+        const __m128 cv = _mm_sub_ps(_mm_mul_ps(tc, cs), _mm_mul_ps(ts, sn));
+        const __m128 sv = _mm_add_ps(_mm_mul_ps(ts, cs), _mm_mul_ps(tc, sn));
+        const __m128 mag = _mm_sqrt_ps(_mm_add_ps(_mm_mul_ps(cv, cv), _mm_mul_ps(sv, sv)));
+        cs = _mm_div_ps(cv, mag);
+        sn = _mm_div_ps(sv, mag);
+    }
+    _mm_storeu_ps(s.cs, cs);
+    _mm_storeu_ps(s.sn, sn);
+#else
     const volatile float tc = s.tab[31][0], ts = s.tab[31][1];   // after 32 groups vals = table[31] * starts
     for (size_t b = 0; b < n128; b++) {
         for (int j = 0; j < 4; j++) {
@@ -316,12 +339,15 @@ void nco_advance(NcoState& s, size_t n128) {
             s.sn[j] = sv / mag;
         }
     }
+#endif
 }
 
-// Apply the fine-tune NCO to the n_out complex samples a launch just produced (same stream).
-int nco_stage(r2iq_cuda_t h, float* d_out, size_t n_out, float** d_starts, size_t* cap, cudaStream_t stream) {
+// Fine-tune NCO for the n_out complex samples of one launch: nco_prepare advances the phasor recurrence on the host
+// and uploads the start phasors of every 128-sample block (on the launch stream, BEFORE the kernel, so that a kernel
+// with the mixer in its store epilogue can read them); nco_stage is prepare + the stand-alone in-place pass for the
+// kernels that do not mix themselves.
+int nco_prepare(r2iq_cuda_t h, size_t n_out, float** d_starts, size_t* cap, cudaStream_t stream) {
     NcoState& s = h->nco;
-    if (!s.on || n_out == 0) return R2IQ_OK;
     if (n_out % 128) return fail(R2IQ_E_INVALID, "fine-tune mixer needs a multiple of 128 output samples per call");
     const size_t n128 = n_out / 128;
     if (*cap < n128) {
@@ -335,8 +361,27 @@ int nco_stage(r2iq_cuda_t h, float* d_out, size_t n_out, float** d_starts, size_
     nco_advance(s, n128);
     // pageable source: the call returns once the data sits in the driver's staging buffer, so h_starts may be reused
     CU(h, cudaMemcpyAsync(*d_starts, s.h_starts.data(), sizeof(float) * 8 * n128, cudaMemcpyHostToDevice, stream));
+    return R2IQ_OK;
+}
+int nco_stage(r2iq_cuda_t h, float* d_out, size_t n_out, float** d_starts, size_t* cap, cudaStream_t stream) {
+    NcoState& s = h->nco;
+    if (!s.on || n_out == 0) return R2IQ_OK;
+    int rc = nco_prepare(h, n_out, d_starts, cap, stream);
+    if (rc != R2IQ_OK) return rc;
     CU(h, launch_nco_mix(d_out, (long long)n_out, *d_starts, s.d_tab, stream));
     return R2IQ_OK;
+}
+// The default dual-frame kernels (d = 0..5, FFTN 2048) CAN mix in their store epilogue (R2IQ_NCO_FUSED=1; bit-identical,
+// tests/test_gpu_parity.py).  It is not the default: measured on B200 (tools/mixer_bench.py) the mixer is bounded by
+// the sequential start-phasor recurrence on the host, and the stand-alone pass lets the main kernel run while the host
+// is still computing it, whereas the fused kernel has to wait for the upload.
+bool nco_fusable(int d) {
+    if (d > 5 || getenv("R2IQ_VARIANT")) return false;
+    if (const char* g = getenv("R2IQ_KERNEL_GEN")) {
+        if (atoi(g) != 0) return false;
+    }
+    const char* f = getenv("R2IQ_NCO_FUSED");
+    return f && atoi(f) != 0;
 }
 
 // FFTN 8192: static twiddles once per handle, filter gains (and small-transform twiddles) per (d, tune bin).
@@ -443,10 +488,21 @@ int launch(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d_out, cuda
     p.rand_mul = h->rand_on ? 0xFFFEu : 0u;
     p.imag_sign = h->latched_sideband ? -1.0f : 1.0f;
     p.work_counter = h->next_counter();
+    p.nco_starts = nullptr;
+    p.nco_tab = nullptr;
+    const size_t n_out = (size_t)n_blocks * (size_t)((kTransferSamples / 2) >> d);
+    const bool fused_mix = h->nco.on && n_out > 0 && nco_fusable(d);
+    if (fused_mix) {
+        rc = nco_prepare(h, n_out, nco_starts, nco_cap, stream);
+        if (rc != R2IQ_OK) return rc;
+        p.nco_starts = (const float2*)*nco_starts;
+        p.nco_tab = (const float2*)h->nco.d_tab;
+    }
     CU(h, launch_fused(d, p, h->sm_count, stream));
     h->stats.kernel_launches++;
     h->stats.blocks_processed += (uint64_t)n_blocks;
-    return nco_stage(h, d_out, (size_t)n_blocks * (size_t)((kTransferSamples / 2) >> d), nco_starts, nco_cap, stream);
+    if (fused_mix) return R2IQ_OK;
+    return nco_stage(h, d_out, n_out, nco_starts, nco_cap, stream);
 }
 
 // Channelizer launch: per-d filter table in inverse-FFT bin order + the tune-bin list on the device.

@@ -150,6 +150,7 @@ __global__ void __launch_bounds__(kDualThreads, kStage == 1 ? 2 : 3) r2iq_dual_d
     constexpr bool kDyn = (kVar & 1) != 0;
     constexpr bool kFree = (kVar & 2) != 0;
     constexpr bool kShfl = (kVar & 16) != 0;
+    constexpr bool kMix = (kVar & kVarMix) != 0;    // fine-tune NCO in the store epilogue
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
@@ -328,8 +329,16 @@ __global__ void __launch_bounds__(kDualThreads, kStage == 1 ? 2 : 3) r2iq_dual_d
             float ar, br, ai, bi;
             upk(t[k1].re, ar, br);
             upk(t[k1].im, ai, bi);
-            if (!idle && idx >= oa.lo) p.out[oa.base + idx] = make_float2(ar, flip(ai, sgn));
-            if (!idle && ob.live && idx >= ob.lo) p.out[ob.base + idx] = make_float2(br, flip(bi, sgn));
+            if (!idle && idx >= oa.lo) {
+                float2 va = make_float2(ar, flip(ai, sgn));
+                if constexpr (kMix) va = nco_mix_sample(va, oa.base + idx, p.nco_starts, p.nco_tab);
+                p.out[oa.base + idx] = va;
+            }
+            if (!idle && ob.live && idx >= ob.lo) {
+                float2 vb = make_float2(br, flip(bi, sgn));
+                if constexpr (kMix) vb = nco_mix_sample(vb, ob.base + idx, p.nco_starts, p.nco_tab);
+                p.out[ob.base + idx] = vb;
+            }
         }
         work.advance();
         q = qn;
@@ -354,6 +363,7 @@ cudaError_t setup_dual_d0_kernels() {
     if ((e = setup_dual_one<1, 8>()) != cudaSuccess) return e;
     if ((e = setup_dual_one<1, 9>()) != cudaSuccess) return e;
     if ((e = setup_dual_one<1, 17>()) != cudaSuccess) return e;
+    if ((e = setup_dual_one<1, 1 | kVarMix>()) != cudaSuccess) return e;
     if ((e = setup_dual_one<1, 25>()) != cudaSuccess) return e;
     if ((e = setup_dual_one<2, 0>()) != cudaSuccess) return e;
     if ((e = setup_dual_one<2, 1>()) != cudaSuccess) return e;
@@ -398,6 +408,7 @@ static cudaError_t launch_dual_var(const FusedParams& p, int sm_count, cudaStrea
 
 cudaError_t launch_dual_d0(const FusedParams& p, int sm_count, cudaStream_t stream, bool tma) {
     if (!tma) return launch_dual_one<0, 0>(p, sm_count, stream);
+    if (p.nco_starts) return launch_dual_one<1, 1 | kVarMix>(p, sm_count, stream);   // default variant + fused mixer
     switch (kernel_variant()) {   // bit 3: inter-pass twiddles from the packed power recurrence
         case 8: return launch_dual_one<1, 8>(p, sm_count, stream);
         case 9: return launch_dual_one<1, 9>(p, sm_count, stream);

@@ -158,6 +158,7 @@ template <bool kTma, int kVar = 0>
 __global__ void __launch_bounds__(kDualThreads, kTma ? 2 : 3) r2iq_dual_d1_kernel(const FusedParams p) {
     constexpr bool kDyn = (kVar & 1) != 0;
     constexpr bool kFree = (kVar & 2) != 0;
+    constexpr bool kMix = (kVar & kVarMix) != 0;    // fine-tune NCO in the store epilogue
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
@@ -288,8 +289,16 @@ __global__ void __launch_bounds__(kDualThreads, kTma ? 2 : 3) r2iq_dual_d1_kerne
             float ar, br, ai, bi;
             upk(t[q4].re, ar, br);
             upk(t[q4].im, ai, bi);
-            if (!idle && idx >= oa.lo) p.out[oa.base + idx] = make_float2(ar, ai * p.imag_sign);
-            if (!idle && ob.live && idx >= ob.lo) p.out[ob.base + idx] = make_float2(br, bi * p.imag_sign);
+            if (!idle && idx >= oa.lo) {
+                float2 va = make_float2(ar, ai * p.imag_sign);
+                if constexpr (kMix) va = nco_mix_sample(va, oa.base + idx, p.nco_starts, p.nco_tab);
+                p.out[oa.base + idx] = va;
+            }
+            if (!idle && ob.live && idx >= ob.lo) {
+                float2 vb = make_float2(br, bi * p.imag_sign);
+                if constexpr (kMix) vb = nco_mix_sample(vb, ob.base + idx, p.nco_starts, p.nco_tab);
+                p.out[ob.base + idx] = vb;
+            }
         }
         work.advance();
         q = qn;
@@ -311,6 +320,7 @@ cudaError_t setup_dual_d1_kernels() {
     if ((e = setup_dual_one<true, 1>()) != cudaSuccess) return e;
     if ((e = setup_dual_one<true, 2>()) != cudaSuccess) return e;
     if ((e = setup_dual_one<true, 3>()) != cudaSuccess) return e;
+    if ((e = setup_dual_one<true, 1 | kVarMix>()) != cudaSuccess) return e;
     return setup_dual_one<false, 0>();
 }
 
@@ -340,6 +350,7 @@ static cudaError_t launch_dual_one(const FusedParams& p, int sm_count, cudaStrea
 
 cudaError_t launch_dual_d1(const FusedParams& p, int sm_count, cudaStream_t stream, bool tma) {
     if (!tma) return launch_dual_one<false, 0>(p, sm_count, stream);
+    if (p.nco_starts) return launch_dual_one<true, 1 | kVarMix>(p, sm_count, stream);   // default variant + fused mixer
     switch (kernel_variant() & 3) {
         case 1: return launch_dual_one<true, 1>(p, sm_count, stream);
         case 2: return launch_dual_one<true, 2>(p, sm_count, stream);

@@ -143,6 +143,7 @@ __global__ void __launch_bounds__(kDualThreads, kStage == 2 ? 3 : 2) r2iq_dual_d
     static_assert(kStage != 2 || 32 * ((32 >> D) + 1) * 8 <= kLandOff, "backward transposition overlaps the landing zone");
     constexpr bool kDyn = (kVar & 1) != 0;
     constexpr bool kFree = (kVar & 2) != 0;
+    constexpr bool kMix = (kVar & kVarMix) != 0;    // fine-tune NCO in the store epilogue
     constexpr int M = kHalfFft >> D;
     constexpr int R = 32 >> D;            // band bins per lane = size of the register DFTs
     constexpr int G = 32 / R;             // lanes sharing one 32-point DFT in pass 2
@@ -301,8 +302,16 @@ __global__ void __launch_bounds__(kDualThreads, kStage == 2 ? 3 : 2) r2iq_dual_d
             float ar, br, ai, bi;
             upk(t[q4].re, ar, br);
             upk(t[q4].im, ai, bi);
-            if (!idle && idx >= oa.lo && idx < 3 * M / 4) p.out[oa.base + idx] = make_float2(ar, ai * p.imag_sign);
-            if (!idle && ob.live && idx >= ob.lo && idx < 3 * M / 4) p.out[ob.base + idx] = make_float2(br, bi * p.imag_sign);
+            if (!idle && idx >= oa.lo && idx < 3 * M / 4) {
+                float2 va = make_float2(ar, ai * p.imag_sign);
+                if constexpr (kMix) va = nco_mix_sample(va, oa.base + idx, p.nco_starts, p.nco_tab);
+                p.out[oa.base + idx] = va;
+            }
+            if (!idle && ob.live && idx >= ob.lo && idx < 3 * M / 4) {
+                float2 vb = make_float2(br, bi * p.imag_sign);
+                if constexpr (kMix) vb = nco_mix_sample(vb, ob.base + idx, p.nco_starts, p.nco_tab);
+                p.out[ob.base + idx] = vb;
+            }
         }
         work.advance();
         q = qn;
@@ -326,6 +335,7 @@ static cudaError_t setup_dual_all() {
     if ((e = setup_dual_one<D, 2>()) != cudaSuccess) return e;
     if ((e = setup_dual_one<D, 1, 2>()) != cudaSuccess) return e;
     if ((e = setup_dual_one<D, 3, 2>()) != cudaSuccess) return e;
+    if ((e = setup_dual_one<D, 3 | kVarMix, 2>()) != cudaSuccess) return e;
     return setup_dual_one<D, 3>();
 }
 
@@ -366,6 +376,7 @@ template <int D>
 static cudaError_t launch_dual_var(const FusedParams& p, int sm_count, cudaStream_t stream) {
     // default 7 (measured on B200, 8192 blocks): 12 free-running warps per SM + dynamic distribution give
     // 760 / 869 / 929 / 968 Gsamples/s at d = 2..5, the 8-warp lock-step form (variant 1) 710 / 791 / 858 / 878
+    if (p.nco_starts) return launch_dual_one<D, 3 | kVarMix, 2>(p, sm_count, stream);   // default variant + fused mixer
     switch (kernel_variant(7)) {
         case 0: return launch_dual_one<D, 0>(p, sm_count, stream);
         case 1: return launch_dual_one<D, 1>(p, sm_count, stream);

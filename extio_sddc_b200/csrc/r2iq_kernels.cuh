@@ -32,7 +32,33 @@ struct FusedParams {
     uint32_t rand_mul;          // 0xFFFE when the ADC randomizer is on, else 0
     float imag_sign;            // -1 when sideband inversion (copy<true>) is requested, else +1
     unsigned long long* work_counter;   // device counter handing out frame pairs (dynamic work distribution)
+    // Fine-tune NCO folded into the store epilogue (variant bit 5 of the default dual-frame kernels; null = off):
+    // start phasors of every 128-sample block of this launch's output and the 33-entry group table, as nco_mix_kernel
+    const float2* nco_starts;
+    const float2* nco_tab;
 };
+// bit 5 of a kernel's kVar: multiply every output sample by the fine-tune phasor before it is stored
+constexpr int kVarMix = 32;
+
+#ifdef __CUDACC__
+// Residual fine-tune mixer on one output sample (see nco_mix_kernel in r2iq_kernels.cu for the derivation): i is the
+// sample's index in this launch's output stream.  Separately rounded products and sums, the order of the reference's
+// SSE code (Core/pffft/pf_mixer.cpp:791-856), so a kernel that mixes in its store epilogue delivers the same bits as
+// the stand-alone pass -- without reading and writing the IQ a second time.
+__device__ __forceinline__ float2 nco_mix_sample(float2 v, long long i, const float2* __restrict__ starts,
+                                                 const float2* __restrict__ tab) {
+    const float2 s = __ldg(&starts[(i >> 7) * 4 + (i & 3)]);
+    const int g = (int)((i & 127) >> 2);
+    float2 ph = s;
+    if (g) {
+        const float2 t = __ldg(&tab[g - 1]);
+        ph.x = __fsub_rn(__fmul_rn(t.x, s.x), __fmul_rn(t.y, s.y));
+        ph.y = __fadd_rn(__fmul_rn(t.y, s.x), __fmul_rn(t.x, s.y));
+    }
+    return make_float2(__fsub_rn(__fmul_rn(v.x, ph.x), __fmul_rn(v.y, ph.y)),
+                       __fadd_rn(__fmul_rn(v.y, ph.x), __fmul_rn(v.x, ph.y)));
+}
+#endif
 // Measurement variants of the persistent kernels (env R2IQ_VARIANT, read at every launch): bit 0 = dynamic work
 // distribution (work_dispenser.cuh), bit 1 = no block barriers between phases (warps run free), bit 2 = TMA
 // input lands in the transposition tile itself (12 instead of 8 warps per SM; d = 0 and d >= 2 kernels), bit 3 =

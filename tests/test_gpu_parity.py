@@ -306,11 +306,15 @@ def test_config4_channelizer(op):
     op.TurnOff()
 
 
-def test_fine_tune_mixer_bit_exact(op):
+@pytest.mark.parametrize("fused", ["0", "1"])
+def test_fine_tune_mixer_bit_exact(op, fused, monkeypatch):
     """Next row: the residual NCO mixer RadioHandlerClass applies after the operator, run on
     the device.  Applied to the same IQ, the device result must equal the reference's own mixer
-    (Core/pffft/pf_mixer.cpp compiled in place) BIT FOR BIT, with the phase carried across calls."""
+    (Core/pffft/pf_mixer.cpp compiled in place) BIT FOR BIT, with the phase carried across calls -- as a stand-alone
+    pass (default) and folded into the store epilogue of the d = 0, d = 1 and d = 2..5 kernels (R2IQ_NCO_FUSED=1,
+    read at every launch)."""
     from oracle import ref_lib
+    monkeypatch.setenv("R2IQ_NCO_FUSED", fused)
     if not ref_lib.mixer_available():
         pytest.skip("oracle/_ref/libref_mixer.so not built")
     x = orc.rx888_blocks(6, 1, 256, randomized=True, seed=77)
