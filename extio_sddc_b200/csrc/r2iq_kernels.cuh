@@ -62,7 +62,10 @@ __device__ __forceinline__ float2 nco_mix_sample(float2 v, long long i, const fl
 // Measurement variants of the persistent kernels (env R2IQ_VARIANT, read at every launch): bit 0 = dynamic work
 // distribution (work_dispenser.cuh), bit 1 = no block barriers between phases (warps run free), bit 2 = TMA
 // input lands in the transposition tile itself (12 instead of 8 warps per SM; d = 0 and d >= 2 kernels), bit 3 =
-// inter-pass twiddles from a packed power recurrence instead of table loads (d = 0 kernel).  Without the
+// inter-pass twiddles from a packed power recurrence instead of table loads (d = 0 kernel), bit 4 = mirror bins of the
+// real-FFT split by warp shuffle instead of a shared-memory round trip (d = 0 kernel; measured: no gain).  Bit 5
+// (kVarMix) is not a measurement switch: it selects the instantiation with the fine-tune mixer in the store epilogue
+// and is set by the launcher when FusedParams::nco_starts is non-null.  Without the
 // variable every family runs its fastest measured combination: 1 for d = 0 and d = 1, 7 for d = 2..5, bit 0 for
 // the one-frame, FFTN 8192 and channelizer kernels.
 int kernel_variant(int dflt = 1);

@@ -391,7 +391,7 @@ def test_chunks_in_flight_on_several_streams_do_not_share_work_counters():
     r.close()
 
 
-@pytest.mark.parametrize("variant", ["0", "1", "2", "3", "5", "7", "9"])
+@pytest.mark.parametrize("variant", ["0", "1", "2", "3", "5", "7", "9", "17"])
 def test_measurement_variants_meet_the_bar(variant):
     """Every work-distribution / staging variant kept behind R2IQ_VARIANT (r2iq_kernels.cuh) meets the parity bar,
     on the device path and through the pipelined host path."""
