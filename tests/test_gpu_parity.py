@@ -557,3 +557,47 @@ def test_kernels_write_exactly_their_output_range(fftn):
                 assert bool((raw[2 * (guard + n_out):] == 0x7FC0DEAD).all()), (fftn, d, tb, nb, "write above the output range")
                 assert not bool((out == 0x7FC0DEAD).any()), (fftn, d, tb, nb, "output sample never written")
     r.close()
+
+
+def test_reference_signal_integrity_assertions():
+    """The assertions of the reference's own unittest/signal_integrity_test.cpp, restated on the CUDA path (Dummy radio:
+    64 Msps, BBRF103 gain, decimation index 0 -> 32 MS/s):
+      :338-354  5 MHz sine, amplitude 10000 -> a clear dominant tone, RMS > 0.1 (checked at its true place: tuned to
+                5 MHz the tone sits at DC + residual; untuned at 5 MHz - tunebin frequency)
+      :591-595  zeros in -> RMS < 1 (here: exactly zero)
+      :746-750  amplitude x2 -> RMS ratio in (1, 4) (here: 2 within 1e-3)
+      :813-817  phase-derivative stddev < 1 across buffer boundaries (here: < 1e-3 for a pure tone)
+      :557-559  run-to-run RMS within 5 % (here: bit-identical output, also with the dynamic work distribution)"""
+    gain = orc.BBRF103_GAINFACTOR
+    r = CudaR2IQ()
+    r.Init(gain)
+    r.setDecimate(0)
+    r.updateRand(False)
+    r.tunebin = 256                                   # constructor default mtunebin = halfFft/4 = 8 MHz at 64 Msps
+
+    def go(x):
+        r.TurnOn()
+        y = r.process(x)
+        r.TurnOff()
+        return y
+
+    x = orc.sine_blocks(8, 5e6, 64e6, amplitude=10000)
+    y = go(x)
+    assert y.shape == (8 * 32768,)                    # core_test.cpp:165-167: 32768 complex per block at every rate
+    steady = y[4096:]                                 # skip the zero-history transient of the first frame
+    rms = float(np.sqrt(np.mean(np.abs(steady) ** 2)))
+    assert rms > 0.1
+    spec = np.abs(np.fft.fft(steady[:65536] * np.hanning(65536)))
+    k = int(np.argmax(spec))
+    f_det = (k if k < 32768 else k - 65536) * 32e6 / 65536
+    assert abs(f_det - (5e6 - 8e6)) <= 2 * 32e6 / 4096, f_det     # tone lands at f_in - f_tune, within the test's 2 bins
+    assert spec[k] > 100 * np.median(spec)                         # dominant, not noise
+    ph = np.unwrap(np.angle(steady[:10000].astype(np.complex128)))
+    assert float(np.std(np.diff(ph))) < 1e-3                       # continuous phase across frame and block edges
+    assert np.array_equal(go(x).view(np.uint32), y.view(np.uint32))   # run to run: the same bits
+    y2 = go(orc.sine_blocks(8, 5e6, 64e6, amplitude=5000))            # half amplitude
+    ratio = rms / float(np.sqrt(np.mean(np.abs(y2[4096:]) ** 2)))
+    assert 1.0 < ratio < 4.0 and abs(ratio - 2.0) < 1e-3, ratio
+    z = go(np.zeros(4 * 65536, dtype=np.int16))
+    assert not z.any()
+    r.close()
