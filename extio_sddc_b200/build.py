@@ -15,8 +15,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB_DIR = os.path.join(HERE, "lib")
 LIB_PATH = os.path.join(LIB_DIR, "libr2iq_cuda.so")
-SOURCES = ["r2iq_kernels.cu", "r2iq_dual.cu", "r2iq_dual_d0.cu", "r2iq_dual_d1.cu", "r2iq_dual_dn.cu", "r2iq_channels.cu", "r2iq_wide.cu", "r2iq_capi.cu", "fir_design.cpp"]
-HEADERS = ["r2iq_kernels.cuh", "dft_regs.cuh", "dft_regs2.cuh", "r2iq_common.cuh", "work_dispenser.cuh", "fir_design.h", os.path.join("..", "..", "include", "r2iq_cuda.h")]
+SOURCES = ["r2iq_kernels.cu", "r2iq_dual.cu", "r2iq_dual_d0.cu", "r2iq_dual_d1.cu", "r2iq_dual_dn.cu", "r2iq_pair.cu", "r2iq_channels.cu", "r2iq_wide.cu", "r2iq_capi.cu", "fir_design.cpp"]
+HEADERS = ["r2iq_kernels.cuh", "dft_regs.cuh", "dft_regs2.cuh", "r2iq_common.cuh", "work_dispenser.cuh", "dual_frame.cuh", "fir_design.h", os.path.join("..", "..", "include", "r2iq_cuda.h")]
 ARCH_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a"]
 NVCC_FLAGS = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden",
               "--cudart", "static"]
@@ -41,16 +41,25 @@ def build(force: bool = False, verbose: bool = False) -> str:
     if not force and not _stale():
         return LIB_PATH
     os.makedirs(LIB_DIR, exist_ok=True)
-    objs = []
-    for src in SOURCES:
+    from concurrent.futures import ThreadPoolExecutor
+    hdr_time = max(os.path.getmtime(os.path.join(CSRC, h)) for h in HEADERS)
+    hdr_time = max(hdr_time, os.path.getmtime(os.path.abspath(__file__)))
+
+    def compile_one(src: str) -> str:
         obj = os.path.join(LIB_DIR, os.path.splitext(src)[0] + ".o")
-        cmd = [nvcc(), *ARCH_FLAGS, *NVCC_FLAGS, "-c", os.path.join(CSRC, src), "-o", obj]
+        path = os.path.join(CSRC, src)
+        if not force and os.path.exists(obj) and os.path.getmtime(obj) >= max(os.path.getmtime(path), hdr_time):
+            return obj                    # translation unit and every header older than its object
+        cmd = [nvcc(), *ARCH_FLAGS, *NVCC_FLAGS, "-c", path, "-o", obj]
         if verbose:
             cmd.insert(1, "-Xptxas")
             cmd.insert(2, "-v")
             print(" ".join(cmd), flush=True)
         subprocess.run(cmd, check=True)
-        objs.append(obj)
+        return obj
+
+    with ThreadPoolExecutor(max_workers=min(len(SOURCES), os.cpu_count() or 1)) as pool:
+        objs = list(pool.map(compile_one, SOURCES))
     cmd = [nvcc(), *ARCH_FLAGS, "--cudart", "static", "-shared", "-o", LIB_PATH, *objs]
     if verbose:
         print(" ".join(cmd), flush=True)

@@ -174,4 +174,27 @@ __device__ __forceinline__ void dit2(c2 (&v)[N]) {
     }
 }
 
+// dit2 whose first stage (the trivial a +- b butterflies) is written as fma(+-one, b, a) with a run-time packed 1.0:
+// the same bits as the additions (1.0 * b is exact) on the same pipe, but every value of the pass now depends on
+// `one`.  The FMA-token kernels (r2iq_tok.cu) load `one` from shared memory right after they acquire the token, which
+// keeps ptxas from hoisting the whole register pass above the barrier (it does: only memory operations are ordered
+// against BAR.SYNC).
+template <int N, bool INV>
+__device__ __forceinline__ void dit2_pinned(c2 (&v)[N], u64 one) {
+    if constexpr (N >= 2) {
+        const u64 mone = neg2(one);
+#pragma unroll
+        for (int i = 0; i < N / 2; i++) {
+            c2& a = v[2 * i];
+            c2& b = v[2 * i + 1];
+            const c2 t = b;
+            b.re = fma2(mone, t.re, a.re);
+            b.im = fma2(mone, t.im, a.im);
+            a.re = fma2(one, t.re, a.re);
+            a.im = fma2(one, t.im, a.im);
+        }
+        if constexpr (N > 2) dit2<N, INV, 4>(v);
+    }
+}
+
 }  // namespace r2iq

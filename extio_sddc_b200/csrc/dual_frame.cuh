@@ -1,0 +1,111 @@
+// dual_frame.cuh -- device helpers shared by the dual-frame (two frames per warp on packed fp32x2 lanes) kernels:
+// mbarrier / TMA bulk-copy wrappers, the two-plane shared-memory tile accessors, the de-randomise + int16 -> float
+// unpack of two frames at once, frame addressing and output placement.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "dft_regs2.cuh"
+#include "r2iq_kernels.cuh"
+
+namespace r2iq {
+namespace dualf {
+
+constexpr int kTile = 32 * 33;                // elements per plane: 32x32 tile, pitch 33 (conflict-free for 8 B accesses)
+constexpr int kFrameBytes = kFftN * 2;        // 4096 B of int16 per frame
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t mbar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(mbar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t mbar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t mbar, uint32_t parity) {
+    uint32_t done;
+    do {
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+            "selp.u32 %0, 1, 0, p;\n"
+            "}\n"
+            : "=r"(done)
+            : "r"(mbar), "r"(parity)
+            : "memory");
+    } while (!done);
+}
+// TMA 1-D bulk copy global -> shared, completion signalled on the mbarrier (SASS: UBLKCP)
+__device__ __forceinline__ void tma_load_1d(uint32_t dst, const void* src, uint32_t bytes, uint32_t mbar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+                 "l"(src), "r"(bytes), "r"(mbar)
+                 : "memory");
+}
+
+// first word of frame f = 43*block + k inside [halo | blocks] (hop 1536 samples = 768 words)
+__device__ __forceinline__ const uint32_t* frame_src(const FusedParams& p, long long f) {
+    const long long b = f / kFramesPerBlock;
+    const int k = (int)(f - b * kFramesPerBlock);
+    return p.in_words + b * (kTransferSamples / 2) + k * (kHop / 2);
+}
+
+__device__ __forceinline__ int brev5(int v) { return (int)(__brev((unsigned)v) >> 27); }
+__device__ __forceinline__ int brev_n(int v, int bits) { return bits == 0 ? 0 : (int)(__brev((unsigned)v) >> (32 - bits)); }
+__device__ __forceinline__ float flip(float x, uint32_t sgn) { return __uint_as_float(__float_as_uint(x) ^ sgn); }
+
+// Shared-memory exchanges use two 64-bit planes (re pairs, im pairs) rather than one 128-bit element: a v2.b64
+// access needs re and im in four consecutive registers (ptxas paid ~400 MOVs per iteration to arrange that); plane
+// accesses have no such constraint and stay conflict-free at pitch 33.  Stored as float2 halves: a plain 64-bit
+// store of the packed register makes ptxas copy the pair into a scratch pair first.
+__device__ __forceinline__ void sts2(u64* S, int idx, c2 v) {
+    float a, b, c, d;
+    upk(v.re, a, b);
+    upk(v.im, c, d);
+    reinterpret_cast<float2*>(S)[idx] = make_float2(a, b);
+    reinterpret_cast<float2*>(S)[kTile + idx] = make_float2(c, d);
+}
+__device__ __forceinline__ c2 lds2(const u64* S, int idx) {
+    const float2 r = reinterpret_cast<const float2*>(S)[idx];
+    const float2 i = reinterpret_cast<const float2*>(S)[kTile + idx];
+    c2 v;
+    v.re = pk(r.x, r.y);
+    v.im = pk(i.x, i.y);
+    return v;
+}
+
+// One word of frame A and one of frame B (two int16 each = one packed complex input point per frame):
+// de-randomise both halves (Core/fft_mt_r2iq.h:41-44: x ^= 0xFFFE when the LSB is set), then int16 -> float.
+// The conversion is the integer-pipe "magic number" form: 0x4B000000 | (x ^ 0x8000) is the float 2^23 + (x + 32768)
+// exactly, so one exact packed subtraction of 2^23 + 32768 yields float(x) -- the same bits as I2F (every int16 is
+// representable), without the half-rate conversion unit.
+__device__ __forceinline__ void unpack_words(uint32_t wa, uint32_t wb, uint32_t rand_mul, c2& v) {
+    wa ^= ((wa & 0x00010001u) * rand_mul) ^ 0x80008000u;
+    wb ^= ((wb & 0x00010001u) * rand_mul) ^ 0x80008000u;
+    const uint32_t are = __byte_perm(wa, 0x4B000000u, 0x7610), aim = __byte_perm(wa, 0x4B000000u, 0x7632);
+    const uint32_t bre = __byte_perm(wb, 0x4B000000u, 0x7610), bim = __byte_perm(wb, 0x4B000000u, 0x7632);
+    const u64 bias = bc(8421376.0f);   // 2^23 + 2^15
+    v.re = sub2(pk(__uint_as_float(are), __uint_as_float(bre)), bias);
+    v.im = sub2(pk(__uint_as_float(aim), __uint_as_float(bim)), bias);
+}
+
+struct FrameOut2 {
+    long long base;   // out[base + idx] receives backward-transform sample idx of this frame
+    int lo;           // first kept idx (the kept range ends at 3*mfft/4)
+    bool live;        // false for the phantom second frame of an odd total
+};
+// impl.hpp:117-138: frame 0 of a block keeps y[mfft/4, 3mfft/4), the others y[0, 3mfft/4) at mfft/2 + (k-1)*3mfft/4
+template <int D>
+__device__ __forceinline__ FrameOut2 frame_out2(long long f, long long total) {
+    constexpr int M = kHalfFft >> D;
+    const long long b = f / kFramesPerBlock;
+    const int k = (int)(f - b * kFramesPerBlock);
+    FrameOut2 o;
+    o.live = f < total;
+    o.lo = k ? 0 : M / 4;
+    o.base = b * (long long)((kTransferSamples / 2) >> D) + (k ? (M / 2 + (k - 1) * (3 * M / 4)) : 0) - o.lo;
+    return o;
+}
+
+}  // namespace dualf
+}  // namespace r2iq

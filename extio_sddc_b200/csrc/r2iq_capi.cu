@@ -41,6 +41,8 @@ int fail(int code, const char* fmt, ...) {
     return code;
 }
 
+void poison(r2iq_cuda_t h, const char* why);   // defined once the handle type is complete
+
 constexpr double kPiD = 3.14159265358979323846;
 constexpr int kDefaultChunkBlocks = 256;
 constexpr int kSlots = 3;                 // pipelined chunks in flight on the host-buffer path
@@ -106,6 +108,7 @@ struct r2iq_cuda_s {
     bool latched_sideband = false;
 
     bool poisoned = false;        // a CUDA error happened: refuse further work
+    char poison_msg[256] = "";    // what poisoned it (g_err is thread-local: the application thread asks later)
     std::mutex mu;
 
     std::vector<std::complex<float>> hw[kNDec];   // filterHw[d], host copy
@@ -139,20 +142,59 @@ struct r2iq_cuda_s {
 
 namespace {
 
+void poison(r2iq_cuda_t h, const char* why) {
+    if (!h || h->poisoned) return;
+    h->poisoned = true;
+    snprintf(h->poison_msg, sizeof(h->poison_msg), "%s", why);
+}
+
 #define CU(h, call)                                                                                       \
     do {                                                                                                  \
         cudaError_t e__ = (call);                                                                         \
         if (e__ != cudaSuccess) {                                                                         \
-            if (h) (h)->poisoned = true;                                                                  \
-            return fail(R2IQ_E_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, __LINE__); \
+            const int rc__ = fail(R2IQ_E_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, __LINE__); \
+            poison(h, g_err);                                                                             \
+            return rc__;                                                                                  \
         }                                                                                                 \
     } while (0)
 
 int check_handle(r2iq_cuda_t h) {
     if (!h) return fail(R2IQ_E_INVALID, "null handle");
-    if (h->poisoned) return fail(R2IQ_E_CUDA, "handle is unusable after an earlier CUDA error: %s", g_err);
+    if (h->poisoned) return fail(R2IQ_E_CUDA, "handle is unusable after an earlier CUDA error: %s", h->poison_msg);
     return R2IQ_OK;
 }
+
+// Frees device allocations when an entry point leaves early (the CU() macro returns from the middle of a function).
+struct DeviceScratch {
+    void* ptrs[4] = {nullptr, nullptr, nullptr, nullptr};
+    int n = 0;
+    template <typename T>
+    cudaError_t alloc(T** p, size_t bytes) {
+        cudaError_t e = cudaMalloc((void**)p, bytes);
+        if (e == cudaSuccess) ptrs[n++] = (void*)*p;
+        return e;
+    }
+    ~DeviceScratch() {
+        for (int i = 0; i < n; i++) cudaFree(ptrs[i]);
+    }
+};
+
+// Makes the handle's device current for the duration of an entry point and puts the caller's device back afterwards.
+struct DeviceGuard {
+    int prev = -1;
+    bool switched = false;
+    cudaError_t err = cudaSuccess;
+    explicit DeviceGuard(int device) {
+        if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+        if (prev != device) {
+            err = cudaSetDevice(device);
+            switched = err == cudaSuccess;
+        }
+    }
+    ~DeviceGuard() {
+        if (switched && prev >= 0) cudaSetDevice(prev);
+    }
+};
 
 // Twiddles of the R = M/32 register scheme for an M-point backward transform on 32 lanes (r2iq_dual_dn.cu,
 // r2iq_wide.cu): [R][32] exp(+2 pi i lane k2 / M), then [32][32] exp(+2 pi i (lane % G) n1 / 32), G = 32/R.
@@ -634,7 +676,8 @@ int r2iq_cuda_create(const r2iq_cuda_config* cfg, r2iq_cuda_t* out) {
         r2iq_cuda_destroy(h);
         return rc;
     };
-    if ((e = cudaSetDevice(dev)) != cudaSuccess) return bail(fail(R2IQ_E_CUDA, "cudaSetDevice: %s", cudaGetErrorString(e)));
+    DeviceGuard dg(dev);                  // the caller's current device is put back when create returns
+    if ((e = dg.err) != cudaSuccess) return bail(fail(R2IQ_E_CUDA, "cudaSetDevice: %s", cudaGetErrorString(e)));
     if (const char* gen = getenv("R2IQ_KERNEL_GEN")) set_kernel_generation(atoi(gen));   // A/B measurements only
     if ((e = setup_channel_kernels()) != cudaSuccess)
         return bail(fail(R2IQ_E_CUDA, "channelizer kernel setup: %s", cudaGetErrorString(e)));
@@ -667,7 +710,7 @@ int r2iq_cuda_create(const r2iq_cuda_config* cfg, r2iq_cuda_t* out) {
 
 int r2iq_cuda_destroy(r2iq_cuda_t h) {
     if (!h) return R2IQ_OK;
-    cudaSetDevice(h->device);
+    DeviceGuard dg(h->device);
     cudaDeviceSynchronize();
     free_tables(h);
     free_channel_tables(h);
@@ -771,6 +814,8 @@ int r2iq_cuda_get_sideband(r2iq_cuda_t h) { return h ? (int)h->sideband.load() :
 float r2iq_cuda_set_fine_tune(r2iq_cuda_t h, float fc) {
     if (!h || h->poisoned) return 0.f;
     std::lock_guard<std::mutex> lk(h->mu);
+    DeviceGuard dg(h->device);            // the table lives on the operator's device, whatever the caller's current one is
+    if (dg.err != cudaSuccess) return 0.f;
     NcoState& s = h->nco;
     if (fc == 0.0f) {                 // RadioHandler.cpp:33: the mixer is skipped when fc == 0
         s.on = false;
@@ -783,8 +828,8 @@ float r2iq_cuda_set_fine_tune(r2iq_cuda_t h, float fc) {
     // ordered after everything already queued: the table may still be read by launches in flight
     if (cudaDeviceSynchronize() != cudaSuccess ||
         cudaMemcpy(s.d_tab, &s.tab[0][0], sizeof(float) * 66, cudaMemcpyHostToDevice) != cudaSuccess) {
-        h->poisoned = true;
         fail(R2IQ_E_CUDA, "fine-tune table upload failed");
+        poison(h, g_err);
         return 0.f;
     }
     s.on = true;
@@ -876,6 +921,13 @@ int r2iq_cuda_process_rates(r2iq_cuda_t h, const int16_t* blocks, long n_blocks,
     for (int r = 0; r < n_rates; r++)
         if (decimations[r] < 0 || decimations[r] >= kNDec || (n_blocks > 0 && !iq_outs[r]))
             return fail(R2IQ_E_INVALID, "process_rates: bad decimation index or output buffer at position %d", r);
+    // every rate at most once: the per-chunk device buffer holds ONE copy of each decimation's output
+    // (sum over d of 32768 >> d < 2 * 32768 complex per block)
+    for (int r = 0; r < n_rates; r++)
+        for (int q = 0; q < r; q++)
+            if (decimations[q] == decimations[r])
+                return fail(R2IQ_E_INVALID, "process_rates: decimation index %d listed twice (positions %d and %d)",
+                            decimations[r], q, r);
     if (h->nco.on) return fail(R2IQ_E_STATE, "process_rates: the fine-tune mixer belongs to one rate; switch it off first");
     if (n_blocks < 0 || (n_blocks > 0 && !blocks)) return fail(R2IQ_E_INVALID, "process_rates: bad buffers");
     if (n_blocks == 0) return R2IQ_OK;
@@ -911,6 +963,10 @@ int r2iq_cuda_process_rates(r2iq_cuda_t h, const int16_t* blocks, long n_blocks,
         for (int r = 0; r < n_rates && rc == R2IQ_OK; r++) {
             const int d = decimations[r];
             const size_t opb = (size_t)((kTransferSamples / 2) >> d);
+            if (off + 2 * (size_t)nb * opb > rates_floats) {
+                rc = fail(R2IQ_E_INVALID, "process_rates: outputs exceed the per-chunk device buffer");
+                break;
+            }
             h->latched_decimate = d;      // the kernels and tables are chosen per launch from the latched index
             rc = launch(h, s.d_in, nb, s.d_out_rates + off, s.stream, &s.d_starts, &s.starts_cap);
             if (rc != R2IQ_OK) break;
@@ -949,6 +1005,8 @@ int r2iq_cuda_process_device(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, 
         return fail(R2IQ_E_INVALID, "process_device: input must be 16-byte and output 8-byte aligned");
     if (n_blocks == 0) return R2IQ_OK;
     std::lock_guard<std::mutex> lk(h->mu);
+    DeviceGuard dg(h->device);            // tables are built (cudaMalloc/cudaMemcpy) on first use of a (d, tune bin)
+    CU(h, dg.err);
     return launch(h, d_in, n_blocks, d_iq_out, (cudaStream_t)stream, &h->nco.d_starts, &h->nco.starts_cap);
 }
 
@@ -963,7 +1021,8 @@ int r2iq_cuda_process_channels_device(r2iq_cuda_t h, const int16_t* d_in, long n
         return fail(R2IQ_E_INVALID, "process_channels_device: input must be 16-byte and output 8-byte aligned");
     if (n_blocks == 0 || n_channels == 0) return R2IQ_OK;
     std::lock_guard<std::mutex> lk(h->mu);
-    CU(h, cudaSetDevice(h->device));
+    DeviceGuard dg(h->device);
+    CU(h, dg.err);
     return launch_channels_impl(h, d_in, n_blocks, tunebins, n_channels, d_iq_out, (cudaStream_t)stream);
 }
 
@@ -982,11 +1041,12 @@ int r2iq_cuda_process_channels(r2iq_cuda_t h, const int16_t* blocks, long n_bloc
     const size_t per_ch = (size_t)n_blocks * ((kTransferSamples / 2) >> d);
     int16_t* d_in = nullptr;
     float* d_out = nullptr;
-    CU(h, cudaMalloc(&d_in, sizeof(int16_t) * ((size_t)kHalfFft + (size_t)n_blocks * kTransferSamples)));
-    cudaError_t e = cudaMalloc(&d_out, sizeof(float) * 2 * per_ch * (size_t)n_channels);
+    DeviceScratch scratch;                // freed on every way out, the early returns of CU() included
+    cudaError_t e = scratch.alloc(&d_in, sizeof(int16_t) * ((size_t)kHalfFft + (size_t)n_blocks * kTransferSamples));
+    if (e == cudaSuccess) e = scratch.alloc(&d_out, sizeof(float) * 2 * per_ch * (size_t)n_channels);
     if (e != cudaSuccess) {
-        cudaFree(d_in);
-        return fail(R2IQ_E_NOMEM, "cudaMalloc(channel output): %s", cudaGetErrorString(e));
+        cudaGetLastError();               // out of memory is the caller's problem, not a poisoned handle
+        return fail(R2IQ_E_NOMEM, "cudaMalloc(channelizer buffers): %s", cudaGetErrorString(e));
     }
     if (history) CU(h, cudaMemcpyAsync(d_in, history, sizeof(int16_t) * kHalfFft, cudaMemcpyHostToDevice, h->util_stream));
     else CU(h, cudaMemsetAsync(d_in, 0, sizeof(int16_t) * kHalfFft, h->util_stream));
@@ -1000,8 +1060,6 @@ int r2iq_cuda_process_channels(r2iq_cuda_t h, const int16_t* blocks, long n_bloc
         h->stats.d2h_bytes += sizeof(float) * 2 * per_ch * (size_t)n_channels;
     }
     CU(h, cudaStreamSynchronize(h->util_stream));
-    cudaFree(d_in);
-    cudaFree(d_out);
     return rc;
 }
 
@@ -1081,14 +1139,17 @@ int r2iq_cuda_convert(r2iq_cuda_t h, const int16_t* in, long n, int rand, float*
     CU(h, cudaSetDevice(h->device));
     int16_t* d_in = nullptr;
     float* d_out = nullptr;
-    CU(h, cudaMalloc(&d_in, sizeof(int16_t) * (size_t)n));
-    CU(h, cudaMalloc(&d_out, sizeof(float) * (size_t)n));
+    DeviceScratch scratch;
+    cudaError_t e = scratch.alloc(&d_in, sizeof(int16_t) * (size_t)n);
+    if (e == cudaSuccess) e = scratch.alloc(&d_out, sizeof(float) * (size_t)n);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(R2IQ_E_NOMEM, "cudaMalloc(convert buffers): %s", cudaGetErrorString(e));
+    }
     CU(h, cudaMemcpy(d_in, in, sizeof(int16_t) * (size_t)n, cudaMemcpyHostToDevice));
     CU(h, launch_convert(d_in, d_out, n, rand, h->util_stream));
     CU(h, cudaStreamSynchronize(h->util_stream));
     CU(h, cudaMemcpy(out, d_out, sizeof(float) * (size_t)n, cudaMemcpyDeviceToHost));
-    cudaFree(d_in);
-    cudaFree(d_out);
     return R2IQ_OK;
 }
 

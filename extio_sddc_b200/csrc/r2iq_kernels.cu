@@ -242,6 +242,7 @@ static cudaError_t setup_one() {
 }
 cudaError_t setup_fused_kernels() {
     cudaError_t e;
+    if ((e = setup_pair_kernels()) != cudaSuccess) return e;
     if ((e = setup_dual_kernels()) != cudaSuccess) return e;
     if ((e = setup_dual_d0_kernels()) != cudaSuccess) return e;
     if ((e = setup_dual_d1_kernels()) != cudaSuccess) return e;
@@ -263,9 +264,13 @@ cudaError_t launch_fused(int d, const FusedParams& p, int sm_count, cudaStream_t
     //   first-generation one-frame-per-warp kernel.
     //   1: first generation everywhere; 2: first dual-frame family (scalar backward batch), direct loads;
     //   3: the same with TMA; 4: generic packed-backward kernel also for d = 1.
-    if (g_kernel_gen == 0 || g_kernel_gen == 4) {
+    //   generation 0 (default): r2iq_pair.cu -- 8 free-running warps per SM for d = 0, 12 for d = 1..5
+    //   (B200, 8192 blocks: 514 / 597 / 788 / 905 / 977 / 994 Gsamples/s against 454 / 601 / 759 / 865 / 929 / 963 of
+    //   the round-1 kernels below, which stay reachable as generation 5 for A/B runs)
+    if (g_kernel_gen == 0 && d <= 5) return launch_pair(d, d == 0 ? 8 : 12, p, sm_count, stream);
+    if (g_kernel_gen == 5 || g_kernel_gen == 4) {
         if (d == 0) return launch_dual_d0(p, sm_count, stream, true);
-        if (d == 1 && g_kernel_gen == 0) return launch_dual_d1(p, sm_count, stream, true);
+        if (d == 1 && g_kernel_gen == 5) return launch_dual_d1(p, sm_count, stream, true);
         if (d <= 5) return launch_dual_dn(d, p, sm_count, stream);
     } else if (g_kernel_gen != 1) {
         return launch_dual(d, p, sm_count, stream, g_kernel_gen == 3);

@@ -126,6 +126,10 @@ cudaError_t launch_dual_d1(const FusedParams& p, int sm_count, cudaStream_t stre
 // specialised d = 0 dual-frame kernel (r2iq_dual_d0.cu)
 cudaError_t setup_dual_d0_kernels();
 cudaError_t launch_dual_d0(const FusedParams& p, int sm_count, cudaStream_t stream, bool tma);
+// third-generation dual-frame kernels (r2iq_pair.cu): one CTA of `warps` (8 or 12) free-running warps per SM, tables in
+// shared memory, one TMA copy per frame pair; d = 0..5 (12 warps: d >= 1 only).  Mixes when p.nco_starts is set.
+cudaError_t setup_pair_kernels();
+cudaError_t launch_pair(int d, int warps, const FusedParams& p, int sm_count, cudaStream_t stream);
 // One-time per-device setup (opt-in shared memory sizes).
 cudaError_t setup_fused_kernels();
 // Fine-tune NCO applied in place to n_complex output samples (see nco_mix_kernel).

@@ -1,0 +1,348 @@
+// r2iq_pair.cu -- the default fused kernels for d = 0..5, FFTN 2048 (third generation of the dual-frame family).
+//
+// Two frames per warp on packed fp32x2 lanes as in r2iq_dual_d0.cu / r2iq_dual_dn.cu (same mathematics, same register
+// passes).  What changed, each from a measurement of the round-1 kernels (profiles/r01_kernels.json, ncu source page):
+//   * ONE persistent CTA per SM of W free-running warps (W = 8 at 255 registers for d = 0 and 1, W = 12 at 168 for
+//     d >= 2); every warp takes its frame pairs one at a time from the device-wide counter and never meets a block
+//     barrier after the prologue.
+//   * The twiddle and filter tables live in SHARED memory, copied once per CTA.  The round-1 kernels read them with
+//     LDG: 32 KB of tables against the ~26 KB of L1 that the shared-memory carve-out leaves -- l1tex sector hit rate
+//     58 % at d = 0, as many L2->L1 sectors for tables as for the input itself, `long_scoreboard` the third-largest
+//     stall.
+//   * A frame pair is fetched by ONE TMA bulk copy: frames A and B of a pair are consecutive (hop 1536 or, across a
+//     block edge, 1024 samples), so the pair is 7168 (6144) contiguous bytes instead of 2 x 4096 -- 12.5 % less
+//     L2->SM traffic and the shared memory that makes room for the tables.
+//   * int16 -> float on the integer pipe (dual_frame.cuh: unpack_words) instead of the conversion unit.
+// Reference lines replaced: Core/fft_mt_r2iq_impl.hpp:40-54,84-138 (see r2iq_kernels.cu).
+#include "dual_frame.cuh"
+#include "r2iq_kernels.cuh"
+
+namespace r2iq {
+
+using namespace dualf;
+
+namespace {
+
+constexpr int kPairBytes = (kHop + kFftN) * 2;   // 7168: frames A and B of a pair, hop 1536 samples apart
+
+// Shared memory of one CTA: [tables][W per-warp areas].
+//   per warp, W = 8 : tile (2 planes x 8448 B) | pair buffer 7168 B | mbarrier 16 B
+//   per warp, W = 12: tile | mbarrier; the pair lands in the tail of the tile once the tile is free
+template <int W>
+__host__ __device__ constexpr int pair_warp_bytes() {
+    return kTile * 16 + (W == 8 ? kPairBytes : 0) + 16;
+}
+// tables: d = 0: tw_fwd, tw_inv, gp, gq (4 x 8 KB); d >= 1: tw_fwd (8 KB) + tw_aux ((R + 32) x 256 B); gp/gq stay
+// in global memory there (R <= 16 loads per frame pair)
+template <int D>
+__host__ __device__ constexpr int pair_table_float2() {
+    return D == 0 ? 4 * 1024 : 1024 + ((32 >> D) + 32) * 32;
+}
+template <int D, int W>
+__host__ __device__ constexpr int pair_smem_bytes() {
+    return pair_table_float2<D>() * 8 + W * pair_warp_bytes<W>();
+}
+constexpr int kLandOff = kTile * 16 - kPairBytes;   // W = 12: the pair occupies the last 7168 B of the tile
+
+// backward transposition of the d >= 1 kernels: two planes of 32 x (R + 1) elements packed at the head of the tile
+// (pitch R + 1, conflict-free), so that the tail of the tile is free for the next pair while it runs
+template <int R>
+__device__ __forceinline__ void sts2r(u64* S, int idx, c2 v) {
+    float a, b, c, d;
+    upk(v.re, a, b);
+    upk(v.im, c, d);
+    reinterpret_cast<float2*>(S)[idx] = make_float2(a, b);
+    reinterpret_cast<float2*>(S)[32 * (R + 1) + idx] = make_float2(c, d);
+}
+template <int R>
+__device__ __forceinline__ c2 lds2r(const u64* S, int idx) {
+    const float2 r = reinterpret_cast<const float2*>(S)[idx];
+    const float2 i = reinterpret_cast<const float2*>(S)[32 * (R + 1) + idx];
+    c2 v;
+    v.re = pk(r.x, r.y);
+    v.im = pk(i.x, i.y);
+    return v;
+}
+
+}  // namespace
+
+template <int D, int W, bool kMix>
+__global__ void __launch_bounds__(W * 32, 1) r2iq_pair_kernel(const FusedParams p) {
+    constexpr bool kLandInTile = W == 12;
+    constexpr int M = kHalfFft >> D;
+    constexpr int R = 32 >> D;            // band bins per lane (d >= 1)
+    constexpr int G = 32 / R;             // lanes sharing one 32-point DFT in pass 2 of the backward transform
+    constexpr int RB = ilog2(R);
+    static_assert(D == 0 || 2 * 32 * (R + 1) * 8 <= kLandOff, "backward transposition overlaps the landing zone");
+    static_assert(D != 0 || !kLandInTile, "d = 0 uses the whole tile until the last pass: W = 8 only");
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    float2* tab = reinterpret_cast<float2*>(smem_raw);
+    constexpr int kWarpBytes = pair_warp_bytes<W>();
+    unsigned char* wbase = smem_raw + pair_table_float2<D>() * 8 + (size_t)warp * kWarpBytes;
+    u64* S = reinterpret_cast<u64*>(wbase);
+    const uint32_t* inA = reinterpret_cast<const uint32_t*>(wbase + (kLandInTile ? kLandOff : kTile * 16));
+    const uint32_t mbar = smem_u32(wbase + kWarpBytes - 16);
+    const uint32_t dst = smem_u32(inA);
+
+    // ---- tables -> shared memory ------------------------------------------------------------------------------
+    for (int i = threadIdx.x; i < 1024; i += W * 32) tab[i] = __ldg(p.tw_fwd + i);
+    if constexpr (D == 0) {
+        for (int i = threadIdx.x; i < 1024; i += W * 32) {
+            tab[1024 + i] = __ldg(p.tw_inv + i);
+            tab[2048 + i] = __ldg(p.gp + i);
+            tab[3072 + i] = __ldg(p.gq + i);
+        }
+    } else {
+        for (int i = threadIdx.x; i < (R + 32) * 32; i += W * 32) tab[1024 + i] = __ldg(p.tw_aux + i);
+    }
+    if (lane == 0) {
+        mbar_init(mbar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+
+    const long long n_pairs = (p.total_frames + 1) / 2;
+    // one bulk copy per pair; B = A + hop (1536 samples, 1024 across a block edge).  The last pair of an odd total has
+    // no B: only A is copied, B's lanes then transform stale bytes and are never stored (packed lanes are independent).
+    auto issue = [&](long long pair) {
+        const long long fa = 2 * pair;
+        const uint32_t* src = frame_src(p, fa);
+        uint32_t bytes = kFrameBytes;
+        if (fa + 1 < p.total_frames) bytes += (uint32_t)(frame_src(p, fa + 1) - src) * 4;
+        mbar_expect_tx(mbar, bytes);
+        tma_load_1d(dst, src, bytes, mbar);
+    };
+
+    // ---- work: one pair at a time from the device-wide counter, one grab kept in flight ---------------------------
+    unsigned long long g0 = 0, g1 = 0, pend = 0;
+    if (lane == 0) {
+        g0 = atomicAdd(p.work_counter, 1ULL);
+        g1 = atomicAdd(p.work_counter, 1ULL);
+        pend = atomicAdd(p.work_counter, 1ULL);
+    }
+    long long q = (long long)__shfl_sync(0xffffffffu, g0, 0);
+    long long qn = (long long)__shfl_sync(0xffffffffu, g1, 0);
+    if (lane == 0 && q < n_pairs) issue(q);
+    uint32_t phase = 0;
+
+    const float2* twf = tab + lane;
+    const uint32_t sgn = __float_as_uint(p.imag_sign) & 0x80000000u;   // sideband inversion as a sign-bit flip
+
+    while (q < n_pairs) {
+        const long long qnn = (long long)__shfl_sync(0xffffffffu, pend, 0);
+        if (lane == 0) pend = atomicAdd(p.work_counter, 1ULL);
+        // word offset of frame B inside the pair buffer: 768, or 512 when A is the last frame of a block
+        const int offB = ((2 * q) % kFramesPerBlock == kFramesPerBlock - 1) ? kHalfFft / 2 : kHop / 2;
+        const uint32_t* inB = inA + offB;
+        c2 v[32];
+        mbar_wait(mbar, phase);
+        phase ^= 1;
+#pragma unroll
+        for (int j = 0; j < 32; j++) unpack_words(inA[lane + 32 * j], inB[lane + 32 * j], p.rand_mul, v[brev5(j)]);
+        __syncwarp();   // every lane has consumed its words: the buffer may be overwritten
+        if constexpr (!kLandInTile) {
+            if (lane == 0 && qn < n_pairs) issue(qn);
+        }
+
+        // ---- forward 1024-point transform of z = x[2n] + i x[2n+1] ------------------------------
+        dit2<32, false>(v);
+#pragma unroll
+        for (int k2 = 1; k2 < 32; k2++) v[k2] = cmul2s(v[k2], twf[32 * k2]);
+#pragma unroll
+        for (int k2 = 0; k2 < 32; k2++) sts2(S, lane * 33 + k2, v[k2]);
+        __syncwarp();
+#pragma unroll
+        for (int n1 = 0; n1 < 32; n1++) v[brev5(n1)] = lds2(S, n1 * 33 + lane);
+        __syncwarp();
+        dit2<32, false>(v);                       // v[k1] = Z[32*k1 + lane]
+
+        if constexpr (D == 0) {
+            // ---- real-FFT split + tune rotation + filter, in place; mirror bins through shared memory ----
+            const float2* twi = tab + 1024 + lane;
+            const float2* gp = tab + 2048 + lane;
+            const float2* gq = tab + 3072 + lane;
+            const int n1_inv = (lane - p.tunebin) & 31;
+            c2 t[32];
+#pragma unroll
+            for (int k1 = 0; k1 < 32; k1++) sts2(S, 32 * k1 + lane, v[k1]);
+            __syncwarp();
+#pragma unroll
+            for (int k1 = 0; k1 < 32; k1++) {
+                const c2 a = v[k1];
+                const c2 b = lds2(S, (kHalfFft - (32 * k1 + lane)) & (kHalfFft - 1));
+                const float2 P = gp[32 * k1];
+                const float2 Q = gq[32 * k1];
+                c2 y;
+                y.re = fma2(bc(Q.y), b.im, fma2(bc(Q.x), b.re, fma2(bc(-P.y), a.im, mul2(bc(P.x), a.re))));
+                y.im = fma2(bc(Q.y), b.re, fma2(bc(-Q.x), b.im, fma2(bc(P.y), a.re, mul2(bc(P.x), a.im))));
+                t[brev5(k1)] = y;                     // bit-reversed placement for the backward pass
+            }
+            __syncwarp();
+            // ---- backward 1024-point transform; lane l is residue (l - tunebin) mod 32 ---------------
+            dit2<32, true>(t);
+#pragma unroll
+            for (int k2 = 1; k2 < 32; k2++) t[k2] = cmul2s(t[k2], twi[32 * k2]);
+#pragma unroll
+            for (int k2 = 0; k2 < 32; k2++) sts2(S, n1_inv * 33 + k2, t[k2]);
+            __syncwarp();
+#pragma unroll
+            for (int n = 0; n < 32; n++) t[brev5(n)] = lds2(S, n * 33 + lane);
+            __syncwarp();
+            dit2<32, true>(t);                        // t[k1] = y[lane + 32*k1] for both frames
+
+            // ---- overlap-save discard + placement (impl.hpp:117-138) --------------------------------
+            const FrameOut2 oa = frame_out2<0>(2 * q, p.total_frames);
+            const FrameOut2 ob = frame_out2<0>(2 * q + 1, p.total_frames);
+#pragma unroll
+            for (int k1 = 0; k1 < 24; k1++) {         // idx >= 768 is always discarded
+                const int idx = lane + 32 * k1;
+                float ar, br, ai, bi;
+                upk(t[k1].re, ar, br);
+                upk(t[k1].im, ai, bi);
+                if (idx >= oa.lo) {
+                    float2 va = make_float2(ar, flip(ai, sgn));
+                    if constexpr (kMix) va = nco_mix_sample(va, oa.base + idx, p.nco_starts, p.nco_tab);
+                    p.out[oa.base + idx] = va;
+                }
+                if (ob.live && idx >= ob.lo) {
+                    float2 vb = make_float2(br, flip(bi, sgn));
+                    if constexpr (kMix) vb = nco_mix_sample(vb, ob.base + idx, p.nco_starts, p.nco_tab);
+                    p.out[ob.base + idx] = vb;
+                }
+            }
+        } else {
+            const float2* twi = tab + 1024 + lane;            // [R][32]  exp(+2 pi i lane k2 / M)
+            const float2* tw2 = tab + 1024 + R * 32 + lane;   // [32][32] exp(+2 pi i (lane % G) n1 / 32)
+            // ---- spectrum to shared memory in natural order; only the rows the band cut will read -------
+#pragma unroll
+            for (int k1 = 0; k1 < 32; k1++)
+                if ((p.row_mask >> k1) & 1u) sts2(S, 32 * k1 + lane, v[k1]);
+            __syncwarp();
+            // ---- band cut in backward-transform order: m = lane + 32*j, bin k = tunebin + s(m) --------
+            c2 y[R];
+#pragma unroll
+            for (int j = 0; j < R; j++) {
+                const int m = lane + 32 * j;
+                const int s = m < M / 2 ? m : m - M;                     // upper half of the band is below the tune bin
+                const int kk = (p.tunebin + s) & (kHalfFft - 1);         // wrapped bins meet P = Q = 0: zero fill
+                const c2 a = lds2(S, kk);
+                const c2 b = lds2(S, (kHalfFft - kk) & (kHalfFft - 1));
+                const float2 P = __ldg(p.gp + kk);
+                const float2 Q = __ldg(p.gq + kk);
+                c2 r;
+                r.re = fma2(bc(Q.y), b.im, fma2(bc(Q.x), b.re, fma2(bc(-P.y), a.im, mul2(bc(P.x), a.re))));
+                r.im = fma2(bc(Q.y), b.re, fma2(bc(-Q.x), b.im, fma2(bc(P.y), a.re, mul2(bc(P.x), a.im))));
+                y[brev_n(j, RB)] = r;                                    // bit-reversed placement
+            }
+            __syncwarp();   // every lane is done with the spectrum: the tile is free
+            if constexpr (kLandInTile) {
+                // ... its tail for the next pair of frames (generic-proxy reads ordered before the async-proxy writes),
+                // its head for the backward transposition
+                if (lane == 0 && qn < n_pairs) {
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                    issue(qn);
+                }
+            }
+            // ---- backward mfft-point transform: n = lane + 32*n2, k = k2 + R*k1 ------------------------
+            dit2<R, true>(y);                         // pass 1 over n2
+#pragma unroll
+            for (int k2 = 1; k2 < R; k2++) y[k2] = cmul2s(y[k2], twi[32 * k2]);   // exp(+2 pi i lane k2 / M)
+#pragma unroll
+            for (int k2 = 0; k2 < R; k2++) sts2r<R>(S, lane * (R + 1) + k2, y[k2]);
+            __syncwarp();
+            const int k2p = lane / G;                 // which 32-point DFT this lane works on
+            const int h = lane % G;                   // it computes outputs k1 = h + G*q
+            c2 t[R];
+#pragma unroll
+            for (int n1 = 0; n1 < 32; n1++) {         // u_j = sum_r x[j + R*r] * exp(+2 pi i h (j + R*r) / 32)
+                const c2 x = lds2r<R>(S, n1 * (R + 1) + k2p);
+                const float2 w = tw2[32 * n1];
+                const int j = n1 % R;
+                c2& u = t[brev_n(j, RB)];
+                if (n1 < R) {
+                    u.re = fma2(bc(w.x), x.re, mul2(bc(-w.y), x.im));
+                    u.im = fma2(bc(w.x), x.im, mul2(bc(w.y), x.re));
+                } else {
+                    u.re = fma2(bc(w.x), x.re, fma2(bc(-w.y), x.im, u.re));
+                    u.im = fma2(bc(w.x), x.im, fma2(bc(w.y), x.re, u.im));
+                }
+            }
+            __syncwarp();
+            dit2<R, true>(t);                         // t[q] = y_out[k2p + R*h + 32*q] for both frames
+
+            // ---- overlap-save discard + placement (impl.hpp:117-138) --------------------------------
+            const FrameOut2 oa = frame_out2<D>(2 * q, p.total_frames);
+            const FrameOut2 ob = frame_out2<D>(2 * q + 1, p.total_frames);
+            const int idx0 = k2p + R * h;
+#pragma unroll
+            for (int q4 = 0; q4 < R; q4++) {
+                const int idx = idx0 + 32 * q4;
+                float ar, br, ai, bi;
+                upk(t[q4].re, ar, br);
+                upk(t[q4].im, ai, bi);
+                if (idx >= oa.lo && idx < 3 * M / 4) {
+                    float2 va = make_float2(ar, flip(ai, sgn));
+                    if constexpr (kMix) va = nco_mix_sample(va, oa.base + idx, p.nco_starts, p.nco_tab);
+                    p.out[oa.base + idx] = va;
+                }
+                if (ob.live && idx >= ob.lo && idx < 3 * M / 4) {
+                    float2 vb = make_float2(br, flip(bi, sgn));
+                    if constexpr (kMix) vb = nco_mix_sample(vb, ob.base + idx, p.nco_starts, p.nco_tab);
+                    p.out[ob.base + idx] = vb;
+                }
+            }
+        }
+        q = qn;
+        qn = qnn;
+    }
+}
+
+template <int D, int W, bool kMix>
+static cudaError_t setup_pair_one() {
+    cudaError_t e = cudaFuncSetAttribute(r2iq_pair_kernel<D, W, kMix>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         pair_smem_bytes<D, W>());
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(r2iq_pair_kernel<D, W, kMix>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                cudaSharedmemCarveoutMaxShared);
+}
+
+template <int D, int W, bool kMix>
+static cudaError_t launch_pair_one(const FusedParams& p, int sm_count, cudaStream_t stream) {
+    const long long n_pairs = (p.total_frames + 1) / 2;
+    long long grid = sm_count;                 // persistent: one CTA per SM
+    const long long want = (n_pairs + W - 1) / W;
+    if (grid > want) grid = want;
+    if (grid < 1) grid = 1;
+    cudaError_t e = cudaMemsetAsync(p.work_counter, 0, sizeof(unsigned long long), stream);
+    if (e != cudaSuccess) return e;
+    r2iq_pair_kernel<D, W, kMix><<<(unsigned)grid, W * 32, pair_smem_bytes<D, W>(), stream>>>(p);
+    return cudaGetLastError();
+}
+
+// (D, W) combinations that are built: W = 8 for every d, W = 12 for d >= 1
+#define R2IQ_PAIR_FOR_ALL(X) \
+    X(0, 8) X(1, 8) X(2, 8) X(3, 8) X(4, 8) X(5, 8) X(1, 12) X(2, 12) X(3, 12) X(4, 12) X(5, 12)
+
+cudaError_t setup_pair_kernels() {
+    cudaError_t e;
+#define X(D, W)                                                        \
+    if ((e = setup_pair_one<D, W, false>()) != cudaSuccess) return e; \
+    if ((e = setup_pair_one<D, W, true>()) != cudaSuccess) return e;
+    R2IQ_PAIR_FOR_ALL(X)
+#undef X
+    return cudaSuccess;
+}
+
+cudaError_t launch_pair(int d, int warps, const FusedParams& p, int sm_count, cudaStream_t stream) {
+    const bool mix = p.nco_starts != nullptr;
+#define X(D, W)                                                                              \
+    if (d == D && warps == W)                                                                \
+        return mix ? launch_pair_one<D, W, true>(p, sm_count, stream) : launch_pair_one<D, W, false>(p, sm_count, stream);
+    R2IQ_PAIR_FOR_ALL(X)
+#undef X
+    return cudaErrorInvalidValue;
+}
+
+}  // namespace r2iq
