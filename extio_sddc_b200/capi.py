@@ -20,6 +20,7 @@ HALF_FFT = FFTN // 2
 
 OK = 0
 E_INVALID, E_CUDA, E_NOMEM, E_STATE, E_NODEVICE = -1, -2, -3, -4, -5
+NCO_REFERENCE, NCO_DIRECT = 0, 1
 
 
 class Config(ctypes.Structure):
@@ -69,6 +70,15 @@ _SIGNATURES = {
     "r2iq_cuda_process_channels": (_I, [_VP, _VP, _L, _VP, _VP, _I, _VP]),
     "r2iq_cuda_process_channels_device": (_I, [_VP, _VP, _L, _VP, _I, _VP, _VP]),
     "r2iq_cuda_set_fine_tune": (_F, [_VP, _F]),
+    "r2iq_cuda_set_fine_tune_mode": (_I, [_VP, _I]),
+    "r2iq_cuda_get_fine_tune_mode": (_I, [_VP]),
+    "r2iq_cuda_process_async": (_I, [_VP, _VP, _L, _VP, _VP, ctypes.POINTER(ctypes.c_uint64)]),
+    "r2iq_cuda_wait_input": (_I, [_VP, ctypes.c_uint64]),
+    "r2iq_cuda_wait": (_I, [_VP, ctypes.c_uint64]),
+    "r2iq_cuda_read": (_I, [_VP, ctypes.c_uint64, _L, _L, _VP]),
+    "r2iq_cuda_release": (_I, [_VP, ctypes.c_uint64]),
+    "r2iq_cuda_host_register": (_I, [_VP, ctypes.c_size_t]),
+    "r2iq_cuda_host_unregister": (_I, [_VP]),
     "r2iq_cuda_sync": (_I, [_VP]),
     "r2iq_cuda_host_alloc": (_VP, [ctypes.c_size_t]),
     "r2iq_cuda_host_alloc_on": (_VP, [ctypes.c_size_t, _I]),

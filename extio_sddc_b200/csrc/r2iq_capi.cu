@@ -19,6 +19,7 @@
 #include <emmintrin.h>
 #endif
 #include <unistd.h>
+#include <condition_variable>
 #include <mutex>
 #include <new>
 #include <vector>
@@ -45,7 +46,7 @@ void poison(r2iq_cuda_t h, const char* why);   // defined once the handle type i
 
 constexpr double kPiD = 3.14159265358979323846;
 constexpr int kDefaultChunkBlocks = 256;
-constexpr int kSlots = 3;                 // pipelined chunks in flight on the host-buffer path
+constexpr int kSlots = 4;                 // chunks / submissions in flight on the host-buffer paths
 constexpr size_t kMaxTableSets = 1024;    // cached (d, tunebin) table sets before the cache is recycled
 
 struct TableSet {   // device tables for one (decimation, tune bin)
@@ -59,15 +60,27 @@ struct TableSet {   // device tables for one (decimation, tune bin)
     uint32_t row_mask = 0xFFFFFFFFu;
 };
 
+// One submission in flight on the host-buffer paths: its own stream, device buffers and pinned history.
+//   kFree: nothing pending.
+//   kAuto: the result is being copied to the caller's iq_out; whoever waits for `done` frees the slot
+//          (r2iq_cuda_process, r2iq_cuda_process_rates, r2iq_cuda_process_async with an output pointer).
+//   kHeld: the result stays in d_out until r2iq_cuda_release (r2iq_cuda_process_async without an output pointer:
+//          the ring-buffer adapter fetches it slot by slot with r2iq_cuda_read).
 struct Slot {
+    enum State { kFree, kAuto, kHeld };
     cudaStream_t stream = nullptr;
-    cudaEvent_t done = nullptr;
+    cudaEvent_t h2d_done = nullptr;   // the input of this submission has left the caller's buffer
+    cudaEvent_t done = nullptr;       // everything enqueued for this submission has finished
     int16_t* d_in = nullptr;     // [halfFft | chunk_blocks * 65536]
     float* d_out = nullptr;      // chunk_blocks * 32768 complex (sized for d = 0)
     float* d_out_rates = nullptr;   // r2iq_cuda_process_rates: the chunk's output at up to 7 rates, allocated on first use
     float* d_starts = nullptr;   // fine-tune NCO: start phasors of the chunk's 128-sample blocks
     size_t starts_cap = 0;       // capacity of d_starts in 128-sample blocks
-    bool busy = false;
+    int16_t* carry = nullptr;    // pinned: the halfFft samples in front of this submission
+    State state = kFree;
+    uint64_t ticket = 0;
+    long n_blocks = 0;
+    int d = 0;                   // decimation this submission ran at
 };
 
 // Host side of the fine-tune NCO: the state and small table of shift_limited_unroll_C_sse_init
@@ -78,6 +91,10 @@ struct NcoState {
     float fc = 0.f;
     float tab[33][2];       // phasor of 4*(g+1) phase increments, g = 0..32 (dinterl_trig)
     float cs[4], sn[4];     // phase_state_i / phase_state_q
+    // Direct-phase mode (R2IQ_NCO_DIRECT): no recurrence; phase of the next output sample in cycles, [0, 1)
+    int mode = R2IQ_NCO_REFERENCE;
+    double phase = 0.0;
+    float* d_rot = nullptr;      // [32] exp(2 pi j fc 32 k)
     float* d_tab = nullptr;
     float* d_starts = nullptr;   // device-path scratch (caller's stream keeps launches ordered)
     size_t starts_cap = 0;
@@ -131,7 +148,9 @@ struct r2iq_cuda_s {
     struct WideSet { float2* g = nullptr; float2* tw_sub = nullptr; };
     std::map<long long, WideSet> wide_tables;      // per (filter version, d, tunebin)
     Slot slots[kSlots];
-    int16_t* carry = nullptr;                      // pinned: last halfFft samples of the stream
+    uint64_t next_ticket = 1;                      // submissions are numbered; ticket t uses slot t % kSlots
+    std::condition_variable cv;                    // a held slot was released / the operator was switched off
+    int16_t* carry = nullptr;                      // last halfFft samples of the stream (host copy, updated at submit)
     bool carry_valid = false;
     cudaStream_t util_stream = nullptr;
 
@@ -413,17 +432,10 @@ int nco_stage(r2iq_cuda_t h, float* d_out, size_t n_out, float** d_starts, size_
     CU(h, launch_nco_mix(d_out, (long long)n_out, *d_starts, s.d_tab, stream));
     return R2IQ_OK;
 }
-// The default dual-frame kernels (d = 0..5, FFTN 2048) CAN mix in their store epilogue (R2IQ_NCO_FUSED=1; bit-identical,
-// tests/test_gpu_parity.py).  It is not the default: measured on B200 (tools/mixer_bench.py) the mixer is bounded by
-// the sequential start-phasor recurrence on the host, and the stand-alone pass lets the main kernel run while the host
-// is still computing it, whereas the fused kernel has to wait for the upload.
-bool nco_fusable(int d) {
-    if (d > 5 || getenv("R2IQ_VARIANT")) return false;
-    if (const char* g = getenv("R2IQ_KERNEL_GEN")) {
-        if (atoi(g) != 0) return false;
-    }
-    const char* f = getenv("R2IQ_NCO_FUSED");
-    return f && atoi(f) != 0;
+// Direct-phase mode: the phase moves on by fc * n cycles per launch (float64; fc is a float32 value, n < 2^31).
+void nco_direct_advance(NcoState& s, size_t n_out) {
+    double ph = s.phase + (double)s.fc * (double)n_out;
+    s.phase = ph - floor(ph);
 }
 
 // FFTN 8192: static twiddles once per handle, filter gains (and small-transform twiddles) per (d, tune bin).
@@ -503,8 +515,13 @@ int launch(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d_out, cuda
         if (rc != R2IQ_OK) return rc;
         h->stats.kernel_launches++;
         h->stats.blocks_processed += (uint64_t)n_blocks;
-        return nco_stage(h, d_out, (size_t)n_blocks * (size_t)((kTransferSamples / 2) >> h->latched_decimate), nco_starts,
-                         nco_cap, stream);
+        const size_t n_out8 = (size_t)n_blocks * (size_t)((kTransferSamples / 2) >> h->latched_decimate);
+        if (h->nco.on && n_out8 > 0 && h->nco.mode == R2IQ_NCO_DIRECT) {
+            CU(h, launch_nco_mix_direct(d_out, (long long)n_out8, h->nco.phase, (double)h->nco.fc, stream));
+            nco_direct_advance(h->nco, n_out8);
+            return R2IQ_OK;
+        }
+        return nco_stage(h, d_out, n_out8, nco_starts, nco_cap, stream);
     }
     TableSet ts;
     const int d = h->latched_decimate;
@@ -532,18 +549,21 @@ int launch(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d_out, cuda
     p.work_counter = h->next_counter();
     p.nco_starts = nullptr;
     p.nco_tab = nullptr;
+    p.nco_rot = nullptr;
+    p.nco_phase0 = 0.0;
+    p.nco_fc = 0.0;
     const size_t n_out = (size_t)n_blocks * (size_t)((kTransferSamples / 2) >> d);
-    const bool fused_mix = h->nco.on && n_out > 0 && nco_fusable(d);
-    if (fused_mix) {
-        rc = nco_prepare(h, n_out, nco_starts, nco_cap, stream);
-        if (rc != R2IQ_OK) return rc;
-        p.nco_starts = (const float2*)*nco_starts;
-        p.nco_tab = (const float2*)h->nco.d_tab;
+    const bool direct = h->nco.on && n_out > 0 && h->nco.mode == R2IQ_NCO_DIRECT;
+    if (direct) {                         // the default kernels mix in their store epilogue: no second pass, no host work
+        p.nco_rot = (const float2*)h->nco.d_rot;
+        p.nco_phase0 = h->nco.phase;
+        p.nco_fc = (double)h->nco.fc;
+        nco_direct_advance(h->nco, n_out);
     }
     CU(h, launch_fused(d, p, h->sm_count, stream));
     h->stats.kernel_launches++;
     h->stats.blocks_processed += (uint64_t)n_blocks;
-    if (fused_mix) return R2IQ_OK;
+    if (direct) return R2IQ_OK;
     return nco_stage(h, d_out, n_out, nco_starts, nco_cap, stream);
 }
 
@@ -623,7 +643,9 @@ int ensure_slots(r2iq_cuda_t h) {
         Slot& s = h->slots[i];
         if (s.d_in) continue;
         CU(h, cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+        CU(h, cudaEventCreateWithFlags(&s.h2d_done, cudaEventDisableTiming));
         CU(h, cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
+        CU(h, cudaMallocHost(&s.carry, sizeof(int16_t) * (size_t)h->half));
         CU(h, cudaMalloc(&s.d_in, sizeof(int16_t) * ((size_t)h->half + (size_t)h->chunk_blocks * kTransferSamples)));
         CU(h, cudaMalloc(&s.d_out, sizeof(float) * 2 * (size_t)h->chunk_blocks * (kTransferSamples / 2)));
     }
@@ -696,7 +718,7 @@ int r2iq_cuda_create(const r2iq_cuda_config* cfg, r2iq_cuda_t* out) {
         (e = cudaMemset(h->d_work_counter, 0, sizeof(unsigned long long) * r2iq_cuda_s::kCounterRing)) != cudaSuccess ||
         (e = cudaMalloc(&h->d_tw_fwd, sizeof(float2) * 32 * 32)) != cudaSuccess ||
         (e = cudaMemcpy(h->d_tw_fwd, tw.data(), sizeof(float2) * 32 * 32, cudaMemcpyHostToDevice)) != cudaSuccess ||
-        (e = cudaMallocHost(&h->carry, sizeof(int16_t) * h->half)) != cudaSuccess ||
+        (h->carry = (int16_t*)malloc(sizeof(int16_t) * h->half)) == nullptr ||
         (e = cudaStreamCreateWithFlags(&h->util_stream, cudaStreamNonBlocking)) != cudaSuccess)
         return bail(fail(R2IQ_E_CUDA, "device setup: %s", cudaGetErrorString(e)));
     memset(h->carry, 0, sizeof(int16_t) * h->half);
@@ -725,17 +747,20 @@ int r2iq_cuda_destroy(r2iq_cuda_t h) {
         Slot& s = h->slots[i];
         cudaFree(s.d_out_rates);
         if (s.stream) cudaStreamDestroy(s.stream);
+        if (s.h2d_done) cudaEventDestroy(s.h2d_done);
         if (s.done) cudaEventDestroy(s.done);
+        if (s.carry) cudaFreeHost(s.carry);
         cudaFree(s.d_in);
         cudaFree(s.d_out);
         cudaFree(s.d_starts);
     }
     cudaFree(h->nco.d_tab);
+    cudaFree(h->nco.d_rot);
     cudaFree(h->nco.d_starts);
     if (h->util_stream) cudaStreamDestroy(h->util_stream);
     cudaFree(h->d_tw_fwd);
     cudaFree(h->d_work_counter);
-    if (h->carry) cudaFreeHost(h->carry);
+    free(h->carry);
     delete h;
     return R2IQ_OK;
 }
@@ -824,9 +849,19 @@ float r2iq_cuda_set_fine_tune(r2iq_cuda_t h, float fc) {
     }
     if (s.on && s.fc == fc) return fc;   // RadioHandler.cpp:292: the state restarts only when fc changes
     nco_init(s, fc);
+    s.phase = 0.0;                        // phase_start_rad = 0 (RadioHandler.cpp:295)
+    float rot[64];
+    for (int k = 0; k < 32; k++) {
+        double ph = (double)fc * 32.0 * (double)k;
+        ph = 2.0 * kPiD * (ph - floor(ph));
+        rot[2 * k] = (float)cos(ph);
+        rot[2 * k + 1] = (float)sin(ph);
+    }
     if (!s.d_tab && cudaMalloc(&s.d_tab, sizeof(float) * 66) != cudaSuccess) return 0.f;
-    // ordered after everything already queued: the table may still be read by launches in flight
+    if (!s.d_rot && cudaMalloc(&s.d_rot, sizeof(float) * 64) != cudaSuccess) return 0.f;
+    // ordered after everything already queued: the tables may still be read by launches in flight
     if (cudaDeviceSynchronize() != cudaSuccess ||
+        cudaMemcpy(s.d_rot, rot, sizeof(rot), cudaMemcpyHostToDevice) != cudaSuccess ||
         cudaMemcpy(s.d_tab, &s.tab[0][0], sizeof(float) * 66, cudaMemcpyHostToDevice) != cudaSuccess) {
         fail(R2IQ_E_CUDA, "fine-tune table upload failed");
         poison(h, g_err);
@@ -836,6 +871,18 @@ float r2iq_cuda_set_fine_tune(r2iq_cuda_t h, float fc) {
     return fc;
 }
 
+int r2iq_cuda_set_fine_tune_mode(r2iq_cuda_t h, int mode) {
+    int rc = check_handle(h);
+    if (rc) return rc;
+    if (mode != R2IQ_NCO_REFERENCE && mode != R2IQ_NCO_DIRECT) return fail(R2IQ_E_INVALID, "fine-tune mode %d", mode);
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (h->nco.on && h->nco.mode != mode)
+        return fail(R2IQ_E_STATE, "switch the fine-tune mixer off (fc = 0) before changing its mode: the two forms keep separate phase state");
+    h->nco.mode = mode;
+    return R2IQ_OK;
+}
+int r2iq_cuda_get_fine_tune_mode(r2iq_cuda_t h) { return h ? h->nco.mode : R2IQ_E_INVALID; }
+
 int r2iq_cuda_turn_on(r2iq_cuda_t h) {
     int rc = check_handle(h);
     if (rc) return rc;
@@ -844,13 +891,21 @@ int r2iq_cuda_turn_on(r2iq_cuda_t h) {
     h->latched_sideband = h->sideband.load();
     memset(h->carry, 0, sizeof(int16_t) * h->half);
     h->carry_valid = false;
+    for (int i = 0; i < kSlots; i++) {      // results nobody fetched before the last TurnOff are gone
+        if (h->slots[i].state != Slot::kFree && h->slots[i].done) cudaEventSynchronize(h->slots[i].done);
+        h->slots[i].state = Slot::kFree;
+    }
     h->on = true;
     return R2IQ_OK;
 }
 
 int r2iq_cuda_turn_off(r2iq_cuda_t h) {
     if (!h) return fail(R2IQ_E_INVALID, "null handle");
-    h->on = false;
+    {
+        std::lock_guard<std::mutex> lk(h->mu);
+        h->on = false;
+    }
+    h->cv.notify_all();                     // a submitter waiting for a held slot gives up
     if (h->poisoned) return R2IQ_OK;
     return r2iq_cuda_sync(h);
 }
@@ -858,57 +913,216 @@ int r2iq_cuda_is_on(r2iq_cuda_t h) { return h ? (int)h->on : 0; }
 
 long r2iq_cuda_out_per_block(r2iq_cuda_t h) { return h ? (long)((kTransferSamples / 2) >> h->latched_decimate) : 0; }
 
+// ---- host-buffer paths: a ring of kSlots submissions -----------------------------------------------------------
+}  // extern "C"
+
+namespace {
+
+// Next slot of the ring, free for a new submission.  An automatic slot is freed here by waiting for its work; a held
+// slot belongs to the caller until r2iq_cuda_release -- wait for that (another thread of the caller does it: the
+// ring-buffer adapter's publisher) unless the operator is switched off meanwhile.
+int acquire_slot(r2iq_cuda_t h, std::unique_lock<std::mutex>& lk, Slot** out) {
+    Slot& s = h->slots[h->next_ticket % kSlots];
+    while (s.state != Slot::kFree) {
+        if (s.state == Slot::kAuto) {
+            CU(h, cudaEventSynchronize(s.done));
+            s.state = Slot::kFree;
+        } else {
+            h->cv.wait(lk, [&] { return s.state != Slot::kHeld || !h->on || h->poisoned; });
+            if (s.state == Slot::kHeld)
+                return fail(R2IQ_E_STATE, "submission %llu still holds its result (r2iq_cuda_release) and the operator was switched off",
+                            (unsigned long long)s.ticket);
+        }
+    }
+    s.ticket = h->next_ticket++;
+    *out = &s;
+    return R2IQ_OK;
+}
+
+// [history | blocks] -> s.d_in on the slot's stream.  The history comes from the handle's carry (copied into the
+// slot's own pinned buffer: several submissions are in flight), which then moves on to the tail of these blocks.
+int upload_input(r2iq_cuda_t h, Slot& s, const int16_t* blocks, long nb) {
+    memcpy(s.carry, h->carry, sizeof(int16_t) * h->half);
+    CU(h, cudaMemcpyAsync(s.d_in, s.carry, sizeof(int16_t) * h->half, cudaMemcpyHostToDevice, s.stream));
+    CU(h, cudaMemcpyAsync(s.d_in + h->half, blocks, sizeof(int16_t) * (size_t)nb * kTransferSamples, cudaMemcpyHostToDevice,
+                          s.stream));
+    CU(h, cudaEventRecord(s.h2d_done, s.stream));
+    memcpy(h->carry, blocks + (size_t)nb * kTransferSamples - h->half, sizeof(int16_t) * h->half);
+    h->carry_valid = true;
+    h->stats.h2d_bytes += sizeof(int16_t) * ((size_t)h->half + (size_t)nb * kTransferSamples);
+    s.n_blocks = nb;
+    return R2IQ_OK;
+}
+
+// One submission of nb <= chunk_blocks blocks at the latched decimation; iq_out == nullptr keeps the result on the device.
+int submit(r2iq_cuda_t h, std::unique_lock<std::mutex>& lk, const int16_t* blocks, long nb, float* iq_out, uint64_t* ticket) {
+    Slot* sp = nullptr;
+    int rc = acquire_slot(h, lk, &sp);
+    if (rc != R2IQ_OK) return rc;
+    Slot& s = *sp;
+    s.d = h->latched_decimate;
+    if ((rc = upload_input(h, s, blocks, nb)) != R2IQ_OK) return rc;
+    if ((rc = launch(h, s.d_in, nb, s.d_out, s.stream, &s.d_starts, &s.starts_cap)) != R2IQ_OK) return rc;
+    if (iq_out) {
+        const size_t out_bytes = sizeof(float) * 2 * (size_t)nb * (size_t)((kTransferSamples / 2) >> s.d);
+        CU(h, cudaMemcpyAsync(iq_out, s.d_out, out_bytes, cudaMemcpyDeviceToHost, s.stream));
+        h->stats.d2h_bytes += out_bytes;
+    }
+    CU(h, cudaEventRecord(s.done, s.stream));
+    s.state = iq_out ? Slot::kAuto : Slot::kHeld;
+    if (ticket) *ticket = s.ticket;
+    return R2IQ_OK;
+}
+
+int drain_auto_slots(r2iq_cuda_t h) {
+    for (int i = 0; i < kSlots; i++) {
+        Slot& s = h->slots[i];
+        if (s.state == Slot::kAuto) {
+            CU(h, cudaEventSynchronize(s.done));
+            s.state = Slot::kFree;
+        }
+    }
+    return R2IQ_OK;
+}
+
+Slot* find_ticket(r2iq_cuda_t h, uint64_t ticket) {
+    Slot& s = h->slots[ticket % kSlots];
+    return (s.state != Slot::kFree && s.ticket == ticket) ? &s : nullptr;
+}
+
+}  // namespace
+
+extern "C" {
+
 int r2iq_cuda_process(r2iq_cuda_t h, const int16_t* blocks, long n_blocks, const int16_t* history, float* iq_out) {
     int rc = check_handle(h);
     if (rc) return rc;
     if (!h->on) return fail(R2IQ_E_STATE, "process called while the operator is off (call r2iq_cuda_turn_on)");
     if (n_blocks < 0 || (n_blocks > 0 && (!blocks || !iq_out))) return fail(R2IQ_E_INVALID, "process: bad buffers");
     if (n_blocks == 0) return R2IQ_OK;
-    std::lock_guard<std::mutex> lk(h->mu);
-    CU(h, cudaSetDevice(h->device));
+    std::unique_lock<std::mutex> lk(h->mu);
+    DeviceGuard dg(h->device);
+    CU(h, dg.err);
     if ((rc = ensure_slots(h)) != R2IQ_OK) return rc;
-    const int d = h->latched_decimate;
-    const size_t out_per_block = (size_t)((kTransferSamples / 2) >> d);
+    const size_t out_per_block = (size_t)((kTransferSamples / 2) >> h->latched_decimate);
     if (history) memcpy(h->carry, history, sizeof(int16_t) * h->half);
-    long done = 0;
-    int si = 0;
-    while (done < n_blocks) {
-        Slot& s = h->slots[si];
-        if (s.busy) {
-            CU(h, cudaEventSynchronize(s.done));
-            s.busy = false;
-        }
+    for (long done = 0; done < n_blocks;) {
         const long nb = (n_blocks - done) < h->chunk_blocks ? (n_blocks - done) : h->chunk_blocks;
-        if (done == 0) {
-            CU(h, cudaMemcpyAsync(s.d_in, h->carry, sizeof(int16_t) * h->half, cudaMemcpyHostToDevice, s.stream));
-            CU(h, cudaMemcpyAsync(s.d_in + h->half, blocks, sizeof(int16_t) * (size_t)nb * kTransferSamples,
-                                  cudaMemcpyHostToDevice, s.stream));
-        } else {
-            // history of this chunk = tail of the previous block, contiguous in the caller's buffer
-            CU(h, cudaMemcpyAsync(s.d_in, blocks + (size_t)done * kTransferSamples - h->half,
-                                  sizeof(int16_t) * ((size_t)h->half + (size_t)nb * kTransferSamples),
-                                  cudaMemcpyHostToDevice, s.stream));
-        }
-        h->stats.h2d_bytes += sizeof(int16_t) * ((size_t)h->half + (size_t)nb * kTransferSamples);
-        if ((rc = launch(h, s.d_in, nb, s.d_out, s.stream, &s.d_starts, &s.starts_cap)) != R2IQ_OK) return rc;
-        const size_t out_bytes = sizeof(float) * 2 * (size_t)nb * out_per_block;
-        CU(h, cudaMemcpyAsync(iq_out + 2 * (size_t)done * out_per_block, s.d_out, out_bytes, cudaMemcpyDeviceToHost,
-                              s.stream));
-        h->stats.d2h_bytes += out_bytes;
-        CU(h, cudaEventRecord(s.done, s.stream));
-        s.busy = true;
+        rc = submit(h, lk, blocks + (size_t)done * kTransferSamples, nb, iq_out + 2 * (size_t)done * out_per_block, nullptr);
+        if (rc != R2IQ_OK) return rc;
         done += nb;
-        si = (si + 1) % kSlots;
     }
-    // the first chunk reads h->carry asynchronously: drain before overwriting it
-    for (int i = 0; i < kSlots; i++) {
-        if (h->slots[i].busy) {
-            CU(h, cudaEventSynchronize(h->slots[i].done));
-            h->slots[i].busy = false;
-        }
+    return drain_auto_slots(h);   // returns when iq_out is complete
+}
+
+int r2iq_cuda_process_async(r2iq_cuda_t h, const int16_t* blocks, long n_blocks, const int16_t* history, float* iq_out,
+                            uint64_t* ticket) {
+    int rc = check_handle(h);
+    if (rc) return rc;
+    if (!h->on) return fail(R2IQ_E_STATE, "process_async called while the operator is off (call r2iq_cuda_turn_on)");
+    if (!ticket || n_blocks < 1 || !blocks) return fail(R2IQ_E_INVALID, "process_async: bad arguments");
+    if (n_blocks > h->chunk_blocks)
+        return fail(R2IQ_E_INVALID, "process_async: %ld blocks exceed one submission (chunk_blocks = %d)", n_blocks, h->chunk_blocks);
+    std::unique_lock<std::mutex> lk(h->mu);
+    DeviceGuard dg(h->device);
+    CU(h, dg.err);
+    if ((rc = ensure_slots(h)) != R2IQ_OK) return rc;
+    if (history) memcpy(h->carry, history, sizeof(int16_t) * h->half);
+    return submit(h, lk, blocks, n_blocks, iq_out, ticket);
+}
+
+int r2iq_cuda_wait_input(r2iq_cuda_t h, uint64_t ticket) {
+    int rc = check_handle(h);
+    if (rc) return rc;
+    cudaEvent_t ev;
+    {
+        std::lock_guard<std::mutex> lk(h->mu);
+        Slot* s = find_ticket(h, ticket);
+        if (!s) return R2IQ_OK;            // already waited for and recycled: its input left the host long ago
+        ev = s->h2d_done;
     }
-    memcpy(h->carry, blocks + (size_t)n_blocks * kTransferSamples - h->half, sizeof(int16_t) * h->half);
-    h->carry_valid = true;
+    DeviceGuard dg(h->device);
+    CU(h, dg.err);
+    CU(h, cudaEventSynchronize(ev));
+    return R2IQ_OK;
+}
+
+int r2iq_cuda_wait(r2iq_cuda_t h, uint64_t ticket) {
+    int rc = check_handle(h);
+    if (rc) return rc;
+    cudaEvent_t ev;
+    {
+        std::lock_guard<std::mutex> lk(h->mu);
+        Slot* s = find_ticket(h, ticket);
+        if (!s) return R2IQ_OK;
+        ev = s->done;
+    }
+    DeviceGuard dg(h->device);
+    CU(h, dg.err);
+    CU(h, cudaEventSynchronize(ev));
+    std::lock_guard<std::mutex> lk(h->mu);
+    Slot* s = find_ticket(h, ticket);
+    if (s && s->state == Slot::kAuto) s->state = Slot::kFree;
+    return R2IQ_OK;
+}
+
+int r2iq_cuda_read(r2iq_cuda_t h, uint64_t ticket, long first_complex, long n_complex, float* dst) {
+    int rc = check_handle(h);
+    if (rc) return rc;
+    cudaStream_t stream;
+    const float* src;
+    {
+        std::lock_guard<std::mutex> lk(h->mu);
+        Slot* s = find_ticket(h, ticket);
+        if (!s || s->state != Slot::kHeld) return fail(R2IQ_E_STATE, "read: ticket %llu holds no result", (unsigned long long)ticket);
+        const long have = s->n_blocks * (long)((kTransferSamples / 2) >> s->d);
+        if (first_complex < 0 || n_complex < 0 || first_complex + n_complex > have || (n_complex > 0 && !dst))
+            return fail(R2IQ_E_INVALID, "read: [%ld, %ld) outside the %ld complex samples of ticket %llu", first_complex,
+                        first_complex + n_complex, have, (unsigned long long)ticket);
+        stream = s->stream;
+        src = s->d_out + 2 * (size_t)first_complex;
+        h->stats.d2h_bytes += sizeof(float) * 2 * (size_t)n_complex;
+    }
+    if (n_complex == 0) return R2IQ_OK;
+    DeviceGuard dg(h->device);
+    CU(h, dg.err);
+    // same stream as the kernel: ordered behind it without an event
+    CU(h, cudaMemcpyAsync(dst, src, sizeof(float) * 2 * (size_t)n_complex, cudaMemcpyDeviceToHost, stream));
+    CU(h, cudaStreamSynchronize(stream));
+    return R2IQ_OK;
+}
+
+int r2iq_cuda_release(r2iq_cuda_t h, uint64_t ticket) {
+    if (!h) return fail(R2IQ_E_INVALID, "null handle");
+    {
+        std::lock_guard<std::mutex> lk(h->mu);
+        Slot* s = find_ticket(h, ticket);
+        if (s && s->state == Slot::kHeld) s->state = Slot::kFree;   // its stream is idle: every read was synchronous
+    }
+    h->cv.notify_all();
+    return R2IQ_OK;
+}
+
+int r2iq_cuda_host_register(void* p, size_t bytes) {
+    if (!p || !bytes) return fail(R2IQ_E_INVALID, "host_register: null range");
+    cudaError_t e = cudaHostRegister(p, bytes, cudaHostRegisterPortable);
+    if (e == cudaErrorHostMemoryAlreadyRegistered) {
+        cudaGetLastError();
+        return R2IQ_OK;
+    }
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(R2IQ_E_NOMEM, "cudaHostRegister(%zu bytes): %s", bytes, cudaGetErrorString(e));
+    }
+    return R2IQ_OK;
+}
+int r2iq_cuda_host_unregister(void* p) {
+    if (!p) return R2IQ_OK;
+    cudaError_t e = cudaHostUnregister(p);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(R2IQ_E_INVALID, "cudaHostUnregister: %s", cudaGetErrorString(e));
+    }
     return R2IQ_OK;
 }
 
@@ -931,34 +1145,21 @@ int r2iq_cuda_process_rates(r2iq_cuda_t h, const int16_t* blocks, long n_blocks,
     if (h->nco.on) return fail(R2IQ_E_STATE, "process_rates: the fine-tune mixer belongs to one rate; switch it off first");
     if (n_blocks < 0 || (n_blocks > 0 && !blocks)) return fail(R2IQ_E_INVALID, "process_rates: bad buffers");
     if (n_blocks == 0) return R2IQ_OK;
-    std::lock_guard<std::mutex> lk(h->mu);
-    CU(h, cudaSetDevice(h->device));
+    std::unique_lock<std::mutex> lk(h->mu);
+    DeviceGuard dg(h->device);
+    CU(h, dg.err);
     if ((rc = ensure_slots(h)) != R2IQ_OK) return rc;
-    // a chunk's output at every rate: sum over d of 32768 >> d  <  2 * 32768 complex per block
     const size_t rates_floats = 2 * 2 * (size_t)h->chunk_blocks * (kTransferSamples / 2);
     for (int i = 0; i < kSlots; i++)
         if (!h->slots[i].d_out_rates) CU(h, cudaMalloc(&h->slots[i].d_out_rates, sizeof(float) * rates_floats));
     if (history) memcpy(h->carry, history, sizeof(int16_t) * h->half);
     const int latched = h->latched_decimate;
-    long done = 0;
-    int si = 0;
-    while (done < n_blocks && rc == R2IQ_OK) {
-        Slot& s = h->slots[si];
-        if (s.busy) {
-            CU(h, cudaEventSynchronize(s.done));
-            s.busy = false;
-        }
+    for (long done = 0; done < n_blocks && rc == R2IQ_OK;) {
         const long nb = (n_blocks - done) < h->chunk_blocks ? (n_blocks - done) : h->chunk_blocks;
-        if (done == 0) {
-            CU(h, cudaMemcpyAsync(s.d_in, h->carry, sizeof(int16_t) * h->half, cudaMemcpyHostToDevice, s.stream));
-            CU(h, cudaMemcpyAsync(s.d_in + h->half, blocks, sizeof(int16_t) * (size_t)nb * kTransferSamples,
-                                  cudaMemcpyHostToDevice, s.stream));
-        } else {
-            CU(h, cudaMemcpyAsync(s.d_in, blocks + (size_t)done * kTransferSamples - h->half,
-                                  sizeof(int16_t) * ((size_t)h->half + (size_t)nb * kTransferSamples),
-                                  cudaMemcpyHostToDevice, s.stream));
-        }
-        h->stats.h2d_bytes += sizeof(int16_t) * ((size_t)h->half + (size_t)nb * kTransferSamples);
+        Slot* sp = nullptr;
+        if ((rc = acquire_slot(h, lk, &sp)) != R2IQ_OK) break;
+        Slot& s = *sp;
+        if ((rc = upload_input(h, s, blocks + (size_t)done * kTransferSamples, nb)) != R2IQ_OK) break;
         size_t off = 0;   // floats into d_out_rates
         for (int r = 0; r < n_rates && rc == R2IQ_OK; r++) {
             const int d = decimations[r];
@@ -980,20 +1181,11 @@ int r2iq_cuda_process_rates(r2iq_cuda_t h, const int16_t* blocks, long n_blocks,
         h->latched_decimate = latched;
         if (rc != R2IQ_OK) break;
         CU(h, cudaEventRecord(s.done, s.stream));
-        s.busy = true;
+        s.state = Slot::kAuto;
         done += nb;
-        si = (si + 1) % kSlots;
     }
-    for (int i = 0; i < kSlots; i++) {
-        if (h->slots[i].busy) {
-            CU(h, cudaEventSynchronize(h->slots[i].done));
-            h->slots[i].busy = false;
-        }
-    }
-    if (rc != R2IQ_OK) return rc;
-    memcpy(h->carry, blocks + (size_t)n_blocks * kTransferSamples - h->half, sizeof(int16_t) * h->half);
-    h->carry_valid = true;
-    return R2IQ_OK;
+    const int rc2 = drain_auto_slots(h);
+    return rc != R2IQ_OK ? rc : rc2;
 }
 
 int r2iq_cuda_process_device(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d_iq_out, void* stream) {

@@ -267,7 +267,7 @@ cudaError_t launch_fused(int d, const FusedParams& p, int sm_count, cudaStream_t
     //   generation 0 (default): r2iq_pair.cu -- 8 free-running warps per SM for d = 0, 12 for d = 1..5
     //   (B200, 8192 blocks: 514 / 597 / 788 / 905 / 977 / 994 Gsamples/s against 454 / 601 / 759 / 865 / 929 / 963 of
     //   the round-1 kernels below, which stay reachable as generation 5 for A/B runs)
-    if (g_kernel_gen == 0 && d <= 5) return launch_pair(d, d == 0 ? 8 : 12, p, sm_count, stream);
+    if (g_kernel_gen == 0) return launch_pair(d, d == 0 ? 8 : 12, p, sm_count, stream);
     if (g_kernel_gen == 5 || g_kernel_gen == 4) {
         if (d == 0) return launch_dual_d0(p, sm_count, stream, true);
         if (d == 1 && g_kernel_gen == 5) return launch_dual_d1(p, sm_count, stream, true);
@@ -314,6 +314,36 @@ __global__ void nco_mix_kernel(float2* __restrict__ iq, long long n, const float
         iq[i] = make_float2(__fsub_rn(__fmul_rn(v.x, ph.x), __fmul_rn(v.y, ph.y)),
                             __fadd_rn(__fmul_rn(v.y, ph.x), __fmul_rn(v.x, ph.y)));
     }
+}
+
+// Direct-phase mixer as a stand-alone in-place pass: one accurate phasor per thread and trip, then 4 samples by
+// multiplying with exp(2 pi j fc k), k = 1..3 (rounding of the order of the float32 ulp).
+__global__ void nco_mix_direct_kernel(float2* __restrict__ iq, long long n, double phase0, double fc) {
+    float2 step[3];
+#pragma unroll
+    for (int k = 0; k < 3; k++) step[k] = nco_direct_phasor(0.0, fc, k + 1);
+    long long i = (blockIdx.x * (long long)blockDim.x + threadIdx.x) * 4;
+    const long long stride = (long long)gridDim.x * blockDim.x * 4;
+    for (; i < n; i += stride) {
+        const float2 ph0 = nco_direct_phasor(phase0, fc, i);
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            if (i + k >= n) break;
+            float2 ph = ph0;
+            if (k) ph = make_float2(ph0.x * step[k - 1].x - ph0.y * step[k - 1].y, ph0.x * step[k - 1].y + ph0.y * step[k - 1].x);
+            const float2 v = iq[i + k];
+            iq[i + k] = make_float2(v.x * ph.x - v.y * ph.y, v.x * ph.y + v.y * ph.x);
+        }
+    }
+}
+
+cudaError_t launch_nco_mix_direct(float* iq, long long n_complex, double phase0, double fc, cudaStream_t stream) {
+    if (n_complex <= 0) return cudaSuccess;
+    long long blocks = (n_complex / 4 + 255) / 256;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    if (blocks < 1) blocks = 1;
+    nco_mix_direct_kernel<<<(unsigned)blocks, 256, 0, stream>>>((float2*)iq, n_complex, phase0, fc);
+    return cudaGetLastError();
 }
 
 cudaError_t launch_nco_mix(float* iq, long long n_complex, const float* starts, const float* tab, cudaStream_t stream) {

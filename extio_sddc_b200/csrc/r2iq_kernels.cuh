@@ -36,6 +36,11 @@ struct FusedParams {
     // start phasors of every 128-sample block of this launch's output and the 33-entry group table, as nco_mix_kernel
     const float2* nco_starts;
     const float2* nco_tab;
+    // Direct-phase form of the same mixer (R2IQ_NCO_DIRECT; null = off): output sample i of this launch is multiplied
+    // by exp(2 pi j (nco_phase0 + nco_fc * i)); nco_rot[k] = exp(2 pi j nco_fc * 32 k), k < 32.  No host recurrence.
+    const float2* nco_rot;
+    double nco_phase0;          // cycles, in [0, 1)
+    double nco_fc;              // cycles per output sample
 };
 // bit 5 of a kernel's kVar: multiply every output sample by the fine-tune phasor before it is stored
 constexpr int kVarMix = 32;
@@ -57,6 +62,15 @@ __device__ __forceinline__ float2 nco_mix_sample(float2 v, long long i, const fl
     }
     return make_float2(__fsub_rn(__fmul_rn(v.x, ph.x), __fmul_rn(v.y, ph.y)),
                        __fadd_rn(__fmul_rn(v.y, ph.x), __fmul_rn(v.x, ph.y)));
+}
+// Direct-phase mixer: the phasor of output sample i, argument reduced in float64 (fc * i reaches 2^27 cycles within
+// one launch), sine and cosine in float32.
+__device__ __forceinline__ float2 nco_direct_phasor(double phase0, double fc, long long i) {
+    double ph = fma(fc, (double)i, phase0);
+    ph -= floor(ph);
+    float s, c;
+    sincospif((float)(2.0 * ph), &s, &c);
+    return make_float2(c, s);
 }
 #endif
 // Measurement variants of the persistent kernels (env R2IQ_VARIANT, read at every launch): bit 0 = dynamic work
@@ -134,6 +148,8 @@ cudaError_t launch_pair(int d, int warps, const FusedParams& p, int sm_count, cu
 cudaError_t setup_fused_kernels();
 // Fine-tune NCO applied in place to n_complex output samples (see nco_mix_kernel).
 cudaError_t launch_nco_mix(float* iq, long long n_complex, const float* starts, const float* tab, cudaStream_t stream);
+// The direct-phase form as a stand-alone pass (kernel families without a mixing epilogue: FFTN 8192).
+cudaError_t launch_nco_mix_direct(float* iq, long long n_complex, double phase0, double fc, cudaStream_t stream);
 // int16 -> float with optional de-randomisation (the bit-exact stage, exposed for parity tests).
 cudaError_t launch_convert(const int16_t* in, float* out, long long n, int rand, cudaStream_t stream);
 

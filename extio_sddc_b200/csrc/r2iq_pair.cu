@@ -34,10 +34,18 @@ __host__ __device__ constexpr int pair_warp_bytes() {
 }
 // tables: d = 0: tw_fwd, tw_inv, gp, gq (4 x 8 KB); d >= 1: tw_fwd (8 KB) + tw_aux ((R + 32) x 256 B); gp/gq stay
 // in global memory there (R <= 16 loads per frame pair)
+// d = 0 keeps its four tables TRANSPOSED, [lane][34]: rows k and k+1 of a lane are 16 contiguous bytes, one LDS.128
+// (pitch 34 float2 = 272 B keeps the eight lanes of a quarter-warp on distinct bank groups)
+constexpr int kTabPitch = 34;
 template <int D>
 __host__ __device__ constexpr int pair_table_float2() {
-    return D == 0 ? 4 * 1024 : 1024 + ((32 >> D) + 32) * 32;
+    return D == 0 ? 4 * 32 * kTabPitch : D == 6 ? 1024 + 16 : 1024 + ((32 >> D) + 32) * 32;
 }
+// d = 6: exp(+2 pi i j / 16), the 16-point backward transform's twiddles
+#define R2IQ_W16(j) {(float)cx_cos2pi(j, 16), (float)cx_sin2pi(j, 16)}
+__constant__ float2 kW16[16] = {R2IQ_W16(0), R2IQ_W16(1), R2IQ_W16(2),  R2IQ_W16(3),  R2IQ_W16(4),  R2IQ_W16(5),  R2IQ_W16(6),  R2IQ_W16(7),
+                                R2IQ_W16(8), R2IQ_W16(9), R2IQ_W16(10), R2IQ_W16(11), R2IQ_W16(12), R2IQ_W16(13), R2IQ_W16(14), R2IQ_W16(15)};
+#undef R2IQ_W16
 template <int D, int W>
 __host__ __device__ constexpr int pair_smem_bytes() {
     return pair_table_float2<D>() * 8 + W * pair_warp_bytes<W>();
@@ -64,13 +72,33 @@ __device__ __forceinline__ c2 lds2r(const u64* S, int idx) {
     return v;
 }
 
+// Direct-phase mixer on the packed lanes: the phasors of the two frames' samples at output positions ia / ib ...
+__device__ __forceinline__ c2 direct_phasors(const FusedParams& p, long long ia, long long ib) {
+    const float2 pa = nco_direct_phasor(p.nco_phase0, p.nco_fc, ia);
+    const float2 pb = nco_direct_phasor(p.nco_phase0, p.nco_fc, ib);
+    c2 ph;
+    ph.re = pk(pa.x, pb.x);
+    ph.im = pk(pa.y, pb.y);
+    return ph;
+}
+// ... advanced by `rot` (32 k samples further on: the lane's k-th stored row) and applied to t after the sideband
+// conjugation (the mixer follows the operator, Core/RadioHandler.cpp:33-37): 9 packed instructions per row
+__device__ __forceinline__ c2 direct_mix(c2 t, c2 ph0, float2 rot, float imag_sign) {
+    const c2 ph = cmul2s(ph0, rot);
+    const u64 ti = mul2(bc(imag_sign), t.im);
+    c2 o;
+    o.re = fma2(t.re, ph.re, neg2(mul2(ti, ph.im)));
+    o.im = fma2(t.re, ph.im, mul2(ti, ph.re));
+    return o;
+}
+
 }  // namespace
 
-template <int D, int W, bool kMix>
+template <int D, int W, int kMix>
 __global__ void __launch_bounds__(W * 32, 1) r2iq_pair_kernel(const FusedParams p) {
     constexpr bool kLandInTile = W == 12;
     constexpr int M = kHalfFft >> D;
-    constexpr int R = 32 >> D;            // band bins per lane (d >= 1)
+    constexpr int R = D == 6 ? 1 : 32 >> D;   // band bins per lane (d = 1..5; d = 6: one bin on each of 16 lanes)
     constexpr int G = 32 / R;             // lanes sharing one 32-point DFT in pass 2 of the backward transform
     constexpr int RB = ilog2(R);
     static_assert(D == 0 || 2 * 32 * (R + 1) * 8 <= kLandOff, "backward transposition overlaps the landing zone");
@@ -87,14 +115,19 @@ __global__ void __launch_bounds__(W * 32, 1) r2iq_pair_kernel(const FusedParams 
     const uint32_t dst = smem_u32(inA);
 
     // ---- tables -> shared memory ------------------------------------------------------------------------------
-    for (int i = threadIdx.x; i < 1024; i += W * 32) tab[i] = __ldg(p.tw_fwd + i);
     if constexpr (D == 0) {
         for (int i = threadIdx.x; i < 1024; i += W * 32) {
-            tab[1024 + i] = __ldg(p.tw_inv + i);
-            tab[2048 + i] = __ldg(p.gp + i);
-            tab[3072 + i] = __ldg(p.gq + i);
+            const int o = (i & 31) * kTabPitch + (i >> 5);      // [row][lane] -> [lane][row]
+            tab[o] = __ldg(p.tw_fwd + i);
+            tab[32 * kTabPitch + o] = __ldg(p.tw_inv + i);
+            tab[64 * kTabPitch + o] = __ldg(p.gp + i);
+            tab[96 * kTabPitch + o] = __ldg(p.gq + i);
         }
+    } else if constexpr (D == 6) {
+        for (int i = threadIdx.x; i < 1024; i += W * 32) tab[i] = __ldg(p.tw_fwd + i);
+        if (threadIdx.x < 16) tab[1024 + threadIdx.x] = kW16[threadIdx.x];
     } else {
+        for (int i = threadIdx.x; i < 1024; i += W * 32) tab[i] = __ldg(p.tw_fwd + i);
         for (int i = threadIdx.x; i < (R + 32) * 32; i += W * 32) tab[1024 + i] = __ldg(p.tw_aux + i);
     }
     if (lane == 0) {
@@ -127,7 +160,7 @@ __global__ void __launch_bounds__(W * 32, 1) r2iq_pair_kernel(const FusedParams 
     if (lane == 0 && q < n_pairs) issue(q);
     uint32_t phase = 0;
 
-    const float2* twf = tab + lane;
+    const float2* twf = tab + (D == 0 ? lane * kTabPitch : lane);
     const uint32_t sgn = __float_as_uint(p.imag_sign) & 0x80000000u;   // sideband inversion as a sign-bit flip
 
     while (q < n_pairs) {
@@ -148,8 +181,17 @@ __global__ void __launch_bounds__(W * 32, 1) r2iq_pair_kernel(const FusedParams 
 
         // ---- forward 1024-point transform of z = x[2n] + i x[2n+1] ------------------------------
         dit2<32, false>(v);
+        if constexpr (D == 0) {
 #pragma unroll
-        for (int k2 = 1; k2 < 32; k2++) v[k2] = cmul2s(v[k2], twf[32 * k2]);
+            for (int k2 = 0; k2 < 32; k2 += 2) {
+                const float4 w = *reinterpret_cast<const float4*>(twf + k2);
+                if (k2) v[k2] = cmul2s(v[k2], make_float2(w.x, w.y));
+                v[k2 + 1] = cmul2s(v[k2 + 1], make_float2(w.z, w.w));
+            }
+        } else {
+#pragma unroll
+            for (int k2 = 1; k2 < 32; k2++) v[k2] = cmul2s(v[k2], twf[32 * k2]);
+        }
 #pragma unroll
         for (int k2 = 0; k2 < 32; k2++) sts2(S, lane * 33 + k2, v[k2]);
         __syncwarp();
@@ -159,31 +201,39 @@ __global__ void __launch_bounds__(W * 32, 1) r2iq_pair_kernel(const FusedParams 
         dit2<32, false>(v);                       // v[k1] = Z[32*k1 + lane]
 
         if constexpr (D == 0) {
-            // ---- real-FFT split + tune rotation + filter, in place; mirror bins through shared memory ----
-            const float2* twi = tab + 1024 + lane;
-            const float2* gp = tab + 2048 + lane;
-            const float2* gq = tab + 3072 + lane;
+            // ---- real-FFT split + tune rotation + filter, in place ---------------------------------------
+            const float2* twi = tab + 32 * kTabPitch + lane * kTabPitch;
+            const float2* gp = tab + 64 * kTabPitch + lane * kTabPitch;
+            const float2* gq = tab + 96 * kTabPitch + lane * kTabPitch;
             const int n1_inv = (lane - p.tunebin) & 31;
             c2 t[32];
 #pragma unroll
             for (int k1 = 0; k1 < 32; k1++) sts2(S, 32 * k1 + lane, v[k1]);
             __syncwarp();
 #pragma unroll
-            for (int k1 = 0; k1 < 32; k1++) {
-                const c2 a = v[k1];
-                const c2 b = lds2(S, (kHalfFft - (32 * k1 + lane)) & (kHalfFft - 1));
-                const float2 P = gp[32 * k1];
-                const float2 Q = gq[32 * k1];
-                c2 y;
-                y.re = fma2(bc(Q.y), b.im, fma2(bc(Q.x), b.re, fma2(bc(-P.y), a.im, mul2(bc(P.x), a.re))));
-                y.im = fma2(bc(Q.y), b.re, fma2(bc(-Q.x), b.im, fma2(bc(P.y), a.re, mul2(bc(P.x), a.im))));
-                t[brev5(k1)] = y;                     // bit-reversed placement for the backward pass
+            for (int k1 = 0; k1 < 32; k1 += 2) {
+                const float4 P = *reinterpret_cast<const float4*>(gp + k1);
+                const float4 Q = *reinterpret_cast<const float4*>(gq + k1);
+#pragma unroll
+                for (int e = 0; e < 2; e++) {
+                    const float Px = e ? P.z : P.x, Py = e ? P.w : P.y, Qx = e ? Q.z : Q.x, Qy = e ? Q.w : Q.y;
+                    const c2 a = v[k1 + e];
+                    const c2 b = lds2(S, (kHalfFft - (32 * (k1 + e) + lane)) & (kHalfFft - 1));
+                    c2 y;
+                    y.re = fma2(bc(Qy), b.im, fma2(bc(Qx), b.re, fma2(bc(-Py), a.im, mul2(bc(Px), a.re))));
+                    y.im = fma2(bc(Qy), b.re, fma2(bc(-Qx), b.im, fma2(bc(Py), a.re, mul2(bc(Px), a.im))));
+                    t[brev5(k1 + e)] = y;             // bit-reversed placement for the backward pass
+                }
             }
             __syncwarp();
             // ---- backward 1024-point transform; lane l is residue (l - tunebin) mod 32 ---------------
             dit2<32, true>(t);
 #pragma unroll
-            for (int k2 = 1; k2 < 32; k2++) t[k2] = cmul2s(t[k2], twi[32 * k2]);
+            for (int k2 = 0; k2 < 32; k2 += 2) {
+                const float4 w = *reinterpret_cast<const float4*>(twi + k2);
+                if (k2) t[k2] = cmul2s(t[k2], make_float2(w.x, w.y));
+                t[k2 + 1] = cmul2s(t[k2 + 1], make_float2(w.z, w.w));
+            }
 #pragma unroll
             for (int k2 = 0; k2 < 32; k2++) sts2(S, n1_inv * 33 + k2, t[k2]);
             __syncwarp();
@@ -195,21 +245,76 @@ __global__ void __launch_bounds__(W * 32, 1) r2iq_pair_kernel(const FusedParams 
             // ---- overlap-save discard + placement (impl.hpp:117-138) --------------------------------
             const FrameOut2 oa = frame_out2<0>(2 * q, p.total_frames);
             const FrameOut2 ob = frame_out2<0>(2 * q + 1, p.total_frames);
+            c2 ph0;
+            if constexpr (kMix == 2) ph0 = direct_phasors(p, oa.base + lane, ob.base + lane);
 #pragma unroll
-            for (int k1 = 0; k1 < 24; k1++) {         // idx >= 768 is always discarded
+            for (int k1 = 0; k1 < 24; k1++) {     // idx >= 768 is always discarded
                 const int idx = lane + 32 * k1;
+                if constexpr (kMix == 2) t[k1] = direct_mix(t[k1], ph0, __ldg(p.nco_rot + k1), p.imag_sign);
                 float ar, br, ai, bi;
                 upk(t[k1].re, ar, br);
                 upk(t[k1].im, ai, bi);
                 if (idx >= oa.lo) {
-                    float2 va = make_float2(ar, flip(ai, sgn));
-                    if constexpr (kMix) va = nco_mix_sample(va, oa.base + idx, p.nco_starts, p.nco_tab);
+                    float2 va = kMix == 2 ? make_float2(ar, ai) : make_float2(ar, flip(ai, sgn));
                     p.out[oa.base + idx] = va;
                 }
                 if (ob.live && idx >= ob.lo) {
-                    float2 vb = make_float2(br, flip(bi, sgn));
-                    if constexpr (kMix) vb = nco_mix_sample(vb, ob.base + idx, p.nco_starts, p.nco_tab);
+                    float2 vb = kMix == 2 ? make_float2(br, bi) : make_float2(br, flip(bi, sgn));
                     p.out[ob.base + idx] = vb;
+                }
+            }
+        } else if constexpr (D == 6) {
+            // ---- d = 6 (mfft 16 < 32 lanes): lane m < 16 cuts band bin m, then lane n < 16 sums its output sample
+            //      y[n] = sum_m Y[m] exp(+2 pi i m n / 16) from shared memory (16 broadcast reads); both frames packed
+#pragma unroll
+            for (int k1 = 0; k1 < 32; k1++)
+                if ((p.row_mask >> k1) & 1u) sts2(S, 32 * k1 + lane, v[k1]);
+            __syncwarp();
+            const int m = lane & 15;
+            const int s6 = m < 8 ? m : m - 16;                          // upper half of the band is below the tune bin
+            const int kk = (p.tunebin + s6) & (kHalfFft - 1);
+            c2 r;
+            {
+                const c2 a = lds2(S, kk);
+                const c2 b = lds2(S, (kHalfFft - kk) & (kHalfFft - 1));
+                const float2 P = __ldg(p.gp + kk);
+                const float2 Q = __ldg(p.gq + kk);
+                r.re = fma2(bc(Q.y), b.im, fma2(bc(Q.x), b.re, fma2(bc(-P.y), a.im, mul2(bc(P.x), a.re))));
+                r.im = fma2(bc(Q.y), b.re, fma2(bc(-Q.x), b.im, fma2(bc(P.y), a.re, mul2(bc(P.x), a.im))));
+            }
+            __syncwarp();   // every lane is done with the spectrum: the tile is free
+            if (lane == 0 && qn < n_pairs) {
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                issue(qn);
+            }
+            if (lane < 16) sts2r<1>(S, lane, r);                        // planes of 64 elements at the head of the tile
+            __syncwarp();
+            const float2* w16 = tab + 1024;
+            c2 acc;
+            acc.re = acc.im = bc(0.0f);
+#pragma unroll
+            for (int mm = 0; mm < 16; mm++) {
+                const c2 x = lds2r<1>(S, mm);
+                const float2 w = w16[(mm * m) & 15];
+                acc.re = fma2(bc(w.x), x.re, fma2(bc(-w.y), x.im, acc.re));
+                acc.im = fma2(bc(w.x), x.im, fma2(bc(w.y), x.re, acc.im));
+            }
+            __syncwarp();
+            const FrameOut2 oa = frame_out2<6>(2 * q, p.total_frames);
+            const FrameOut2 ob = frame_out2<6>(2 * q + 1, p.total_frames);
+            if constexpr (kMix == 2)
+                acc = direct_mix(acc, direct_phasors(p, oa.base + lane, ob.base + lane), make_float2(1.0f, 0.0f), p.imag_sign);
+            float ar, br, ai, bi;
+            upk(acc.re, ar, br);
+            upk(acc.im, ai, bi);
+            if (lane < 3 * M / 4) {
+                if (lane >= oa.lo) {
+                    float2 va = kMix == 2 ? make_float2(ar, ai) : make_float2(ar, flip(ai, sgn));
+                    p.out[oa.base + lane] = va;
+                }
+                if (ob.live && lane >= ob.lo) {
+                    float2 vb = kMix == 2 ? make_float2(br, bi) : make_float2(br, flip(bi, sgn));
+                    p.out[ob.base + lane] = vb;
                 }
             }
         } else {
@@ -276,20 +381,21 @@ __global__ void __launch_bounds__(W * 32, 1) r2iq_pair_kernel(const FusedParams 
             const FrameOut2 oa = frame_out2<D>(2 * q, p.total_frames);
             const FrameOut2 ob = frame_out2<D>(2 * q + 1, p.total_frames);
             const int idx0 = k2p + R * h;
+            c2 ph0;
+            if constexpr (kMix == 2) ph0 = direct_phasors(p, oa.base + idx0, ob.base + idx0);
 #pragma unroll
             for (int q4 = 0; q4 < R; q4++) {
                 const int idx = idx0 + 32 * q4;
+                if constexpr (kMix == 2) t[q4] = direct_mix(t[q4], ph0, __ldg(p.nco_rot + q4), p.imag_sign);
                 float ar, br, ai, bi;
                 upk(t[q4].re, ar, br);
                 upk(t[q4].im, ai, bi);
                 if (idx >= oa.lo && idx < 3 * M / 4) {
-                    float2 va = make_float2(ar, flip(ai, sgn));
-                    if constexpr (kMix) va = nco_mix_sample(va, oa.base + idx, p.nco_starts, p.nco_tab);
+                    float2 va = kMix == 2 ? make_float2(ar, ai) : make_float2(ar, flip(ai, sgn));
                     p.out[oa.base + idx] = va;
                 }
                 if (ob.live && idx >= ob.lo && idx < 3 * M / 4) {
-                    float2 vb = make_float2(br, flip(bi, sgn));
-                    if constexpr (kMix) vb = nco_mix_sample(vb, ob.base + idx, p.nco_starts, p.nco_tab);
+                    float2 vb = kMix == 2 ? make_float2(br, bi) : make_float2(br, flip(bi, sgn));
                     p.out[ob.base + idx] = vb;
                 }
             }
@@ -299,7 +405,7 @@ __global__ void __launch_bounds__(W * 32, 1) r2iq_pair_kernel(const FusedParams 
     }
 }
 
-template <int D, int W, bool kMix>
+template <int D, int W, int kMix>
 static cudaError_t setup_pair_one() {
     cudaError_t e = cudaFuncSetAttribute(r2iq_pair_kernel<D, W, kMix>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          pair_smem_bytes<D, W>());
@@ -308,7 +414,7 @@ static cudaError_t setup_pair_one() {
                                 cudaSharedmemCarveoutMaxShared);
 }
 
-template <int D, int W, bool kMix>
+template <int D, int W, int kMix>
 static cudaError_t launch_pair_one(const FusedParams& p, int sm_count, cudaStream_t stream) {
     const long long n_pairs = (p.total_frames + 1) / 2;
     long long grid = sm_count;                 // persistent: one CTA per SM
@@ -321,25 +427,25 @@ static cudaError_t launch_pair_one(const FusedParams& p, int sm_count, cudaStrea
     return cudaGetLastError();
 }
 
-// (D, W) combinations that are built: W = 8 for every d, W = 12 for d >= 1
+// (D, W) combinations that are built
 #define R2IQ_PAIR_FOR_ALL(X) \
-    X(0, 8) X(1, 8) X(2, 8) X(3, 8) X(4, 8) X(5, 8) X(1, 12) X(2, 12) X(3, 12) X(4, 12) X(5, 12)
+    X(0, 8) X(1, 8) X(1, 12) X(2, 12) X(3, 12) X(4, 12) X(5, 12) X(6, 12)
 
 cudaError_t setup_pair_kernels() {
     cudaError_t e;
-#define X(D, W)                                                        \
-    if ((e = setup_pair_one<D, W, false>()) != cudaSuccess) return e; \
-    if ((e = setup_pair_one<D, W, true>()) != cudaSuccess) return e;
+#define X(D, W)                                                    \
+    if ((e = setup_pair_one<D, W, 0>()) != cudaSuccess) return e; \
+    if ((e = setup_pair_one<D, W, 2>()) != cudaSuccess) return e;
     R2IQ_PAIR_FOR_ALL(X)
 #undef X
     return cudaSuccess;
 }
 
 cudaError_t launch_pair(int d, int warps, const FusedParams& p, int sm_count, cudaStream_t stream) {
-    const bool mix = p.nco_starts != nullptr;
-#define X(D, W)                                                                              \
-    if (d == D && warps == W)                                                                \
-        return mix ? launch_pair_one<D, W, true>(p, sm_count, stream) : launch_pair_one<D, W, false>(p, sm_count, stream);
+    // kMix: 0 = no mixer, 2 = direct-phase mixer in the store epilogue (the reference-bit mixer is a separate pass)
+#define X(D, W)           \
+    if (d == D && warps == W) \
+        return p.nco_rot ? launch_pair_one<D, W, 2>(p, sm_count, stream) : launch_pair_one<D, W, 0>(p, sm_count, stream);
     R2IQ_PAIR_FOR_ALL(X)
 #undef X
     return cudaErrorInvalidValue;

@@ -101,6 +101,11 @@ class CudaR2IQ:
         run on the device instead: ``fc`` is what :meth:`setFreqOffset` returned; 0 switches it off."""
         return float(self._lib.r2iq_cuda_set_fine_tune(self._handle(), float(fc)))
 
+    def setFineTuneMode(self, mode: int) -> None:  # noqa: N802
+        """``capi.NCO_REFERENCE`` (bit-identical float32 recurrence, host-bound) or ``capi.NCO_DIRECT``
+        (phase computed on the device, mixer free in the kernel's store epilogue, own tolerance)."""
+        capi.check(self._lib.r2iq_cuda_set_fine_tune_mode(self._handle(), int(mode)))
+
     # -- extras the reference keeps private ---------------------------------------------------
     @property
     def tunebin(self) -> int:
@@ -152,6 +157,38 @@ class CudaR2IQ:
         capi.check(self._lib.r2iq_cuda_process(self._handle(), blocks.ctypes.data, n_blocks, hist_p,
                                                out.ctypes.data if n_out else None))
         return out
+
+    # -- submissions in flight (r2iq_cuda_process_async & co.) --------------------------------------
+    def process_async(self, blocks: np.ndarray, out: np.ndarray | None = None, history: np.ndarray | None = None) -> int:
+        """Enqueue one submission (<= chunk_blocks blocks) and return its ticket.  ``out`` None keeps the result on the
+        device (fetch with :meth:`read`, then :meth:`release`).  The caller keeps ``blocks`` alive until
+        :meth:`wait_input`, ``out`` until :meth:`wait`."""
+        if blocks.dtype != np.int16 or not blocks.flags.c_contiguous or blocks.size % TRANSFER_SAMPLES:
+            raise ValueError("blocks must be contiguous int16, a whole number of 65536-sample blocks")
+        n_blocks = blocks.size // TRANSFER_SAMPLES
+        if out is not None and (out.dtype != np.complex64 or out.size != n_blocks * self.out_per_block() or not out.flags.c_contiguous):
+            raise ValueError("out must be a contiguous complex64 array of n_blocks*(32768>>d) samples")
+        hist_p = None
+        if history is not None:
+            history = np.ascontiguousarray(history, dtype=np.int16)
+            hist_p = history.ctypes.data
+        ticket = ctypes.c_uint64(0)
+        capi.check(self._lib.r2iq_cuda_process_async(self._handle(), blocks.ctypes.data, n_blocks, hist_p,
+                                                     out.ctypes.data if out is not None else None, ctypes.byref(ticket)))
+        return int(ticket.value)
+
+    def wait_input(self, ticket: int) -> None:
+        capi.check(self._lib.r2iq_cuda_wait_input(self._handle(), ctypes.c_uint64(ticket)))
+
+    def wait(self, ticket: int) -> None:
+        capi.check(self._lib.r2iq_cuda_wait(self._handle(), ctypes.c_uint64(ticket)))
+
+    def read(self, ticket: int, first: int, out: np.ndarray) -> np.ndarray:
+        capi.check(self._lib.r2iq_cuda_read(self._handle(), ctypes.c_uint64(ticket), int(first), int(out.size), out.ctypes.data))
+        return out
+
+    def release(self, ticket: int) -> None:
+        capi.check(self._lib.r2iq_cuda_release(self._handle(), ctypes.c_uint64(ticket)))
 
     def process_device(self, d_in_ptr: int, n_blocks: int, d_out_ptr: int, stream_ptr: int = 0) -> None:
         """Device-resident variant: ``d_in_ptr`` -> [1024 history samples | n_blocks blocks] int16,

@@ -125,6 +125,32 @@ R2IQ_API long r2iq_cuda_out_per_block(r2iq_cuda_t h);
  * Pinned host memory (r2iq_cuda_host_alloc) is needed for the copies to overlap. */
 R2IQ_API int r2iq_cuda_process(r2iq_cuda_t h, const int16_t* blocks, long n_blocks, const int16_t* history, float* iq_out);
 
+/* The same, without waiting: the worker loop of the reference overlaps its producer, its FFTs and its consumer through
+ * the two rings (Core/fft_mt_r2iq_impl.hpp:15-33,100-148); over PCIe that overlap needs submissions in flight.
+ *  process_async  enqueues host->device copy, fused kernel and (when iq_out is not NULL) the copy back for
+ *                 n_blocks <= chunk_blocks blocks and returns a ticket; history is carried exactly as by
+ *                 r2iq_cuda_process (the tail of `blocks` is saved before the call returns).  Up to 4 submissions
+ *                 are in flight; a further one first waits for the oldest.  With iq_out == NULL the result stays on
+ *                 the device until r2iq_cuda_release: fetch it in pieces with r2iq_cuda_read (the adapter copies
+ *                 straight into output-ring slots as they become free).
+ *  wait_input     returns when the submission's blocks have left the caller's buffer (the input-ring slots may be
+ *                 handed back to the producer: ReadDone, Core/dsp/ringbuffer.h:29-42).
+ *  wait           returns when everything enqueued for the ticket has finished (iq_out complete).
+ *  read           copies complex samples [first, first + n) of a held result to dst and waits for the copy.
+ *  release        gives a held submission's device buffers back.
+ * Tickets complete in submission order.  Host buffers should be page-locked (r2iq_cuda_host_alloc, or memory the
+ * caller owns made so with r2iq_cuda_host_register: the reference's rings are one `new T[]` each,
+ * Core/dsp/ringbuffer.h:154-170) for the copies to be asynchronous. */
+R2IQ_API int r2iq_cuda_process_async(r2iq_cuda_t h, const int16_t* blocks, long n_blocks, const int16_t* history,
+                                     float* iq_out, uint64_t* ticket);
+R2IQ_API int r2iq_cuda_wait_input(r2iq_cuda_t h, uint64_t ticket);
+R2IQ_API int r2iq_cuda_wait(r2iq_cuda_t h, uint64_t ticket);
+R2IQ_API int r2iq_cuda_read(r2iq_cuda_t h, uint64_t ticket, long first_complex, long n_complex, float* dst);
+R2IQ_API int r2iq_cuda_release(r2iq_cuda_t h, uint64_t ticket);
+/* Page-lock / unlock memory the caller allocated (cudaHostRegister); registering a range twice is not an error. */
+R2IQ_API int r2iq_cuda_host_register(void* p, size_t bytes);
+R2IQ_API int r2iq_cuda_host_unregister(void* p);
+
 /* One ADC stream at several output rates.  In the reference every rate is its own fft_mt_r2iq instance reading
  * the SAME input ring slots in place (Core/fft_mt_r2iq_impl.hpp:20-33; RadioHandlerClass owns the ring,
  * Core/RadioHandler.h:111); here the capture crosses PCIe once and is transformed n_rates times on the device:
@@ -163,6 +189,21 @@ R2IQ_API int r2iq_cuda_process_channels_device(r2iq_cuda_t h, const int16_t* d_i
  * it off; the same fc again leaves the running phase alone).  Returns fc, or 0 when switched off / on error.
  * Not applied by the channelizer entry points. */
 R2IQ_API float r2iq_cuda_set_fine_tune(r2iq_cuda_t h, float fc);
+/* How the mixer's phasors are formed.
+ *  R2IQ_NCO_REFERENCE (default): the reference's float32 recurrence (one renormalised step per 128 samples, run on
+ *      the host because every step depends on the one before) -- bit-identical to Core/pffft/pf_mixer.cpp:791-856,
+ *      and bounded by that sequential recurrence (about 30 ms per 2^21 steps) and a second pass over the IQ.
+ *  R2IQ_NCO_DIRECT: sample n since the last r2iq_cuda_set_fine_tune(fc != 0) is multiplied by exp(2 pi j fc n), the
+ *      phase reduced in float64 on the device, in the store epilogue of the fused kernel: no host work, no second
+ *      pass.  This is the mixer the reference's recurrence approximates; it is NOT bit-identical to it.  Stated
+ *      tolerance: relative L2 error <= 1e-6 and max-abs <= 1e-5 of full scale against the float64 ideal
+ *      exp(2 pi j fc n) applied to the unmixed float32 stream, at any n; against the reference's own float32
+ *      recurrence the difference is the reference's accumulated rounding (a phase random walk of about
+ *      6e-8 rad * sqrt(n / 128)), see tests/test_gpu_parity.py::test_fine_tune_mixer_direct_mode.
+ * The mode can be changed only while the mixer is off (the two forms keep separate phase state). */
+enum { R2IQ_NCO_REFERENCE = 0, R2IQ_NCO_DIRECT = 1 };
+R2IQ_API int r2iq_cuda_set_fine_tune_mode(r2iq_cuda_t h, int mode);
+R2IQ_API int r2iq_cuda_get_fine_tune_mode(r2iq_cuda_t h);
 
 /* Block until everything issued through this handle has finished. */
 R2IQ_API int r2iq_cuda_sync(r2iq_cuda_t h);

@@ -36,8 +36,9 @@ def build(force: bool = False) -> bool:
     """Run ``make ref`` when the reference tree is present (this container).  On the GPU box the
     prebuilt libraries travel with the snapshot and /root/reference does not exist."""
     have = all(os.path.exists(lib_path(n)) for n in (2048, 8192)) and mixer_available() and os.path.exists(RADIO_DROPIN)
-    if os.path.isdir(os.path.join(REFERENCE_ROOT, "Core")) and (force or not have):
-        subprocess.run(["make", "-C", _HERE, "ref"], check=True, stdout=subprocess.DEVNULL)
+    if os.path.isdir(os.path.join(REFERENCE_ROOT, "Core")):
+        # always: make is incremental, and ref_radio_dropin links the adapter sources of this repo
+        subprocess.run(["make", "-C", _HERE, "ref"] + (["-B"] if force else []), check=True, stdout=subprocess.DEVNULL)
         have = True
     return have
 

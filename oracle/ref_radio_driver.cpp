@@ -122,7 +122,7 @@ bool run_once(const Scenario& sc, int which, std::vector<float>& iq, int& decima
     double f_tone = (sc.mode == VHFMODE ? 4570000.0 : (double)sc.tune_hz) + 0.1 * out_rate;
     MockFx3* usb = new MockFx3(sc, f_tone);
     RadioHandlerClass* radio = new RadioHandlerClass();   // leaked like the applications do (operators are never deleted)
-    cuda_r2iq* op = which ? new cuda_r2iq(0, 1, which == 2) : nullptr;
+    cuda_r2iq* op = which ? new cuda_r2iq(0, 16, which == 2 ? 1 : 0) : nullptr;
     Sink sink;
     sink.iq.reserve((size_t)(sc.n_blocks >> decimate) * 2 * EXT_BLOCKLEN);
     radio->Init(usb, on_iq, op, &sink);

@@ -26,8 +26,12 @@ static void make_block(std::vector<int16_t>& v, long first_sample) {
 // feed n_blocks through the rings, return everything the operator published
 // `prebuilt` (optional): 16 pre-generated blocks cycled by memcpy, like fx3handler_benchmark
 // (unittest/benchmark_test.cpp:78-107), so that the producer is not the bottleneck of a throughput check.
+// `discard`: the consumer only touches every slot (first and last sample summed into the returned vector's single
+// element), like the counting callbacks of unittest/benchmark_test.cpp -- a throughput check must not be bounded by
+// this test allocating and page-faulting gigabytes.
 static std::vector<float> stream(cuda_r2iq& op, ringbuffer<int16_t>& in, ringbuffer<float>& out, int d, int n_blocks,
-                                 bool retune, const std::vector<int16_t>* prebuilt = nullptr, bool hammer = false) {
+                                 bool retune, const std::vector<int16_t>* prebuilt = nullptr, bool hammer = false,
+                                 bool discard = false) {
     op.setDecimate(d);
     op.TurnOn();
     CHECK(op.IsOn());
@@ -55,10 +59,11 @@ static std::vector<float> stream(cuda_r2iq& op, ringbuffer<int16_t>& in, ringbuf
         }
     });
     const int n_slots = n_blocks >> d;
-    std::vector<float> got((size_t)n_slots * R2IQ_TRANSFER_SAMPLES);
+    std::vector<float> got(discard ? 1 : (size_t)n_slots * R2IQ_TRANSFER_SAMPLES);
     for (int s = 0; s < n_slots; s++) {
         const float* p = out.getReadPtr();
-        memcpy(got.data() + (size_t)s * R2IQ_TRANSFER_SAMPLES, p, sizeof(float) * R2IQ_TRANSFER_SAMPLES);
+        if (discard) got[0] += p[0] + p[R2IQ_TRANSFER_SAMPLES - 1];
+        else memcpy(got.data() + (size_t)s * R2IQ_TRANSFER_SAMPLES, p, sizeof(float) * R2IQ_TRANSFER_SAMPLES);
         out.ReadDone();
     }
     prod.join();
@@ -114,14 +119,54 @@ int main() {
             memcpy(pre.data() + (size_t)b * R2IQ_TRANSFER_SAMPLES, one.data(), sizeof(int16_t) * R2IQ_TRANSFER_SAMPLES);
         }
         for (int d : {0, 5}) {
-            const int n_blocks = 4096;
+            const int n_blocks = 16384;
             auto t0 = std::chrono::steady_clock::now();
-            std::vector<float> got = stream(op, in, out, d, n_blocks, false, &pre);
+            std::vector<float> got = stream(op, in, out, d, n_blocks, false, &pre, false, true);
             double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
             double msps = (double)n_blocks * R2IQ_TRANSFER_SAMPLES / sec / 1e6;
-            printf("live path d=%d: %.0f Msps through the rings (RX-888 full rate is 128 Msps)\n", d, msps);
-            CHECK(msps > 128.0);
+            printf("live path d=%d: %.0f Msps through the rings (RX-888 full rate is 128 Msps), %llu submissions\n", d, msps, op.batches());
+            // round 1 (one blocking launch per output slot, two host memcpys per block): 365 / 4769 Msps.  The producer
+            // and the consumer of this test are single memcpy threads; thresholds sit well below what was measured
+            // (profiles/r02_live_path.txt) so that a slower host does not fail the suite.
+            CHECK(msps > (d == 0 ? 1500.0 : 4000.0));
         }
+    }
+    {   // added latency at the RX-888's real rate: the producer publishes one block every 512 us, the consumer stamps
+        // the arrival of the output slot that carries it (d = 0: one slot per block)
+        const int n_blocks = 400;
+        std::vector<double> t_in(n_blocks), t_out(n_blocks);
+        op.setDecimate(0);
+        op.TurnOn();
+        auto t0 = std::chrono::steady_clock::now();
+        auto now = [&] { return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count(); };
+        std::thread prod([&] {
+            for (int b = 0; b < n_blocks; b++) {
+                const double due = (b + 1) * (65536.0 / 128e6);        // the block is complete when its last sample arrives
+                while (now() < due) std::this_thread::yield();
+                int16_t* p = in.getWritePtr();
+                memset(p, 0x11, sizeof(int16_t) * R2IQ_TRANSFER_SAMPLES);
+                t_in[b] = now();
+                in.WriteDone();
+            }
+        });
+        for (int s = 0; s < n_blocks; s++) {
+            (void)out.getReadPtr();
+            t_out[s] = now();
+            out.ReadDone();
+        }
+        prod.join();
+        op.TurnOff();
+        double mean = 0, worst = 0;
+        for (int b = 50; b < n_blocks; b++) {          // skip the start-up transient (first launches build tables)
+            const double l = t_out[b] - t_in[b];
+            mean += l;
+            if (l > worst) worst = l;
+        }
+        mean /= (n_blocks - 50);
+        const double blk = 65536.0 / 128e6;
+        printf("paced 128 Msps producer, d=0: added latency mean %.0f us (%.2f blocks), worst %.0f us (%.2f blocks)\n", mean * 1e6,
+               mean / blk, worst * 1e6, worst / blk);
+        CHECK(mean < 2.0 * blk);
     }
     {   // retune while streaming
         std::vector<float> got = stream(op, in, out, 2, 128, true);
@@ -140,8 +185,8 @@ int main() {
         }
         op.setFreqOffset(0.25f);
     }
-    for (int cycle = 0; cycle < 6; cycle++) {   // start/stop cycles over the rates, stopping mid-stream
-        int d = cycle % 6;
+    for (int cycle = 0; cycle < 21; cycle++) {   // unittest/stability_test.cpp:255-301: 20+ start/stop cycles over all the rates, stopping mid-stream
+        int d = cycle % 7;
         op.setDecimate(d);
         op.TurnOn();
         std::thread prod([&] {
@@ -158,7 +203,7 @@ int main() {
     }
     printf("start/stop cycles done\n");
     {   // fused fine-tune: setFreqOffset returns 0 to the caller and the device applies the residual NCO
-        cuda_r2iq fused(-1, 1, true);
+        cuda_r2iq fused(-1, 16, 1);
         fused.Init(gain, &in, &out);
         fused.updateRand(false);
         const float r = fused.setFreqOffset(0.2503f);
@@ -173,6 +218,18 @@ int main() {
         CHECK(fabs(ea - eb) < 1e-4 * eb);   // a pure rotation keeps the energy ...
         CHECK(diff > 1e-3 * eb);            // ... but changes the samples
         printf("fused fine-tune mixer: energy kept (%.6g vs %.6g), samples rotated\n", ea, eb);
+        // the direct-phase form (mode 2) gives the same stream within its stated tolerance (1e-6 rel-L2 to the ideal
+        // mixer; the reference-bit form differs from the ideal by its own float32 rounding)
+        cuda_r2iq direct(-1, 16, 2);
+        direct.Init(gain, &in, &out);
+        direct.updateRand(false);
+        CHECK(direct.setFreqOffset(0.2503f) == 0.0f);
+        std::vector<float> c = stream(direct, in, out, 1, 32, false);
+        CHECK(c.size() == a.size());
+        double dd = 0;
+        for (size_t i = 0; i < a.size(); i++) dd += (double)(a[i] - c[i]) * (a[i] - c[i]);
+        CHECK(sqrt(dd / ea) < 1e-3);   // the reference-bit form's own float32 frequency error (tests/test_gpu_parity.py)
+        printf("direct-phase mixer vs reference-bit mixer: rel-L2 %.3g\n", sqrt(dd / ea));
     }
     r2iq_cuda_destroy(h);
     printf(failures ? "FAILED %d\n" : "ALL PASS\n", failures);

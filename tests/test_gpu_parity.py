@@ -306,15 +306,11 @@ def test_config4_channelizer(op):
     op.TurnOff()
 
 
-@pytest.mark.parametrize("fused", ["0", "1"])
-def test_fine_tune_mixer_bit_exact(op, fused, monkeypatch):
+def test_fine_tune_mixer_bit_exact(op):
     """Next row: the residual NCO mixer RadioHandlerClass applies after the operator, run on
-    the device.  Applied to the same IQ, the device result must equal the reference's own mixer
-    (Core/pffft/pf_mixer.cpp compiled in place) BIT FOR BIT, with the phase carried across calls -- as a stand-alone
-    pass (default) and folded into the store epilogue of the d = 0, d = 1 and d = 2..5 kernels (R2IQ_NCO_FUSED=1,
-    read at every launch)."""
+    the device (mode R2IQ_NCO_REFERENCE, the default).  Applied to the same IQ, the device result must equal the
+    reference's own mixer (Core/pffft/pf_mixer.cpp compiled in place) BIT FOR BIT, with the phase carried across calls."""
     from oracle import ref_lib
-    monkeypatch.setenv("R2IQ_NCO_FUSED", fused)
     if not ref_lib.mixer_available():
         pytest.skip("oracle/_ref/libref_mixer.so not built")
     x = orc.rx888_blocks(6, 1, 256, randomized=True, seed=77)
@@ -335,6 +331,120 @@ def test_fine_tune_mixer_bit_exact(op, fused, monkeypatch):
         assert np.array_equal(mixed.view(np.uint32), want.view(np.uint32)), (d, off)
         assert not np.array_equal(mixed, plain)
     op.tunebin = 256
+
+
+def test_fine_tune_mixer_direct_mode(op):
+    """R2IQ_NCO_DIRECT (include/r2iq_cuda.h): sample n since the mixer was set is multiplied by exp(2 pi j fc n), phase
+    reduced in float64 on the device, inside the fused kernel's store epilogue.  Stated tolerance: rel-L2 <= 1e-6 and
+    max-abs <= 1e-5 of full scale against the float64 ideal applied to the unmixed float32 stream -- at the start of the
+    stream and after 2.7e8 output samples (phase carried over 65 calls); every decimation, sideband on and off, both
+    FFTN families (8192 mixes in a separate pass).  The reference's own mixer is further from that ideal than this one:
+    its phase increment and its 128-sample step are float32 values, so its frequency is off by a few 1e-8 relative and
+    the two streams drift apart linearly (measured 1.2e-4 rel-L2 over 2e5 samples at d = 0) -- checked loosely."""
+    from extio_sddc_b200 import capi as _capi
+    from oracle import ref_lib
+    fs = orc.full_scale(GAIN)
+
+    def ideal(plain, fc, n0):
+        n = np.arange(n0, n0 + plain.size, dtype=np.float64)
+        ph = np.float64(np.float32(fc)) * n
+        ph -= np.floor(ph)
+        return plain.astype(np.complex128) * np.exp(2j * np.pi * ph)
+
+    x = orc.rx888_blocks(6, 1, 256, randomized=True, seed=78)
+    for fftn in (2048, 8192):
+        r = op if fftn == 2048 else CudaR2IQ(fftn=8192)
+        if fftn == 8192:
+            r.Init(GAIN)
+        for d, off, sb in ((0, 0.2503, False), (1, 0.1431, True), (2, 0.3337, False), (4, 0.6002, False), (5, 0.0107, True), (6, 0.4411, False)):
+            r.setDecimate(d); r.updateRand(True); r.setSideband(sb)
+            fc = r.setFreqOffset(off)
+            assert fc != 0.0
+            r.setFineTune(0.0)
+            r.TurnOn()
+            plain = r.process(x)
+            r.TurnOff()
+            r.setFineTuneMode(_capi.NCO_DIRECT)
+            assert r.setFineTune(fc) == pytest.approx(fc)
+            r.TurnOn()
+            mixed = np.concatenate([r.process(x[: 2 * 65536]), r.process(x[2 * 65536:])])   # phase carries over
+            r.TurnOff()
+            want = ideal(plain, fc, 0)
+            err = np.linalg.norm(mixed - want) / np.linalg.norm(want)
+            mx = np.abs(mixed - want).max() / fs
+            assert err <= 1e-6 and mx <= 1e-5, (fftn, d, err, mx)
+            assert not np.array_equal(mixed, plain)
+            if ref_lib.mixer_available() and fftn == 2048:
+                cpu = ref_lib.mixer_apply(plain, fc, slot=32768)
+                e2 = np.linalg.norm(mixed - cpu) / np.linalg.norm(cpu)
+                assert e2 <= 1e-3, (d, e2)          # the reference's float32 phase increment, not ours, carries this error
+            r.setFineTune(0.0)
+            r.setFineTuneMode(_capi.NCO_REFERENCE)
+        if fftn == 8192:
+            r.close()
+    # long run at d = 0: 64 calls of 128 blocks (2.7e8 output samples) with the mixer on, then one checked call
+    op.setDecimate(0); op.updateRand(True); op.setSideband(False)
+    fc = op.setFreqOffset(0.2503)
+    big = np.tile(x[: 4 * 65536], 32)
+    op.setFineTune(0.0)
+    op.TurnOn(); op.process(big); plain = op.process(x); op.TurnOff()   # same history in front of the checked call
+    op.setFineTuneMode(_capi.NCO_DIRECT)
+    op.setFineTune(fc)
+    op.TurnOn()
+    for _ in range(64):
+        op.process(big)
+    mixed = op.process(x)
+    op.TurnOff()
+    n0 = 64 * 128 * 32768
+    want = ideal(plain, fc, n0)
+    err = np.linalg.norm(mixed - want) / np.linalg.norm(want)
+    assert err <= 1e-6 and np.abs(mixed - want).max() / fs <= 1e-5, err
+    with pytest.raises(Exception):
+        op.setFineTuneMode(_capi.NCO_REFERENCE)          # only while the mixer is off
+    op.setFineTune(0.0)
+    op.setFineTuneMode(_capi.NCO_REFERENCE)
+    op.tunebin = 256
+
+
+def test_async_submissions_equal_blocking_call():
+    """r2iq_cuda_process_async / wait_input / wait / read / release: submissions in flight (more than there are slots),
+    results delivered to host buffers or held on the device and fetched in pieces, all bit-identical to one blocking
+    r2iq_cuda_process over the same stream; history is carried at submit time."""
+    r = CudaR2IQ(chunk_blocks=4)
+    r.Init(GAIN)
+    r.updateRand(True); r.tunebin = 148
+    x = orc.rx888_blocks(26, 2, 148, randomized=True, seed=19).reshape(-1)
+    for d in (0, 3, 6):
+        opb = 32768 >> d
+        r.setDecimate(d); r.TurnOn()
+        want = r.process(x)
+        r.TurnOff()
+        r.TurnOn()
+        got = np.zeros_like(want)
+        sizes = [4, 1, 3, 4, 2, 4, 4, 1, 3]          # 26 blocks, nine submissions, four slots
+        tickets, pos = [], 0
+        for i, nb in enumerate(sizes):
+            blk = x[pos * 65536:(pos + nb) * 65536]
+            if i % 2 == 0:                             # host output
+                t = r.process_async(blk, out=got[pos * opb:(pos + nb) * opb])
+                tickets.append((t, None, pos, nb))
+            else:                                      # held on the device
+                t = r.process_async(blk)
+                r.wait_input(t)
+                half = nb * opb // 2
+                r.read(t, half, got[pos * opb + half:(pos + nb) * opb])     # second half first
+                r.read(t, 0, got[pos * opb:pos * opb + half])
+                r.release(t)
+            pos += nb
+        for t, _, _, _ in tickets:
+            r.wait(t)
+        r.TurnOff()
+        assert np.array_equal(got, want), d
+    r.setDecimate(1); r.TurnOn()
+    with pytest.raises(Exception):
+        r.process_async(x[: 5 * 65536])                # more than chunk_blocks
+    r.TurnOff()
+    r.close()
 
 
 def test_process_rates_equals_one_operator_per_rate():
@@ -362,6 +472,11 @@ def test_process_rates_equals_one_operator_per_rate():
     check(np.concatenate([a[1], b[1]]), ref, GAIN, "rates d5")
     with pytest.raises(Exception):
         r.process_rates(x, [7])
+    for dup in ([0, 0, 1], [0, 0, 0], [3, 5, 3]):        # a repeated rate would overrun the per-chunk device buffer
+        with pytest.raises(Exception, match="listed twice"):
+            r.process_rates(x, dup)
+    got3b = r.process(x, history=np.zeros(1024, np.int16))   # the handle stays usable after the rejected calls
+    assert np.array_equal(got3b, want[3])
     r.TurnOff()
     r.close()
 
