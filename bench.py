@@ -35,6 +35,12 @@ WORKLOAD = ("config2: RX-888 Mk II 128 Msps synthetic int16 ADC, randomizer on, 
             "2/4/8/16/32/64 (six fused-kernel launches per step), FFTN 2048, tune offset 0.25")
 
 
+# The `config` both arms print, key for key: the workload only.  What differs per arm (blocks per GPU, instances ...)
+# goes under "arm".
+CONFIG = {"workload": WORKLOAD, "fftn": 2048, "adc_msps": 128, "randomizer": True, "decimation_indices": list(DECIMS),
+          "tune_offset": 0.25, "samples_per_block": SAMPLES_PER_BLOCK}
+
+
 def bytes_per_sample(d: int) -> float:
     """Algorithmic bytes per input sample: 2 B int16 in + 8 B complex64 out per 2^(d+1)."""
     return 2.0 + 8.0 / (1 << (d + 1))
@@ -49,15 +55,54 @@ def measured_peak():
         return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
-def ncu_traffic(d: int):
-    """dram bytes per launch from the committed ncu summary, if one exists for this decimation."""
+def ncu_traffic(kernel: str, n_blocks: int):
+    """dram__bytes_read + dram__bytes_write per launch from the committed `ncu --set full` capture of THIS kernel
+    (profiles/traffic.json: {kernel name: {"blocks": B, "dram_bytes": N}}), scaled to this launch's block count; None
+    when the kernel that ran has no capture (the name comes from the C ABI, not from a table here)."""
     p = os.path.join(ROOT, "profiles", "traffic.json")
     try:
         with open(p) as f:
-            t = json.load(f)
-        return t.get(f"d{d}")
+            t = json.load(f).get(kernel)
+        return int(t["dram_bytes"] * n_blocks / t["blocks"]) if t else None
     except Exception:
         return None
+
+
+def packed_fp32_per_pair(kernel: str):
+    """Packed FP32 instructions (FFMA2 + FADD2 + FMUL2) one warp issues per frame pair in `kernel`, counted in the SASS of
+    the library that is loaded (cuobjdump, loop body = everything after the prologue's block barrier).  None when
+    cuobjdump is not on the box: the committed count in profiles/r02_sass_opcodes.txt documents the same number."""
+    import re
+    import shutil
+    import subprocess
+    from extio_sddc_b200 import capi
+    exe = shutil.which("cuobjdump") or "/usr/local/cuda/bin/cuobjdump"
+    if not os.path.exists(exe):
+        return None
+    m = re.match(r"r2iq_pair_kernel<(\d+), (\d+), (\d+)>", kernel)
+    if not m:
+        return None
+    mangled = f"_ZN4r2iq16r2iq_pair_kernelILi{m.group(1)}ELi{m.group(2)}ELi{m.group(3)}EEEvNS_11FusedParamsE"
+    try:
+        out = subprocess.run([exe, "-sass", "-fun", mangled, capi.LIB_PATH], capture_output=True, text=True, timeout=120).stdout
+    except Exception:
+        return None
+    # the persistent loop = the longest backward branch; count inside it only (the function also holds the prologue and
+    # out-of-line wait loops)
+    ins = [(int(a, 16), t) for a, t in re.findall(r"/\*([0-9a-f]{4,6})\*/\s+([^;]*);", out)]
+    best = None
+    for a, t in ins:
+        m = re.search(r"\bBRA(?:\.\w+)*\s+(?:\w+,\s*)?0x([0-9a-f]+)", t)
+        if m and int(m.group(1), 16) < a and (best is None or a - int(m.group(1), 16) > best[1] - best[0]):
+            best = (int(m.group(1), 16), a)
+    if best is None:
+        return None
+    n = sum(1 for a, t in ins if best[0] <= a <= best[1] and re.search(r"\b(?:FFMA2|FADD2|FMUL2)\b", t))
+    return n or None
+
+
+FP32_PEAK_THREAD_INST = 18.33e12   # packed FP32 thread-instructions/s, B200 at 1965 MHz: tools/ubench/fp32_pipes.cu, ffma2 at 32
+                                   # warps/SM (profiles/r01_ubench_fp32_pipes.txt) = 64 lanes x 148 SMs x 1.935 GHz effective
 
 
 # ------------------------------------------------------------------------------------------------
@@ -180,8 +225,8 @@ def run_reference(args, rank: int, world: int):
     line = {"impl": "reference", "metric": METRIC, "value": round(value, 4), "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(secs / args.steps * 1e3, 3),
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "sample_blocks_per_instance": blocks, "instances": cores,
-                       "host_cpus": os.cpu_count()},
+            "config": CONFIG,
+            "arm": {"sample_blocks_per_instance": blocks, "instances": cores, "host_cpus": os.cpu_count()},
             "cpu_baseline": {"value": round(value, 4), "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample},
             "e2e": {"value": round(value, 4), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "per_decimation": detail, "gpu_launches": 0}
@@ -301,12 +346,25 @@ def run_ours(args, rank: int, local_rank: int, world: int):
                       "alg_bytes_per_sample": bytes_per_sample(d), "achieved_gbs": round(gbs, 1),
                       "hbm_frac": round(gbs / peak, 4)})
     dom = max(per_d, key=lambda r: r["kernel_ms"])
-    names = {0: "r2iq_dual_d0_kernel<tma>", 1: "r2iq_dual_kernel<1,direct>"}
-    roofline = {"bound": "hbm", "kernel": f"{names.get(dom['d'], 'r2iq_fused_kernel<%d>' % dom['d'])} (decimation {dom['decimation']})",
+    for r in per_d:
+        r["kernel"] = op.kernel_name(r["d"])
+    dom_kernel = dom["kernel"]
+    roofline = {"bound": "hbm", "kernel": f"{dom_kernel} (decimation {dom['decimation']})",
                 "achieved": dom["achieved_gbs"], "peak": peak, "unit": "GB/s", "frac": round(dom["achieved_gbs"] / peak, 4),
-                "traffic": ncu_traffic(dom["d"]), "peak_source": peak_src,
-                "algorithmic_bytes_per_launch": samples_per_launch * bytes_per_sample(dom["d"]),
-                "note": "FP32 issue is the co-roof of this FFT path; see DESIGN.md and profiles/"}
+                "traffic": ncu_traffic(dom_kernel, n_blocks), "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": samples_per_launch * bytes_per_sample(dom["d"])}
+    # FP32 co-roof: this FFT path is bound by the FP32 pipe and what feeds it, not by HBM
+    if rank == 0:
+        fp = packed_fp32_per_pair(dom_kernel)
+        if fp:
+            pairs_per_s = (n_blocks * 43 / 2) / (dom["kernel_ms"] * 1e-3)
+            ach = fp * 32 * pairs_per_s
+            roofline["fp32"] = {"packed_fp32_inst_per_frame_pair": fp,
+                                "packed_fp32_inst_per_sample": round(fp * 32 / 3072.0, 3),   # 32 lanes; a pair adds 2 x 1536 new samples
+                                "achieved_thread_inst_per_s": round(ach / 1e12, 3), "peak_thread_inst_per_s": FP32_PEAK_THREAD_INST / 1e12,
+                                "unit": "T packed-FP32 thread-instructions/s", "frac": round(ach / FP32_PEAK_THREAD_INST, 4),
+                                "achieved_tflops": round(ach * 3.0 / 1e12, 1),   # ~1.5 flop per lane-op (FFMA2 : FADD2+FMUL2 = 1 : 1), 2 lanes
+                                "peak_source": "tools/ubench/fp32_pipes.cu on B200 (profiles/r01_ubench_fp32_pipes.txt)"}
 
     # ---- e2e: same sweep through the host-buffer C-ABI call, pinned host memory -------------------
     e2e = None
@@ -371,6 +429,14 @@ def run_ours(args, rank: int, local_rank: int, world: int):
         e2e["per_operator"] = timed(e2e_step_per_operator)
         e2e["per_operator"]["api"] = ("r2iq_cuda_process once per decimation (one operator per rate): the capture is "
                                       "copied to the device six times")
+        # the host-buffer path and the device-resident path give the same bits (same kernels, same capture)
+        op.setDecimate(DECIMS[-1])
+        op.TurnOn()
+        op.process_device(x.data_ptr(), n_blocks, out.data_ptr(), stream)
+        torch.cuda.synchronize()
+        n_last = n_blocks * (32768 >> DECIMS[-1])
+        dev_last = out[:n_last].cpu().numpy()
+        e2e["verified"] = bool(np.array_equal(dev_last, houts[-1].array)) and bool(np.array_equal(dev_last, hout.array[:n_last]))
         for b in houts:
             b.free()
         # the device-resident and host-buffer paths must agree on the last decimation
@@ -379,17 +445,41 @@ def run_ours(args, rank: int, local_rank: int, world: int):
         hin.free()
         hout.free()
 
-    # ---- gather of IQ to rank 0 over NCCL (north star: only collective on the path) --------------
+    # ---- IQ of all ranks on rank 0 (north star: the only exchange on the path) --------------------------------
     gather = None
+    config5 = None
     if world > 1:
+        from extio_sddc_b200 import shard
         gather = []
         warm = torch.zeros(1024, dtype=torch.float32, device=dev)      # bring the NCCL communicator up untimed
         dist.gather(warm, [torch.empty_like(warm) for _ in range(world)] if rank == 0 else None, dst=0)
         torch.cuda.synchronize()
+        check_rng = np.random.default_rng(2024)
+
+        def verify(gathered, d, slabs, regen):
+            """Rank 0 recomputes the last rank's slab and one more picked at random from the same seeded generator and
+            requires the gathered ranges to hold the same bits."""
+            picks = sorted({world - 1, int(check_rng.integers(0, world))})
+            worst = 0.0
+            ok = True
+            for r in picks:
+                first, count = slabs[r]
+                xin = regen(r)
+                ref = torch.empty(count * (32768 >> d), dtype=torch.complex64, device=dev)
+                op.process_device(xin.data_ptr(), count, ref.data_ptr(), stream)
+                torch.cuda.synchronize()
+                got = gathered[first * (32768 >> d):(first + count) * (32768 >> d)]
+                ok = ok and bool(torch.equal(torch.view_as_real(got), torch.view_as_real(ref)))
+                worst = max(worst, float((torch.view_as_real(got) - torch.view_as_real(ref)).abs().max()))
+                del xin, ref
+            return ok, worst, picks
+
+        weak_slabs = [(r * n_blocks, n_blocks) for r in range(world)]
         for d in (DECIMS[-1], DECIMS[0]):
             n_out = n_blocks * (32768 >> d)
             op.setDecimate(d)
             op.TurnOn()
+            # (1) NCCL gather after the kernel (round 1's form, kept as the comparison)
             mine = torch.view_as_real(out[:n_out])
             dst = [torch.empty_like(mine) for _ in range(world)] if rank == 0 else None
             barrier()
@@ -403,9 +493,71 @@ def run_ours(args, rank: int, local_rank: int, world: int):
             torch.cuda.synchronize()
             t = torch.tensor([g0.elapsed_time(g1)], dtype=torch.float64, device=dev)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            gather.append({"d": d, "ms_compute_plus_gather": round(float(t.item()), 3),
-                           "gathered_bytes": int(n_out * 8 * (world - 1))})
+            entry = {"d": d, "gathered_bytes": int(n_out * 8 * (world - 1)),
+                     "nccl_after_kernel_ms": round(float(t.item()), 3)}
+            if rank == 0:
+                allg = torch.view_as_complex(torch.cat(dst).view(-1, 2))
+                ok, worst, picks = verify(allg, d, weak_slabs, lambda r: synth_capture(torch, dev, n_blocks, seed=888 + r, first_block=r * n_blocks))
+                entry["nccl_verified"] = ok
+                del allg
             del dst
+            # (2) peer stores: every rank's kernel writes its IQ into rank 0's buffer over NVLink while it computes
+            po = shard.PeerOutput(world * n_out, rank, world, local_rank)
+            op.process_device(x.data_ptr(), n_blocks, po.ptr(rank * n_out), stream)      # warm the mapping
+            po.fence()
+            g0 = torch.cuda.Event(enable_timing=True)
+            g1 = torch.cuda.Event(enable_timing=True)
+            g0.record()
+            op.process_device(x.data_ptr(), n_blocks, po.ptr(rank * n_out), stream)
+            g1.record()
+            po.fence()
+            t = torch.tensor([g0.elapsed_time(g1)], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            entry["ms_compute_plus_gather"] = round(float(t.item()), 3)
+            entry["method"] = "fused kernel stores into rank 0's buffer through a CUDA-IPC peer mapping (NVLink), no gather after the kernel"
+            entry["into_rank0_gbs"] = round(entry["gathered_bytes"] / (float(t.item()) * 1e-3) / 1e9, 1)
+            if rank == 0:
+                ok, worst, picks = verify(po.tensor(), d, weak_slabs, lambda r: synth_capture(torch, dev, n_blocks, seed=888 + r, first_block=r * n_blocks))
+                entry.update({"verified": ok, "max_abs_diff": worst, "slabs_recomputed_on_rank0": picks})
+            po.close()
+            gather.append(entry)
+
+        # ---- config 5 (BASELINE.json configs[4]): ONE 19968-block capture, time-sharded with halos: strong scaling ----
+        config5 = {"workload": "config5: 10.2 s capture (19968 blocks = 1.31 G samples) time-sharded with halfFft halos, IQ on rank 0",
+                   "total_blocks": 19968, "scaling": "strong", "results": []}
+        for d in (DECIMS[0], DECIMS[-1]):
+            slabs = shard.time_slabs(19968, world, d)
+            first, count = slabs[rank]
+            opb = 32768 >> d
+            xs = synth_capture(torch, dev, count, seed=555, first_block=first)
+            local_out = torch.empty(count * opb, dtype=torch.complex64, device=dev)
+            op.setDecimate(d)
+            op.TurnOn()
+            po = shard.PeerOutput(19968 * opb, rank, world, local_rank)
+            for _ in range(2):
+                op.process_device(xs.data_ptr(), count, local_out.data_ptr(), stream)
+                op.process_device(xs.data_ptr(), count, po.ptr(first * opb), stream)
+            po.fence()
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+            ev[0].record()
+            op.process_device(xs.data_ptr(), count, local_out.data_ptr(), stream)
+            ev[1].record()
+            po.fence()
+            ev[2].record()
+            op.process_device(xs.data_ptr(), count, po.ptr(first * opb), stream)
+            ev[3].record()
+            po.fence()
+            t = torch.tensor([ev[0].elapsed_time(ev[1]), ev[2].elapsed_time(ev[3])], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            res = {"d": d, "blocks_per_gpu": count, "compute_ms": round(float(t[0]), 3), "compute_plus_gather_ms": round(float(t[1]), 3),
+                   "compute_gsamples_s": round(19968 * 65536 / float(t[0]) / 1e6, 1),
+                   "gathered_gsamples_s": round(19968 * 65536 / float(t[1]) / 1e6, 1), "iq_bytes_total": int(19968 * opb * 8)}
+            if rank == 0:
+                ok, worst, picks = verify(po.tensor(), d, slabs, lambda r: synth_capture(torch, dev, slabs[r][1], seed=555, first_block=slabs[r][0]))
+                res.update({"verified": ok, "max_abs_diff": worst, "slabs_recomputed_on_rank0": picks})
+            config5["results"].append(res)
+            po.close()
+            del xs, local_out
 
     # ---- config 4: 64-channel channelizer at d = 5, channels sharded over the ranks ---------------------
     channelizer = None
@@ -434,7 +586,27 @@ def run_ours(args, rank: int, local_rank: int, world: int):
             t = torch.tensor([cms], dtype=torch.float64, device=dev)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             cms = float(t.item())
+        # every channel equals a separate operator tuned to its bin (Core/fft_mt_r2iq_impl.hpp:76-138 per channel): check
+        # the first and the last channel of this rank bit for bit against r2iq_cuda_process_device
+        per_ch = n_blocks * (32768 >> cd)
+        chan_ok = True
+        one = torch.empty(per_ch, dtype=torch.complex64, device=dev)
+        for ci in sorted({0, len(mine) - 1}):
+            op.tunebin = mine[ci]
+            op.process_device(x.data_ptr(), n_blocks, one.data_ptr(), stream)
+            torch.cuda.synchronize()
+            a = torch.view_as_real(cout[ci * per_ch:(ci + 1) * per_ch])
+            b = torch.view_as_real(one)
+            rel = float(torch.linalg.vector_norm(a - b) / torch.linalg.vector_norm(b))
+            chan_ok = chan_ok and rel <= 1e-5
+        op.tunebin = TUNEBIN
+        del one
+        if world > 1:
+            t = torch.tensor([1.0 if chan_ok else 0.0], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MIN)
+            chan_ok = bool(t.item() > 0.5)
         channelizer = {"channels": 64, "channels_per_gpu": len(mine), "d": cd, "decimation": 64, "ms": round(cms, 3),
+                       "verified": chan_ok,
                        "input_gsamples_s": round(samples_per_launch / (cms * 1e-3) / 1e9, 2),
                        "channel_gsamples_s": round(64 * samples_per_launch / (cms * 1e-3) / 1e9, 1),
                        "note": "every rank reads the same capture; one forward FFT per frame shared by its channels"}
@@ -501,15 +673,18 @@ def run_ours(args, rank: int, local_rank: int, world: int):
         line = {"metric": METRIC, "value": round(value, 3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": round(ms_total / args.steps, 4), "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": {"workload": WORKLOAD, "blocks_per_gpu": n_blocks, "input_samples_per_step": samples_per_step,
-                           "parallelism": f"time-slab x{world} (slab + halfFft halo per GPU, no data-path collective)",
-                           "l2": f"input capture {samples_per_launch * 2 / 1e9:.2f} GB per GPU is larger than the 126 MB L2; "
-                                 "no explicit flush"},
+                "config": CONFIG,
+                "arm": {"blocks_per_gpu": n_blocks, "input_samples_per_step": samples_per_step,
+                        "parallelism": f"time-slab x{world} (slab + halfFft halo per GPU, no data-path collective)",
+                        "l2": f"input capture {samples_per_launch * 2 / 1e9:.2f} GB per GPU is larger than the 126 MB L2; "
+                              "no explicit flush"},
                 "roofline": roofline, "per_decimation": per_d, "clocks": clocks, "gpu_launches": launches}
         if e2e is not None:
             line["e2e"] = e2e
         if gather is not None:
             line["gather"] = gather
+        if config5 is not None:
+            line["config5"] = config5
         if channelizer is not None:
             line["channelizer"] = channelizer
         if wide is not None:

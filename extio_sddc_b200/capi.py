@@ -84,9 +84,15 @@ _SIGNATURES = {
     "r2iq_cuda_host_alloc_on": (_VP, [ctypes.c_size_t, _I]),
     "r2iq_cuda_device_numa_node": (_I, [_I]),
     "r2iq_cuda_host_free": (_I, [_VP]),
+    "r2iq_cuda_device_alloc": (_VP, [_I, ctypes.c_size_t]),
+    "r2iq_cuda_device_free": (_I, [_VP]),
+    "r2iq_cuda_ipc_export": (_I, [_VP, _VP]),
+    "r2iq_cuda_ipc_open": (_I, [_I, _VP, ctypes.POINTER(_VP)]),
+    "r2iq_cuda_ipc_close": (_I, [_VP]),
     "r2iq_cuda_convert": (_I, [_VP, _VP, _L, _I, _VP]),
     "r2iq_cuda_get_stats": (_I, [_VP, ctypes.POINTER(Stats)]),
     "r2iq_cuda_get_fftn": (_I, [_VP]),
+    "r2iq_cuda_kernel_name": (_I, [_VP, _I, ctypes.c_char_p, _I]),
     "r2iq_cuda_design_filter": (_I, [_F, _I, _VP, _I]),
     "r2iq_cuda_kaiser": (_I, [_I, _F, _F, _F, _VP]),
     "r2iq_cuda_freq_to_tunebin": (_F, [_F, _I, ctypes.POINTER(_I)]),

@@ -125,7 +125,7 @@ struct r2iq_cuda_s {
     bool latched_sideband = false;
 
     bool poisoned = false;        // a CUDA error happened: refuse further work
-    char poison_msg[256] = "";    // what poisoned it (g_err is thread-local: the application thread asks later)
+    char poison_msg[512] = "";    // what poisoned it (g_err is thread-local: the application thread asks later)
     std::mutex mu;
 
     std::vector<std::complex<float>> hw[kNDec];   // filterHw[d], host copy
@@ -1322,6 +1322,67 @@ int r2iq_cuda_host_free(void* p) {
     return R2IQ_OK;
 }
 
+// ---- device memory shared between the ranks of one box (time-slab / channel sharding) ---------------
+// One process per GPU: the rank that collects the IQ allocates the destination, the others map it (CUDA IPC, peer
+// access over NVLink) and hand the mapped pointer to r2iq_cuda_process_device as d_iq_out -- the fused kernel's own
+// stores then cross NVLink while it computes, and no gather follows the kernel.
+void* r2iq_cuda_device_alloc(int device, size_t bytes) {
+    DeviceGuard dg(device);
+    if (dg.err != cudaSuccess) {
+        fail(R2IQ_E_CUDA, "cudaSetDevice(%d): %s", device, cudaGetErrorString(dg.err));
+        return nullptr;
+    }
+    void* p = nullptr;
+    cudaError_t e = cudaMalloc(&p, bytes ? bytes : 1);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        fail(R2IQ_E_NOMEM, "cudaMalloc(%zu): %s", bytes, cudaGetErrorString(e));
+        return nullptr;
+    }
+    return p;
+}
+int r2iq_cuda_device_free(void* p) {
+    if (!p) return R2IQ_OK;
+    cudaError_t e = cudaFree(p);
+    if (e != cudaSuccess) return fail(R2IQ_E_CUDA, "cudaFree: %s", cudaGetErrorString(e));
+    return R2IQ_OK;
+}
+int r2iq_cuda_ipc_export(void* device_ptr, unsigned char handle[R2IQ_IPC_HANDLE_BYTES]) {
+    static_assert(sizeof(cudaIpcMemHandle_t) == R2IQ_IPC_HANDLE_BYTES, "handle size");
+    if (!device_ptr || !handle) return fail(R2IQ_E_INVALID, "ipc_export: null argument");
+    cudaIpcMemHandle_t hnd;
+    cudaError_t e = cudaIpcGetMemHandle(&hnd, device_ptr);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(R2IQ_E_CUDA, "cudaIpcGetMemHandle: %s", cudaGetErrorString(e));
+    }
+    memcpy(handle, &hnd, sizeof(hnd));
+    return R2IQ_OK;
+}
+int r2iq_cuda_ipc_open(int device, const unsigned char handle[R2IQ_IPC_HANDLE_BYTES], void** device_ptr) {
+    if (!handle || !device_ptr) return fail(R2IQ_E_INVALID, "ipc_open: null argument");
+    *device_ptr = nullptr;
+    DeviceGuard dg(device);
+    if (dg.err != cudaSuccess) return fail(R2IQ_E_CUDA, "cudaSetDevice(%d): %s", device, cudaGetErrorString(dg.err));
+    cudaIpcMemHandle_t hnd;
+    memcpy(&hnd, handle, sizeof(hnd));
+    cudaError_t e = cudaIpcOpenMemHandle(device_ptr, hnd, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(R2IQ_E_CUDA, "cudaIpcOpenMemHandle: %s", cudaGetErrorString(e));
+    }
+    return R2IQ_OK;
+}
+int r2iq_cuda_ipc_close(void* device_ptr) {
+    if (!device_ptr) return R2IQ_OK;
+    cudaError_t e = cudaIpcCloseMemHandle(device_ptr);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(R2IQ_E_CUDA, "cudaIpcCloseMemHandle: %s", cudaGetErrorString(e));
+    }
+    return R2IQ_OK;
+}
+
 int r2iq_cuda_convert(r2iq_cuda_t h, const int16_t* in, long n, int rand, float* out) {
     int rc = check_handle(h);
     if (rc) return rc;
@@ -1346,6 +1407,13 @@ int r2iq_cuda_convert(r2iq_cuda_t h, const int16_t* in, long n, int rand, float*
 }
 
 int r2iq_cuda_get_fftn(r2iq_cuda_t h) { return h ? h->fftn : R2IQ_E_INVALID; }
+
+int r2iq_cuda_kernel_name(r2iq_cuda_t h, int d, char* buf, int n) {
+    if (!h || !buf || n < 1 || d < 0 || d >= kNDec) return fail(R2IQ_E_INVALID, "kernel_name: bad arguments");
+    if (h->fftn == 8192) snprintf(buf, (size_t)n, "r2iq_wide_kernel<%d, 1>", d);
+    else snprintf(buf, (size_t)n, "%s", fused_kernel_name(d, h->nco.on && h->nco.mode == R2IQ_NCO_DIRECT));
+    return R2IQ_OK;
+}
 
 int r2iq_cuda_get_stats(r2iq_cuda_t h, r2iq_cuda_stats* out) {
     if (!h || !out) return fail(R2IQ_E_INVALID, "null argument");

@@ -22,6 +22,7 @@
 // No cuFFT, no tensor cores, no CPU fallback.
 #include "r2iq_kernels.cuh"
 
+#include <cstdio>
 #include <cstdlib>
 
 #include "r2iq_common.cuh"
@@ -255,6 +256,19 @@ cudaError_t setup_fused_kernels() {
     if ((e = setup_one<5>()) != cudaSuccess) return e;
     if ((e = setup_one<6>()) != cudaSuccess) return e;
     return cudaSuccess;
+}
+
+// Name (as ncu and cuobjdump print it) of the kernel launch_fused picks for decimation index d -- reported through the
+// C ABI so that measurements name the kernel that actually ran.
+const char* fused_kernel_name(int d, bool direct_mixer) {
+    static char names[kNDec][2][64];
+    if (d < 0 || d >= kNDec) return "";
+    char* n = names[d][direct_mixer ? 1 : 0];
+    if (!n[0]) {
+        if (g_kernel_gen == 0) snprintf(n, 64, "r2iq_pair_kernel<%d, %d, %d>", d, d == 0 ? 8 : 12, direct_mixer ? 2 : 0);
+        else snprintf(n, 64, "kernel generation %d (A/B build), d=%d", g_kernel_gen, d);
+    }
+    return n;
 }
 
 cudaError_t launch_fused(int d, const FusedParams& p, int sm_count, cudaStream_t stream) {

@@ -122,6 +122,7 @@ struct WideParams {
 cudaError_t setup_wide_kernels();
 cudaError_t launch_wide(int d, const WideParams& p, int sm_count, cudaStream_t stream);
 
+const char* fused_kernel_name(int d, bool direct_mixer);
 // Launch the fused kernel for decimation index d on `stream`.  Returns cudaGetLastError().
 cudaError_t launch_fused(int d, const FusedParams& p, int sm_count, cudaStream_t stream);
 // Kernel generation selector for A/B measurements (env R2IQ_KERNEL_GEN): 0 = the fastest measured kernel

@@ -132,6 +132,11 @@ class CudaR2IQ:
         capi.check(self._lib.r2iq_cuda_get_stats(self._handle(), ctypes.byref(st)))
         return st
 
+    def kernel_name(self, d: int) -> str:
+        buf = ctypes.create_string_buffer(128)
+        capi.check(self._lib.r2iq_cuda_kernel_name(self._handle(), int(d), buf, 128))
+        return buf.value.decode()
+
     def sync(self) -> None:
         capi.check(self._lib.r2iq_cuda_sync(self._handle()))
 

@@ -88,6 +88,74 @@ def gather_to_rank0(local, sizes: Sequence[int], rank: int, world: int, group=No
     return None
 
 
+class PeerOutput:
+    """The gathered IQ as ONE device buffer on rank 0 that every rank's kernel stores into directly (CUDA IPC mapping,
+    peer stores over NVLink; include/r2iq_cuda.h "Output shared between the ranks").  ``n_complex`` = total complex64
+    samples; ``ptr(offset_complex)`` is what a rank passes as ``d_out_ptr`` of ``process_device``.  Collective: every
+    rank constructs it; the handle travels through torch.distributed (any backend).  ``fence()`` = stream sync + barrier,
+    after which rank 0 may read ``tensor()`` (a torch view of the buffer)."""
+
+    def __init__(self, n_complex: int, rank: int, world: int, device_index: int, group=None):
+        import ctypes
+        import torch
+        import torch.distributed as dist
+        from . import capi
+        self._lib = capi.load()
+        self.rank, self.world, self.n_complex, self.group = rank, world, int(n_complex), group
+        self._owned = self._mapped = None
+        hbytes = [None]
+        if rank == 0:
+            p = self._lib.r2iq_cuda_device_alloc(int(device_index), self.n_complex * 8)
+            if not p:
+                raise capi.R2iqError(capi.E_NOMEM, capi.last_error())
+            self._owned = p
+            buf = (ctypes.c_ubyte * 64)()
+            capi.check(self._lib.r2iq_cuda_ipc_export(ctypes.c_void_p(p), buf))
+            hbytes = [bytes(buf)]
+        if world > 1:
+            dist.broadcast_object_list(hbytes, src=0, group=group)
+        if rank == 0:
+            self.base = self._owned
+        else:
+            buf = (ctypes.c_ubyte * 64).from_buffer_copy(hbytes[0])
+            mapped = ctypes.c_void_p()
+            capi.check(self._lib.r2iq_cuda_ipc_open(int(device_index), buf, ctypes.byref(mapped)))
+            self._mapped = mapped.value
+            self.base = self._mapped
+        self._torch = torch
+        self._dist = dist
+
+    def ptr(self, offset_complex: int = 0) -> int:
+        return self.base + 8 * int(offset_complex)
+
+    def fence(self) -> None:
+        self._torch.cuda.synchronize()
+        if self.world > 1:
+            self._dist.barrier(group=self.group)
+
+    def tensor(self):
+        """complex64 view of the whole buffer (rank 0 only)."""
+        if self.rank != 0:
+            raise RuntimeError("only the collecting rank reads the gathered buffer")
+        torch = self._torch
+
+        class _Arr:
+            pass
+        a = _Arr()
+        a.__cuda_array_interface__ = {"shape": (2 * self.n_complex,), "typestr": "<f4", "data": (self.base, False), "version": 3}
+        return torch.view_as_complex(torch.as_tensor(a, device=torch.device("cuda", torch.cuda.current_device())).view(-1, 2))
+
+    def close(self) -> None:
+        if self._mapped:
+            self._lib.r2iq_cuda_ipc_close(self._mapped)
+            self._mapped = None
+        if self.world > 1:
+            self._dist.barrier(group=self.group)      # nobody frees before every mapping is closed
+        if self._owned:
+            self._lib.r2iq_cuda_device_free(self._owned)
+            self._owned = None
+
+
 def run_time_sharded(process: Callable[[np.ndarray, int], "np.ndarray"], capture: np.ndarray, d: int, rank: int,
                      world: int, history: np.ndarray | None = None):
     """Rank-local part of a time-sharded run: `process(slab_with_halo, n_blocks)` must return the

@@ -219,6 +219,19 @@ R2IQ_API void* r2iq_cuda_host_alloc_on(size_t bytes, int device);
 R2IQ_API int r2iq_cuda_device_numa_node(int device);
 R2IQ_API int r2iq_cuda_host_free(void* p);
 
+/* Output shared between the ranks of one box (one process per GPU; SURVEY.md 8e: "gather IQ to one rank").  The
+ * collecting rank allocates the destination with device_alloc and exports it; every other rank opens the handle
+ * (CUDA IPC, peer access over NVLink) and passes `mapped + its offset` as d_iq_out of r2iq_cuda_process_device /
+ * r2iq_cuda_process_channels_device: the fused kernel stores its IQ into the collecting rank's memory while it
+ * computes, in place of a gather after the kernel.  The caller synchronises its stream and then the ranks (any
+ * barrier) before the collecting rank reads.  The handle is an opaque 64-byte token to be sent between the processes. */
+#define R2IQ_IPC_HANDLE_BYTES 64
+R2IQ_API void* r2iq_cuda_device_alloc(int device, size_t bytes);
+R2IQ_API int r2iq_cuda_device_free(void* p);
+R2IQ_API int r2iq_cuda_ipc_export(void* device_ptr, unsigned char handle[R2IQ_IPC_HANDLE_BYTES]);
+R2IQ_API int r2iq_cuda_ipc_open(int device, const unsigned char handle[R2IQ_IPC_HANDLE_BYTES], void** device_ptr);
+R2IQ_API int r2iq_cuda_ipc_close(void* device_ptr);
+
 /* convert_float<rand>  (Core/fft_mt_r2iq.h:36-51) on its own: n int16 host samples (n even) ->
  * n floats, through the same device code the fused kernel uses.  Parity hook for the stage that
  * must be bit-exact. */
@@ -227,6 +240,9 @@ R2IQ_API int r2iq_cuda_convert(r2iq_cuda_t h, const int16_t* in, long n, int ran
 R2IQ_API int r2iq_cuda_get_stats(r2iq_cuda_t h, r2iq_cuda_stats* out);
 /* FFTN_R_ADC this operator was created with (2048 or 8192). */
 R2IQ_API int r2iq_cuda_get_fftn(r2iq_cuda_t h);
+/* Name of the device kernel a launch at decimation index d uses on this handle, as profilers print it (measurement
+ * records name the kernel that ran instead of assuming one). */
+R2IQ_API int r2iq_cuda_kernel_name(r2iq_cuda_t h, int d, char* buf, int n);
 
 /* Device-free host logic (usable without a GPU; exercised by the CPU test suite).
  *  design_filter:  filterHw[d] exactly as r2iq_cuda_create designs it (KaiserWindow + tap placement +
