@@ -15,11 +15,17 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB_DIR = os.path.join(HERE, "lib")
 LIB_PATH = os.path.join(LIB_DIR, "libr2iq_cuda.so")
-SOURCES = ["r2iq_kernels.cu", "r2iq_dual.cu", "r2iq_dual_d0.cu", "r2iq_dual_d1.cu", "r2iq_dual_dn.cu", "r2iq_pair.cu", "r2iq_channels.cu", "r2iq_wide.cu", "r2iq_capi.cu", "fir_design.cpp"]
+# The shipped library: one fused kernel per (FFTN, decimation) plus channelizer, mixer pass and the C ABI.
+SOURCES = ["r2iq_pair.cu", "r2iq_launch.cu", "r2iq_channels.cu", "r2iq_wide.cu", "r2iq_capi.cu", "fir_design.cpp"]
+# R2IQ_AB_VARIANTS=1 at build time adds the older kernel generations and their run-time switches (R2IQ_KERNEL_GEN,
+# R2IQ_VARIANT, R2IQ_CTAS_PER_SM) for comparison runs (tools/variant_sweep.py); `r2iq_cuda_version()` then says so.
+AB_VARIANTS = os.environ.get("R2IQ_AB_VARIANTS", "0") not in ("", "0")
+if AB_VARIANTS:
+    SOURCES += ["r2iq_gen1.cu", "r2iq_dual.cu", "r2iq_dual_d0.cu", "r2iq_dual_d1.cu", "r2iq_dual_dn.cu"]
 HEADERS = ["r2iq_kernels.cuh", "dft_regs.cuh", "dft_regs2.cuh", "r2iq_common.cuh", "work_dispenser.cuh", "dual_frame.cuh", "fir_design.h", os.path.join("..", "..", "include", "r2iq_cuda.h")]
 ARCH_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a"]
 NVCC_FLAGS = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden",
-              "--cudart", "static"]
+              "--cudart", "static", "-Xfatbin", "-compress-all"] + (["-DR2IQ_AB_VARIANTS"] if AB_VARIANTS else [])
 
 
 def nvcc() -> str:
@@ -34,7 +40,10 @@ def _stale() -> bool:
         return True
     t = os.path.getmtime(LIB_PATH)
     deps = [os.path.join(CSRC, s) for s in SOURCES + HEADERS] + [os.path.abspath(__file__)]
-    return any(os.path.getmtime(d) > t for d in deps)
+    if any(os.path.getmtime(d) > t for d in deps):
+        return True
+    flavour = os.path.join(LIB_DIR, ".flavour")          # a library of the other flavour is stale too
+    return not os.path.exists(flavour) or open(flavour).read().strip() != ("ab" if AB_VARIANTS else "product")
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
@@ -48,6 +57,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     def compile_one(src: str) -> str:
         obj = os.path.join(LIB_DIR, os.path.splitext(src)[0] + ".o")
         path = os.path.join(CSRC, src)
+        obj = obj[:-2] + ("_ab.o" if AB_VARIANTS else ".o")      # the two flavours never share objects
         if not force and os.path.exists(obj) and os.path.getmtime(obj) >= max(os.path.getmtime(path), hdr_time):
             return obj                    # translation unit and every header older than its object
         cmd = [nvcc(), *ARCH_FLAGS, *NVCC_FLAGS, "-c", path, "-o", obj]
@@ -64,6 +74,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
     if verbose:
         print(" ".join(cmd), flush=True)
     subprocess.run(cmd, check=True)
+    with open(os.path.join(LIB_DIR, ".flavour"), "w") as f:
+        f.write("ab" if AB_VARIANTS else "product")
     return LIB_PATH
 
 

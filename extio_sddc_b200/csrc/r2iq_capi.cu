@@ -657,7 +657,11 @@ int ensure_slots(r2iq_cuda_t h) {
 extern "C" {
 
 const char* r2iq_cuda_last_error(void) { return g_err; }
-const char* r2iq_cuda_version(void) { return "r2iq-b200 0.1 sm_100a fftn=2048,8192"; }
+#ifdef R2IQ_AB_VARIANTS
+const char* r2iq_cuda_version(void) { return "r2iq-b200 0.2 sm_100a fftn=2048,8192 ab-variants"; }
+#else
+const char* r2iq_cuda_version(void) { return "r2iq-b200 0.2 sm_100a fftn=2048,8192"; }
+#endif
 
 int r2iq_cuda_create(const r2iq_cuda_config* cfg, r2iq_cuda_t* out) {
     if (!cfg || !out) return fail(R2IQ_E_INVALID, "null argument");
@@ -700,7 +704,9 @@ int r2iq_cuda_create(const r2iq_cuda_config* cfg, r2iq_cuda_t* out) {
     };
     DeviceGuard dg(dev);                  // the caller's current device is put back when create returns
     if ((e = dg.err) != cudaSuccess) return bail(fail(R2IQ_E_CUDA, "cudaSetDevice: %s", cudaGetErrorString(e)));
-    if (const char* gen = getenv("R2IQ_KERNEL_GEN")) set_kernel_generation(atoi(gen));   // A/B measurements only
+#ifdef R2IQ_AB_VARIANTS
+    if (const char* gen = getenv("R2IQ_KERNEL_GEN")) set_kernel_generation(atoi(gen));   // comparison builds only
+#endif
     if ((e = setup_channel_kernels()) != cudaSuccess)
         return bail(fail(R2IQ_E_CUDA, "channelizer kernel setup: %s", cudaGetErrorString(e)));
     if ((e = setup_fused_kernels()) != cudaSuccess)

@@ -129,6 +129,9 @@ cudaError_t launch_fused(int d, const FusedParams& p, int sm_count, cudaStream_t
 // per decimation (default, see launch_fused); 1..4 = older or alternative families kept for comparison.
 // All meet the parity bar.
 void set_kernel_generation(int gen);
+// first-generation kernels (r2iq_gen1.cu; comparison builds only, like the four families below)
+cudaError_t setup_gen1_kernels();
+cudaError_t launch_gen1(int d, const FusedParams& p, int sm_count, cudaStream_t stream);
 // second-generation kernels (r2iq_dual.cu): two frames per warp on packed fp32x2 lanes + TMA input
 cudaError_t setup_dual_kernels();
 cudaError_t launch_dual(int d, const FusedParams& p, int sm_count, cudaStream_t stream, bool tma);

@@ -429,7 +429,7 @@ static cudaError_t launch_pair_one(const FusedParams& p, int sm_count, cudaStrea
 
 // (D, W) combinations that are built
 #define R2IQ_PAIR_FOR_ALL(X) \
-    X(0, 8) X(1, 8) X(1, 12) X(2, 12) X(3, 12) X(4, 12) X(5, 12) X(6, 12)
+    X(0, 8) X(1, 12) X(2, 12) X(3, 12) X(4, 12) X(5, 12) X(6, 12)
 
 cudaError_t setup_pair_kernels() {
     cudaError_t e;

@@ -276,8 +276,10 @@ static cudaError_t setup_qv() {
 }
 template <int D>
 static cudaError_t setup_q() {
-    cudaError_t e = setup_qv<D, false>();
+#ifdef R2IQ_AB_VARIANTS
+    cudaError_t e = setup_qv<D, false>();      // fixed-stride form, comparison builds only
     if (e != cudaSuccess) return e;
+#endif
     return setup_qv<D, true>();
 }
 
@@ -307,7 +309,10 @@ static cudaError_t launch_qv(const WideParams& p, int sm_count, cudaStream_t str
 }
 template <int D>
 static cudaError_t launch_q(const WideParams& p, int sm_count, cudaStream_t stream) {
-    return (kernel_variant() & 1) ? launch_qv<D, true>(p, sm_count, stream) : launch_qv<D, false>(p, sm_count, stream);
+#ifdef R2IQ_AB_VARIANTS
+    if (!(kernel_variant() & 1)) return launch_qv<D, false>(p, sm_count, stream);
+#endif
+    return launch_qv<D, true>(p, sm_count, stream);
 }
 
 cudaError_t launch_wide(int d, const WideParams& p, int sm_count, cudaStream_t stream) {

@@ -1,4 +1,5 @@
-"""Development aid: A/B timing of the measurement variants of the dual-frame kernels (env R2IQ_VARIANT,
+"""Development aid (needs a comparison build: R2IQ_AB_VARIANTS=1 python -m extio_sddc_b200.build --force; generation 5 =
+the round-1 kernels): A/B timing of the measurement variants of the dual-frame kernels (env R2IQ_VARIANT,
 R2IQ_CTAS_PER_SM) on a B200, with a parity check of every variant first.
     python tools/variant_sweep.py [--blocks N] [--variants 0,1,2,3] [--decims 0,2,5] [--ctas 1,2]
 """
