@@ -16,7 +16,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIB_DIR = os.path.join(HERE, "lib")
 LIB_PATH = os.path.join(LIB_DIR, "libr2iq_cuda.so")
 # The shipped library: one fused kernel per (FFTN, decimation) plus channelizer, mixer pass and the C ABI.
-SOURCES = ["r2iq_pair.cu", "r2iq_launch.cu", "r2iq_channels.cu", "r2iq_wide.cu", "r2iq_capi.cu", "fir_design.cpp"]
+SOURCES = ["r2iq_pair.cu", "r2iq_launch.cu", "r2iq_channels.cu", "r2iq_wide.cu", "r2iq_fft.cu", "r2iq_capi.cu", "fir_design.cpp"]
 # R2IQ_AB_VARIANTS=1 at build time adds the older kernel generations and their run-time switches (R2IQ_KERNEL_GEN,
 # R2IQ_VARIANT, R2IQ_CTAS_PER_SM) for comparison runs (tools/variant_sweep.py); `r2iq_cuda_version()` then says so.
 AB_VARIANTS = os.environ.get("R2IQ_AB_VARIANTS", "0") not in ("", "0")
@@ -82,17 +82,22 @@ def build(force: bool = False, verbose: bool = False) -> str:
 HOST = os.path.join(HERE, "host")
 BIN_DIR = os.path.join(HERE, "bin")
 REPLAY_PATH = os.path.join(BIN_DIR, "r2iq_replay")
+FFT_BENCH_PATH = os.path.join(BIN_DIR, "fft_benchmark_cuda")
 
 
 def build_tools(force: bool = False) -> str:
     """Host-side tools over the C ABI (g++ only): bin/r2iq_replay, the capture-file replayer (host/r2iq_replay.cpp)."""
     srcs = [os.path.join(HOST, "r2iq_replay.cpp"), os.path.join(HOST, "wav_capture.cpp")]
-    deps = srcs + [os.path.join(HOST, "wav_capture.h"), LIB_PATH]
-    if not force and os.path.exists(REPLAY_PATH) and all(os.path.getmtime(d) <= os.path.getmtime(REPLAY_PATH) for d in deps):
+    deps = srcs + [os.path.join(HOST, f) for f in ("wav_capture.h", "fft_benchmark_cuda.cpp", "cuda_fft_backend.cpp", "cuda_fft_backend.h")] + [LIB_PATH]
+    if not force and os.path.exists(REPLAY_PATH) and os.path.exists(FFT_BENCH_PATH) and all(os.path.getmtime(d) <= os.path.getmtime(REPLAY_PATH) for d in deps):
         return REPLAY_PATH
     os.makedirs(BIN_DIR, exist_ok=True)
-    subprocess.run(["g++", "-std=c++17", "-O2", "-I", os.path.join(HERE, "..", "include"), "-I", HOST, *srcs,
-                    "-L", LIB_DIR, "-lr2iq_cuda", "-Wl,-rpath,$ORIGIN/../lib", "-o", REPLAY_PATH], check=True)
+    common = ["g++", "-std=c++17", "-O2", "-I", os.path.join(HERE, "..", "include"), "-I", HOST]
+    link = ["-L", LIB_DIR, "-lr2iq_cuda", "-Wl,-rpath,$ORIGIN/../lib"]
+    subprocess.run([*common, *srcs, *link, "-o", REPLAY_PATH], check=True)
+    # bin/fft_benchmark_cuda: the reference's FFT backend benchmark table for CudaFFTBackend (host/fft_benchmark_cuda.cpp)
+    subprocess.run([*common, os.path.join(HOST, "fft_benchmark_cuda.cpp"), os.path.join(HOST, "cuda_fft_backend.cpp"), *link,
+                    "-o", FFT_BENCH_PATH], check=True)
     return REPLAY_PATH
 
 

@@ -21,6 +21,7 @@ HALF_FFT = FFTN // 2
 OK = 0
 E_INVALID, E_CUDA, E_NOMEM, E_STATE, E_NODEVICE = -1, -2, -3, -4, -5
 NCO_REFERENCE, NCO_DIRECT = 0, 1
+FFT_R2C, FFT_C2C_FORWARD, FFT_C2C_BACKWARD = 0, 1, 2
 
 
 class Config(ctypes.Structure):
@@ -96,6 +97,11 @@ _SIGNATURES = {
     "r2iq_cuda_design_filter": (_I, [_F, _I, _VP, _I]),
     "r2iq_cuda_kaiser": (_I, [_I, _F, _F, _F, _VP]),
     "r2iq_cuda_freq_to_tunebin": (_F, [_F, _I, ctypes.POINTER(_I)]),
+    "r2iq_cuda_fft_plan": (_I, [_I, _I, _I, _L, ctypes.POINTER(_VP)]),
+    "r2iq_cuda_fft_execute": (_I, [_VP, _VP, _VP]),
+    "r2iq_cuda_fft_execute_device": (_I, [_VP, _VP, _VP, _L, _VP]),
+    "r2iq_cuda_fft_batch": (_L, [_VP]),
+    "r2iq_cuda_fft_destroy": (_I, [_VP]),
 }
 
 

@@ -43,6 +43,13 @@ int fail(int code, const char* fmt, ...) {
 }
 
 void poison(r2iq_cuda_t h, const char* why);   // defined once the handle type is complete
+}  // namespace
+
+namespace r2iq {
+void set_last_error(const char* msg) { snprintf(g_err, sizeof(g_err), "%s", msg); }   // for the other translation units
+}
+
+namespace {
 
 constexpr double kPiD = 3.14159265358979323846;
 constexpr int kDefaultChunkBlocks = 256;

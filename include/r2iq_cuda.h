@@ -254,6 +254,25 @@ R2IQ_API int r2iq_cuda_design_filter(float gain, int d, float* hw_interleaved, i
 R2IQ_API int r2iq_cuda_kaiser(int num_taps, float astop_db, float f_pass, float f_stop, float* taps);
 R2IQ_API float r2iq_cuda_freq_to_tunebin(float offset, int d, int* tunebin);
 
+/* ---- Stand-alone batched transforms: the CUDA side of the reference's FFT backend abstraction --------------------
+ * Core/fft_backend.h:22-50 (FFTBackend: plan_r2c / plan_c2c / execute_r2c / execute_c2c / destroy_plan / alloc / free)
+ * at the sizes Core/fft_benchmark.cpp:12-15 sweeps.  FFTW conventions: unnormalised, forward = exp(-2 pi i nk/n),
+ * r2c of n reals -> n/2 + 1 bins.  One plan runs `batch` transforms per launch, laid out back to back (input pitch n,
+ * output pitch n/2 + 1 for r2c, n for c2c).  Lengths: r2c 128...8192, c2c 64...4096, powers of two.
+ *   fft_plan            plan_r2c / plan_c2c: twiddles (float64, rounded once), kernel choice, a private stream.
+ *   fft_execute         execute_r2c / execute_c2c on HOST buffers, blocking like the reference's backends: page-locked
+ *                       buffers (r2iq_cuda_host_alloc, the backend's alloc()) of up to 256 KiB are read and written in
+ *                       place by the kernel, anything else is staged through device memory.
+ *   fft_execute_device  the same kernel on DEVICE buffers, asynchronous on `stream`, `batch` <= any size.
+ * The register DFTs are the ones of the fused r2iq kernels (csrc/dft_regs.cuh); there is no CPU path. */
+enum { R2IQ_FFT_R2C = 0, R2IQ_FFT_C2C_FORWARD = 1, R2IQ_FFT_C2C_BACKWARD = 2 };
+typedef struct r2iq_cuda_fft_s* r2iq_cuda_fft_t;
+R2IQ_API int r2iq_cuda_fft_plan(int device, int kind, int n, long batch, r2iq_cuda_fft_t* out);
+R2IQ_API int r2iq_cuda_fft_execute(r2iq_cuda_fft_t plan, const void* in_host, void* out_host);
+R2IQ_API int r2iq_cuda_fft_execute_device(r2iq_cuda_fft_t plan, const void* d_in, void* d_out, long batch, void* stream);
+R2IQ_API long r2iq_cuda_fft_batch(r2iq_cuda_fft_t plan);
+R2IQ_API int r2iq_cuda_fft_destroy(r2iq_cuda_fft_t plan);
+
 #ifdef __cplusplus
 }
 #endif

@@ -136,6 +136,17 @@ struct fftwshim_plan_s {
     DFTI_HANDLE mkl_outplace = nullptr;  // MKL backend, in != out
 };
 
+// A program that never calls fftwshim_set_backend (the reference's own fft_benchmark main) selects MKL through the
+// environment: FFTW3_SHIM_MKL=<path of a library exporting the DFTI entry points> is honoured at the first plan.
+static void backend_from_env() {
+    static std::once_flag once;
+    std::call_once(once, [] {
+        const char* path = getenv("FFTW3_SHIM_MKL");
+        if (path && *path && fftwshim_set_backend(FFTWSHIM_BACKEND_MKL, path) != 0)
+            fprintf(stderr, "fftw3 shim: FFTW3_SHIM_MKL=%s not usable, staying on the float64 FFT\n", path);
+    });
+}
+
 static fftwf_plan make_plan(int n, int sign, bool r2c) {
     fftwshim_plan_s* p = new fftwshim_plan_s();
     p->n = n;
@@ -177,9 +188,13 @@ void* fftwf_malloc(size_t n) {
 void fftwf_free(void* p) { free(p); }
 
 fftwf_plan fftwf_plan_dft_1d(int n, fftwf_complex*, fftwf_complex*, int sign, unsigned) {
+    backend_from_env();
     return make_plan(n, sign, false);
 }
-fftwf_plan fftwf_plan_dft_r2c_1d(int n, float*, fftwf_complex*, unsigned) { return make_plan(n, -1, true); }
+fftwf_plan fftwf_plan_dft_r2c_1d(int n, float*, fftwf_complex*, unsigned) {
+    backend_from_env();
+    return make_plan(n, -1, true);
+}
 
 void fftwf_execute_dft(const fftwf_plan p, fftwf_complex* in, fftwf_complex* out) {
     if (p->backend == FFTWSHIM_BACKEND_MKL) {

@@ -122,3 +122,21 @@ def test_numa_helpers_degrade_without_device(monkeypatch):
         assert lib.r2iq_cuda_device_numa_node(0) == -1
         assert not lib.r2iq_cuda_host_alloc_on(4096, 0)
         assert "cudaMallocHost" in capi.last_error()
+
+
+def test_fft_plan_argument_checks_need_no_device():
+    """r2iq_cuda_fft_plan (Core/fft_backend.h:30-31 plan_r2c / plan_c2c) refuses unsupported lengths, kinds and batches
+    with R2IQ_E_INVALID before it looks for a device; a supported request on a box without a GPU says so."""
+    import ctypes
+
+    import torch
+    lib = capi.load()
+    h = ctypes.c_void_p()
+    for kind, n, batch in ((capi.FFT_C2C_FORWARD, 1000, 1), (capi.FFT_C2C_FORWARD, 8192, 1), (capi.FFT_R2C, 64, 1),
+                           (capi.FFT_R2C, 16384, 1), (7, 1024, 1), (capi.FFT_C2C_BACKWARD, 1024, 0)):
+        assert lib.r2iq_cuda_fft_plan(-1, kind, n, batch, ctypes.byref(h)) == capi.E_INVALID, (kind, n, batch)
+        assert not h.value and capi.last_error()
+    if not torch.cuda.is_available():
+        assert lib.r2iq_cuda_fft_plan(-1, capi.FFT_R2C, 2048, 1, ctypes.byref(h)) == capi.E_NODEVICE
+        assert "no CPU path" in capi.last_error()
+    assert lib.r2iq_cuda_fft_destroy(None) == capi.OK

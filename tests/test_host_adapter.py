@@ -140,3 +140,38 @@ def test_replay_capture_matches_oracle(d, tune_hz, tunebin, rand):
     err = orc.rel_l2(got, ref)
     mx = float(np.abs(got - ref).max()) / orc.full_scale(gain)
     assert err <= 1e-5 and mx <= 1e-4, (err, mx)   # north-star tolerance
+
+
+# ---- FFT backend abstraction: Core/fft_backend.h + Core/fft_benchmark.cpp ------------------------
+@pytest.mark.gpu
+def test_cuda_fft_backend_through_reference_interface():
+    """CudaFFTBackend driven through the FFTBackend interface alone (alloc / plan / execute / destroy / free) at the
+    benchmark's six sizes, r2c + c2c both ways, against a float64 DFT: rel-L2 <= 1e-6 (tests/host/test_fft_backend.cpp)."""
+    capi.load()
+    lib_dir = os.path.dirname(capi.LIB_PATH)
+    exe = _compile(os.path.join(ROOT, "tests", "host", "test_fft_backend.cpp"), os.path.join(OUT, "test_fft_backend"),
+                   extra=[os.path.join(HOST, "cuda_fft_backend.cpp"), "-L", lib_dir, "-lr2iq_cuda", f"-Wl,-rpath,{lib_dir}"])
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "ALL PASS" in r.stdout, r.stdout + r.stderr
+
+
+@pytest.mark.gpu
+def test_reference_fft_benchmark_runs_on_cuda_backend():
+    """The reference's UNMODIFIED Core/fft_benchmark.cpp, linked with CudaFFTBackend as getFFTBackend()
+    (oracle/_ref/fft_benchmark_dropin, built here where the reference tree is), prints its table for all six sizes."""
+    exe = os.path.join(ROOT, "oracle", "_ref", "fft_benchmark_dropin")
+    if not os.path.exists(exe):
+        pytest.skip("oracle/_ref/fft_benchmark_dropin not built (needs /root/reference at build time)")
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "Backend: CUDA sm_100a register FFT" in r.stdout
+    rows = [l for l in r.stdout.splitlines() if l.strip()[:4].strip().isdigit() and "|" in l]
+    assert [int(l.split("|")[0]) for l in rows] == [4096, 2048, 1024, 512, 256, 128], r.stdout
+    for l in rows:                       # every timing is a positive number of microseconds
+        assert all(float(c) > 0 for c in l.split("|")[1:]), l
+
+
+@pytest.mark.skipif(not os.path.isdir("/root/reference/Core"), reason="reference tree not present on this box")
+def test_fft_backend_compiles_against_reference_header():
+    subprocess.run(["g++", "-std=c++17", "-fsyntax-only", "-DR2IQ_USE_REFERENCE_HEADERS", "-DR2IQ_FFT_BACKEND_FACTORY", *INC,
+                    "-I", "/root/reference/Core", os.path.join(HOST, "cuda_fft_backend.cpp")], check=True)
