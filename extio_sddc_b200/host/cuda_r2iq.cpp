@@ -80,23 +80,32 @@ void cuda_r2iq::Init(float gain, ringbuffer<int16_t>* input, ringbuffer<float>* 
 // Core/dsp/ringbuffer.h:154-170), so that the copy engines move data straight between ring slots and the device:
 // no staging buffer, no extra memcpy per block (what Core/arch/linux/FX3handler.cpp:139-147 writes is what the GPU reads).
 void cuda_r2iq::register_rings() {
+    // input ring: RadioHandlerClass::Start turns the operator on BEFORE the USB layer sizes the input ring
+    // (Core/RadioHandler.cpp:165-167), so on a first start there is nothing to lock yet; submit_loop calls again once
+    // the first slot has arrived (no copy has touched the ring by then)
     int16_t* ib = nullptr;
-    float* ob = nullptr;
-    size_t ip = 0, op = 0;
-    int ic = 0, oc = 0;
+    size_t ip = 0;
+    int ic = 0;
     ring_extent(in_, &ib, &ip, &ic);
+    if (ib && !(ib == in_base_ && ip == in_pitch_ && ic == in_count_)) {
+        if (in_registered_) r2iq_cuda_host_unregister(in_base_);
+        in_base_ = ib;
+        in_pitch_ = ip;
+        in_count_ = ic;
+        // a ring that cannot be page-locked still works: the copies are then staged by the driver (slower, not wrong)
+        in_registered_ = r2iq_cuda_host_register(ib, sizeof(int16_t) * ip * (size_t)ic) == R2IQ_OK;
+    }
+    float* ob = nullptr;
+    size_t op = 0;
+    int oc = 0;
     ring_extent(out_, &ob, &op, &oc);
-    if (!ib || !ob) return;
-    if (ib == in_base_ && ob == out_base_ && ip == in_pitch_ && op == out_pitch_) return;
-    unregister_rings();
-    in_base_ = ib;
-    in_pitch_ = ip;
-    in_count_ = ic;
-    out_base_ = ob;
-    out_pitch_ = op;
-    // a ring that cannot be page-locked still works: the copies are then staged by the driver (slower, not wrong)
-    in_registered_ = r2iq_cuda_host_register(ib, sizeof(int16_t) * ip * (size_t)ic) == R2IQ_OK;
-    out_registered_ = r2iq_cuda_host_register(ob, sizeof(float) * op * (size_t)oc) == R2IQ_OK;
+    if (ob && !(ob == out_base_ && op == out_pitch_ && oc == out_count_)) {
+        if (out_registered_) r2iq_cuda_host_unregister(out_base_);
+        out_base_ = ob;
+        out_pitch_ = op;
+        out_count_ = oc;
+        out_registered_ = r2iq_cuda_host_register(ob, sizeof(float) * op * (size_t)oc) == R2IQ_OK;
+    }
 }
 
 void cuda_r2iq::unregister_rings() {
@@ -105,6 +114,8 @@ void cuda_r2iq::unregister_rings() {
     in_registered_ = out_registered_ = false;
     in_base_ = nullptr;
     out_base_ = nullptr;
+    in_pitch_ = out_pitch_ = 0;
+    in_count_ = out_count_ = 0;
 }
 
 float cuda_r2iq::setFreqOffset(float offset) {
@@ -120,7 +131,7 @@ float cuda_r2iq::setFreqOffset(float offset) {
 void cuda_r2iq::TurnOn() {
     if (!handle_ || !in_ || !out_) return;
     r2iq_cuda_set_decimate(handle_, mdecimation);
-    r2iq_cuda_set_sideband(handle_, getSideband() ? 1 : 0);
+    r2iq_cuda_set_sideband(handle_, (controls_ ? controls_ : this)->getSideband() ? 1 : 0);
     if (r2iq_cuda_turn_on(handle_) != R2IQ_OK) {
         error_ = r2iq_cuda_last_error();
         return;
@@ -168,13 +179,14 @@ void cuda_r2iq::submit_loop() {
     while (run_.load()) {
         const int16_t* src = in_->getReadPtr();          // blocks like the reference worker
         if (!run_.load()) return;
+        if (!in_base_) register_rings();                 // first start: the ring was sized after TurnOn
         long avail = (long)(in_->getWriteCount() - in_writes_at_start_) - consumed;
         if (avail < 1) avail = 1;                        // getReadPtr returned: at least this one
         long n = avail < max_batch_ ? avail : max_batch_;
         const long slot_index = in_pitch_ ? (long)((src - in_base_) / (long)in_pitch_) : 0;
         if (slot_index + n > in_count_) n = in_count_ - slot_index;      // contiguous run only; the rest next time round
         if ((size_t)kBlock != in_pitch_) n = 1;          // a ring with padded slots: one slot per submission
-        r2iq_cuda_set_rand(handle_, getRand() ? 1 : 0);  // sampled per batch (impl.hpp:40)
+        r2iq_cuda_set_rand(handle_, (controls_ ? controls_ : this)->getRand() ? 1 : 0);  // sampled per batch (impl.hpp:40)
         uint64_t ticket = 0;
         if (r2iq_cuda_process_async(handle_, src, n, nullptr, nullptr, &ticket) != R2IQ_OK) {
             if (run_.load()) fail_stream();

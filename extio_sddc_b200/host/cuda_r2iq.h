@@ -46,6 +46,10 @@ public:
     float setFreqOffset(float offset) override;
 
     // not part of the reference interface
+    // Take the randomizer and sideband flags from another control object: the non-virtual setters of r2iqControlClass
+    // (updateRand, setSideband: Core/r2iq.h:22-26) land on whatever object the caller holds, so a wrapper that owns a
+    // cuda_r2iq (host/fft_mt_r2iq_cuda.cpp) points this at itself.
+    void follow(const r2iqControlClass* controls) { controls_ = controls; }
     const char* lastError() const { return error_.c_str(); }
     unsigned long long batches() const { return batches_.load(); }
 
@@ -65,6 +69,7 @@ private:
     int device_;
     int max_batch_;
     int fuse_fine_tune_;
+    const r2iqControlClass* controls_ = nullptr;
     r2iq_cuda_t handle_ = nullptr;
     ringbuffer<int16_t>* in_ = nullptr;
     ringbuffer<float>* out_ = nullptr;
@@ -75,7 +80,7 @@ private:
     int16_t* in_base_ = nullptr;
     float* out_base_ = nullptr;
     size_t in_pitch_ = 0, out_pitch_ = 0;   // elements between slots
-    int in_count_ = 0;
+    int in_count_ = 0, out_count_ = 0;
     bool in_registered_ = false, out_registered_ = false;
     int in_writes_at_start_ = 0;
     // submissions handed from the submitter to the publisher, in order

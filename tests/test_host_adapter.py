@@ -175,3 +175,52 @@ def test_reference_fft_benchmark_runs_on_cuda_backend():
 def test_fft_backend_compiles_against_reference_header():
     subprocess.run(["g++", "-std=c++17", "-fsyntax-only", "-DR2IQ_USE_REFERENCE_HEADERS", "-DR2IQ_FFT_BACKEND_FACTORY", *INC,
                     "-I", "/root/reference/Core", os.path.join(HOST, "cuda_fft_backend.cpp")], check=True)
+
+
+# ---- consumers above RadioHandlerClass ----------------------------------------------------------
+REF_BIN = os.path.join(ROOT, "oracle", "_ref")
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("rate,blocks,rand", [(32000000, 48, 0), (8000000, 96, 1), (2000000, 128, 0)])
+def test_libsddc_sync_ring_delivers_reference_iq(rate, blocks, rand):
+    """The reference's UNMODIFIED libsddc.cpp (mock USB layer, -DLIBSDDC_TESTING) streams a capture through
+    sddc_start_streaming / sddc_read_sync (callback -> 1 MiB byte ring, libsddc/libsddc.cpp:79-126,659-695) twice: linked
+    with the reference's fft_mt_r2iq, and with host/fft_mt_r2iq_cuda.cpp in its place (the GPU operator behind the same
+    `new fft_mt_r2iq()` of RadioHandler.cpp:94-95).  The bytes read back must agree at the north-star bar."""
+    import numpy as np
+    cpu, gpu = os.path.join(REF_BIN, "ref_libsddc_cpu"), os.path.join(REF_BIN, "ref_libsddc_cuda")
+    if not (os.path.exists(cpu) and os.path.exists(gpu)):
+        pytest.skip("oracle/_ref/ref_libsddc_{cpu,cuda} not built (needs /root/reference at build time)")
+    os.makedirs(OUT, exist_ok=True)
+    outs = []
+    for exe, tag in ((cpu, "cpu"), (gpu, "cuda")):
+        path = os.path.join(OUT, f"libsddc_{tag}_{rate}.bin")
+        r = subprocess.run([exe, str(rate), str(blocks), path, str(rand)], capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0 and "DONE" in r.stdout, r.stdout + r.stderr[-2000:]
+        outs.append(np.fromfile(path, dtype=np.float32))
+        os.remove(path)
+    ref, got = outs
+    d = {32000000: 0, 8000000: 2, 2000000: 4}[rate]
+    assert ref.size == got.size == (blocks >> d) * 32768 * 2
+    skip = 2 * (32768 >> d)                     # IQ of input block 0: the reference reads uninitialised history there
+    err = np.linalg.norm(got[skip:].astype(np.float64) - ref[skip:]) / np.linalg.norm(ref[skip:].astype(np.float64))
+    peak = float(np.abs(ref[skip:]).max())
+    assert peak > 0
+    assert err <= 1e-5, err
+    assert float(np.abs(got[skip:] - ref[skip:]).max()) <= 1e-4 * peak * 4     # peak >= full scale / 4 for this capture
+
+
+@pytest.mark.gpu
+def test_radiohandler_stability_and_rate_switch_scenarios():
+    """unittest/stability_test.cpp:255-365 (20 start/stop cycles over all rates, continuity) and
+    unittest/benchmark_test.cpp:601-671 (rate switching) restated at RadioHandlerClass level with cuda_r2iq as the operator
+    (oracle/ref_scenarios_driver.cpp; the reference's RadioHandler / mixer / radio models compiled in place)."""
+    exe = os.path.join(REF_BIN, "ref_radio_scenarios")
+    if not os.path.exists(exe):
+        pytest.skip("oracle/_ref/ref_radio_scenarios not built (needs /root/reference at build time)")
+    r = subprocess.run([exe, "15"], capture_output=True, text=True, timeout=900)
+    lines = [l for l in r.stdout.splitlines() if l.startswith(("PASS", "FAIL", "ALL PASS", "  "))]
+    print("\n".join(lines))
+    assert r.returncode == 0 and "ALL PASS" in r.stdout, "\n".join(lines) + r.stderr[-2000:]
+    assert sum(l.startswith("PASS") for l in lines) == 3
