@@ -212,6 +212,37 @@ def test_libsddc_sync_ring_delivers_reference_iq(rate, blocks, rand):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("rate,blocks", [(32000000, 64), (4000000, 128)])
+def test_soapysddc_stream_buffers_deliver_reference_iq(rate, blocks):
+    """The reference's UNMODIFIED SoapySDDC module (16 buffers of 32768 CF32 samples, overflow event: Settings.cpp:14-35,
+    Streaming.cpp:110-182), built in place against declaration-only SoapySDR headers, read through readStream twice:
+    with the reference's fft_mt_r2iq and with host/fft_mt_r2iq_cuda.cpp in its place.  Same IQ at the north-star bar;
+    with a free-running producer the overflow event fires and streaming continues (checked inside the binary)."""
+    import numpy as np
+    cpu, gpu = os.path.join(REF_BIN, "ref_soapy_cpu"), os.path.join(REF_BIN, "ref_soapy_cuda")
+    if not (os.path.exists(cpu) and os.path.exists(gpu)):
+        pytest.skip("oracle/_ref/ref_soapy_{cpu,cuda} not built (needs /root/reference at build time)")
+    os.makedirs(OUT, exist_ok=True)
+    outs = []
+    for exe, tag in ((cpu, "cpu"), (gpu, "cuda")):
+        path = os.path.join(OUT, f"soapy_{tag}_{rate}.bin")
+        r = subprocess.run([exe, str(rate), str(blocks), path], capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0 and "DONE" in r.stdout and " OK" in r.stdout, r.stdout + r.stderr[-2000:]
+        outs.append(np.fromfile(path, dtype=np.float32))
+        os.remove(path)
+    ref, got = outs
+    d = {32000000: 0, 4000000: 3}[rate]
+    n = (blocks >> d) * 32768 * 2
+    assert ref.size >= n and got.size >= n
+    ref, got = ref[:n], got[:n]
+    skip = 2 * (32768 >> d)
+    err = np.linalg.norm(got[skip:].astype(np.float64) - ref[skip:]) / np.linalg.norm(ref[skip:].astype(np.float64))
+    peak = float(np.abs(ref[skip:]).max())
+    assert peak > 0 and err <= 1e-5, err
+    assert float(np.abs(got[skip:] - ref[skip:]).max()) <= 4e-4 * peak
+
+
+@pytest.mark.gpu
 def test_radiohandler_stability_and_rate_switch_scenarios():
     """unittest/stability_test.cpp:255-365 (20 start/stop cycles over all rates, continuity) and
     unittest/benchmark_test.cpp:601-671 (rate switching) restated at RadioHandlerClass level with cuda_r2iq as the operator
