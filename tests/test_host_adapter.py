@@ -255,3 +255,31 @@ def test_radiohandler_stability_and_rate_switch_scenarios():
     print("\n".join(lines))
     assert r.returncode == 0 and "ALL PASS" in r.stdout, "\n".join(lines) + r.stderr[-2000:]
     assert sum(l.startswith("PASS") for l in lines) == 3
+
+
+def test_cmake_switch_swaps_the_operator_sources(tmp_path):
+    """extio_sddc_b200/host/r2iq_cuda.cmake, the build switch INTEGRATION.md describes: with -DSDDC_R2IQ_CUDA=ON the
+    reference's operator sources leave the list and the CUDA ones enter it, the target gains the define, include paths
+    and library; with the switch off nothing changes."""
+    import shutil
+    if not shutil.which("cmake"):
+        pytest.skip("cmake not installed")
+    capi.load()   # the switch refuses to configure without the built library
+    src = os.path.join(ROOT, "tests", "host", "cmake_switch")
+
+    def configure(*flags):
+        build = tmp_path / ("b" + str(len(flags)))
+        r = subprocess.run(["cmake", "-S", src, "-B", str(build), f"-DR2IQ_CUDA_ROOT={ROOT}", *flags],
+                           capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stdout + r.stderr
+        return {k: v for k, v in (l[3:].split("=", 1) for l in r.stdout.splitlines() if l.startswith("-- ") and "_AFTER=" in l)}
+
+    off = configure()
+    assert "fft_mt_r2iq.cpp" in off["SRC_AFTER"] and "fft_mt_r2iq_cuda.cpp" not in off["SRC_AFTER"]
+    assert "r2iq_cuda" not in off["LIBS_AFTER"]
+    on = configure("-DSDDC_R2IQ_CUDA=ON", "-DSDDC_FFT_BACKEND_CUDA=ON")
+    names = [os.path.basename(p) for p in on["SRC_AFTER"].split(";")]
+    assert not [n for n in names if n.startswith("fft_mt_r2iq") and n != "fft_mt_r2iq_cuda.cpp"]
+    assert {"fft_mt_r2iq_cuda.cpp", "cuda_r2iq.cpp", "cuda_fft_backend.cpp", "RadioHandler.cpp", "pf_mixer.cpp"} <= set(names)
+    assert "fft_backend_fftw.cpp" not in names and "fft_benchmark.cpp" in names
+    assert "R2IQ_USE_REFERENCE_HEADERS" in on["DEFS_AFTER"] and "r2iq_cuda" in on["LIBS_AFTER"]
