@@ -559,58 +559,76 @@ def run_ours(args, rank: int, local_rank: int, world: int):
             po.close()
             del xs, local_out
 
-    # ---- config 4: 64-channel channelizer at d = 5, channels sharded over the ranks ---------------------
+    # ---- config 4: 64-channel channelizer at d = 5 ------------------------------------------------------------
+    # N > 1: the capture is cut into TIME SLABS (shard.time_slabs, the scheme of the headline path) and every rank
+    # produces all 64 channels of its slab, so no forward FFT is computed twice; the channel-sharded alternative
+    # (every rank transforms the whole capture for 64/N channels: shard.channel_shards) is timed beside it.
     channelizer = None
     if not args.no_channelizer:
         from extio_sddc_b200 import shard
         all_bins = shard.channel_tunebins(64)
-        mine = [all_bins[c] for c in shard.channel_shards(64, world)[rank]]
         cd = 5
-        cout = torch.empty(len(mine) * n_blocks * (32768 >> cd), dtype=torch.complex64, device=dev)
         op.setDecimate(cd)
         op.TurnOn()
-        for _ in range(2):
-            op.process_channels_device(x.data_ptr(), n_blocks, mine, cout.data_ptr(), stream)
-        barrier()
-        torch.cuda.synchronize()
-        c0 = torch.cuda.Event(enable_timing=True)
-        c1 = torch.cuda.Event(enable_timing=True)
-        c0.record()
-        reps = 5
-        for _ in range(reps):
-            op.process_channels_device(x.data_ptr(), n_blocks, mine, cout.data_ptr(), stream)
-        c1.record()
-        torch.cuda.synchronize()
-        cms = c0.elapsed_time(c1) / reps
-        if world > 1:
-            t = torch.tensor([cms], dtype=torch.float64, device=dev)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            cms = float(t.item())
+
+        def time_channels(bins, first_block, blocks, out_t):
+            src = x.data_ptr() + first_block * 65536 * 2      # [history = tail of the previous block | blocks]
+            for _ in range(2):
+                op.process_channels_device(src, blocks, bins, out_t.data_ptr(), stream)
+            barrier()
+            torch.cuda.synchronize()
+            c0 = torch.cuda.Event(enable_timing=True)
+            c1 = torch.cuda.Event(enable_timing=True)
+            c0.record()
+            reps = 5
+            for _ in range(reps):
+                op.process_channels_device(src, blocks, bins, out_t.data_ptr(), stream)
+            c1.record()
+            torch.cuda.synchronize()
+            ms = c0.elapsed_time(c1) / reps
+            if world > 1:
+                t = torch.tensor([ms], dtype=torch.float64, device=dev)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                ms = float(t.item())
+            return ms
+
+        first, mine_blocks = shard.time_slabs(n_blocks, world, cd)[rank]
+        per_ch = mine_blocks * (32768 >> cd)
+        cout = torch.empty(64 * per_ch, dtype=torch.complex64, device=dev)
+        cms = time_channels(all_bins, first, mine_blocks, cout)
         # every channel equals a separate operator tuned to its bin (Core/fft_mt_r2iq_impl.hpp:76-138 per channel): check
-        # the first and the last channel of this rank bit for bit against r2iq_cuda_process_device
-        per_ch = n_blocks * (32768 >> cd)
+        # the first and the last channel of this rank's slab against r2iq_cuda_process_device on the same slab
         chan_ok = True
         one = torch.empty(per_ch, dtype=torch.complex64, device=dev)
-        for ci in sorted({0, len(mine) - 1}):
-            op.tunebin = mine[ci]
-            op.process_device(x.data_ptr(), n_blocks, one.data_ptr(), stream)
+        for ci in (0, 63):
+            op.tunebin = all_bins[ci]
+            op.process_device(x.data_ptr() + first * 65536 * 2, mine_blocks, one.data_ptr(), stream)
             torch.cuda.synchronize()
             a = torch.view_as_real(cout[ci * per_ch:(ci + 1) * per_ch])
             b = torch.view_as_real(one)
             rel = float(torch.linalg.vector_norm(a - b) / torch.linalg.vector_norm(b))
             chan_ok = chan_ok and rel <= 1e-5
         op.tunebin = TUNEBIN
-        del one
+        del one, cout
+        cms_ch = None
         if world > 1:
             t = torch.tensor([1.0 if chan_ok else 0.0], dtype=torch.float64, device=dev)
             dist.all_reduce(t, op=dist.ReduceOp.MIN)
             chan_ok = bool(t.item() > 0.5)
-        channelizer = {"channels": 64, "channels_per_gpu": len(mine), "d": cd, "decimation": 64, "ms": round(cms, 3),
+            mine = [all_bins[c] for c in shard.channel_shards(64, world)[rank]]
+            cout = torch.empty(len(mine) * n_blocks * (32768 >> cd), dtype=torch.complex64, device=dev)
+            cms_ch = time_channels(mine, 0, n_blocks, cout)
+            del cout
+        channelizer = {"channels": 64, "d": cd, "decimation": 64, "blocks": n_blocks, "ms": round(cms, 3),
+                       "sharding": "time slabs x all channels" if world > 1 else "none",
                        "verified": chan_ok,
                        "input_gsamples_s": round(samples_per_launch / (cms * 1e-3) / 1e9, 2),
                        "channel_gsamples_s": round(64 * samples_per_launch / (cms * 1e-3) / 1e9, 1),
-                       "note": "every rank reads the same capture; one forward FFT per frame shared by its channels"}
-        del cout
+                       "alg_bytes_per_input_sample": 10.0,
+                       "hbm_frac": round(10.0 * samples_per_launch / world / (cms * 1e-3) / 1e9 / peak, 4),
+                       "kernel": "r2iq_channels_lane_kernel<5>",
+                       "ms_channel_sharded": None if cms_ch is None else round(cms_ch, 3),
+                       "note": "one forward FFT per frame shared by all 64 channels; at N > 1 no rank repeats another's transforms"}
 
     # ---- FFTN 8192 (the reference tree as shipped, Core/config.h:49): the same sweep on the wide kernel family ----
     wide = None

@@ -446,7 +446,7 @@ void nco_direct_advance(NcoState& s, size_t n_out) {
 }
 
 // FFTN 8192: static twiddles once per handle, filter gains (and small-transform twiddles) per (d, tune bin).
-int launch_wide_impl(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d_out, cudaStream_t stream) {
+int launch_wide_impl(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d_out, cudaStream_t stream, int tunebin) {
     const int d = h->latched_decimate;
     const int HF = 4096, M = HF >> d;
     if (!h->d_twq) {
@@ -465,7 +465,6 @@ int launch_wide_impl(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d
         CU(h, cudaMemcpy(h->d_twq, tq.data(), sizeof(float2) * tq.size(), cudaMemcpyHostToDevice));
         CU(h, cudaMemcpy(h->d_wctab, ct.data(), sizeof(float2) * ct.size(), cudaMemcpyHostToDevice));
     }
-    const int tunebin = h->tunebin.load();   // one snapshot per launch
     const long long key = ((long long)h->hw_version[d] << 20) | ((long long)d << 16) | (long long)tunebin;
     r2iq_cuda_s::WideSet ws;
     auto it = h->wide_tables.find(key);
@@ -515,28 +514,13 @@ int launch_wide_impl(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d
     return R2IQ_OK;
 }
 
-int launch(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d_out, cudaStream_t stream, float** nco_starts,
-           size_t* nco_cap) {
-    if (h->fftn == 8192) {
-        int rc = launch_wide_impl(h, d_in, n_blocks, d_out, stream);
-        if (rc != R2IQ_OK) return rc;
-        h->stats.kernel_launches++;
-        h->stats.blocks_processed += (uint64_t)n_blocks;
-        const size_t n_out8 = (size_t)n_blocks * (size_t)((kTransferSamples / 2) >> h->latched_decimate);
-        if (h->nco.on && n_out8 > 0 && h->nco.mode == R2IQ_NCO_DIRECT) {
-            CU(h, launch_nco_mix_direct(d_out, (long long)n_out8, h->nco.phase, (double)h->nco.fc, stream));
-            nco_direct_advance(h->nco, n_out8);
-            return R2IQ_OK;
-        }
-        return nco_stage(h, d_out, n_out8, nco_starts, nco_cap, stream);
-    }
+// Parameter block of one single-channel launch at `tunebin` (tables from the per-(d, tune bin) cache), mixer off.
+int fused_params(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d_out, int tunebin, FusedParams* out) {
     TableSet ts;
     const int d = h->latched_decimate;
-    const int tunebin = h->tunebin.load();   // one snapshot per launch: a retune from the application thread between the
-                                             // table lookup and the parameter block would pair tables with another bin
     int rc = get_tables(h, d, tunebin, &ts);
     if (rc != R2IQ_OK) return rc;
-    FusedParams p;
+    FusedParams& p = *out;
     p.in_words = (const uint32_t*)d_in;
     p.out = (float2*)d_out;
     p.total_frames = (long long)n_blocks * kFramesPerBlock;
@@ -559,6 +543,30 @@ int launch(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d_out, cuda
     p.nco_rot = nullptr;
     p.nco_phase0 = 0.0;
     p.nco_fc = 0.0;
+    return R2IQ_OK;
+}
+
+int launch(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d_out, cudaStream_t stream, float** nco_starts,
+           size_t* nco_cap) {
+    if (h->fftn == 8192) {
+        int rc = launch_wide_impl(h, d_in, n_blocks, d_out, stream, h->tunebin.load());   // one snapshot per launch
+        if (rc != R2IQ_OK) return rc;
+        h->stats.kernel_launches++;
+        h->stats.blocks_processed += (uint64_t)n_blocks;
+        const size_t n_out8 = (size_t)n_blocks * (size_t)((kTransferSamples / 2) >> h->latched_decimate);
+        if (h->nco.on && n_out8 > 0 && h->nco.mode == R2IQ_NCO_DIRECT) {
+            CU(h, launch_nco_mix_direct(d_out, (long long)n_out8, h->nco.phase, (double)h->nco.fc, stream));
+            nco_direct_advance(h->nco, n_out8);
+            return R2IQ_OK;
+        }
+        return nco_stage(h, d_out, n_out8, nco_starts, nco_cap, stream);
+    }
+    const int d = h->latched_decimate;
+    const int tunebin = h->tunebin.load();   // one snapshot per launch: a retune from the application thread between the
+                                             // table lookup and the parameter block would pair tables with another bin
+    FusedParams p;
+    int rc = fused_params(h, d_in, n_blocks, d_out, tunebin, &p);
+    if (rc != R2IQ_OK) return rc;
     const size_t n_out = (size_t)n_blocks * (size_t)((kTransferSamples / 2) >> d);
     const bool direct = h->nco.on && n_out > 0 && h->nco.mode == R2IQ_NCO_DIRECT;
     if (direct) {                         // the default kernels mix in their store epilogue: no second pass, no host work
@@ -578,11 +586,30 @@ int launch(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d_out, cuda
 int launch_channels_impl(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, const int* tunebins, int n_channels,
                          float* d_out, cudaStream_t stream) {
     const int d = h->latched_decimate;
-    if (h->fftn != kFftN) return fail(R2IQ_E_INVALID, "the channelizer is built for FFTN %d only", kFftN);
-    if (d < 1) return fail(R2IQ_E_INVALID, "the channelizer needs decimation index >= 1 (latched: %d)", d);
+    const int half = h->half;
     for (int c = 0; c < n_channels; c++)
-        if (tunebins[c] < 0 || tunebins[c] >= kHalfFft || (tunebins[c] & 3))
-            return fail(R2IQ_E_INVALID, "channel %d: tune bin %d must be a multiple of 4 in [0,%d)", c, tunebins[c], kHalfFft);
+        if (tunebins[c] < 0 || tunebins[c] >= half || (tunebins[c] & 3))
+            return fail(R2IQ_E_INVALID, "channel %d: tune bin %d must be a multiple of 4 in [0,%d)", c, tunebins[c], half);
+    if (h->fftn != kFftN || d == 0) {
+        // FFTN 8192, and d = 0 (every channel needs the full-size backward transform, nothing of the forward one is small
+        // beside it): one launch of the single-channel kernel per channel, the way the reference runs one operator per
+        // tuned instance (Core/fft_mt_r2iq_impl.hpp:76-98); same result, no shared forward transform
+        const size_t per_ch = (size_t)n_blocks * (size_t)((kTransferSamples / 2) >> d);
+        for (int c = 0; c < n_channels; c++) {
+            float* dst = d_out + 2 * per_ch * (size_t)c;
+            int rc;
+            if (h->fftn == 8192) rc = launch_wide_impl(h, d_in, n_blocks, dst, stream, tunebins[c]);
+            else {
+                FusedParams p;
+                rc = fused_params(h, d_in, n_blocks, dst, tunebins[c], &p);
+                if (rc == R2IQ_OK) CU(h, launch_fused(d, p, h->sm_count, stream));
+            }
+            if (rc != R2IQ_OK) return rc;
+            h->stats.kernel_launches++;
+        }
+        h->stats.blocks_processed += (uint64_t)n_blocks;
+        return R2IQ_OK;
+    }
     const int M = kHalfFft >> d;
     TableSet ts;   // for tw_inv (independent of the tune bin when d >= 1)
     int rc = get_tables(h, d, 0, &ts);
@@ -1222,8 +1249,8 @@ int r2iq_cuda_process_channels_device(r2iq_cuda_t h, const int16_t* d_in, long n
     if (!h->on) return fail(R2IQ_E_STATE, "process called while the operator is off (call r2iq_cuda_turn_on)");
     if (n_blocks < 0 || n_channels < 0 || ((n_blocks > 0 && n_channels > 0) && (!d_in || !d_iq_out || !tunebins)))
         return fail(R2IQ_E_INVALID, "process_channels_device: bad arguments");
-    if (((uintptr_t)d_in & 15) || ((uintptr_t)d_iq_out & 7))
-        return fail(R2IQ_E_INVALID, "process_channels_device: input must be 16-byte and output 8-byte aligned");
+    if (((uintptr_t)d_in & 15) || ((uintptr_t)d_iq_out & 15))
+        return fail(R2IQ_E_INVALID, "process_channels_device: input and output must be 16-byte aligned");
     if (n_blocks == 0 || n_channels == 0) return R2IQ_OK;
     std::lock_guard<std::mutex> lk(h->mu);
     DeviceGuard dg(h->device);
@@ -1239,7 +1266,6 @@ int r2iq_cuda_process_channels(r2iq_cuda_t h, const int16_t* blocks, long n_bloc
     if (n_blocks < 0 || n_channels < 0 || ((n_blocks > 0 && n_channels > 0) && (!blocks || !iq_out || !tunebins)))
         return fail(R2IQ_E_INVALID, "process_channels: bad arguments");
     if (n_blocks == 0 || n_channels == 0) return R2IQ_OK;
-    if (h->fftn != kFftN) return fail(R2IQ_E_INVALID, "the channelizer is built for FFTN %d only", kFftN);
     std::lock_guard<std::mutex> lk(h->mu);
     CU(h, cudaSetDevice(h->device));
     const int d = h->latched_decimate;
@@ -1247,21 +1273,22 @@ int r2iq_cuda_process_channels(r2iq_cuda_t h, const int16_t* blocks, long n_bloc
     int16_t* d_in = nullptr;
     float* d_out = nullptr;
     DeviceScratch scratch;                // freed on every way out, the early returns of CU() included
-    cudaError_t e = scratch.alloc(&d_in, sizeof(int16_t) * ((size_t)kHalfFft + (size_t)n_blocks * kTransferSamples));
+    const size_t hist = (size_t)h->half;
+    cudaError_t e = scratch.alloc(&d_in, sizeof(int16_t) * (hist + (size_t)n_blocks * kTransferSamples));
     if (e == cudaSuccess) e = scratch.alloc(&d_out, sizeof(float) * 2 * per_ch * (size_t)n_channels);
     if (e != cudaSuccess) {
         cudaGetLastError();               // out of memory is the caller's problem, not a poisoned handle
         return fail(R2IQ_E_NOMEM, "cudaMalloc(channelizer buffers): %s", cudaGetErrorString(e));
     }
-    if (history) CU(h, cudaMemcpyAsync(d_in, history, sizeof(int16_t) * kHalfFft, cudaMemcpyHostToDevice, h->util_stream));
-    else CU(h, cudaMemsetAsync(d_in, 0, sizeof(int16_t) * kHalfFft, h->util_stream));
-    CU(h, cudaMemcpyAsync(d_in + kHalfFft, blocks, sizeof(int16_t) * (size_t)n_blocks * kTransferSamples,
+    if (history) CU(h, cudaMemcpyAsync(d_in, history, sizeof(int16_t) * hist, cudaMemcpyHostToDevice, h->util_stream));
+    else CU(h, cudaMemsetAsync(d_in, 0, sizeof(int16_t) * hist, h->util_stream));
+    CU(h, cudaMemcpyAsync(d_in + hist, blocks, sizeof(int16_t) * (size_t)n_blocks * kTransferSamples,
                           cudaMemcpyHostToDevice, h->util_stream));
     rc = launch_channels_impl(h, d_in, n_blocks, tunebins, n_channels, d_out, h->util_stream);
     if (rc == R2IQ_OK) {
         CU(h, cudaMemcpyAsync(iq_out, d_out, sizeof(float) * 2 * per_ch * (size_t)n_channels, cudaMemcpyDeviceToHost,
                               h->util_stream));
-        h->stats.h2d_bytes += sizeof(int16_t) * ((size_t)kHalfFft + (size_t)n_blocks * kTransferSamples);
+        h->stats.h2d_bytes += sizeof(int16_t) * (hist + (size_t)n_blocks * kTransferSamples);
         h->stats.d2h_bytes += sizeof(float) * 2 * per_ch * (size_t)n_channels;
     }
     CU(h, cudaStreamSynchronize(h->util_stream));

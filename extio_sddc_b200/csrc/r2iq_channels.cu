@@ -8,6 +8,7 @@
 // transformed back at once by inverse_bands (32>>d lanes per channel).  Per channel the result is
 // the stream a separate operator tuned to that bin would produce.
 // Output is channel-major: channel c writes out[c*out_stride + ...].
+#include "dual_frame.cuh"
 #include "r2iq_common.cuh"
 #include "work_dispenser.cuh"
 
@@ -109,6 +110,231 @@ __global__ void __launch_bounds__(kChThreads, 2) r2iq_channels_kernel(const Chan
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------
+// d = 5 and 6 (mfft = 32 / 16: the "many narrow channels" case): ONE LANE PER CHANNEL on the packed two-frame lanes of
+// the current single-channel kernels (r2iq_pair.cu).  Per warp and frame pair:
+//   1. the pair arrives by one TMA bulk copy; forward 1024-point transform, two frames per lane (dual_frame.cuh);
+//   2. the real-FFT split is channel independent: 2 X[k] = (Z[k] + conj Z[1024-k]) + c[k] (Z[k] - conj Z[1024-k]) is
+//      formed ONCE for all 1024 bins and left in shared memory as (re_A, re_B, im_A, im_B) quads;
+//   3. 32 channels at a time, lane = channel: the lane gathers its mfft band bins around its own tune bin with one
+//      LDS.128 each (zero outside [0, 1024): Core/fft_mt_r2iq_impl.hpp:91-96), multiplies by 0.5 H_d[m] and runs the
+//      mfft-point backward transform entirely in its registers (no shuffles, no transposition);
+//   4. the kept 3/4 of both frames is one contiguous run of the channel's output stream (frame k's samples follow
+//      frame k-1's, also across block edges: impl.hpp:117-138), so the lane lays its run out in a shared-memory row
+//      and hands it to the TMA engine as ONE bulk store of up to 384 bytes.  (Direct 16-byte stores from 32 lanes hit
+//      32 different lines per instruction: ncu showed 40 % of all stall samples on the MIO queue behind them.)
+// Per channel and frame that is 4 packed multiplies per bin plus one packed register DFT, against one whole band cut
+// and staged multi-lane inverse per GROUP in the kernel above.
+// ---------------------------------------------------------------------------------------------------------------
+namespace {
+using namespace dualf;
+constexpr int kLaneWarps = 7;
+constexpr int kLanePairBytes = (kHop + kFftN) * 2;                       // 7168: frames A and B of a pair
+template <int D>
+struct LaneGeo {
+    static constexpr int M = kHalfFft >> D;
+    static constexpr int KEEP = 3 * M / 4;
+    static constexpr int kRowBytes = 2 * KEEP * 8 + 16;                  // both frames' kept samples + 16 B of skew
+    static constexpr int kWarpBytes = kTile * 16 + 32 * kRowBytes + 16;  // tile | 32 rows | mbarrier
+    static constexpr int kSmemBytes = (1024 + 1024 + 32) * 8 + 1024 + kLaneWarps * kWarpBytes;
+};
+constexpr int kLaneTabFloat2 = 1024 + 1024 + 32;                         // tw_fwd | ctab | gh
+constexpr int kLaneMaxListed = 256;                                      // tune bins kept in shared memory (1 KB)
+// Slot of spectrum bin k in the quad array.  The lanes of a quarter-warp (one LDS.128 wavefront) read bins that differ
+// by the channel spacing -- a multiple of 4, typically 16 -- which in natural order is one bank group for all of them
+// (measured: 61 % of the kernel's shared-memory wavefronts were conflict replays).  XOR-folding bits 3..8 of k into the
+// three bits that choose the 16-byte column spreads spacings of 4, 8, 16, 32 and 64 bins over all eight columns.
+__device__ __forceinline__ int quad_slot(int k) { return k ^ (((k >> 3) ^ (k >> 6)) & 7); }
+}  // namespace
+
+template <int D>
+__global__ void __launch_bounds__(kLaneWarps * 32, 1) r2iq_channels_lane_kernel(const ChannelParams p) {
+    using LG = LaneGeo<D>;
+    constexpr int M = LG::M;                  // 32 or 16
+    constexpr int MB = ilog2(M);
+    constexpr int KEEP = LG::KEEP;
+    extern __shared__ __align__(128) unsigned char lane_smem[];
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    float2* tab = reinterpret_cast<float2*>(lane_smem);
+    const float2* ctab = tab + 1024;
+    const float2* gh = tab + 2048;
+    int* listed = reinterpret_cast<int*>(lane_smem + kLaneTabFloat2 * 8);
+    unsigned char* wbase = lane_smem + kLaneTabFloat2 * 8 + 1024 + (size_t)warp * LG::kWarpBytes;
+    u64* S = reinterpret_cast<u64*>(wbase);
+    float4* X4 = reinterpret_cast<float4*>(wbase);                       // the split spectrum reuses the tile
+    const uint32_t* inA = reinterpret_cast<const uint32_t*>(wbase);      // ... and so does the incoming pair
+    float4* row = reinterpret_cast<float4*>(wbase + kTile * 16 + lane * LG::kRowBytes);
+    const uint32_t mbar = smem_u32(wbase + LG::kWarpBytes - 16);
+    const uint32_t dst = smem_u32(inA);
+
+    for (int i = threadIdx.x; i < 1024; i += kLaneWarps * 32) {
+        tab[i] = __ldg(p.tw_fwd + i);
+        tab[1024 + i] = __ldg(p.ctab + i);
+    }
+    if (threadIdx.x < M) tab[2048 + threadIdx.x] = __ldg(p.gh + threadIdx.x);
+    const bool in_smem = p.n_channels <= kLaneMaxListed;
+    if (in_smem)
+        for (int i = threadIdx.x; i < p.n_channels; i += kLaneWarps * 32) listed[i] = __ldg(p.tunebins + i);
+    if (lane == 0) {
+        mbar_init(mbar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+
+    FusedParams fp;                 // frame_src only reads in_words
+    fp.in_words = p.in_words;
+    const long long n_pairs = (p.total_frames + 1) / 2;
+    auto issue = [&](long long pair) {
+        const long long fa = 2 * pair;
+        const uint32_t* src = frame_src(fp, fa);
+        uint32_t bytes = kFrameBytes;
+        if (fa + 1 < p.total_frames) bytes += (uint32_t)(frame_src(fp, fa + 1) - src) * 4;
+        mbar_expect_tx(mbar, bytes);
+        tma_load_1d(dst, src, bytes, mbar);
+    };
+    unsigned long long g0 = 0, g1 = 0;
+    if (lane == 0) {
+        g0 = atomicAdd(p.work_counter, 1ULL);
+        g1 = atomicAdd(p.work_counter, 1ULL);
+    }
+    long long q = (long long)__shfl_sync(0xffffffffu, g0, 0);
+    unsigned long long pend = g1;
+    if (lane == 0 && q < n_pairs) issue(q);
+    uint32_t phase = 0;
+    const float2* twf = tab + lane;
+    const uint32_t sgn = __float_as_uint(p.imag_sign) & 0x80000000u;
+
+    while (q < n_pairs) {
+        const long long qn = (long long)__shfl_sync(0xffffffffu, pend, 0);
+        if (lane == 0) pend = atomicAdd(p.work_counter, 1ULL);
+        const int offB = ((2 * q) % kFramesPerBlock == kFramesPerBlock - 1) ? kHalfFft / 2 : kHop / 2;
+        const uint32_t* inB = inA + offB;
+        c2 v[32];
+        mbar_wait(mbar, phase);
+        phase ^= 1;
+#pragma unroll
+        for (int j = 0; j < 32; j++) unpack_words(inA[lane + 32 * j], inB[lane + 32 * j], p.rand_mul, v[brev5(j)]);
+        __syncwarp();                             // every lane holds its words: the tile may be overwritten
+
+        // ---- forward 1024-point transform (as r2iq_pair.cu) ---------------------------------------------------
+        dit2<32, false>(v);
+#pragma unroll
+        for (int k2 = 1; k2 < 32; k2++) v[k2] = cmul2s(v[k2], twf[32 * k2]);
+#pragma unroll
+        for (int k2 = 0; k2 < 32; k2++) sts2(S, lane * 33 + k2, v[k2]);
+        __syncwarp();
+#pragma unroll
+        for (int n1 = 0; n1 < 32; n1++) v[brev5(n1)] = lds2(S, n1 * 33 + lane);
+        __syncwarp();
+        dit2<32, false>(v);                       // v[k1] = Z[32*k1 + lane]
+
+        // ---- channel-independent split: v[k1] <- 2 X[32*k1 + lane] ---------------------------------------------
+#pragma unroll
+        for (int k1 = 0; k1 < 32; k1++) sts2(S, 32 * k1 + lane, v[k1]);
+        __syncwarp();
+#pragma unroll
+        for (int k1 = 0; k1 < 32; k1++) {
+            const int k = 32 * k1 + lane;
+            const c2 a = v[k1];
+            const c2 b = lds2(S, (kHalfFft - k) & (kHalfFft - 1));
+            const float2 c = ctab[k];
+            const u64 ux = add2(a.re, b.re), uy = sub2(a.im, b.im);      // a + conj b
+            const u64 wx = sub2(a.re, b.re), wy = add2(a.im, b.im);      // a - conj b
+            c2 x;
+            x.re = fma2(bc(c.x), wx, fma2(bc(-c.y), wy, ux));
+            x.im = fma2(bc(c.x), wy, fma2(bc(c.y), wx, uy));
+            v[k1] = x;
+        }
+        __syncwarp();                             // every mirrored read is done: the tile becomes the quad array
+#pragma unroll
+        for (int k1 = 0; k1 < 32; k1++) {
+            float ra, rb, ia, ib;
+            upk(v[k1].re, ra, rb);
+            upk(v[k1].im, ia, ib);
+            X4[quad_slot(32 * k1 + lane)] = make_float4(ra, rb, ia, ib);
+        }
+        __syncwarp();
+
+        const FrameOut2 oa = frame_out2<D>(2 * q, p.total_frames);
+        const FrameOut2 ob = frame_out2<D>(2 * q + 1, p.total_frames);
+        const int len_a = KEEP - oa.lo;                                   // samples of the run that come from frame A
+        const uint32_t run_bytes = (uint32_t)(len_a + (ob.live ? KEEP - ob.lo : 0)) * 8u;
+        // ---- 32 channels per pass, lane = channel ----------------------------------------------------------------
+        for (int c0 = 0; c0 < p.n_channels; c0 += 32) {
+            const int ch = c0 + lane;
+            const bool live = ch < p.n_channels;
+            const int tb = !live ? 0 : in_smem ? listed[ch] : __ldg(p.tunebins + ch);
+            c2 t[M];
+#pragma unroll
+            for (int m = 0; m < M; m++) {
+                const int s = m < M / 2 ? m : m - M;
+                const int k = tb + s;
+                const bool inside = k >= 0 && k < kHalfFft;              // outside: zero fill (impl.hpp:91-96)
+                const float4 x = X4[quad_slot(k & (kHalfFft - 1))];
+                const float2 h = gh[m];
+                const float hx = inside ? h.x : 0.0f, hy = inside ? h.y : 0.0f;
+                const u64 xr = pk(x.x, x.y), xi = pk(x.z, x.w);
+                c2 y;
+                y.re = fma2(bc(hx), xr, mul2(bc(-hy), xi));
+                y.im = fma2(bc(hx), xi, mul2(bc(hy), xr));
+                t[brev_n(m, MB)] = y;
+            }
+            if (c0 + 32 >= p.n_channels) {
+                // last pass: the quad array is dead once every lane has gathered -> the next pair may land in the tile
+                __syncwarp();
+                if (lane == 0 && qn < n_pairs) {
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                    issue(qn);
+                }
+            }
+            dit2<M, true>(t);                     // t[n] = y[n] of this lane's channel, both frames
+            // the row may still be being read by the previous pass's bulk store
+            asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+#pragma unroll
+            for (int n = 0; n < KEEP; n += 2) {
+                float a0r, b0r, a0i, b0i, a1r, b1r, a1i, b1i;
+                upk(t[n].re, a0r, b0r);
+                upk(t[n].im, a0i, b0i);
+                upk(t[n + 1].re, a1r, b1r);
+                upk(t[n + 1].im, a1i, b1i);
+                if (n >= oa.lo) row[(n - oa.lo) >> 1] = make_float4(a0r, flip(a0i, sgn), a1r, flip(a1i, sgn));
+                if (ob.live && n >= ob.lo) row[(len_a + n - ob.lo) >> 1] = make_float4(b0r, flip(b0i, sgn), b1r, flip(b1i, sgn));
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            if (live) {
+                float2* run = p.out + (long long)ch * p.out_stride + oa.base + oa.lo;
+                asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(run), "r"(smem_u32(row)), "r"(run_bytes)
+                             : "memory");
+            }
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        }
+        q = qn;
+    }
+    asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");    // shared memory must outlive the engine's reads
+}
+
+template <int D>
+static cudaError_t setup_ch_lane() {
+    cudaError_t e = cudaFuncSetAttribute(r2iq_channels_lane_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, LaneGeo<D>::kSmemBytes);
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(r2iq_channels_lane_kernel<D>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+}
+
+template <int D>
+static cudaError_t launch_ch_lane(const ChannelParams& p, int sm_count, cudaStream_t stream) {
+    const long long n_pairs = (p.total_frames + 1) / 2;
+    long long grid = sm_count;                    // persistent: one CTA per SM
+    const long long want = (n_pairs + kLaneWarps - 1) / kLaneWarps;
+    if (grid > want) grid = want;
+    if (grid < 1) grid = 1;
+    cudaError_t e = cudaMemsetAsync(p.work_counter, 0, sizeof(unsigned long long), stream);
+    if (e != cudaSuccess) return e;
+    r2iq_channels_lane_kernel<D><<<(unsigned)grid, kLaneWarps * 32, LaneGeo<D>::kSmemBytes, stream>>>(p);
+    return cudaGetLastError();
+}
+
 template <int D>
 static cudaError_t setup_ch() {
     cudaError_t e = cudaFuncSetAttribute(r2iq_channels_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -124,8 +350,8 @@ cudaError_t setup_channel_kernels() {
     if ((e = setup_ch<2>()) != cudaSuccess) return e;
     if ((e = setup_ch<3>()) != cudaSuccess) return e;
     if ((e = setup_ch<4>()) != cudaSuccess) return e;
-    if ((e = setup_ch<5>()) != cudaSuccess) return e;
-    if ((e = setup_ch<6>()) != cudaSuccess) return e;
+    if ((e = setup_ch_lane<5>()) != cudaSuccess) return e;
+    if ((e = setup_ch_lane<6>()) != cudaSuccess) return e;
     return cudaSuccess;
 }
 
@@ -152,8 +378,8 @@ cudaError_t launch_channels(int d, const ChannelParams& p, int sm_count, cudaStr
         case 2: return launch_ch<2>(p, sm_count, stream);
         case 3: return launch_ch<3>(p, sm_count, stream);
         case 4: return launch_ch<4>(p, sm_count, stream);
-        case 5: return launch_ch<5>(p, sm_count, stream);
-        case 6: return launch_ch<6>(p, sm_count, stream);
+        case 5: return launch_ch_lane<5>(p, sm_count, stream);
+        case 6: return launch_ch_lane<6>(p, sm_count, stream);
         default: return cudaErrorInvalidValue;
     }
 }

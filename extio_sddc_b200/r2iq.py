@@ -228,7 +228,7 @@ class CudaR2IQ:
         return list(outs)
 
     def process_channels(self, blocks: np.ndarray, tunebins, history: np.ndarray | None = None) -> np.ndarray:
-        """Channelizer: every tune bin in ``tunebins`` from one pass over ``blocks`` (latched d >= 1).
+        """Channelizer: every tune bin in ``tunebins`` from one pass over ``blocks`` (any latched d, either FFTN).
         Returns complex64 [n_channels, n_blocks*(32768>>d)]; row c equals a separate operator tuned to
         ``tunebins[c]``."""
         blocks = np.ascontiguousarray(blocks, dtype=np.int16).reshape(-1)

@@ -167,14 +167,17 @@ R2IQ_API int r2iq_cuda_process_rates(r2iq_cuda_t h, const int16_t* blocks, long 
  * complex floats.  No host synchronisation; stream state is not carried. */
 R2IQ_API int r2iq_cuda_process_device(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d_iq_out, void* stream);
 
-/* Wideband channelizer: n_channels tuned channels from ONE input stream in a single pass (the forward
- * FFT of every frame is computed once and shared).  Channel c is tuned to tunebins[c] (multiples of 4 in
- * [0, halfFft), the value setFreqOffset would store in mtunebin) and receives exactly the stream a
- * separate fft_mt_r2iq tuned there would produce (Core/fft_mt_r2iq_impl.hpp:76-138) at the latched
- * decimation d >= 1, with the current rand / sideband settings.  iq_out is channel-major:
- * channel c occupies [c*n_blocks*(32768>>d), (c+1)*n_blocks*(32768>>d)) complex floats.
+/* Wideband channelizer: n_channels tuned channels from ONE input stream.  Channel c is tuned to tunebins[c]
+ * (multiples of 4 in [0, halfFft), the value setFreqOffset would store in mtunebin) and receives exactly the stream a
+ * separate fft_mt_r2iq tuned there would produce (Core/fft_mt_r2iq_impl.hpp:76-138) at the latched decimation, with
+ * the current rand / sideband settings.  iq_out is channel-major: channel c occupies
+ * [c*n_blocks*(32768>>d), (c+1)*n_blocks*(32768>>d)) complex floats.
+ *   FFTN 2048, d >= 1: a single pass; the forward FFT of every frame is computed once and shared by all channels
+ *                      (d = 5, 6: one channel per lane on the packed two-frame kernels; d = 1..4: lane groups).
+ *   d = 0 or FFTN 8192: one launch of the single-channel kernel per channel (the reference's one operator per tuned
+ *                      instance; same result, forward FFT not shared).
  * Host-buffer form: history as r2iq_cuda_process (NULL = zeros; no state is carried).
- * Device form: d_in = [halfFft history | blocks] (16-byte aligned), asynchronous on `stream`. */
+ * Device form: d_in = [halfFft history | blocks], d_in and d_iq_out 16-byte aligned, asynchronous on `stream`. */
 R2IQ_API int r2iq_cuda_process_channels(r2iq_cuda_t h, const int16_t* blocks, long n_blocks, const int16_t* history,
                                         const int* tunebins, int n_channels, float* iq_out);
 R2IQ_API int r2iq_cuda_process_channels_device(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, const int* tunebins,

@@ -293,17 +293,55 @@ def test_config4_channelizer(op):
         for c, tb in enumerate(bins):
             ref = orc.r2iq(x, d, tb, gain=GAIN, rand=True, history=hist)
             check(got[c], ref, GAIN, ("channelizer", d, tb))
-    # must agree with the single-channel kernels too, and refuse d = 0
+    # odd frame total (3 blocks = 129 frames: the last pair has one frame), lower sideband, more channels than one pass
+    x3 = orc.rx888_blocks(3, 5, 256, randomized=False, seed=14)
+    bins = shard.channel_tunebins(64) + [0, 4, 1016, 1020, 512, 500, 12]
+    for d in (5, 6):
+        op.setDecimate(d); op.updateRand(False); op.setSideband(True)
+        op.TurnOn()
+        got = op.process_channels(x3, bins, history=hist)
+        op.TurnOff()
+        for c, tb in enumerate(bins):
+            check(got[c], orc.r2iq(x3, d, tb, gain=GAIN, rand=False, sideband=True, history=hist), GAIN, ("channelizer lsb", d, tb))
+    op.setSideband(False)
+    # must agree with the single-channel kernels too
     op.setDecimate(5); op.tunebin = 264
     single = run(op, x, 5, 264, rand=True, history=hist)
     op.setDecimate(5); op.TurnOn()
     multi = op.process_channels(x, [264], history=hist)[0]
     op.TurnOff()
     assert orc.rel_l2(multi, single) < 1e-6
-    op.setDecimate(0); op.TurnOn()
-    with pytest.raises(capi.R2iqError):
-        op.process_channels(x, [256])
+    # d = 0: every channel is a full-rate operator (one launch per channel, no shared transform)
+    op.setDecimate(0); op.updateRand(True); op.TurnOn()
+    got = op.process_channels(x, [256, 0, 1020, 512], history=hist)
     op.TurnOff()
+    for c, tb in enumerate([256, 0, 1020, 512]):
+        check(got[c], orc.r2iq(x, 0, tb, gain=GAIN, rand=True, history=hist), GAIN, ("channelizer", 0, tb))
+    # a tune bin that is not a multiple of 4 is refused
+    op.setDecimate(5); op.TurnOn()
+    with pytest.raises(capi.R2iqError):
+        op.process_channels(x, [258])
+    op.TurnOff()
+
+
+def test_config4_channelizer_fftn8192():
+    """The channelizer on the FFTN the reference tree ships (Core/config.h:49): every channel equals an independent
+    reference run at 8192 tuned to that bin (d = 5, 3 and 0; edge bins included)."""
+    from extio_sddc_b200 import CudaR2IQ
+    op8 = CudaR2IQ(device=0, fftn=8192)
+    op8.Init(GAIN)
+    x = orc.rx888_blocks(2, 5, 1024, fftn=8192, randomized=True, seed=41)
+    hist = np.random.default_rng(41).integers(-2000, 2000, 4096).astype(np.int16)
+    for d, bins in ((5, [0, 64, 1024, 2048, 3000, 4092]), (3, [4, 1024, 4000]), (0, [1024, 0])):
+        op8.setDecimate(d); op8.updateRand(True); op8.setSideband(False)
+        op8.TurnOn()
+        got = op8.process_channels(x, bins, history=hist)
+        op8.TurnOff()
+        assert got.shape == (len(bins), 2 * (32768 >> d))
+        for c, tb in enumerate(bins):
+            ref = orc.r2iq(x, d, tb, gain=GAIN, rand=True, history=hist, fftn=8192)
+            check(got[c], ref, GAIN, ("channelizer 8192", d, tb))
+    op8.close()
 
 
 def test_fine_tune_mixer_bit_exact(op):
