@@ -14,6 +14,16 @@ src = os.path.join(ROOT, "gpurun_out")
 dst = os.path.join(ROOT, "profiles")
 os.makedirs(dst, exist_ok=True)
 
+import re
+
+
+def short_name(n):
+    """ncu's demangled name -> the form r2iq_cuda_kernel_name() reports ('r2iq_pair_kernel<0, 8, 0>')."""
+    n = re.sub(r"^void ", "", n)
+    n = re.sub(r"\((?:r2iq::)?\w+\)$", "", n)
+    return n.replace("r2iq::", "").replace("(int)", "").replace("(bool)", "")
+
+
 # ---- launch list -------------------------------------------------------------------------------
 rows = [r for r in csv.reader(l for l in open(os.path.join(src, f"{tag}_launches.csv")) if not l.startswith("=="))]
 hdr = rows[0]
@@ -26,7 +36,7 @@ for r in rows[1:]:
     val = float(r[ix["Metric Value"]].replace(",", ""))
     unit = r[ix["Metric Unit"]]
     us = val / 1000.0 if unit in ("ns", "nsecond") else val * (1000.0 if unit in ("ms", "msecond") else 1.0)
-    name = r[ix["Kernel Name"]]
+    name = short_name(r[ix["Kernel Name"]])
     out.append((r[ix["ID"]], name, r[ix["Grid Size"]], r[ix["Block Size"]], f"{us:.2f}"))
     tot[name] = tot.get(name, 0.0) + us
 with open(os.path.join(dst, f"{tag}_launches.csv"), "w", newline="") as f:
@@ -45,12 +55,15 @@ with open(os.path.join(dst, f"{tag}_launch_shares.txt"), "w") as f:
         for v, k in sorted(((v, k) for k, v in head.items()), reverse=True):
             f.write(f"{100 * v / ht:6.2f}%  {v / 1000:9.3f} ms  {k}\n")
 
-# ---- per-kernel metrics from the full capture ------------------------------------------------------
-rep = os.path.join(src, f"{tag}_full.ncu-rep")
-raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True, check=True).stdout
-rows = list(csv.reader(raw.splitlines()))
-hdr, units, data = rows[0], rows[1], rows[2:]
-ix = {h: i for i, h in enumerate(hdr)}
+# ---- per-kernel metrics from the full captures (FFTN 2048 kernels; FFTN 8192 kernels when captured) -----------------
+captures = []
+for rep_name in (f"{tag}_full.ncu-rep", f"{tag}_wide_full.ncu-rep"):
+    rep = os.path.join(src, rep_name)
+    if not os.path.exists(rep):
+        continue
+    raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True, check=True).stdout
+    rows = list(csv.reader(raw.splitlines()))
+    captures.append((rows[0], rows[1], rows[2:]))
 want = {
     "duration_us": "gpu__time_duration.sum",
     "dram_read_bytes": "dram__bytes_read.sum",
@@ -65,6 +78,7 @@ want = {
     "smem_wavefronts_pct": "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum.pct_of_peak_sustained_elapsed",
     "smem_bank_conflicts": "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum",
     "smem_wavefronts": "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum",
+    "l1_sector_hit_pct": "l1tex__t_sector_hit_rate.pct",
     "icache_hit_pct": "sm__icc_request_hit_rate.pct",
     "l2_hit_pct": "lts__t_sector_hit_rate.pct",
     "warps_active_pct": "sm__warps_active.avg.pct_of_peak_sustained_active",
@@ -78,8 +92,10 @@ want = {
 }
 scale = {"Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "byte": 1.0, "ms": 1e3, "us": 1.0, "ns": 1e-3, "s": 1e6}
 kern, traffic = [], {}
-for r in data:
-    e = {"kernel": r[ix["Kernel Name"]]}
+for hdr, units, data in captures:
+  ix = {h: i for i, h in enumerate(hdr)}
+  for r in data:
+    e = {"kernel": short_name(r[ix["Kernel Name"]])}
     for k, m in want.items():
         if m not in ix:
             e[k] = None
@@ -102,10 +118,8 @@ for r in data:
     name = e["kernel"]
     d = None
     for cand in range(7):
-        if f"<{cand}>" in name or f"<{cand}," in name or f"<(int){cand}" in name:
+        if f"<{cand}>" in name or f"<{cand}," in name:
             d = cand
-    if "d0_kernel" in name:
-        d = 0
     e["d"] = d
     if d is not None:
         alg = blocks * 65536 * (2.0 + 8.0 / (1 << (d + 1)))
@@ -113,7 +127,7 @@ for r in data:
         e["dram_traffic_bytes"] = e["dram_read_bytes"] + e["dram_write_bytes"]
         e["traffic_over_algorithmic"] = round(e["dram_traffic_bytes"] / alg, 4)
         e["gsamples_per_s_under_ncu"] = round(blocks * 65536 / e["duration_us"] / 1e3, 1)
-        traffic[f"d{d}"] = e["dram_traffic_bytes"]
+        traffic[name] = {"blocks": blocks, "dram_bytes": e["dram_traffic_bytes"]}
     kern.append(e)
 json.dump({"blocks": blocks, "note": "one launch per decimation, 8192-block capture resident in HBM; "
            "ncu --set full --clock-control none (durations are cold-cache and serialised)", "kernels": kern},
