@@ -93,13 +93,14 @@ int main(int argc, char** argv) {
     wo.format_tag = 3;
     wo.channels = 2;
     wo.bits_per_sample = 32;
+    wo.reference_block_align = false;        // a standard float WAV: nBlockAlign = 8
     wo.sample_rate = (uint32_t)(fs / 2.0 / (double)(1 << d) + 0.5);
     wo.center_freq = tune_hz >= 0.0 ? (uint32_t)(tune_hz + 0.5) : 0u;
     wo.ad_sample_rate = (uint32_t)(fs + 0.5);
     wo.start = wi.start;
     wo.stop = wi.stop;
     wav_write_header(fout, &wo);
-    wo.stop = wi.stop;   // keep the recording's own time span
+    wo.stop = wi.stop;   // keep the recording's own time span (a stop time of year 0 means: stamp at finalise)
 
     uint64_t out_bytes = 0;
     long done = 0;

@@ -62,7 +62,7 @@ void wav_pack_header(const WavInfo& info, uint64_t data_bytes, unsigned char out
     put16(out + 22, (uint32_t)info.channels);
     put32(out + 24, info.sample_rate);
     put32(out + 28, info.sample_rate * bytes_per_frame);
-    put16(out + 32, (uint32_t)info.channels);                       // nBlockAlign = nChannels, as wavewrite.c:147
+    put16(out + 32, info.reference_block_align ? (uint32_t)info.channels : bytes_per_frame);   // see WavInfo
     put16(out + 34, (uint32_t)info.bits_per_sample);
     memcpy(out + 36, "auxi", 4);
     put32(out + 40, 68);                                            // 2 * 16 + 9 * 4
@@ -88,12 +88,13 @@ int wav_write_header(FILE* f, WavInfo* info) {
     wav_pack_header(*info, 0, h);
     info->data_offset = kWavHeaderBytes;
     info->data_bytes = 0;
+    info->stop = WavTime{};           // open recording: wav_finalize stamps the stop time unless the caller sets one
     return fwrite(h, kWavHeaderBytes, 1, f) == 1 ? 0 : -1;
 }
 
 int wav_finalize(FILE* f, WavInfo* info, uint64_t data_bytes) {
     if (!f || !info) return -1;
-    if (info->stop.year == 0 || memcmp(&info->stop, &info->start, sizeof(WavTime)) == 0) info->stop = now_utc();
+    if (info->stop.year == 0) info->stop = now_utc();
     info->data_bytes = data_bytes;
     unsigned char h[kWavHeaderBytes];
     wav_pack_header(*info, data_bytes, h);

@@ -29,6 +29,9 @@ struct WavInfo {
     int32_t iq_offset = 0;
     uint64_t data_offset = 0;    // byte offset of the first sample
     uint64_t data_bytes = 0;     // payload size; taken from the file length when the header was never finalised
+    // nBlockAlign as the reference's recorder writes it (= nChannels, wavewrite.c:147; byte parity with its files) or
+    // as the WAV format defines it (channels * bits / 8: what standard readers expect; used for the float IQ output)
+    bool reference_block_align = true;
 };
 
 constexpr int kWavHeaderBytes = 120;
@@ -37,7 +40,8 @@ constexpr int kWavHeaderBytes = 120;
 void wav_pack_header(const WavInfo& info, uint64_t data_bytes, unsigned char out[kWavHeaderBytes]);
 // waveWriteHeader (wavewrite.c:171-179): start time = stop time = now (UTC) unless info.start.year != 0.
 int wav_write_header(FILE* f, WavInfo* info);
-// waveFinalizeHeader (wavewrite.c:245-263): stop time = now unless stop.year != 0, sizes fixed, header rewritten.
+// waveFinalizeHeader (wavewrite.c:245-263): stop time = now unless the caller has set one (stop.year != 0) after
+// wav_write_header, sizes fixed, header rewritten.
 int wav_finalize(FILE* f, WavInfo* info, uint64_t data_bytes);
 // Chunk walker: RIFF/WAVE, "fmt ", optional "auxi", "data"; unknown chunks are skipped; a data size of 0 or one
 // running past the end of the file (recording interrupted before waveFinalizeHeader) means "until end of file".

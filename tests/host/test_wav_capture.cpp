@@ -85,6 +85,38 @@ int main(int argc, char** argv) {
         CHECK(wav_read_header(f, &r) < 0);
         fclose(f);
     }
+    {   // float IQ output of the replayer: a standard WAV block alignment, and a restored time span survives finalise
+        FILE* f = fopen(p.c_str(), "wb+");
+        WavInfo w;
+        w.format_tag = 3;
+        w.channels = 2;
+        w.bits_per_sample = 32;
+        w.sample_rate = 2000000;
+        w.reference_block_align = false;
+        w.start.year = 2025; w.start.month = 3; w.start.day = 9; w.start.hour = 11;
+        CHECK(wav_write_header(f, &w) == 0);
+        CHECK(w.stop.year == 0);                       // open recording
+        WavTime stop = w.start;
+        stop.hour = 12;
+        w.stop = stop;                                 // the capture's own stop time
+        std::vector<float> iq(200, 0.25f);
+        CHECK(fwrite(iq.data(), 4, iq.size(), f) == iq.size());
+        CHECK(wav_finalize(f, &w, 800) == 0);
+        unsigned char h[kWavHeaderBytes];
+        fseek(f, 0, SEEK_SET);
+        CHECK(fread(h, kWavHeaderBytes, 1, f) == 1);
+        CHECK(h[32] == 8 && h[33] == 0);               // nBlockAlign = channels * bits / 8
+        fseek(f, 0, SEEK_SET);
+        WavInfo r;
+        CHECK(wav_read_header(f, &r) == 0);
+        CHECK(r.stop.year == 2025 && r.stop.hour == 12 && r.start.hour == 11 && r.format_tag == 3 && r.data_bytes == 800);
+        fclose(f);
+        // and an open recording that nobody stamps gets "now"
+        f = fopen(p.c_str(), "wb+");
+        WavInfo v;
+        CHECK(wav_write_header(f, &v) == 0 && wav_finalize(f, &v, 0) == 0 && v.stop.year >= 2024);
+        fclose(f);
+    }
     remove(p.c_str());
     printf(failures ? "FAILED %d\n" : "ALL PASS\n", failures);
     return failures ? 1 : 0;
