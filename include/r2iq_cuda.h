@@ -164,7 +164,11 @@ R2IQ_API int r2iq_cuda_process_rates(r2iq_cuda_t h, const int16_t* blocks, long 
 /* Same transform on DEVICE memory, asynchronously on the caller's stream (cudaStream_t passed as
  * void*; NULL = the legacy default stream).  d_in points at [halfFft history samples | n_blocks
  * blocks] contiguous in device memory (16-byte aligned: frames are fetched by TMA bulk copies); d_iq_out receives n_blocks*(32768>>d)
- * complex floats.  No host synchronisation; stream state is not carried. */
+ * complex floats.  No host synchronisation; stream state is not carried.
+ * ONE HANDLE, ONE STREAM: a handle's device-path launches share per-handle scratch (the work-counter ring, and in
+ * R2IQ_NCO_REFERENCE mode the start-phasor buffer, whose upload also synchronises the stream), so all device-path calls
+ * on one handle must be issued on the same stream, or be ordered by the caller.  Use one handle per stream for
+ * concurrent work; handles share nothing.  (R2IQ_NCO_DIRECT and mixer-off launches touch no host state at all.) */
 R2IQ_API int r2iq_cuda_process_device(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d_iq_out, void* stream);
 
 /* Wideband channelizer: n_channels tuned channels from ONE input stream.  Channel c is tuned to tunebins[c]
