@@ -50,6 +50,22 @@ def golden_cases():
     return dict(cases=cases, history=z["history"])
 
 
+@pytest.fixture(scope="session")
+def golden_cases_8192():
+    """FFTN_R_ADC 8192 cases (tests/golden/r2iq_cases_8192.npz): outputs of the reference compiled at the size it ships
+    with; the inputs are the ones stored in r2iq_cases.npz."""
+    z = np.load(os.path.join(GOLDEN, "r2iq_cases_8192.npz"))
+    zin = np.load(os.path.join(GOLDEN, "r2iq_cases.npz"))
+    cases = []
+    for entry in z["cases"]:
+        name, sig = str(entry).split(":")
+        d, tb, rnd, sb, nb, use_hist = [int(v) for v in z[f"{name}__meta"]]
+        cases.append(dict(name=name, d=d, tunebin=tb, rand=bool(rnd), sideband=bool(sb), n_blocks=nb,
+                          use_hist=bool(use_hist), gain=float(z[f"{name}__gain"][0]),
+                          clean_in=zin[f"input__{sig}"][: nb * 65536], out=z[f"{name}__out"]))
+    return dict(cases=cases, history=z["history"])
+
+
 def case_input(case, history):
     """Wire-format input (randomized if the case has the ADC randomizer on) and history."""
     from oracle import r2iq_oracle as orc

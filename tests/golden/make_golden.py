@@ -59,6 +59,42 @@ def make_signal(kind, n_blocks):
     return comb_signal(n_blocks)
 
 
+# FFTN_R_ADC = 8192, the value the reference tree ships with (Core/config.h:49): halfFft 4096, tune bins in [0, 4096)
+CASES_8192 = [
+    ("w_hf64_sine5m_d0", 0, 1024, False, False, orc.BBRF103_GAINFACTOR, 1, "sine5m"),
+    ("w_rx888_d1", 1, 1024, True, False, orc.RX888MK2_GAINFACTOR, 1, "comb"),
+    ("w_rx888_d2_lsb", 2, 576, True, True, orc.RX888MK2_GAINFACTOR, 2, "comb"),
+    ("w_rx888_d3", 3, 2000, False, False, orc.RX888MK2_GAINFACTOR, 2, "comb"),
+    ("w_rx888_d4", 4, 1024, True, False, orc.RX888MK2_GAINFACTOR, 2, "comb"),
+    ("w_rx888_d5_dc_edge", 5, 8, True, False, orc.RX888MK2_GAINFACTOR, 2, "comb"),
+    ("w_rx888_d6_nyquist_edge_lsb", 6, 4092, True, True, orc.RX888MK2_GAINFACTOR, 2, "comb"),
+]
+
+
+def main_8192(inputs):
+    """tests/golden/r2iq_cases_8192.npz: the same reference sources compiled with FFTN_R_ADC 8192
+    (oracle/_ref/libref_r2iq_8192.so), on the inputs already stored in r2iq_cases.npz."""
+    R = ref_lib.get(8192)
+    assert R.set_fft_backend(ref_lib.BACKEND_DOUBLE) == 0
+    hist = np.random.default_rng(8).integers(-2000, 2000, 4096).astype(np.int16)
+    bundle = {"history": hist}
+    names = []
+    for (name, d, tb, rnd, sb, gain, nb, sig) in CASES_8192:
+        x = inputs[sig][: nb * orc.TRANSFER_SAMPLES]
+        if rnd:
+            x = orc.randomize(x)
+        use_hist = sig == "comb"
+        h = orc.randomize(hist) if rnd else hist
+        y = R.run(x, d, tb, gain=gain, rand=rnd, sideband=sb, history=h if use_hist else None)
+        names.append(f"{name}:{sig}")
+        bundle[f"{name}__out"] = y
+        bundle[f"{name}__meta"] = np.array([d, tb, int(rnd), int(sb), nb, int(use_hist)], dtype=np.int64)
+        bundle[f"{name}__gain"] = np.array([gain], dtype=np.float64)
+        print(name, x.shape, y.shape, float(np.sqrt(np.mean(np.abs(y) ** 2))))
+    bundle["cases"] = np.array(names)
+    np.savez_compressed(os.path.join(OUT, "r2iq_cases_8192.npz"), **bundle)
+
+
 def main():
     ref_lib.build()
     R = ref_lib.get(2048)
@@ -83,6 +119,7 @@ def main():
         print(name, x.shape, y.shape, float(np.sqrt(np.mean(np.abs(y) ** 2))))
     bundle["cases"] = np.array(names)
     np.savez_compressed(os.path.join(OUT, "r2iq_cases.npz"), **bundle)
+    main_8192(inputs)
 
     # filter design: taps and spectra for every decimation (Core/fir.cpp, fft_mt_r2iq.cpp:181-205)
     filt = {}

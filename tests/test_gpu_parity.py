@@ -71,6 +71,18 @@ def test_golden_cases(golden_cases):
         check(got, c["out"], c["gain"], c["name"])
 
 
+def test_golden_cases_fftn8192(golden_cases_8192):
+    """The FFTN 8192 kernels against vectors from the reference compiled at 8192 (tests/golden/r2iq_cases_8192.npz)."""
+    for c in golden_cases_8192["cases"]:
+        r = CudaR2IQ(fftn=8192)
+        r.Init(c["gain"])
+        x, h = case_input(c, golden_cases_8192["history"])
+        got = run(r, x, c["d"], c["tunebin"], c["rand"], c["sideband"], history=h)
+        r.close()
+        assert got.shape == c["out"].shape
+        check(got, c["out"], c["gain"], c["name"])
+
+
 @pytest.mark.parametrize("d", range(7))
 def test_parity_matrix(op, d):
     # config 2 signal (rand on) at the default tune bin, plus edge tune bins with zero-filled bands

@@ -27,6 +27,18 @@ def test_golden_cases_match_restatement(golden_cases):
         assert np.abs(got - c["out"]).max() <= 1e-6 * orc.full_scale(c["gain"]), c["name"]
 
 
+def test_golden_cases_8192_match_restatement(golden_cases_8192):
+    """The restatement at FFTN_R_ADC 8192 (what the reference tree ships, Core/config.h:49) against vectors produced by
+    the reference compiled at that size."""
+    for c in golden_cases_8192["cases"]:
+        x, h = case_input(c, golden_cases_8192["history"])
+        got = orc.r2iq(x, c["d"], c["tunebin"], gain=c["gain"], rand=c["rand"], sideband=c["sideband"], history=h, fftn=8192)
+        assert got.shape == c["out"].shape, c["name"]
+        err = orc.rel_l2(got, c["out"])
+        assert err < 5e-7, (c["name"], err)
+        assert np.abs(got - c["out"]).max() <= 1e-6 * orc.full_scale(c["gain"]), c["name"]
+
+
 def test_filter_design_matches_reference_golden():
     z = np.load(os.path.join(GOLDEN, "filters.npz"))
     for d in range(7):
