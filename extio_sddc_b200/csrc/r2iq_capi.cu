@@ -1450,7 +1450,7 @@ int r2iq_cuda_get_fftn(r2iq_cuda_t h) { return h ? h->fftn : R2IQ_E_INVALID; }
 
 int r2iq_cuda_kernel_name(r2iq_cuda_t h, int d, char* buf, int n) {
     if (!h || !buf || n < 1 || d < 0 || d >= kNDec) return fail(R2IQ_E_INVALID, "kernel_name: bad arguments");
-    if (h->fftn == 8192) snprintf(buf, (size_t)n, "r2iq_wide_kernel<%d, 1>", d);
+    if (h->fftn == 8192) snprintf(buf, (size_t)n, "%s", wide_kernel_name(d));
     else snprintf(buf, (size_t)n, "%s", fused_kernel_name(d, h->nco.on && h->nco.mode == R2IQ_NCO_DIRECT));
     return R2IQ_OK;
 }

@@ -121,6 +121,10 @@ struct WideParams {
 };
 cudaError_t setup_wide_kernels();
 cudaError_t launch_wide(int d, const WideParams& p, int sm_count, cudaStream_t stream);
+const char* wide_kernel_name(int d);                 // as profilers print it
+cudaError_t setup_wide_gen1_kernels();               // r2iq_wide.cu, comparison builds only
+cudaError_t launch_wide_gen1(int d, const WideParams& p, int sm_count, cudaStream_t stream);
+int kernel_generation();
 
 const char* fused_kernel_name(int d, bool direct_mixer);
 // Launch the fused kernel for decimation index d on `stream`.  Returns cudaGetLastError().

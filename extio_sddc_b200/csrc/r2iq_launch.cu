@@ -10,6 +10,7 @@
 namespace r2iq {
 
 static int g_kernel_gen = 0;
+int kernel_generation() { return g_kernel_gen; }
 #ifdef R2IQ_AB_VARIANTS
 void set_kernel_generation(int gen) { g_kernel_gen = gen; }
 int kernel_variant(int dflt) {

@@ -1,4 +1,5 @@
-// r2iq_wide.cu -- FFTN = 8192 (the value the reference tree ships with, Core/config.h:49), second
+// r2iq_wide.cu -- COMPARISON BUILDS ONLY (R2IQ_AB_VARIANTS; the shipped FFTN 8192 kernels are r2iq_wide_pair.cu).
+// FFTN = 8192 (the value the reference tree ships with, Core/config.h:49), second
 // generation: FOUR WARPS SHARE ONE FRAME.  halfFft = 4096, hop 6144 samples, 11 frames per 65536-sample block,
 // inverse sizes mfft = 4096 >> d; worker-loop semantics of Core/fft_mt_r2iq_impl.hpp:15-151.
 //
@@ -283,7 +284,7 @@ static cudaError_t setup_q() {
     return setup_qv<D, true>();
 }
 
-cudaError_t setup_wide_kernels() {
+cudaError_t setup_wide_gen1_kernels() {
     cudaError_t e;
     if ((e = setup_q<0>()) != cudaSuccess) return e;
     if ((e = setup_q<1>()) != cudaSuccess) return e;
@@ -315,7 +316,7 @@ static cudaError_t launch_q(const WideParams& p, int sm_count, cudaStream_t stre
     return launch_qv<D, true>(p, sm_count, stream);
 }
 
-cudaError_t launch_wide(int d, const WideParams& p, int sm_count, cudaStream_t stream) {
+cudaError_t launch_wide_gen1(int d, const WideParams& p, int sm_count, cudaStream_t stream) {
     switch (d) {
         case 0: return launch_q<0>(p, sm_count, stream);
         case 1: return launch_q<1>(p, sm_count, stream);
