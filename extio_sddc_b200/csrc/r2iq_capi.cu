@@ -152,7 +152,7 @@ struct r2iq_cuda_s {
     // FFTN 8192 family (r2iq_wide.cu)
     float2* d_twq = nullptr;                       // [3][1024] W_4096^(q n)
     float2* d_wctab = nullptr;                     // [2049] -i * W_8192^p
-    struct WideSet { float2* g = nullptr; float2* tw_sub = nullptr; };
+    struct WideSet { float2* g = nullptr; float2* tw_sub = nullptr; float4* pq = nullptr; float2* tw_inv = nullptr; uint32_t row_mask[4] = {0, 0, 0, 0}; };
     std::map<long long, WideSet> wide_tables;      // per (filter version, d, tunebin)
     Slot slots[kSlots];
     uint64_t next_ticket = 1;                      // submissions are numbered; ticket t uses slot t % kSlots
@@ -475,6 +475,8 @@ int launch_wide_impl(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d
             for (auto& kv : h->wide_tables) {
                 cudaFree(kv.second.g);
                 cudaFree(kv.second.tw_sub);
+                cudaFree(kv.second.pq);
+                cudaFree(kv.second.tw_inv);
             }
             h->wide_tables.clear();
         }
@@ -490,6 +492,34 @@ int launch_wide_impl(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d
         }
         CU(h, cudaMalloc(&ws.g, sizeof(float2) * HF));
         CU(h, cudaMemcpy(ws.g, g.data(), sizeof(float2) * HF, cudaMemcpyHostToDevice));
+        // (P, Q) of the packed kernels, plane-major (bin 4 m + r at [r][m]), and the rows of each plane the band cut reads
+        std::vector<float4> pq(HF);
+        for (int k = 0; k < HF; k++) {
+            const std::complex<double> hh(g[k].x, g[k].y);
+            const double th = 2.0 * kPiD * (double)k / 8192.0;
+            const std::complex<double> gc = std::complex<double>(-sin(th), -cos(th)) * hh;   // (-i exp(-i th)) g
+            pq[(size_t)(k & 3) * 1024 + (k >> 2)] = make_float4((float)(hh.real() + gc.real()), (float)(hh.imag() + gc.imag()),
+                                                                (float)(hh.real() - gc.real()), (float)(hh.imag() - gc.imag()));
+        }
+        for (int s = -M / 2; s < M / 2; s++) {
+            const int kk = (tunebin + s) & (HF - 1), km = (HF - kk) & (HF - 1);
+            ws.row_mask[kk & 3] |= 1u << (kk >> 7);
+            ws.row_mask[km & 3] |= 1u << (km >> 7);
+        }
+        CU(h, cudaMalloc(&ws.pq, sizeof(float4) * HF));
+        CU(h, cudaMemcpy(ws.pq, pq.data(), sizeof(float4) * HF, cudaMemcpyHostToDevice));
+        if (d == 0) {
+            // lane l of the backward 1024-point transforms plays residue (l - tunebin/4) mod 32 (r2iq_wide_pair.cu, D1)
+            std::vector<float2> ti(1024);
+            for (int k2 = 0; k2 < 32; k2++)
+                for (int l = 0; l < 32; l++) {
+                    const long long n1 = ((l - tunebin / 4) % 1024 + 1024) % 1024;
+                    const double th = 2.0 * kPiD * (double)((n1 * k2) % 1024) / 1024.0;
+                    ti[k2 * 32 + l] = make_float2((float)cos(th), (float)sin(th));
+                }
+            CU(h, cudaMalloc(&ws.tw_inv, sizeof(float2) * ti.size()));
+            CU(h, cudaMemcpy(ws.tw_inv, ti.data(), sizeof(float2) * ti.size(), cudaMemcpyHostToDevice));
+        }
         if (d >= 1) {
             const std::vector<float2> ta = build_tw_aux(d == 6 ? M : M / 4);
             CU(h, cudaMalloc(&ws.tw_sub, sizeof(float2) * ta.size()));
@@ -506,6 +536,9 @@ int launch_wide_impl(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d
     p.ctab = h->d_wctab;
     p.g = ws.g;
     p.tw_sub = ws.tw_sub;
+    p.pq = ws.pq;
+    p.tw_inv = ws.tw_inv;
+    for (int r = 0; r < 4; r++) p.row_mask[r] = ws.row_mask[r];
     p.tunebin = tunebin;
     p.rand_mul = h->rand_on ? 0xFFFEu : 0u;
     p.imag_sign = h->latched_sideband ? -1.0f : 1.0f;
@@ -780,6 +813,8 @@ int r2iq_cuda_destroy(r2iq_cuda_t h) {
     for (auto& kv : h->wide_tables) {
         cudaFree(kv.second.g);
         cudaFree(kv.second.tw_sub);
+        cudaFree(kv.second.pq);
+        cudaFree(kv.second.tw_inv);
     }
     cudaFree(h->d_twq);
     cudaFree(h->d_wctab);

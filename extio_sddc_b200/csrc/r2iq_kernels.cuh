@@ -103,7 +103,8 @@ struct ChannelParams {
 cudaError_t setup_channel_kernels();
 cudaError_t launch_channels(int d, const ChannelParams& p, int sm_count, cudaStream_t stream);
 
-// FFTN = 8192 family (r2iq_wide.cu): halfFft 4096, 11 frames per block, hop 6144 samples; four warps per frame.
+// FFTN = 8192 family (r2iq_wide_pair.cu; r2iq_wide.cu in comparison builds): halfFft 4096, 11 frames per block,
+// hop 6144 samples; a team of four warps per frame pair.
 struct WideParams {
     const uint32_t* in_words;   // [2048 halo words | n_blocks * 32768 words]
     float2* out;                // n_blocks * (32768 >> d) complex
@@ -114,6 +115,10 @@ struct WideParams {
     const float2* g;            // [4096]    0.5 * H_d[(k - tunebin) mod 4096] inside the band, else 0
     const float2* tw_sub;       // d >= 1: [R][32] exp(+2 pi i lane k2 / S), then [32][32] exp(+2 pi i (lane % (32/R)) n1 / 32),
                                 // R = S/32, S = the per-plane size mfft/4 (d = 1..5) or mfft = 64 (d = 6)
+    const float4* pq;           // [4][1024] plane-major: (P, Q) of bin 4 m + r at [r][m]; Y[k] = P[k] Z[k] + Q[k] conj(Z[4096-k]),
+                                // P = g (1 + c), Q = g (1 - c), zero outside the band (r2iq_wide_pair.cu)
+    const float2* tw_inv;       // d = 0: [32][32] exp(+2 pi i ((l - tunebin/4) mod 1024) k2 / 1024), backward inter-pass twiddles
+    uint32_t row_mask[4];       // per plane: rows of 32 slots that the band cut reads (band bins and their mirrors)
     int tunebin;
     uint32_t rand_mul;
     float imag_sign;

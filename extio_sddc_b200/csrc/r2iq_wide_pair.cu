@@ -4,23 +4,29 @@
 //
 // The decomposition is that of the first wide kernel (r2iq_wide.cu, comparison builds): 4096 = 4 x 1024, a radix-4
 // stage across four shared-memory planes and one 1024-point register FFT per plane and warp, so a TEAM of four warps
-// owns a transform.  What changed:
+// owns a transform.  What this generation does differently, each from a measurement (ncu source page of its
+// predecessors: the shared-memory data pipe is the busiest unit at 72 %, the split phase cost a quarter of the time):
 //   * a team transforms a PAIR of consecutive frames at once, every value an (A, B) pair in one 64-bit register,
 //     every butterfly one FFMA2 / FADD2 / FMUL2 (dft_regs2.cuh): half the issue slots per sample;
-//   * ONE persistent CTA per SM of T teams (T = 3 at 168 registers; T = 2 where the d = 0 backward transform needs
-//     more), teams synchronise among their own 128 threads with named barriers and take frame pairs from the
-//     device-wide counter -- a team waiting at a barrier leaves the SM to the other teams, and no CTA is relaunched;
-//   * the forward twiddles (W_1024 and W_4096^n, W_4096^2n; W^3n is their product) live in shared memory, loaded once
-//     per CTA, instead of being fetched through a 28 KB L1 by every frame.
+//   * ONE persistent CTA per SM of three teams; teams synchronise among their own 128 threads with named barriers and
+//     take frame pairs from the device-wide counter -- a team waiting at a barrier leaves the SM to the other teams;
+//   * no separate split phase: the backward transform reads bin k from its own plane and bin 4096-k from the mirror
+//     plane and applies Y = P[k] Z[k] + Q[k] conj(Z[4096-k]) (split, filter and band edge in two table values, as
+//     the 2048 family) on the way into its registers; the forward transform stores only the rows of its plane that
+//     some backward transform will read;
+//   * d = 0: the tune rotation costs nothing -- lane l of the backward transform plays residue (l - tunebin/4) mod 32,
+//     which only changes the inter-pass twiddle table and the tile row the lane writes (as r2iq_pair.cu, d = 0);
+//   * the first half of the NEXT pair's input words is fetched into registers before the last phase of the current
+//     pair and the second half while the first is being transformed, so phase A no longer waits on HBM;
+//   * all twiddle tables live in shared memory (W_4096^2n and ^3n are products of W_4096^n: no table, no load).
 // Phases per pair (B = team barrier):
-//   A  128 threads: de-randomise + int16 -> float (integer pipe, dual_frame.cuh) and radix-4 decimation in frequency
-//      over the four quarters of both frames, twiddle W_4096^(q n), result to plane q                              B
-//   B  warp q: 1024-point forward transform of plane q in place (two radix-32 register passes)                      B
-//   C  128 threads: real-FFT split + filter on mirror pairs (k, 4096-k), in place, only the bins of the band         B
-//   D  warp r: backward transform of plane r (the tune bin is a multiple of 4, Core/fft_mt_r2iq.cpp:101-109, so the
-//      band's bins 4m'+r are plane r rotated by tunebin/4): 1024 points for d = 0, the R = mfft/128 register scheme
-//      for d = 1..5, then W_mfft^(-r n')                                                                              B
-//   E  128 threads: last radix-4 stage across the planes, overlap-save discard, placement of both frames            B
+//   A   128 threads: de-randomise + int16 -> float (integer pipe, dual_frame.cuh) and radix-4 decimation in frequency
+//       over the four quarters of both frames, twiddle W_4096^(q n), result to plane q                             B
+//   B   warp q: 1024-point forward transform of plane q (two radix-32 register passes), needed rows back to plane q  B
+//   D1  warp r: band bins of plane r (the tune bin is a multiple of 4, Core/fft_mt_r2iq.cpp:101-109, so the band's
+//       bins 4m'+r are plane r rotated by tunebin/4) and their mirrors -> P/Q -> first register pass                 B
+//   D2  warp r: transposition through its own plane, second pass, W_mfft^(-r n'), S_r to plane r                    B
+//   E   128 threads: last radix-4 stage across the planes, overlap-save discard, placement of both frames          B
 //   d = 6 (mfft = 64 is too small to split): warp 0 of the team transforms the band alone.
 #include "dual_frame.cuh"
 #include "r2iq_common.cuh"
@@ -39,12 +45,19 @@ constexpr int kWHopWords = 3 * kWHalf / 2 / 2;      // 6144 samples = 3072 words
 constexpr int kWFrames = kTransferSamples / (3 * kWHalf / 2) + 1;   // fftPerBuf = 11
 constexpr int kWPlane = 1060;                       // 64-bit slots per plane: >= 32*33 (transposition tile), == 4 mod 16 (skew)
 constexpr int kTeamThreads = 128;
+constexpr int kTeams = 3;
 constexpr int kTeamBytes = 2 * 4 * kWPlane * 8;     // four planes of (re_A, re_B) then four of (im_A, im_B)
-constexpr int kWTabFloat2 = 3 * 1024;               // tw1024 | W_4096^n | W_4096^(2n)
 
-template <int T>
+// tables in shared memory: W_1024 inter-pass twiddles | W_4096^n | d = 0: backward inter-pass twiddles of this tune bin,
+// d >= 1: the R-scheme twiddles and weights (build_tw_aux)
+template <int D>
+__host__ __device__ constexpr int wide_tab_float2() {
+    constexpr int S = D == 6 ? 64 : (kWHalf >> D) / 4;
+    return 2048 + (D == 0 ? 1024 : (S / 32 + 32) * 32);
+}
+template <int D>
 __host__ __device__ constexpr int wide_smem_bytes() {
-    return kWTabFloat2 * 8 + T * kTeamBytes;
+    return wide_tab_float2<D>() * 8 + kTeams * kTeamBytes;
 }
 
 struct Planes {
@@ -69,28 +82,26 @@ __device__ __forceinline__ int waddr(int k) { return (k & 3) * kWPlane + (k >> 2
 __device__ __forceinline__ c2 cadd(c2 a, c2 b) { return c2{add2(a.re, b.re), add2(a.im, b.im)}; }
 __device__ __forceinline__ c2 csub(c2 a, c2 b) { return c2{sub2(a.re, b.re), sub2(a.im, b.im)}; }
 __device__ __forceinline__ c2 cmul_conj2s(c2 v, float2 w) { return cmul2s(v, make_float2(w.x, -w.y)); }
+__device__ __forceinline__ float2 csqr(float2 w) { return make_float2(fmaf(w.x, w.x, -w.y * w.y), 2.0f * w.x * w.y); }
 __device__ __forceinline__ void team_barrier(int team) {
     asm volatile("bar.sync %0, %1;" ::"r"(team + 1), "r"(kTeamThreads) : "memory");
 }
-
-// 1024-point transform of x[lane + 32 j] (v[brev5(j)] on entry) -> X[lane + 32 k1] (v[k1] on return): two radix-32
-// register passes around one transposition through this warp's own plane (pitch 33); twiddles from shared memory
-template <bool INV>
-__device__ __forceinline__ void fft1024p(c2 (&v)[32], const Planes& P, int base, const float2* tw1024, int lane) {
-    dit2<32, INV>(v);
-#pragma unroll
-    for (int k2 = 1; k2 < 32; k2++) {
-        const float2 w = tw1024[32 * k2 + lane];
-        v[k2] = INV ? cmul_conj2s(v[k2], w) : cmul2s(v[k2], w);
-    }
-#pragma unroll
-    for (int k2 = 0; k2 < 32; k2++) pst(P, base + lane * 33 + k2, v[k2]);
-    __syncwarp();
-#pragma unroll
-    for (int n1 = 0; n1 < 32; n1++) v[brev5(n1)] = pld(P, base + n1 * 33 + lane);
-    __syncwarp();
-    dit2<32, INV>(v);
+// W_4096^(r e) for r = 1..3 from the table of W_4096^e (e < 1024)
+__device__ __forceinline__ float2 wpow(const float2* twq1, int r, int e) {
+    const float2 w1 = twq1[e];
+    if (r == 1) return w1;
+    const float2 w2 = csqr(w1);
+    return r == 2 ? w2 : cmul(w1, w2);
 }
+// split + filter + band edge: Y = P a + Q conj(b), a = Z[k], b = Z[4096 - k]; pq = (P.re, P.im, Q.re, Q.im)
+__device__ __forceinline__ c2 split_pq(c2 a, c2 b, float4 pq) {
+    c2 y;
+    y.re = fma2(bc(pq.w), b.im, fma2(bc(pq.z), b.re, fma2(bc(-pq.y), a.im, mul2(bc(pq.x), a.re))));
+    y.im = fma2(bc(pq.w), b.re, fma2(bc(-pq.z), b.im, fma2(bc(pq.y), a.re, mul2(bc(pq.x), a.im))));
+    return y;
+}
+// slot of bin 4096 - (4 mm + r) inside plane (4 - r) & 3
+__device__ __forceinline__ int mirror_slot(int r, int mm) { return r == 0 ? ((1024 - mm) & 1023) : 1023 - mm; }
 
 template <int D>
 __device__ __forceinline__ FrameOut2 wide_frame_out(long long f, long long total) {
@@ -113,13 +124,81 @@ __device__ __forceinline__ void store_pair(float2* out, const FrameOut2& oa, con
     if (ob.live && idx >= ob.lo) out[ob.base + idx] = make_float2(br, flip(bi, sgn));
 }
 
+// Input words of one half of a frame pair: thread tt's points n = tt + 128 (j0 + jj), jj < 4, of the four quarters.
+struct HalfWords {
+    uint32_t a[4][4], b[4][4];   // [jj][quarter], frame A / frame B
+};
+__device__ __forceinline__ void load_half(const WideParams& p, long long pair, int tt, int j0, HalfWords& w) {
+    const long long fa = 2 * pair;
+    const long long blk = fa / kWFrames;
+    const int kf = (int)(fa - blk * kWFrames);
+    const uint32_t* srcA = p.in_words + blk * (kTransferSamples / 2) + kf * kWHopWords + tt + 128 * j0;
+    // frame B starts one hop later (2048 words later across a block edge); the phantom B of an odd total reads A
+    const int offB = fa + 1 >= p.total_frames ? 0 : (kf == kWFrames - 1 ? kWHalf / 2 : kWHopWords);
+    const uint32_t* srcB = srcA + offB;
+#pragma unroll
+    for (int jj = 0; jj < 4; jj++)
+#pragma unroll
+        for (int qq = 0; qq < 4; qq++) {
+            w.a[jj][qq] = __ldg(srcA + 128 * jj + 1024 * qq);
+            w.b[jj][qq] = __ldg(srcB + 128 * jj + 1024 * qq);
+        }
+}
+// phase A on one half: radix-4 decimation in frequency over the quarters, twiddles, planes
+__device__ __forceinline__ void quarter_stage(const HalfWords& w, const Planes& P, const float2* twq1, uint32_t rand_mul, int tt, int j0) {
+#pragma unroll
+    for (int jj = 0; jj < 4; jj++) {
+        const int n = tt + 128 * (j0 + jj);
+        c2 z0, z1, z2, z3;
+        unpack_words(w.a[jj][0], w.b[jj][0], rand_mul, z0);
+        unpack_words(w.a[jj][1], w.b[jj][1], rand_mul, z1);
+        unpack_words(w.a[jj][2], w.b[jj][2], rand_mul, z2);
+        unpack_words(w.a[jj][3], w.b[jj][3], rand_mul, z3);
+        const c2 a0 = cadd(z0, z2), a1 = csub(z0, z2), a2 = cadd(z1, z3), a3 = csub(z1, z3);
+        const c2 u0 = cadd(a0, a2), u2 = csub(a0, a2);
+        const c2 u1 = c2{add2(a1.re, a3.im), sub2(a1.im, a3.re)};      // a1 - i a3
+        const c2 u3 = c2{sub2(a1.re, a3.im), add2(a1.im, a3.re)};      // a1 + i a3
+        const float2 w1 = twq1[n], w2 = csqr(w1);
+        pst(P, 0 * kWPlane + n, u0);
+        pst(P, 1 * kWPlane + n, cmul2s(u1, w1));
+        pst(P, 2 * kWPlane + n, cmul2s(u2, w2));
+        pst(P, 3 * kWPlane + n, cmul2s(u3, cmul(w1, w2)));               // W_4096^(3 n)
+    }
+}
+
+// R-scheme backward transform of an S = 32 R point sequence on one warp, second half: y[k2] (pass-1 outputs times
+// their twiddles, one column per lane) -> u[q] = s[k2p + R h + 32 q]; scratch = 32 x (R + 1) slots at `base`
+template <int R>
+__device__ __forceinline__ void rscheme_pass2(c2 (&y)[R], c2 (&u)[R], const Planes& P, int base, const float2* wts, int lane) {
+    constexpr int G = 32 / R;
+    constexpr int RB = ilog2(R);
+#pragma unroll
+    for (int k2 = 0; k2 < R; k2++) pst(P, base + lane * (R + 1) + k2, y[k2]);
+    __syncwarp();
+    const int k2p = lane / G;
+#pragma unroll
+    for (int n1 = 0; n1 < 32; n1++) {                     // u_j = sum_r x[j + R r] exp(+2 pi i h (j + R r) / 32)
+        const c2 x = pld(P, base + n1 * (R + 1) + k2p);
+        const float2 w = wts[n1 * 32 + lane];
+        c2& acc = u[brev_n(n1 % R, RB)];
+        if (n1 < R) {
+            acc = cmul2s(x, w);
+        } else {
+            acc.re = fma2(bc(w.x), x.re, fma2(bc(-w.y), x.im, acc.re));
+            acc.im = fma2(bc(w.x), x.im, fma2(bc(w.y), x.re, acc.im));
+        }
+    }
+    __syncwarp();
+    dit2<R, true>(u);
+}
+
 }  // namespace
 
-template <int D, int T>
-__global__ void __launch_bounds__(T* kTeamThreads, 1) r2iq_wide_pair_kernel(const WideParams p) {
+template <int D>
+__global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_pair_kernel(const WideParams p) {
     constexpr int M = kWHalf >> D;
     extern __shared__ __align__(128) unsigned char wsmem[];
-    __shared__ long long s_pair[T];
+    __shared__ long long s_pair[kTeams];
     const int team = threadIdx.x / kTeamThreads;
     const int tt = threadIdx.x % kTeamThreads;
     const int lane = tt & 31;
@@ -127,164 +206,131 @@ __global__ void __launch_bounds__(T* kTeamThreads, 1) r2iq_wide_pair_kernel(cons
     float2* tab = reinterpret_cast<float2*>(wsmem);
     const float2* tw1024 = tab;
     const float2* twq1 = tab + 1024;                   // W_4096^n
-    const float2* twq2 = tab + 2048;                   // W_4096^(2n)
+    const float2* tabx = tab + 2048;                   // d = 0: tw_inv; d >= 1: tw_sub
     Planes P;
-    P.re = reinterpret_cast<float2*>(wsmem + kWTabFloat2 * 8 + (size_t)team * kTeamBytes);
+    P.re = reinterpret_cast<float2*>(wsmem + wide_tab_float2<D>() * 8 + (size_t)team * kTeamBytes);
     P.im = P.re + 4 * kWPlane;
     const int wbase = warp * kWPlane;
+    const int mbase = ((4 - warp) & 3) * kWPlane;      // the plane that holds this plane's mirror bins
     const int tb = p.tunebin;
     const int tb4 = tb >> 2;
     const uint32_t sgn = __float_as_uint(p.imag_sign) & 0x80000000u;
+    const uint32_t row_mask = warp == 0 ? p.row_mask[0] : warp == 1 ? p.row_mask[1] : warp == 2 ? p.row_mask[2] : p.row_mask[3];
+    const float4* pq = p.pq + warp * 1024;
 
-    for (int i = threadIdx.x; i < 1024; i += T * kTeamThreads) {
+    for (int i = threadIdx.x; i < 1024; i += kTeams * kTeamThreads) {
         tab[i] = __ldg(p.tw1024 + i);
         tab[1024 + i] = __ldg(p.twq + i);
-        tab[2048 + i] = __ldg(p.twq + 1024 + i);
     }
+    for (int i = threadIdx.x; i < wide_tab_float2<D>() - 2048; i += kTeams * kTeamThreads)
+        tab[2048 + i] = __ldg((D == 0 ? p.tw_inv : p.tw_sub) + i);
     const long long n_pairs = (p.total_frames + 1) / 2;
     if (tt == 0) s_pair[team] = (long long)atomicAdd(p.work_counter, 1ULL);
     __syncthreads();
 
-    while (true) {
-        const long long q = s_pair[team];
-        if (q >= n_pairs) break;
+    long long q = s_pair[team];
+    HalfWords w0;
+    load_half(p, q < n_pairs ? q : 0, tt, 0, w0);
+    while (q < n_pairs) {
         // ---------------- A: radix-4 DIF over the four quarters of both frames -------------------------------
         {
-            const long long fa = 2 * q;
-            const long long b = fa / kWFrames;
-            const int kf = (int)(fa - b * kWFrames);
-            const uint32_t* srcA = p.in_words + b * (kTransferSamples / 2) + kf * kWHopWords + tt;
-            // frame B starts one hop later (2048 words later across a block edge); the phantom B of an odd total reads A
-            const int offB = fa + 1 >= p.total_frames ? 0 : (kf == kWFrames - 1 ? kWHalf / 2 : kWHopWords);
-            const uint32_t* srcB = srcA + offB;
-#pragma unroll 4
-            for (int j = 0; j < 8; j++) {
-                const int n = tt + 128 * j;
-                c2 z0, z1, z2, z3;
-                unpack_words(__ldg(srcA + 128 * j), __ldg(srcB + 128 * j), p.rand_mul, z0);
-                unpack_words(__ldg(srcA + 128 * j + 1024), __ldg(srcB + 128 * j + 1024), p.rand_mul, z1);
-                unpack_words(__ldg(srcA + 128 * j + 2048), __ldg(srcB + 128 * j + 2048), p.rand_mul, z2);
-                unpack_words(__ldg(srcA + 128 * j + 3072), __ldg(srcB + 128 * j + 3072), p.rand_mul, z3);
-                const c2 a0 = cadd(z0, z2), a1 = csub(z0, z2), a2 = cadd(z1, z3), a3 = csub(z1, z3);
-                const c2 u0 = cadd(a0, a2), u2 = csub(a0, a2);
-                const c2 u1 = c2{add2(a1.re, a3.im), sub2(a1.im, a3.re)};      // a1 - i a3
-                const c2 u3 = c2{sub2(a1.re, a3.im), add2(a1.im, a3.re)};      // a1 + i a3
-                const float2 w1 = twq1[n], w2 = twq2[n];
-                pst(P, 0 * kWPlane + n, u0);
-                pst(P, 1 * kWPlane + n, cmul2s(u1, w1));
-                pst(P, 2 * kWPlane + n, cmul2s(u2, w2));
-                pst(P, 3 * kWPlane + n, cmul2s(u3, cmul(w1, w2)));               // W_4096^(3 n)
-            }
+            HalfWords w1;
+            load_half(p, q, tt, 4, w1);
+            quarter_stage(w0, P, twq1, p.rand_mul, tt, 0);
+            quarter_stage(w1, P, twq1, p.rand_mul, tt, 4);
         }
         team_barrier(team);
-        if (tt == 0) s_pair[team] = (long long)atomicAdd(p.work_counter, 1ULL);   // every thread has read q; next read is after barrier E
+        if (tt == 0) s_pair[team] = (long long)atomicAdd(p.work_counter, 1ULL);   // every thread has read q; read again after barrier D2
 
-        // ---------------- B: warp q transforms plane q in place -------------------------------------------------
+        // ---------------- B: warp q transforms plane q; rows some backward transform reads go back ------------
         {
             c2 v[32];
 #pragma unroll
             for (int j = 0; j < 32; j++) v[brev5(j)] = pld(P, wbase + lane + 32 * j);
             __syncwarp();
-            fft1024p<false>(v, P, wbase, tw1024, lane);
+            dit2<32, false>(v);
 #pragma unroll
-            for (int k1 = 0; k1 < 32; k1++) pst(P, wbase + lane + 32 * k1, v[k1]);   // bin 4 (lane + 32 k1) + warp
+            for (int k2 = 1; k2 < 32; k2++) v[k2] = cmul2s(v[k2], tw1024[32 * k2 + lane]);
+#pragma unroll
+            for (int k2 = 0; k2 < 32; k2++) pst(P, wbase + lane * 33 + k2, v[k2]);
+            __syncwarp();
+#pragma unroll
+            for (int n1 = 0; n1 < 32; n1++) v[brev5(n1)] = pld(P, wbase + n1 * 33 + lane);
+            __syncwarp();
+            dit2<32, false>(v);
+#pragma unroll
+            for (int k1 = 0; k1 < 32; k1++)                                         // bin 4 (lane + 32 k1) + warp
+                if (D == 0 || ((row_mask >> k1) & 1u)) pst(P, wbase + lane + 32 * k1, v[k1]);
         }
         team_barrier(team);
 
-        // ---------------- C: real-FFT split + filter, in place on mirror pairs ------------------------------
-#pragma unroll 2
-        for (int i = 0; i <= 16; i++) {
-            const int pp = i < 16 ? tt + 128 * i : 2048;
-            if (i < 16 || tt == 0) {
-                const int pm = (kWHalf - pp) & (kWHalf - 1);
-                if constexpr (D > 0) {      // only bins of the selected band are read by the backward transform
-                    const bool inp = ((pp - tb + M / 2) & (kWHalf - 1)) < M, inm = ((pm - tb + M / 2) & (kWHalf - 1)) < M;
-                    if (!(inp || inm)) continue;
-                }
-                const c2 a = pld(P, waddr(pp));
-                const c2 bq = pld(P, waddr(pm));
-                const float2 c = __ldg(&p.ctab[pp]);                 // -i * W_8192^p
-                const float2 gp = __ldg(&p.g[pp]);
-                const float2 gm = __ldg(&p.g[pm]);
-                const c2 u = c2{add2(a.re, bq.re), sub2(a.im, bq.im)};      // a + conj b
-                const c2 w = c2{sub2(a.re, bq.re), add2(a.im, bq.im)};      // a - conj b
-                const c2 t = cmul2s(w, c);
-                const c2 xp = cadd(u, t);                                   // 2 X[p]
-                const c2 xm = c2{sub2(u.re, t.re), sub2(t.im, u.im)};       // 2 X[4096-p] = conj(u - t)
-                pst(P, waddr(pp), cmul2s(xp, gp));
-                if (pp != 0 && pm != pp) pst(P, waddr(pm), cmul2s(xm, gm));
-            }
-        }
-        team_barrier(team);
-
-        // ---------------- D + E: backward transform, discard, placement ------------------------------------------
         const FrameOut2 oa = wide_frame_out<D>(2 * q, p.total_frames);
         const FrameOut2 ob = wide_frame_out<D>(2 * q + 1, p.total_frames);
-        if constexpr (D <= 5) {
-            constexpr int MS = M / 4;                                 // points per plane: 1024 >> D
-            if constexpr (D == 0) {
-                c2 v[32];
+        long long qn;
+        if constexpr (D == 0) {
+            // ---------------- D1: split + filter into registers, first backward pass ---------------------------
+            c2 t[32];
 #pragma unroll
-                for (int j = 0; j < 32; j++) v[brev5(j)] = pld(P, wbase + ((tb4 + lane + 32 * j) & 1023));
-                __syncwarp();
-                fft1024p<true>(v, P, wbase, tw1024, lane);
-                if (warp) {
-#pragma unroll
-                    for (int k1 = 0; k1 < 32; k1++) {                 // W_4096^(-warp n')
-                        const int n = lane + 32 * k1;
-                        const float2 w = warp == 1 ? twq1[n] : warp == 2 ? twq2[n] : cmul(twq1[n], twq2[n]);
-                        v[k1] = cmul_conj2s(v[k1], w);
-                    }
-                }
-#pragma unroll
-                for (int k1 = 0; k1 < 32; k1++) pst(P, wbase + lane + 32 * k1, v[k1]);
-            } else {
-                constexpr int R = MS / 32;                            // band bins of this plane per lane
-                constexpr int G = 32 / R;
-                constexpr int RB = ilog2(R);
-                c2 y[R];
-#pragma unroll
-                for (int j = 0; j < R; j++) {
-                    const int m = lane + 32 * j;
-                    y[brev_n(j, RB)] = pld(P, wbase + ((tb4 + (m < MS / 2 ? m : m - MS)) & 1023));
-                }
-                __syncwarp();
-                dit2<R, true>(y);                                     // pass 1 over n2 (m' = lane + 32 n2)
-#pragma unroll
-                for (int k2 = 1; k2 < R; k2++) y[k2] = cmul2s(y[k2], __ldg(&p.tw_sub[k2 * 32 + lane]));   // exp(+2 pi i lane k2 / MS)
-#pragma unroll
-                for (int k2 = 0; k2 < R; k2++) pst(P, wbase + lane * (R + 1) + k2, y[k2]);
-                __syncwarp();
-                const int k2p = lane / G, h = lane % G;
-                c2 u[R];
-#pragma unroll
-                for (int n1 = 0; n1 < 32; n1++) {                     // u_j = sum_r x[j + R r] exp(+2 pi i h (j + R r) / 32)
-                    const c2 x = pld(P, wbase + n1 * (R + 1) + k2p);
-                    const float2 w = __ldg(&p.tw_sub[(R + n1) * 32 + lane]);
-                    c2& acc = u[brev_n(n1 % R, RB)];
-                    if (n1 < R) {
-                        acc = cmul2s(x, w);
-                    } else {
-                        acc.re = fma2(bc(w.x), x.re, fma2(bc(-w.y), x.im, acc.re));
-                        acc.im = fma2(bc(w.x), x.im, fma2(bc(w.y), x.re, acc.im));
-                    }
-                }
-                __syncwarp();
-                dit2<R, true>(u);                                     // u[q] = S_warp[k2p + R h + 32 q]
-#pragma unroll
-                for (int qq = 0; qq < R; qq++) {
-                    const int n = k2p + R * h + 32 * qq;
-                    c2 s = u[qq];
-                    if (warp) {                                       // W_mfft^(-warp n') = W_4096^(-warp (n' << D))
-                        const int e = n << D;
-                        const float2 w = warp == 1 ? twq1[e] : warp == 2 ? twq2[e] : cmul(twq1[e], twq2[e]);
-                        s = cmul_conj2s(s, w);
-                    }
-                    pst(P, wbase + n, s);
-                }
+            for (int k1 = 0; k1 < 32; k1++) {
+                const int mm = lane + 32 * k1;
+                const c2 a = pld(P, wbase + mm);
+                const c2 b = pld(P, mbase + mirror_slot(warp, mm));
+                t[brev5(k1)] = split_pq(a, b, __ldg(pq + mm));
             }
+            dit2<32, true>(t);
+#pragma unroll
+            for (int k2 = 1; k2 < 32; k2++) t[k2] = cmul2s(t[k2], tabx[32 * k2 + lane]);   // residue (lane - tb4) mod 32
+            team_barrier(team);                       // every mirror read of the team is done: the planes are free
+            // ---------------- D2: transposition, second pass, W_4096^(-warp n), S_warp to the plane ------------
+            const int n1_inv = (lane - tb4) & 31;
+#pragma unroll
+            for (int k2 = 0; k2 < 32; k2++) pst(P, wbase + n1_inv * 33 + k2, t[k2]);
+            __syncwarp();
+#pragma unroll
+            for (int n1 = 0; n1 < 32; n1++) t[brev5(n1)] = pld(P, wbase + n1 * 33 + lane);
+            __syncwarp();
+            dit2<32, true>(t);
+            if (warp) {
+#pragma unroll
+                for (int k1 = 0; k1 < 32; k1++) t[k1] = cmul_conj2s(t[k1], wpow(twq1, warp, lane + 32 * k1));
+            }
+#pragma unroll
+            for (int k1 = 0; k1 < 32; k1++) pst(P, wbase + lane + 32 * k1, t[k1]);
+        } else if constexpr (D <= 5) {
+            constexpr int MS = M / 4;                                 // points per plane: 1024 >> D
+            constexpr int R = MS / 32;                                // band bins of this plane per lane
+            constexpr int G = 32 / R;
+            constexpr int RB = ilog2(R);
+            c2 y[R];
+#pragma unroll
+            for (int j = 0; j < R; j++) {
+                const int m = lane + 32 * j;
+                const int mm = (tb4 + (m < MS / 2 ? m : m - MS)) & 1023;
+                const c2 a = pld(P, wbase + mm);
+                const c2 b = pld(P, mbase + mirror_slot(warp, mm));
+                y[brev_n(j, RB)] = split_pq(a, b, __ldg(pq + mm));
+            }
+            dit2<R, true>(y);                                         // pass 1 over n2 (m' = lane + 32 n2)
+#pragma unroll
+            for (int k2 = 1; k2 < R; k2++) y[k2] = cmul2s(y[k2], tabx[k2 * 32 + lane]);   // exp(+2 pi i lane k2 / MS)
+            team_barrier(team);                       // every band read of the team is done: the planes are free
+            c2 u[R];
+            rscheme_pass2<R>(y, u, P, wbase, tabx + R * 32, lane);    // u[q] = S_warp[k2p + R h + 32 q]
+            const int k2p = lane / G, h = lane % G;
+#pragma unroll
+            for (int qq = 0; qq < R; qq++) {
+                const int n = k2p + R * h + 32 * qq;
+                c2 s = u[qq];
+                if (warp) s = cmul_conj2s(s, wpow(twq1, warp, n << D));   // W_mfft^(-warp n') = W_4096^(-warp (n' << D))
+                pst(P, wbase + n, s);
+            }
+        }
+        if constexpr (D <= 5) {
             team_barrier(team);
-            // last radix-4 stage across the planes: y[n' + MS a] = sum_r i^(r a) S_r[n'], a = 0..2 kept
+            qn = s_pair[team];
+            load_half(p, qn < n_pairs ? qn : q, tt, 0, w0);           // in flight during E (past the end: this pair again, unused)
+            // ---------------- E: last radix-4 stage across the planes: y[n' + MS a] = sum_r i^(r a) S_r[n'], a = 0..2 kept
+            constexpr int MS = M / 4;
 #pragma unroll
             for (int i = 0; i < (MS + kTeamThreads - 1) / kTeamThreads; i++) {
                 const int n = tt + kTeamThreads * i;
@@ -298,34 +344,26 @@ __global__ void __launch_bounds__(T* kTeamThreads, 1) r2iq_wide_pair_kernel(cons
             }
         } else {
             // d = 6: mfft = 64, warp 0 alone (R = 2 register scheme over the whole band)
+            qn = s_pair[team];
+            load_half(p, qn < n_pairs ? qn : q, tt, 0, w0);
             if (warp == 0) {
                 constexpr int R = M / 32, G = 32 / R, RB = ilog2(R);
-                auto ysrc = [&](int m) { return waddr((tb + (m < M / 2 ? m : m - M)) & (kWHalf - 1)); };
                 c2 y[R];
 #pragma unroll
-                for (int j = 0; j < R; j++) y[brev_n(j, RB)] = pld(P, ysrc(lane + 32 * j));
+                for (int j = 0; j < R; j++) {
+                    const int m = lane + 32 * j;
+                    const int k = (tb + (m < M / 2 ? m : m - M)) & (kWHalf - 1);
+                    const c2 a = pld(P, waddr(k));
+                    const c2 b = pld(P, waddr((kWHalf - k) & (kWHalf - 1)));
+                    y[brev_n(j, RB)] = split_pq(a, b, __ldg(p.pq + (k & 3) * 1024 + (k >> 2)));
+                }
                 __syncwarp();
                 dit2<R, true>(y);
 #pragma unroll
-                for (int k2 = 1; k2 < R; k2++) y[k2] = cmul2s(y[k2], __ldg(&p.tw_sub[k2 * 32 + lane]));
-#pragma unroll
-                for (int k2 = 0; k2 < R; k2++) pst(P, lane * (R + 1) + k2, y[k2]);
-                __syncwarp();
-                const int k2p = lane / G, h = lane % G;
+                for (int k2 = 1; k2 < R; k2++) y[k2] = cmul2s(y[k2], tabx[k2 * 32 + lane]);
                 c2 u[R];
-#pragma unroll
-                for (int n1 = 0; n1 < 32; n1++) {
-                    const c2 x = pld(P, n1 * (R + 1) + k2p);
-                    const float2 w = __ldg(&p.tw_sub[(R + n1) * 32 + lane]);
-                    c2& acc = u[brev_n(n1 % R, RB)];
-                    if (n1 < R) {
-                        acc = cmul2s(x, w);
-                    } else {
-                        acc.re = fma2(bc(w.x), x.re, fma2(bc(-w.y), x.im, acc.re));
-                        acc.im = fma2(bc(w.x), x.im, fma2(bc(w.y), x.re, acc.im));
-                    }
-                }
-                dit2<R, true>(u);
+                rscheme_pass2<R>(y, u, P, 0, tabx + R * 32, lane);
+                const int k2p = lane / G, h = lane % G;
 #pragma unroll
                 for (int qq = 0; qq < R; qq++) {
                     const int idx = k2p + R * h + 32 * qq;
@@ -334,36 +372,36 @@ __global__ void __launch_bounds__(T* kTeamThreads, 1) r2iq_wide_pair_kernel(cons
             }
         }
         team_barrier(team);                                           // the planes are rewritten by the next pair
+        q = qn;
     }
 }
 
-template <int D, int T>
+template <int D>
 static cudaError_t setup_wp() {
-    cudaError_t e = cudaFuncSetAttribute(r2iq_wide_pair_kernel<D, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, wide_smem_bytes<T>());
+    cudaError_t e = cudaFuncSetAttribute(r2iq_wide_pair_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, wide_smem_bytes<D>());
     if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(r2iq_wide_pair_kernel<D, T>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    return cudaFuncSetAttribute(r2iq_wide_pair_kernel<D>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
 }
 
-template <int D, int T>
+template <int D>
 static cudaError_t launch_wp(const WideParams& p, int sm_count, cudaStream_t stream) {
     const long long n_pairs = (p.total_frames + 1) / 2;
     long long grid = sm_count;                        // persistent: one CTA per SM
-    const long long want = (n_pairs + T - 1) / T;
+    const long long want = (n_pairs + kTeams - 1) / kTeams;
     if (grid > want) grid = want;
     if (grid < 1) grid = 1;
     cudaError_t e = cudaMemsetAsync(p.work_counter, 0, sizeof(unsigned long long), stream);
     if (e != cudaSuccess) return e;
-    r2iq_wide_pair_kernel<D, T><<<(unsigned)grid, T * kTeamThreads, wide_smem_bytes<T>(), stream>>>(p);
+    r2iq_wide_pair_kernel<D><<<(unsigned)grid, kTeams * kTeamThreads, wide_smem_bytes<D>(), stream>>>(p);
     return cudaGetLastError();
 }
 
-// teams per CTA for each decimation
-#define R2IQ_WIDE_FOR_ALL(X) X(0, 3) X(1, 3) X(2, 3) X(3, 3) X(4, 3) X(5, 3) X(6, 3)
+#define R2IQ_WIDE_FOR_ALL(X) X(0) X(1) X(2) X(3) X(4) X(5) X(6)
 
 cudaError_t setup_wide_kernels() {
     cudaError_t e;
-#define X(D, T) \
-    if ((e = setup_wp<D, T>()) != cudaSuccess) return e;
+#define X(D) \
+    if ((e = setup_wp<D>()) != cudaSuccess) return e;
     R2IQ_WIDE_FOR_ALL(X)
 #undef X
 #ifdef R2IQ_AB_VARIANTS
@@ -376,8 +414,8 @@ cudaError_t launch_wide(int d, const WideParams& p, int sm_count, cudaStream_t s
 #ifdef R2IQ_AB_VARIANTS
     if (kernel_generation() != 0) return launch_wide_gen1(d, p, sm_count, stream);   // the four-warps-per-frame scalar kernels
 #endif
-#define X(D, T) \
-    if (d == D) return launch_wp<D, T>(p, sm_count, stream);
+#define X(D) \
+    if (d == D) return launch_wp<D>(p, sm_count, stream);
     R2IQ_WIDE_FOR_ALL(X)
 #undef X
     return cudaErrorInvalidValue;
@@ -386,7 +424,7 @@ cudaError_t launch_wide(int d, const WideParams& p, int sm_count, cudaStream_t s
 const char* wide_kernel_name(int d) {
     static char names[kNDec][48];
     if (d < 0 || d >= kNDec) return "";
-    if (!names[d][0]) snprintf(names[d], sizeof(names[d]), "r2iq_wide_pair_kernel<%d, %d>", d, 3);
+    if (!names[d][0]) snprintf(names[d], sizeof(names[d]), "r2iq_wide_pair_kernel<%d>", d);
     return names[d];
 }
 
