@@ -57,11 +57,15 @@ with open(os.path.join(dst, f"{tag}_launch_shares.txt"), "w") as f:
 
 # ---- per-kernel metrics from the full captures (FFTN 2048 kernels; FFTN 8192 kernels when captured) -----------------
 captures = []
-for rep_name in (f"{tag}_full.ncu-rep", f"{tag}_wide_full.ncu-rep"):
+for rep_name in (f"{tag}_full.ncu-rep", f"{tag}_wide_full.ncu-rep", f"{tag}_chan_full.ncu-rep"):
     rep = os.path.join(src, rep_name)
-    if not os.path.exists(rep):
+    csv_path = rep[:-len(".ncu-rep")] + ".raw.csv"          # tools/profile_round.sh exports the raw page on the box
+    if os.path.exists(csv_path):
+        raw = open(csv_path).read()
+    elif os.path.exists(rep):
+        raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True, check=True).stdout
+    else:
         continue
-    raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True, check=True).stdout
     rows = list(csv.reader(raw.splitlines()))
     captures.append((rows[0], rows[1], rows[2:]))
 want = {
