@@ -82,9 +82,14 @@ def packed_fp32_per_pair(kernel: str):
     m = re.match(r"r2iq_pair_kernel<(\d+), (\d+), (\d+)>", kernel)
     if not m:
         return None
-    mangled = f"_ZN4r2iq16r2iq_pair_kernelILi{m.group(1)}ELi{m.group(2)}ELi{m.group(3)}EEEvNS_11FusedParamsE"
+    # the parameter list of the symbol depends on the decimation (FusedParams, or PairParams + PairNco: r2iq_pair.cu)
+    stem = f"_ZN4r2iq16r2iq_pair_kernelILi{m.group(1)}ELi{m.group(2)}ELi{m.group(3)}EEEv"
     try:
-        out = subprocess.run([exe, "-sass", "-fun", mangled, capi.LIB_PATH], capture_output=True, text=True, timeout=120).stdout
+        out = ""
+        for mangled in (stem + "NS_11FusedParamsE", stem + "NS_10PairParamsENS_7PairNcoE"):
+            out = subprocess.run([exe, "-sass", "-fun", mangled, capi.LIB_PATH], capture_output=True, text=True, timeout=120).stdout
+            if "Function :" in out:
+                break
     except Exception:
         return None
     # the persistent loop = the longest backward branch; count inside it only (the function also holds the prologue and

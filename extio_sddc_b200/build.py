@@ -19,10 +19,11 @@ LIB_PATH = os.path.join(LIB_DIR, "libr2iq_cuda.so")
 SOURCES = ["r2iq_pair.cu", "r2iq_launch.cu", "r2iq_channels.cu", "r2iq_wide_pair.cu", "r2iq_fft.cu", "r2iq_capi.cu", "fir_design.cpp"]
 # R2IQ_AB_VARIANTS=1 at build time adds the older kernel generations and their run-time switches (R2IQ_KERNEL_GEN,
 # R2IQ_VARIANT, R2IQ_CTAS_PER_SM) for comparison runs (tools/variant_sweep.py); `r2iq_cuda_version()` then says so.
+SOURCES += [os.path.join("wide_tu", f"r2iq_wide_pair_d{d}{m}.cu") for d in range(7) for m in ("", "m")]   # one module per kernel
 AB_VARIANTS = os.environ.get("R2IQ_AB_VARIANTS", "0") not in ("", "0")
 if AB_VARIANTS:
     SOURCES += ["r2iq_wide.cu", "r2iq_gen1.cu", "r2iq_dual.cu", "r2iq_dual_d0.cu", "r2iq_dual_d1.cu", "r2iq_dual_dn.cu"]
-HEADERS = ["r2iq_kernels.cuh", "dft_regs.cuh", "dft_regs2.cuh", "r2iq_common.cuh", "work_dispenser.cuh", "dual_frame.cuh", "fir_design.h", os.path.join("..", "..", "include", "r2iq_cuda.h")]
+HEADERS = ["r2iq_wide_pair.cu", "r2iq_kernels.cuh", "dft_regs.cuh", "dft_regs2.cuh", "r2iq_common.cuh", "work_dispenser.cuh", "dual_frame.cuh", "fir_design.h", os.path.join("..", "..", "include", "r2iq_cuda.h")]
 ARCH_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a"]
 NVCC_FLAGS = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden",
               "--cudart", "static", "-Xfatbin", "-compress-all"] + (["-DR2IQ_AB_VARIANTS"] if AB_VARIANTS else [])
@@ -55,7 +56,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     hdr_time = max(hdr_time, os.path.getmtime(os.path.abspath(__file__)))
 
     def compile_one(src: str) -> str:
-        obj = os.path.join(LIB_DIR, os.path.splitext(src)[0] + ".o")
+        obj = os.path.join(LIB_DIR, os.path.splitext(os.path.basename(src))[0] + ".o")
         path = os.path.join(CSRC, src)
         obj = obj[:-2] + ("_ab.o" if AB_VARIANTS else ".o")      # the two flavours never share objects
         if not force and os.path.exists(obj) and os.path.getmtime(obj) >= max(os.path.getmtime(path), hdr_time):

@@ -44,7 +44,8 @@ __device__ __forceinline__ void tma_load_1d(uint32_t dst, const void* src, uint3
 }
 
 // first word of frame f = 43*block + k inside [halo | blocks] (hop 1536 samples = 768 words)
-__device__ __forceinline__ const uint32_t* frame_src(const FusedParams& p, long long f) {
+template <class Params>
+__device__ __forceinline__ const uint32_t* frame_src(const Params& p, long long f) {
     const long long b = f / kFramesPerBlock;
     const int k = (int)(f - b * kFramesPerBlock);
     return p.in_words + b * (kTransferSamples / 2) + k * (kHop / 2);
@@ -104,6 +105,26 @@ __device__ __forceinline__ FrameOut2 frame_out2(long long f, long long total) {
     o.live = f < total;
     o.lo = k ? 0 : M / 4;
     o.base = b * (long long)((kTransferSamples / 2) >> D) + (k ? (M / 2 + (k - 1) * (3 * M / 4)) : 0) - o.lo;
+    return o;
+}
+
+// Direct-phase mixer on the packed lanes: the phasors of the two frames' samples at output positions ia / ib ...
+__device__ __forceinline__ c2 direct_phasors(double phase0, double fc, long long ia, long long ib) {
+    const float2 pa = nco_direct_phasor(phase0, fc, ia);
+    const float2 pb = nco_direct_phasor(phase0, fc, ib);
+    c2 ph;
+    ph.re = pk(pa.x, pb.x);
+    ph.im = pk(pa.y, pb.y);
+    return ph;
+}
+// ... advanced by `rot` (32 k samples further on: the lane's k-th stored row) and applied to t after the sideband
+// conjugation (the mixer follows the operator, Core/RadioHandler.cpp:33-37): 9 packed instructions per row
+__device__ __forceinline__ c2 direct_mix(c2 t, c2 ph0, float2 rot, float imag_sign) {
+    const c2 ph = cmul2s(ph0, rot);
+    const u64 ti = mul2(bc(imag_sign), t.im);
+    c2 o;
+    o.re = fma2(t.re, ph.re, neg2(mul2(ti, ph.im)));
+    o.im = fma2(t.re, ph.im, mul2(ti, ph.re));
     return o;
 }
 

@@ -101,7 +101,7 @@ struct NcoState {
     // Direct-phase mode (R2IQ_NCO_DIRECT): no recurrence; phase of the next output sample in cycles, [0, 1)
     int mode = R2IQ_NCO_REFERENCE;
     double phase = 0.0;
-    float* d_rot = nullptr;      // [32] exp(2 pi j fc 32 k)
+    float* d_rot = nullptr;      // [128] exp(2 pi j fc 32 k): the 2048 family reads k < 32, the 8192 family k < 128
     float* d_tab = nullptr;
     float* d_starts = nullptr;   // device-path scratch (caller's stream keeps launches ordered)
     size_t starts_cap = 0;
@@ -446,7 +446,8 @@ void nco_direct_advance(NcoState& s, size_t n_out) {
 }
 
 // FFTN 8192: static twiddles once per handle, filter gains (and small-transform twiddles) per (d, tune bin).
-int launch_wide_impl(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d_out, cudaStream_t stream, int tunebin) {
+int launch_wide_impl(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d_out, cudaStream_t stream, int tunebin,
+                     bool direct_mixer = false) {
     const int d = h->latched_decimate;
     const int HF = 4096, M = HF >> d;
     if (!h->d_twq) {
@@ -543,7 +544,13 @@ int launch_wide_impl(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d
     p.rand_mul = h->rand_on ? 0xFFFEu : 0u;
     p.imag_sign = h->latched_sideband ? -1.0f : 1.0f;
     p.work_counter = h->next_counter();
-    CU(h, launch_wide(d, p, h->sm_count, stream));
+    WideNco nco{nullptr, 0.0, 0.0};
+    if (direct_mixer) {                   // mixed in the store epilogue, as the 2048 family does
+        nco.nco_rot = (const float2*)h->nco.d_rot;
+        nco.nco_phase0 = h->nco.phase;
+        nco.nco_fc = (double)h->nco.fc;
+    }
+    CU(h, launch_wide(d, p, nco, h->sm_count, stream));
     return R2IQ_OK;
 }
 
@@ -582,13 +589,13 @@ int fused_params(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d_out
 int launch(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d_out, cudaStream_t stream, float** nco_starts,
            size_t* nco_cap) {
     if (h->fftn == 8192) {
-        int rc = launch_wide_impl(h, d_in, n_blocks, d_out, stream, h->tunebin.load());   // one snapshot per launch
+        const size_t n_out8 = (size_t)n_blocks * (size_t)((kTransferSamples / 2) >> h->latched_decimate);
+        const bool direct8 = h->nco.on && n_out8 > 0 && h->nco.mode == R2IQ_NCO_DIRECT;
+        int rc = launch_wide_impl(h, d_in, n_blocks, d_out, stream, h->tunebin.load(), direct8);   // one snapshot per launch
         if (rc != R2IQ_OK) return rc;
         h->stats.kernel_launches++;
         h->stats.blocks_processed += (uint64_t)n_blocks;
-        const size_t n_out8 = (size_t)n_blocks * (size_t)((kTransferSamples / 2) >> h->latched_decimate);
-        if (h->nco.on && n_out8 > 0 && h->nco.mode == R2IQ_NCO_DIRECT) {
-            CU(h, launch_nco_mix_direct(d_out, (long long)n_out8, h->nco.phase, (double)h->nco.fc, stream));
+        if (direct8) {
             nco_direct_advance(h->nco, n_out8);
             return R2IQ_OK;
         }
@@ -925,15 +932,15 @@ float r2iq_cuda_set_fine_tune(r2iq_cuda_t h, float fc) {
     if (s.on && s.fc == fc) return fc;   // RadioHandler.cpp:292: the state restarts only when fc changes
     nco_init(s, fc);
     s.phase = 0.0;                        // phase_start_rad = 0 (RadioHandler.cpp:295)
-    float rot[64];
-    for (int k = 0; k < 32; k++) {
+    float rot[256];
+    for (int k = 0; k < 128; k++) {
         double ph = (double)fc * 32.0 * (double)k;
         ph = 2.0 * kPiD * (ph - floor(ph));
         rot[2 * k] = (float)cos(ph);
         rot[2 * k + 1] = (float)sin(ph);
     }
     if (!s.d_tab && cudaMalloc(&s.d_tab, sizeof(float) * 66) != cudaSuccess) return 0.f;
-    if (!s.d_rot && cudaMalloc(&s.d_rot, sizeof(float) * 64) != cudaSuccess) return 0.f;
+    if (!s.d_rot && cudaMalloc(&s.d_rot, sizeof(rot)) != cudaSuccess) return 0.f;
     // ordered after everything already queued: the tables may still be read by launches in flight
     if (cudaDeviceSynchronize() != cudaSuccess ||
         cudaMemcpy(s.d_rot, rot, sizeof(rot), cudaMemcpyHostToDevice) != cudaSuccess ||
@@ -1485,7 +1492,7 @@ int r2iq_cuda_get_fftn(r2iq_cuda_t h) { return h ? h->fftn : R2IQ_E_INVALID; }
 
 int r2iq_cuda_kernel_name(r2iq_cuda_t h, int d, char* buf, int n) {
     if (!h || !buf || n < 1 || d < 0 || d >= kNDec) return fail(R2IQ_E_INVALID, "kernel_name: bad arguments");
-    if (h->fftn == 8192) snprintf(buf, (size_t)n, "%s", wide_kernel_name(d));
+    if (h->fftn == 8192) snprintf(buf, (size_t)n, "%s", wide_kernel_name(d, h->nco.on && h->nco.mode == R2IQ_NCO_DIRECT));
     else snprintf(buf, (size_t)n, "%s", fused_kernel_name(d, h->nco.on && h->nco.mode == R2IQ_NCO_DIRECT));
     return R2IQ_OK;
 }

@@ -124,9 +124,18 @@ struct WideParams {
     float imag_sign;
     unsigned long long* work_counter;   // as FusedParams
 };
+// Direct-phase fine-tune mixer in the store epilogue of the FFTN 8192 kernels (nco_rot null = off), as the fields of the
+// same names in FusedParams; nco_rot has 128 entries here.  A kernel parameter of its own on purpose: with these three
+// fields inside WideParams the mixer-less d = 1 kernel compiled to 40 more instructions and 88 bytes of spills
+// (418 -> 396 Gsamples/s) -- code generation follows the size of the parameter block.
+struct WideNco {
+    const float2* nco_rot;
+    double nco_phase0;
+    double nco_fc;
+};
 cudaError_t setup_wide_kernels();
-cudaError_t launch_wide(int d, const WideParams& p, int sm_count, cudaStream_t stream);
-const char* wide_kernel_name(int d);                 // as profilers print it
+cudaError_t launch_wide(int d, const WideParams& p, const WideNco& nco, int sm_count, cudaStream_t stream);
+const char* wide_kernel_name(int d, bool direct_mixer = false);   // as profilers print it
 cudaError_t setup_wide_gen1_kernels();               // r2iq_wide.cu, comparison builds only
 cudaError_t launch_wide_gen1(int d, const WideParams& p, int sm_count, cudaStream_t stream);
 int kernel_generation();

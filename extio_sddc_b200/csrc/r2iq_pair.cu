@@ -72,30 +72,38 @@ __device__ __forceinline__ c2 lds2r(const u64* S, int idx) {
     return v;
 }
 
-// Direct-phase mixer on the packed lanes: the phasors of the two frames' samples at output positions ia / ib ...
-__device__ __forceinline__ c2 direct_phasors(const FusedParams& p, long long ia, long long ib) {
-    const float2 pa = nco_direct_phasor(p.nco_phase0, p.nco_fc, ia);
-    const float2 pb = nco_direct_phasor(p.nco_phase0, p.nco_fc, ib);
-    c2 ph;
-    ph.re = pk(pa.x, pb.x);
-    ph.im = pk(pa.y, pb.y);
-    return ph;
-}
-// ... advanced by `rot` (32 k samples further on: the lane's k-th stored row) and applied to t after the sideband
-// conjugation (the mixer follows the operator, Core/RadioHandler.cpp:33-37): 9 packed instructions per row
-__device__ __forceinline__ c2 direct_mix(c2 t, c2 ph0, float2 rot, float imag_sign) {
-    const c2 ph = cmul2s(ph0, rot);
-    const u64 ti = mul2(bc(imag_sign), t.im);
-    c2 o;
-    o.re = fma2(t.re, ph.re, neg2(mul2(ti, ph.im)));
-    o.im = fma2(t.re, ph.im, mul2(ti, ph.re));
-    return o;
-}
-
 }  // namespace
 
-template <int D, int W, int kMix>
-__global__ void __launch_bounds__(W * 32, 1) r2iq_pair_kernel(const FusedParams p) {
+// What the kernels really read, as their parameter block: FusedParams (the launchers' common currency, 152 bytes with
+// the tables of the older generations and all mixer forms) narrowed to 88 bytes, the direct-phase mixer's three fields
+// as a second parameter.  Code generation follows the size of the parameter block: with the wide block the d = 0 kernel
+// carries 115 more integer instructions per frame pair (3443 vs 3315) and d = 1 73 more -- at their register limits
+// ptxas re-derives addresses instead of keeping them.
+struct PairParams {
+    const uint32_t* in_words;
+    float2* out;
+    long long total_frames;
+    const float2* tw_fwd;
+    const float2* gp;
+    const float2* gq;
+    const float2* tw_inv;
+    const float2* tw_aux;
+    int tunebin;
+    uint32_t row_mask;
+    uint32_t rand_mul;
+    float imag_sign;
+    unsigned long long* work_counter;
+};
+struct PairNco {
+    const float2* nco_rot;
+    double nco_phase0;
+    double nco_fc;
+};
+
+// P: the parameter block (FusedParams or PairParams), N: where the direct-phase mixer's fields live (the same
+// FusedParams object, or a PairNco)
+template <int D, int W, int kMix, class P, class N>
+__device__ __forceinline__ void pair_body(const P& p, const N& nco) {
     constexpr bool kLandInTile = W == 12;
     constexpr int M = kHalfFft >> D;
     constexpr int R = D == 6 ? 1 : 32 >> D;   // band bins per lane (d = 1..5; d = 6: one bin on each of 16 lanes)
@@ -180,6 +188,9 @@ __global__ void __launch_bounds__(W * 32, 1) r2iq_pair_kernel(const FusedParams 
         }
 
         // ---- forward 1024-point transform of z = x[2n] + i x[2n+1] ------------------------------
+        // (both radix-32 passes are straight-line code on purpose: running them through one copy of the butterflies in
+        // a two-trip loop takes 6 KB off a 33..55 KB loop body that shares a 32 KB instruction cache, and costs
+        // 7..46 % of the throughput -- loop-carried register moves, a weaker static schedule; measured, round 2)
         dit2<32, false>(v);
         if constexpr (D == 0) {
 #pragma unroll
@@ -246,11 +257,11 @@ __global__ void __launch_bounds__(W * 32, 1) r2iq_pair_kernel(const FusedParams 
             const FrameOut2 oa = frame_out2<0>(2 * q, p.total_frames);
             const FrameOut2 ob = frame_out2<0>(2 * q + 1, p.total_frames);
             c2 ph0;
-            if constexpr (kMix == 2) ph0 = direct_phasors(p, oa.base + lane, ob.base + lane);
+            if constexpr (kMix == 2) ph0 = direct_phasors(nco.nco_phase0, nco.nco_fc, oa.base + lane, ob.base + lane);
 #pragma unroll
             for (int k1 = 0; k1 < 24; k1++) {     // idx >= 768 is always discarded
                 const int idx = lane + 32 * k1;
-                if constexpr (kMix == 2) t[k1] = direct_mix(t[k1], ph0, __ldg(p.nco_rot + k1), p.imag_sign);
+                if constexpr (kMix == 2) t[k1] = direct_mix(t[k1], ph0, __ldg(nco.nco_rot + k1), p.imag_sign);
                 float ar, br, ai, bi;
                 upk(t[k1].re, ar, br);
                 upk(t[k1].im, ai, bi);
@@ -303,7 +314,7 @@ __global__ void __launch_bounds__(W * 32, 1) r2iq_pair_kernel(const FusedParams 
             const FrameOut2 oa = frame_out2<6>(2 * q, p.total_frames);
             const FrameOut2 ob = frame_out2<6>(2 * q + 1, p.total_frames);
             if constexpr (kMix == 2)
-                acc = direct_mix(acc, direct_phasors(p, oa.base + lane, ob.base + lane), make_float2(1.0f, 0.0f), p.imag_sign);
+                acc = direct_mix(acc, direct_phasors(nco.nco_phase0, nco.nco_fc, oa.base + lane, ob.base + lane), make_float2(1.0f, 0.0f), p.imag_sign);
             float ar, br, ai, bi;
             upk(acc.re, ar, br);
             upk(acc.im, ai, bi);
@@ -382,11 +393,11 @@ __global__ void __launch_bounds__(W * 32, 1) r2iq_pair_kernel(const FusedParams 
             const FrameOut2 ob = frame_out2<D>(2 * q + 1, p.total_frames);
             const int idx0 = k2p + R * h;
             c2 ph0;
-            if constexpr (kMix == 2) ph0 = direct_phasors(p, oa.base + idx0, ob.base + idx0);
+            if constexpr (kMix == 2) ph0 = direct_phasors(nco.nco_phase0, nco.nco_fc, oa.base + idx0, ob.base + idx0);
 #pragma unroll
             for (int q4 = 0; q4 < R; q4++) {
                 const int idx = idx0 + 32 * q4;
-                if constexpr (kMix == 2) t[q4] = direct_mix(t[q4], ph0, __ldg(p.nco_rot + q4), p.imag_sign);
+                if constexpr (kMix == 2) t[q4] = direct_mix(t[q4], ph0, __ldg(nco.nco_rot + q4), p.imag_sign);
                 float ar, br, ai, bi;
                 upk(t[q4].re, ar, br);
                 upk(t[q4].im, ai, bi);
@@ -405,25 +416,48 @@ __global__ void __launch_bounds__(W * 32, 1) r2iq_pair_kernel(const FusedParams 
     }
 }
 
+// The two forms of the parameter block (see PairParams): which one a decimation gets is a measurement --
+// B200, 8192 blocks, narrow vs wide block: d = 0 516 vs 500 Gsamples/s, d = 2 790 vs 786, and the other way round at
+// d = 1 (594 vs 607), d = 3 (905 vs 921), d = 4 (979 vs 997), d = 5 (998 vs 1013); d = 6 no difference.
+template <int D>
+constexpr bool kNarrowParams = D == 0 || D == 2;
+
 template <int D, int W, int kMix>
-static cudaError_t setup_pair_one() {
-    cudaError_t e = cudaFuncSetAttribute(r2iq_pair_kernel<D, W, kMix>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         pair_smem_bytes<D, W>());
-    if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(r2iq_pair_kernel<D, W, kMix>, cudaFuncAttributePreferredSharedMemoryCarveout,
-                                cudaSharedmemCarveoutMaxShared);
+__global__ void __launch_bounds__(W * 32, 1) r2iq_pair_kernel(const FusedParams p) {
+    pair_body<D, W, kMix>(p, p);
+}
+template <int D, int W, int kMix>
+__global__ void __launch_bounds__(W * 32, 1) r2iq_pair_kernel(const PairParams p, const PairNco nco) {
+    pair_body<D, W, kMix>(p, nco);
 }
 
 template <int D, int W, int kMix>
-static cudaError_t launch_pair_one(const FusedParams& p, int sm_count, cudaStream_t stream) {
-    const long long n_pairs = (p.total_frames + 1) / 2;
+static cudaError_t setup_pair_one() {
+    const void* fn;
+    if constexpr (kNarrowParams<D>) fn = (const void*)static_cast<void (*)(PairParams, PairNco)>(r2iq_pair_kernel<D, W, kMix>);
+    else fn = (const void*)static_cast<void (*)(FusedParams)>(r2iq_pair_kernel<D, W, kMix>);
+    cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, pair_smem_bytes<D, W>());
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(fn, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+}
+
+template <int D, int W, int kMix>
+static cudaError_t launch_pair_one(const FusedParams& fp, int sm_count, cudaStream_t stream) {
+    const long long n_pairs = (fp.total_frames + 1) / 2;
     long long grid = sm_count;                 // persistent: one CTA per SM
     const long long want = (n_pairs + W - 1) / W;
     if (grid > want) grid = want;
     if (grid < 1) grid = 1;
-    cudaError_t e = cudaMemsetAsync(p.work_counter, 0, sizeof(unsigned long long), stream);
+    cudaError_t e = cudaMemsetAsync(fp.work_counter, 0, sizeof(unsigned long long), stream);
     if (e != cudaSuccess) return e;
-    r2iq_pair_kernel<D, W, kMix><<<(unsigned)grid, W * 32, pair_smem_bytes<D, W>(), stream>>>(p);
+    if constexpr (kNarrowParams<D>) {
+        const PairParams p{fp.in_words, fp.out, fp.total_frames, fp.tw_fwd, fp.gp, fp.gq, fp.tw_inv, fp.tw_aux,
+                           fp.tunebin, fp.row_mask, fp.rand_mul, fp.imag_sign, fp.work_counter};
+        const PairNco nco{fp.nco_rot, fp.nco_phase0, fp.nco_fc};
+        r2iq_pair_kernel<D, W, kMix><<<(unsigned)grid, W * 32, pair_smem_bytes<D, W>(), stream>>>(p, nco);
+    } else {
+        r2iq_pair_kernel<D, W, kMix><<<(unsigned)grid, W * 32, pair_smem_bytes<D, W>(), stream>>>(fp);
+    }
     return cudaGetLastError();
 }
 

@@ -123,6 +123,17 @@ __device__ __forceinline__ void store_pair(float2* out, const FrameOut2& oa, con
     if (idx >= oa.lo) out[oa.base + idx] = make_float2(ar, flip(ai, sgn));
     if (ob.live && idx >= ob.lo) out[ob.base + idx] = make_float2(br, flip(bi, sgn));
 }
+// the same with the direct-phase fine-tune mixer: ph0 = the two frames' phasors at the thread's first sample, rot = the
+// rotation from there to idx (a table entry: no chain of products); sideband conjugation first (RadioHandler.cpp:33-37)
+__device__ __forceinline__ void store_pair_mixed(float2* out, const FrameOut2& oa, const FrameOut2& ob, int idx, c2 v, c2 ph0,
+                                                 float2 rot, float imag_sign) {
+    v = direct_mix(v, ph0, rot, imag_sign);
+    float ar, br, ai, bi;
+    upk(v.re, ar, br);
+    upk(v.im, ai, bi);
+    if (idx >= oa.lo) out[oa.base + idx] = make_float2(ar, ai);
+    if (ob.live && idx >= ob.lo) out[ob.base + idx] = make_float2(br, bi);
+}
 
 // Input words of one half of a frame pair: thread tt's points n = tt + 128 (j0 + jj), jj < 4, of the four quarters.
 struct HalfWords {
@@ -194,8 +205,8 @@ __device__ __forceinline__ void rscheme_pass2(c2 (&y)[R], c2 (&u)[R], const Plan
 
 }  // namespace
 
-template <int D>
-__global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_pair_kernel(const WideParams p) {
+template <int D, int kMix>
+__global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_pair_kernel(const WideParams p, const WideNco nco) {
     constexpr int M = kWHalf >> D;
     extern __shared__ __align__(128) unsigned char wsmem[];
     __shared__ long long s_pair[kTeams];
@@ -273,7 +284,7 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_pair_kernel
 #pragma unroll
             for (int k1 = 0; k1 < 32; k1++) {
                 const int mm = lane + 32 * k1;
-                const c2 a = pld(P, wbase + mm);
+                const c2 a = pld(P, wbase + mm);      // (keeping phase B's v[k1] alive across the barrier instead: 291 vs 325 Gsamples/s)
                 const c2 b = pld(P, mbase + mirror_slot(warp, mm));
                 t[brev5(k1)] = split_pq(a, b, __ldg(pq + mm));
             }
@@ -331,15 +342,25 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_pair_kernel
             load_half(p, qn < n_pairs ? qn : q, tt, 0, w0);           // in flight during E (past the end: this pair again, unused)
             // ---------------- E: last radix-4 stage across the planes: y[n' + MS a] = sum_r i^(r a) S_r[n'], a = 0..2 kept
             constexpr int MS = M / 4;
+            c2 ph0;
+            if constexpr (kMix == 2) ph0 = direct_phasors(nco.nco_phase0, nco.nco_fc, oa.base + tt, ob.base + tt);
 #pragma unroll
             for (int i = 0; i < (MS + kTeamThreads - 1) / kTeamThreads; i++) {
                 const int n = tt + kTeamThreads * i;
                 if (MS >= kTeamThreads || n < MS) {
                     const c2 s0 = pld(P, n), s1 = pld(P, kWPlane + n), s2 = pld(P, 2 * kWPlane + n), s3 = pld(P, 3 * kWPlane + n);
                     const c2 a0 = cadd(s0, s2), a1 = csub(s0, s2), a2 = cadd(s1, s3), a3 = csub(s1, s3);
-                    store_pair(p.out, oa, ob, n, cadd(a0, a2), sgn);
-                    store_pair(p.out, oa, ob, n + MS, c2{sub2(a1.re, a3.im), add2(a1.im, a3.re)}, sgn);      // a1 + i a3
-                    store_pair(p.out, oa, ob, n + 2 * MS, csub(a0, a2), sgn);
+                    if constexpr (kMix == 2) {
+                        // sample n + MS a is 32 (4 i + (MS / 32) a) samples after sample tt: entries of nco_rot (< 96)
+                        store_pair_mixed(p.out, oa, ob, n, cadd(a0, a2), ph0, __ldg(nco.nco_rot + 4 * i), p.imag_sign);
+                        store_pair_mixed(p.out, oa, ob, n + MS, c2{sub2(a1.re, a3.im), add2(a1.im, a3.re)}, ph0,
+                                         __ldg(nco.nco_rot + 4 * i + MS / 32), p.imag_sign);
+                        store_pair_mixed(p.out, oa, ob, n + 2 * MS, csub(a0, a2), ph0, __ldg(nco.nco_rot + 4 * i + 2 * (MS / 32)), p.imag_sign);
+                    } else {
+                        store_pair(p.out, oa, ob, n, cadd(a0, a2), sgn);
+                        store_pair(p.out, oa, ob, n + MS, c2{sub2(a1.re, a3.im), add2(a1.im, a3.re)}, sgn);      // a1 + i a3
+                        store_pair(p.out, oa, ob, n + 2 * MS, csub(a0, a2), sgn);
+                    }
                 }
             }
         } else {
@@ -364,10 +385,15 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_pair_kernel
                 c2 u[R];
                 rscheme_pass2<R>(y, u, P, 0, tabx + R * 32, lane);
                 const int k2p = lane / G, h = lane % G;
+                c2 ph0;
+                if constexpr (kMix == 2) ph0 = direct_phasors(nco.nco_phase0, nco.nco_fc, oa.base + k2p + R * h, ob.base + k2p + R * h);
 #pragma unroll
                 for (int qq = 0; qq < R; qq++) {
                     const int idx = k2p + R * h + 32 * qq;
-                    if (idx < 3 * M / 4) store_pair(p.out, oa, ob, idx, u[qq], sgn);
+                    if (idx < 3 * M / 4) {
+                        if constexpr (kMix == 2) store_pair_mixed(p.out, oa, ob, idx, u[qq], ph0, __ldg(nco.nco_rot + qq), p.imag_sign);
+                        else store_pair(p.out, oa, ob, idx, u[qq], sgn);
+                    }
                 }
             }
         }
@@ -376,15 +402,15 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_pair_kernel
     }
 }
 
-template <int D>
+template <int D, int kMix>
 static cudaError_t setup_wp() {
-    cudaError_t e = cudaFuncSetAttribute(r2iq_wide_pair_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, wide_smem_bytes<D>());
+    cudaError_t e = cudaFuncSetAttribute(r2iq_wide_pair_kernel<D, kMix>, cudaFuncAttributeMaxDynamicSharedMemorySize, wide_smem_bytes<D>());
     if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(r2iq_wide_pair_kernel<D>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    return cudaFuncSetAttribute(r2iq_wide_pair_kernel<D, kMix>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
 }
 
-template <int D>
-static cudaError_t launch_wp(const WideParams& p, int sm_count, cudaStream_t stream) {
+template <int D, int kMix>
+static cudaError_t launch_wp(const WideParams& p, const WideNco& nco, int sm_count, cudaStream_t stream) {
     const long long n_pairs = (p.total_frames + 1) / 2;
     long long grid = sm_count;                        // persistent: one CTA per SM
     const long long want = (n_pairs + kTeams - 1) / kTeams;
@@ -392,16 +418,43 @@ static cudaError_t launch_wp(const WideParams& p, int sm_count, cudaStream_t str
     if (grid < 1) grid = 1;
     cudaError_t e = cudaMemsetAsync(p.work_counter, 0, sizeof(unsigned long long), stream);
     if (e != cudaSuccess) return e;
-    r2iq_wide_pair_kernel<D><<<(unsigned)grid, kTeams * kTeamThreads, wide_smem_bytes<D>(), stream>>>(p);
+    r2iq_wide_pair_kernel<D, kMix><<<(unsigned)grid, kTeams * kTeamThreads, wide_smem_bytes<D>(), stream>>>(p, nco);
     return cudaGetLastError();
 }
 
+// One translation unit (one device module) per decimation and mixer form: their
+// placement is then independent of their siblings (loop bodies of 45..60 KB against a 32 KB instruction cache shared by
+// three free-running teams; measured round 2: placement inside a module, 0..20 KB of padding, changes nothing), and the
+// fourteen kernels compile in parallel.  r2iq_wide_pair_d<D>[m].cu define R2IQ_WIDE_TU_D (and R2IQ_WIDE_TU_MIX) and
+// include this file; compiled on its own, this file holds the dispatchers only.
+#ifdef R2IQ_WIDE_TU_D
+#ifdef R2IQ_WIDE_TU_MIX
+#define R2IQ_WIDE_TU_FN(name, d) name##_mix_d##d
+constexpr int kTuMix = 2;
+#else
+#define R2IQ_WIDE_TU_FN(name, d) name##_d##d
+constexpr int kTuMix = 0;
+#endif
+#define R2IQ_WIDE_TU_FN2(name, d) R2IQ_WIDE_TU_FN(name, d)
+cudaError_t R2IQ_WIDE_TU_FN2(setup_wide, R2IQ_WIDE_TU_D)() { return setup_wp<R2IQ_WIDE_TU_D, kTuMix>(); }
+cudaError_t R2IQ_WIDE_TU_FN2(launch_wide, R2IQ_WIDE_TU_D)(const WideParams& p, const WideNco& nco, int sm_count, cudaStream_t stream) {
+    return launch_wp<R2IQ_WIDE_TU_D, kTuMix>(p, nco, sm_count, stream);
+}
+#else
 #define R2IQ_WIDE_FOR_ALL(X) X(0) X(1) X(2) X(3) X(4) X(5) X(6)
+#define X(D)                                                                                  \
+    cudaError_t setup_wide_d##D();                                                            \
+    cudaError_t setup_wide_mix_d##D();                                                        \
+    cudaError_t launch_wide_d##D(const WideParams& p, const WideNco& nco, int sm_count, cudaStream_t stream);     \
+    cudaError_t launch_wide_mix_d##D(const WideParams& p, const WideNco& nco, int sm_count, cudaStream_t stream);
+R2IQ_WIDE_FOR_ALL(X)
+#undef X
 
 cudaError_t setup_wide_kernels() {
     cudaError_t e;
-#define X(D) \
-    if ((e = setup_wp<D>()) != cudaSuccess) return e;
+#define X(D)                                                    \
+    if ((e = setup_wide_d##D()) != cudaSuccess) return e;      \
+    if ((e = setup_wide_mix_d##D()) != cudaSuccess) return e;
     R2IQ_WIDE_FOR_ALL(X)
 #undef X
 #ifdef R2IQ_AB_VARIANTS
@@ -410,22 +463,26 @@ cudaError_t setup_wide_kernels() {
     return cudaSuccess;
 }
 
-cudaError_t launch_wide(int d, const WideParams& p, int sm_count, cudaStream_t stream) {
+cudaError_t launch_wide(int d, const WideParams& p, const WideNco& nco, int sm_count, cudaStream_t stream) {
 #ifdef R2IQ_AB_VARIANTS
-    if (kernel_generation() != 0) return launch_wide_gen1(d, p, sm_count, stream);   // the four-warps-per-frame scalar kernels
+    // the four-warps-per-frame scalar kernels have no mixer epilogue
+    if (kernel_generation() != 0 && !nco.nco_rot) return launch_wide_gen1(d, p, sm_count, stream);
 #endif
+    // direct-phase mixer in the store epilogue when nco_rot is set (the reference-bit mixer is a separate pass)
 #define X(D) \
-    if (d == D) return launch_wp<D>(p, sm_count, stream);
+    if (d == D) return nco.nco_rot ? launch_wide_mix_d##D(p, nco, sm_count, stream) : launch_wide_d##D(p, nco, sm_count, stream);
     R2IQ_WIDE_FOR_ALL(X)
 #undef X
     return cudaErrorInvalidValue;
 }
 
-const char* wide_kernel_name(int d) {
-    static char names[kNDec][48];
+const char* wide_kernel_name(int d, bool direct_mixer) {
+    static char names[2][kNDec][48];
     if (d < 0 || d >= kNDec) return "";
-    if (!names[d][0]) snprintf(names[d], sizeof(names[d]), "r2iq_wide_pair_kernel<%d>", d);
-    return names[d];
+    char* n = names[direct_mixer ? 1 : 0][d];
+    if (!n[0]) snprintf(n, sizeof(names[0][0]), "r2iq_wide_pair_kernel<%d, %d>", d, direct_mixer ? 2 : 0);
+    return n;
 }
+#endif
 
 }  // namespace r2iq

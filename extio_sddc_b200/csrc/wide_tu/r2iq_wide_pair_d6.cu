@@ -1,0 +1,4 @@
+// FFTN 8192 kernel for decimation index 6: a module of its own (see r2iq_wide_pair.cu)
+#define R2IQ_WIDE_TU_D 6
+
+#include "../r2iq_wide_pair.cu"

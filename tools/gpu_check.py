@@ -83,7 +83,12 @@ if __name__ == "__main__":
     ap.add_argument("--no-parity", action="store_true")
     ap.add_argument("--decims", default="0,1,2,3,4,5,6")
     ap.add_argument("--fftn", type=int, default=2048)
+    ap.add_argument("--lib", default=None, help="an experiment build of libr2iq_cuda.so (tools/exp_build.py) instead of the product library")
     a = ap.parse_args()
+    if a.lib:
+        from extio_sddc_b200 import capi
+        capi.LIB_PATH = os.path.abspath(a.lib)
+        print("library:", capi.LIB_PATH)
     DECIMS[:] = [int(v) for v in a.decims.split(",")]
     if not a.no_parity:
         parity()
