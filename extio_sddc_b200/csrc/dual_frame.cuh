@@ -44,11 +44,13 @@ __device__ __forceinline__ void tma_load_1d(uint32_t dst, const void* src, uint3
 }
 
 // first word of frame f = 43*block + k inside [halo | blocks] (hop 1536 samples = 768 words)
+// (frame indices fit 32 bits: the launchers refuse captures of 2^31 frames or more -- 6.5 TB of samples -- so the
+// division by 43 is one multiply-high instead of a 64-bit sequence)
 template <class Params>
 __device__ __forceinline__ const uint32_t* frame_src(const Params& p, long long f) {
-    const long long b = f / kFramesPerBlock;
-    const int k = (int)(f - b * kFramesPerBlock);
-    return p.in_words + b * (kTransferSamples / 2) + k * (kHop / 2);
+    const uint32_t b = (uint32_t)f / (uint32_t)kFramesPerBlock;
+    const uint32_t k = (uint32_t)f - b * (uint32_t)kFramesPerBlock;
+    return p.in_words + (size_t)b * (kTransferSamples / 2) + k * (kHop / 2);
 }
 
 __device__ __forceinline__ int brev5(int v) { return (int)(__brev((unsigned)v) >> 27); }
@@ -99,12 +101,12 @@ struct FrameOut2 {
 template <int D>
 __device__ __forceinline__ FrameOut2 frame_out2(long long f, long long total) {
     constexpr int M = kHalfFft >> D;
-    const long long b = f / kFramesPerBlock;
-    const int k = (int)(f - b * kFramesPerBlock);
+    const uint32_t b = (uint32_t)f / (uint32_t)kFramesPerBlock;
+    const int k = (int)((uint32_t)f - b * (uint32_t)kFramesPerBlock);
     FrameOut2 o;
     o.live = f < total;
     o.lo = k ? 0 : M / 4;
-    o.base = b * (long long)((kTransferSamples / 2) >> D) + (k ? (M / 2 + (k - 1) * (3 * M / 4)) : 0) - o.lo;
+    o.base = (long long)((unsigned long long)b * (unsigned)((kTransferSamples / 2) >> D)) + (k ? (M / 2 + (k - 1) * (3 * M / 4)) : 0) - o.lo;
     return o;
 }
 

@@ -446,8 +446,12 @@ void nco_direct_advance(NcoState& s, size_t n_out) {
 }
 
 // FFTN 8192: static twiddles once per handle, filter gains (and small-transform twiddles) per (d, tune bin).
+// The kernels index frames with 32 bits (dual_frame.cuh: frame_src): 2^31 frames is 6.5 TB of samples at FFTN 2048.
+constexpr long kMaxBlocksPerLaunch = 0x7fffffffL / 43 - 1;
+
 int launch_wide_impl(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d_out, cudaStream_t stream, int tunebin,
                      bool direct_mixer = false) {
+    if (n_blocks > kMaxBlocksPerLaunch) return fail(R2IQ_E_INVALID, "%ld blocks in one launch (at most %ld)", n_blocks, kMaxBlocksPerLaunch);
     const int d = h->latched_decimate;
     const int HF = 4096, M = HF >> d;
     if (!h->d_twq) {
@@ -556,6 +560,7 @@ int launch_wide_impl(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d
 
 // Parameter block of one single-channel launch at `tunebin` (tables from the per-(d, tune bin) cache), mixer off.
 int fused_params(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d_out, int tunebin, FusedParams* out) {
+    if (n_blocks > kMaxBlocksPerLaunch) return fail(R2IQ_E_INVALID, "%ld blocks in one launch (at most %ld)", n_blocks, kMaxBlocksPerLaunch);
     TableSet ts;
     const int d = h->latched_decimate;
     int rc = get_tables(h, d, tunebin, &ts);
@@ -625,6 +630,7 @@ int launch(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d_out, cuda
 // Channelizer launch: per-d filter table in inverse-FFT bin order + the tune-bin list on the device.
 int launch_channels_impl(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, const int* tunebins, int n_channels,
                          float* d_out, cudaStream_t stream) {
+    if (n_blocks > kMaxBlocksPerLaunch) return fail(R2IQ_E_INVALID, "%ld blocks in one launch (at most %ld)", n_blocks, kMaxBlocksPerLaunch);
     const int d = h->latched_decimate;
     const int half = h->half;
     for (int c = 0; c < n_channels; c++)

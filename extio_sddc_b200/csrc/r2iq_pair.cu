@@ -175,7 +175,7 @@ __device__ __forceinline__ void pair_body(const P& p, const N& nco) {
         const long long qnn = (long long)__shfl_sync(0xffffffffu, pend, 0);
         if (lane == 0) pend = atomicAdd(p.work_counter, 1ULL);
         // word offset of frame B inside the pair buffer: 768, or 512 when A is the last frame of a block
-        const int offB = ((2 * q) % kFramesPerBlock == kFramesPerBlock - 1) ? kHalfFft / 2 : kHop / 2;
+        const int offB = ((uint32_t)(2 * q) % (uint32_t)kFramesPerBlock == kFramesPerBlock - 1) ? kHalfFft / 2 : kHop / 2;
         const uint32_t* inB = inA + offB;
         c2 v[32];
         mbar_wait(mbar, phase);
@@ -258,20 +258,23 @@ __device__ __forceinline__ void pair_body(const P& p, const N& nco) {
             const FrameOut2 ob = frame_out2<0>(2 * q + 1, p.total_frames);
             c2 ph0;
             if constexpr (kMix == 2) ph0 = direct_phasors(nco.nco_phase0, nco.nco_fc, oa.base + lane, ob.base + lane);
+            // lo is 0 or 256 = eight whole rows: every store's predicate is warp-uniform and computed once
+            const bool headA = oa.lo == 0, liveB = ob.live, headB = liveB && ob.lo == 0;
+            float2* const outA = p.out + (oa.base + lane);
+            float2* const outB = p.out + (ob.base + lane);
 #pragma unroll
             for (int k1 = 0; k1 < 24; k1++) {     // idx >= 768 is always discarded
-                const int idx = lane + 32 * k1;
                 if constexpr (kMix == 2) t[k1] = direct_mix(t[k1], ph0, __ldg(nco.nco_rot + k1), p.imag_sign);
                 float ar, br, ai, bi;
                 upk(t[k1].re, ar, br);
                 upk(t[k1].im, ai, bi);
-                if (idx >= oa.lo) {
+                if (k1 >= 8 || headA) {
                     float2 va = kMix == 2 ? make_float2(ar, ai) : make_float2(ar, flip(ai, sgn));
-                    p.out[oa.base + idx] = va;
+                    outA[32 * k1] = va;
                 }
-                if (ob.live && idx >= ob.lo) {
+                if (k1 >= 8 ? liveB : headB) {
                     float2 vb = kMix == 2 ? make_float2(br, bi) : make_float2(br, flip(bi, sgn));
-                    p.out[ob.base + idx] = vb;
+                    outB[32 * k1] = vb;
                 }
             }
         } else if constexpr (D == 6) {
@@ -394,20 +397,28 @@ __device__ __forceinline__ void pair_body(const P& p, const N& nco) {
             const int idx0 = k2p + R * h;
             c2 ph0;
             if constexpr (kMix == 2) ph0 = direct_phasors(nco.nco_phase0, nco.nco_fc, oa.base + idx0, ob.base + idx0);
+            // d <= 3: mfft/4 and 3 mfft/4 are whole rows of 32 samples -- the kept range is a compile-time set of rows
+            // and lo a warp-uniform choice; d = 4, 5: per-lane comparisons
+            constexpr bool kRows = M / 4 >= 32;
+            const bool headA = oa.lo == 0, liveB = ob.live, headB = liveB && ob.lo == 0;
+            float2* const outA = p.out + (oa.base + idx0);
+            float2* const outB = p.out + (ob.base + idx0);
 #pragma unroll
-            for (int q4 = 0; q4 < R; q4++) {
+            for (int q4 = 0; q4 < (kRows ? 3 * R / 4 : R); q4++) {
                 const int idx = idx0 + 32 * q4;
                 if constexpr (kMix == 2) t[q4] = direct_mix(t[q4], ph0, __ldg(nco.nco_rot + q4), p.imag_sign);
                 float ar, br, ai, bi;
                 upk(t[q4].re, ar, br);
                 upk(t[q4].im, ai, bi);
-                if (idx >= oa.lo && idx < 3 * M / 4) {
+                const bool keepA = kRows ? (q4 >= R / 4 || headA) : (idx >= oa.lo && idx < 3 * M / 4);
+                const bool keepB = kRows ? (q4 >= R / 4 ? liveB : headB) : (liveB && idx >= ob.lo && idx < 3 * M / 4);
+                if (keepA) {
                     float2 va = kMix == 2 ? make_float2(ar, ai) : make_float2(ar, flip(ai, sgn));
-                    p.out[oa.base + idx] = va;
+                    outA[32 * q4] = va;
                 }
-                if (ob.live && idx >= ob.lo && idx < 3 * M / 4) {
+                if (keepB) {
                     float2 vb = kMix == 2 ? make_float2(br, bi) : make_float2(br, flip(bi, sgn));
-                    p.out[ob.base + idx] = vb;
+                    outB[32 * q4] = vb;
                 }
             }
         }

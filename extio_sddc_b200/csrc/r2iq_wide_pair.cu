@@ -106,12 +106,12 @@ __device__ __forceinline__ int mirror_slot(int r, int mm) { return r == 0 ? ((10
 template <int D>
 __device__ __forceinline__ FrameOut2 wide_frame_out(long long f, long long total) {
     constexpr int M = kWHalf >> D;
-    const long long b = f / kWFrames;
-    const int k = (int)(f - b * kWFrames);
+    const uint32_t b = (uint32_t)f / (uint32_t)kWFrames;      // frame indices fit 32 bits (dual_frame.cuh: frame_src)
+    const int k = (int)((uint32_t)f - b * (uint32_t)kWFrames);
     FrameOut2 o;
     o.live = f < total;
     o.lo = k ? 0 : M / 4;
-    o.base = b * (long long)((kTransferSamples / 2) >> D) + (k ? (M / 2 + (k - 1) * (3 * M / 4)) : 0) - o.lo;
+    o.base = (long long)((unsigned long long)b * (unsigned)((kTransferSamples / 2) >> D)) + (k ? (M / 2 + (k - 1) * (3 * M / 4)) : 0) - o.lo;
     return o;
 }
 
@@ -135,15 +135,37 @@ __device__ __forceinline__ void store_pair_mixed(float2* out, const FrameOut2& o
     if (ob.live && idx >= ob.lo) out[ob.base + idx] = make_float2(br, bi);
 }
 
+// Phase E stores: sample n + MS a with n < MS and lo in {0, MS} -- the a = 0 third is kept iff lo == 0 (frames other
+// than the first of a block), the other two always: warp-uniform predicates, computed once per pair
+struct KeepPair {
+    bool a, b;
+};
+__device__ __forceinline__ void store_pair_rows(float2* outA, float2* outB, KeepPair keep, int idx, c2 v, uint32_t sgn) {
+    float ar, br, ai, bi;
+    upk(v.re, ar, br);
+    upk(v.im, ai, bi);
+    if (keep.a) outA[idx] = make_float2(ar, flip(ai, sgn));
+    if (keep.b) outB[idx] = make_float2(br, flip(bi, sgn));
+}
+__device__ __forceinline__ void store_pair_rows_mixed(float2* outA, float2* outB, KeepPair keep, int idx, c2 v, c2 ph0, float2 rot,
+                                                      float imag_sign) {
+    v = direct_mix(v, ph0, rot, imag_sign);
+    float ar, br, ai, bi;
+    upk(v.re, ar, br);
+    upk(v.im, ai, bi);
+    if (keep.a) outA[idx] = make_float2(ar, ai);
+    if (keep.b) outB[idx] = make_float2(br, bi);
+}
+
 // Input words of one half of a frame pair: thread tt's points n = tt + 128 (j0 + jj), jj < 4, of the four quarters.
 struct HalfWords {
     uint32_t a[4][4], b[4][4];   // [jj][quarter], frame A / frame B
 };
 __device__ __forceinline__ void load_half(const WideParams& p, long long pair, int tt, int j0, HalfWords& w) {
     const long long fa = 2 * pair;
-    const long long blk = fa / kWFrames;
-    const int kf = (int)(fa - blk * kWFrames);
-    const uint32_t* srcA = p.in_words + blk * (kTransferSamples / 2) + kf * kWHopWords + tt + 128 * j0;
+    const uint32_t blk = (uint32_t)fa / (uint32_t)kWFrames;
+    const int kf = (int)((uint32_t)fa - blk * (uint32_t)kWFrames);
+    const uint32_t* srcA = p.in_words + (size_t)blk * (kTransferSamples / 2) + kf * kWHopWords + tt + 128 * j0;
     // frame B starts one hop later (2048 words later across a block edge); the phantom B of an odd total reads A
     const int offB = fa + 1 >= p.total_frames ? 0 : (kf == kWFrames - 1 ? kWHalf / 2 : kWHopWords);
     const uint32_t* srcB = srcA + offB;
@@ -344,6 +366,9 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_pair_kernel
             constexpr int MS = M / 4;
             c2 ph0;
             if constexpr (kMix == 2) ph0 = direct_phasors(nco.nco_phase0, nco.nco_fc, oa.base + tt, ob.base + tt);
+            const KeepPair head{oa.lo == 0, ob.live && ob.lo == 0}, rest{true, ob.live};
+            float2* const outA = p.out + oa.base;
+            float2* const outB = p.out + ob.base;
 #pragma unroll
             for (int i = 0; i < (MS + kTeamThreads - 1) / kTeamThreads; i++) {
                 const int n = tt + kTeamThreads * i;
@@ -352,14 +377,15 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_pair_kernel
                     const c2 a0 = cadd(s0, s2), a1 = csub(s0, s2), a2 = cadd(s1, s3), a3 = csub(s1, s3);
                     if constexpr (kMix == 2) {
                         // sample n + MS a is 32 (4 i + (MS / 32) a) samples after sample tt: entries of nco_rot (< 96)
-                        store_pair_mixed(p.out, oa, ob, n, cadd(a0, a2), ph0, __ldg(nco.nco_rot + 4 * i), p.imag_sign);
-                        store_pair_mixed(p.out, oa, ob, n + MS, c2{sub2(a1.re, a3.im), add2(a1.im, a3.re)}, ph0,
-                                         __ldg(nco.nco_rot + 4 * i + MS / 32), p.imag_sign);
-                        store_pair_mixed(p.out, oa, ob, n + 2 * MS, csub(a0, a2), ph0, __ldg(nco.nco_rot + 4 * i + 2 * (MS / 32)), p.imag_sign);
+                        store_pair_rows_mixed(outA, outB, head, n, cadd(a0, a2), ph0, __ldg(nco.nco_rot + 4 * i), p.imag_sign);
+                        store_pair_rows_mixed(outA, outB, rest, n + MS, c2{sub2(a1.re, a3.im), add2(a1.im, a3.re)}, ph0,
+                                              __ldg(nco.nco_rot + 4 * i + MS / 32), p.imag_sign);
+                        store_pair_rows_mixed(outA, outB, rest, n + 2 * MS, csub(a0, a2), ph0, __ldg(nco.nco_rot + 4 * i + 2 * (MS / 32)),
+                                              p.imag_sign);
                     } else {
-                        store_pair(p.out, oa, ob, n, cadd(a0, a2), sgn);
-                        store_pair(p.out, oa, ob, n + MS, c2{sub2(a1.re, a3.im), add2(a1.im, a3.re)}, sgn);      // a1 + i a3
-                        store_pair(p.out, oa, ob, n + 2 * MS, csub(a0, a2), sgn);
+                        store_pair_rows(outA, outB, head, n, cadd(a0, a2), sgn);
+                        store_pair_rows(outA, outB, rest, n + MS, c2{sub2(a1.re, a3.im), add2(a1.im, a3.re)}, sgn);      // a1 + i a3
+                        store_pair_rows(outA, outB, rest, n + 2 * MS, csub(a0, a2), sgn);
                     }
                 }
             }
