@@ -174,6 +174,32 @@ __device__ __forceinline__ void dit2(c2 (&v)[N]) {
     }
 }
 
+// dit2 on inputs that still lack their per-register twiddles: v[i] stands for v[i] * w(i), w(0) = 1.  The twiddles
+// are folded into the first stage (its butterflies are the trivial a +- b):  a' = w_a a + w_b b  (4 + 4 packed
+// instructions; 4 when w_a = 1),  b' = 2 w_a a - a'  (2)  -- 10 per butterfly instead of 4 + 4 for the two products
+// and 4 for the sums: a 32-point pass with its inter-pass twiddles costs 480 instead of 512 packed instructions.
+// `w(i)` is any callable returning the float2 twiddle of register i (a table load, shared by both frames).
+// kFirstOne = false: w(0) is a real twiddle too (the rotated backward transform of d = 0: 4 more instructions).
+template <int N, bool INV, bool kFirstOne = true, class Tw>
+__device__ __forceinline__ void dit2_tw(c2 (&v)[N], Tw w) {
+    static_assert(N >= 4, "first stage folded into a radix-2 pass of at least two stages");
+#pragma unroll
+    for (int i = 0; i < N / 2; i++) {
+        c2& a = v[2 * i];
+        c2& b = v[2 * i + 1];
+        c2 ta = a;
+        if (i || !kFirstOne) ta = cmul2s(a, w(2 * i));
+        const float2 wb = w(2 * i + 1);
+        const u64 ax = fma2(bc(wb.x), b.re, fma2(bc(-wb.y), b.im, ta.re));
+        const u64 ay = fma2(bc(wb.x), b.im, fma2(bc(wb.y), b.re, ta.im));
+        b.re = fma2(bc(2.0f), ta.re, neg2(ax));
+        b.im = fma2(bc(2.0f), ta.im, neg2(ay));
+        a.re = ax;
+        a.im = ay;
+    }
+    dit2<N, INV, 4>(v);
+}
+
 // dit2 whose first stage (the trivial a +- b butterflies) is written as fma(+-one, b, a) with a run-time packed 1.0:
 // the same bits as the additions (1.0 * b is exact) on the same pipe, but every value of the pass now depends on
 // `one`.  The FMA-token kernels (r2iq_tok.cu) load `one` from shared memory right after they acquire the token, which

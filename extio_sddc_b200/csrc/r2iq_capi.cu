@@ -224,7 +224,9 @@ struct DeviceGuard {
 
 // Twiddles of the R = M/32 register scheme for an M-point backward transform on 32 lanes (r2iq_dual_dn.cu,
 // r2iq_wide.cu): [R][32] exp(+2 pi i lane k2 / M), then [32][32] exp(+2 pi i (lane % G) n1 / 32), G = 32/R.
-std::vector<float2> build_tw_aux(int M) {
+// folded: the pass-2 weights carry the inter-pass twiddle exp(+2 pi i n1 (lane / G) / M) of the element they multiply
+// (row n1, column lane / G of the transposition), so the kernels skip the twiddle multiplication before it
+std::vector<float2> build_tw_aux(int M, bool folded = false) {
     const int R = M / 32, G = 32 / R;
     std::vector<float2> ta((size_t)(R + 32) * 32);
     for (int k2 = 0; k2 < R; k2++)
@@ -234,7 +236,8 @@ std::vector<float2> build_tw_aux(int M) {
         }
     for (int n1 = 0; n1 < 32; n1++)
         for (int l = 0; l < 32; l++) {
-            const double th = 2.0 * kPiD * (double)(((l % G) * n1) % 32) / 32.0;
+            double th = 2.0 * kPiD * (double)(((l % G) * n1) % 32) / 32.0;
+            if (folded) th += 2.0 * kPiD * (double)((n1 * (l / G)) % M) / (double)M;
             ta[(R + n1) * 32 + l] = make_float2((float)cos(th), (float)sin(th));
         }
     return ta;
@@ -307,7 +310,19 @@ int get_tables(r2iq_cuda_t h, int d, int tunebin, TableSet* out) {
         }
     }
     std::vector<float2> tw(32 * 32);
-    if (d == 0) {
+    const bool pair_tables = kernel_generation() == 0;   // the shipped kernels (r2iq_pair.cu); comparison builds keep the older forms
+    if (d == 0 && pair_tables) {
+        // The twiddles are applied on the READING side of the backward transposition (dit2_tw): lane k2 reads row n, which
+        // the lane l = (n + tunebin) mod 32 wrote -- the lane that plays residue n1' = (l - tunebin) mod 1024.
+        for (int n = 0; n < 32; n++)
+            for (int k2 = 0; k2 < 32; k2++) {
+                const int l = (n + tunebin) & 31;
+                const long long n1 = ((l - tunebin) % kHalfFft + kHalfFft) % kHalfFft;
+                const long long e = (n1 * k2) % kHalfFft;
+                const double th = 2.0 * kPiD * (double)e / (double)kHalfFft;
+                tw[n * 32 + k2] = make_float2((float)cos(th), (float)sin(th));
+            }
+    } else if (d == 0) {
         // lane l plays residue n1' = (l - tunebin) mod 1024: twiddle exp(+2 pi i n1' k2 / 1024)
         for (int k2 = 0; k2 < 32; k2++)
             for (int l = 0; l < 32; l++) {
@@ -327,7 +342,7 @@ int get_tables(r2iq_cuda_t h, int d, int tunebin, TableSet* out) {
     if (d >= 1 && d <= 5) {
         // dual-frame kernels, backward transform mfft = 32*R on 32 lanes: pass-1 twiddles exp(+2 pi i lane k2 / mfft)
         // (k2 < R), then the pass-2 weights exp(+2 pi i (lane % G) n1 / 32), G = 32/R
-        const std::vector<float2> ta = build_tw_aux(M);
+        const std::vector<float2> ta = build_tw_aux(M, pair_tables);
         CU(h, cudaMalloc(&ts.tw_aux, sizeof(float2) * ta.size()));
         CU(h, cudaMemcpy(ts.tw_aux, ta.data(), sizeof(float2) * ta.size(), cudaMemcpyHostToDevice));
     }

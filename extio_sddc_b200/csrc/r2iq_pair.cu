@@ -100,10 +100,10 @@ struct PairNco {
     double nco_fc;
 };
 
-// P: the parameter block (FusedParams or PairParams), N: where the direct-phase mixer's fields live (the same
+// Params: the parameter block (FusedParams or PairParams), NcoParams: where the direct-phase mixer's fields live (the same
 // FusedParams object, or a PairNco)
-template <int D, int W, int kMix, class P, class N>
-__device__ __forceinline__ void pair_body(const P& p, const N& nco) {
+template <int D, int W, int kMix, class Params, class NcoParams>
+__device__ __forceinline__ void pair_body(const Params& p, const NcoParams& nco) {
     constexpr bool kLandInTile = W == 12;
     constexpr int M = kHalfFft >> D;
     constexpr int R = D == 6 ? 1 : 32 >> D;   // band bins per lane (d = 1..5; d = 6: one bin on each of 16 lanes)
@@ -192,14 +192,12 @@ __device__ __forceinline__ void pair_body(const P& p, const N& nco) {
         // a two-trip loop takes 6 KB off a 33..55 KB loop body that shares a 32 KB instruction cache, and costs
         // 7..46 % of the throughput -- loop-carried register moves, a weaker static schedule; measured, round 2)
         dit2<32, false>(v);
-        if constexpr (D == 0) {
-#pragma unroll
-            for (int k2 = 0; k2 < 32; k2 += 2) {
-                const float4 w = *reinterpret_cast<const float4*>(twf + k2);
-                if (k2) v[k2] = cmul2s(v[k2], make_float2(w.x, w.y));
-                v[k2 + 1] = cmul2s(v[k2 + 1], make_float2(w.z, w.w));
-            }
-        } else {
+        // The inter-pass twiddles W_1024^(n1 lane) ride in the first stage of the second pass (dit2_tw, 32 packed
+        // instructions fewer; the table is symmetric in (n1, k2), so the reader's lane takes the entry the writer's would
+        // have).  Measured per decimation: +1.8 / +3.5 / +0.7 / +0.3 / -0.7 / -0.5 / +1.7 % at d = 0..6 -- d = 4, 5 keep
+        // the multiplication on the writing side.
+        constexpr bool kFoldTw = D != 4 && D != 5;
+        if constexpr (!kFoldTw) {
 #pragma unroll
             for (int k2 = 1; k2 < 32; k2++) v[k2] = cmul2s(v[k2], twf[32 * k2]);
         }
@@ -209,7 +207,19 @@ __device__ __forceinline__ void pair_body(const P& p, const N& nco) {
 #pragma unroll
         for (int n1 = 0; n1 < 32; n1++) v[brev5(n1)] = lds2(S, n1 * 33 + lane);
         __syncwarp();
-        dit2<32, false>(v);                       // v[k1] = Z[32*k1 + lane]
+        if constexpr (kFoldTw) {
+            dit2_tw<32, false>(v, [&](int i) {
+                const int n1 = brev5(i);
+                if constexpr (D == 0) {
+                    const float4 w = *reinterpret_cast<const float4*>(twf + (n1 & ~1));
+                    return (n1 & 1) ? make_float2(w.z, w.w) : make_float2(w.x, w.y);
+                } else {
+                    return twf[32 * n1];
+                }
+            });
+        } else {
+            dit2<32, false>(v);
+        }                                         // v[k1] = Z[32*k1 + lane]
 
         if constexpr (D == 0) {
             // ---- real-FFT split + tune rotation + filter, in place ---------------------------------------
@@ -240,18 +250,18 @@ __device__ __forceinline__ void pair_body(const P& p, const N& nco) {
             // ---- backward 1024-point transform; lane l is residue (l - tunebin) mod 32 ---------------
             dit2<32, true>(t);
 #pragma unroll
-            for (int k2 = 0; k2 < 32; k2 += 2) {
-                const float4 w = *reinterpret_cast<const float4*>(twi + k2);
-                if (k2) t[k2] = cmul2s(t[k2], make_float2(w.x, w.y));
-                t[k2 + 1] = cmul2s(t[k2 + 1], make_float2(w.z, w.w));
-            }
-#pragma unroll
             for (int k2 = 0; k2 < 32; k2++) sts2(S, n1_inv * 33 + k2, t[k2]);
             __syncwarp();
 #pragma unroll
             for (int n = 0; n < 32; n++) t[brev5(n)] = lds2(S, n * 33 + lane);
             __syncwarp();
-            dit2<32, true>(t);                        // t[k1] = y[lane + 32*k1] for both frames
+            // inter-pass twiddles on the reading side, folded into the first stage (tw_inv is laid out for that: row n
+            // holds the twiddle of the element the lane reads from row n)
+            dit2_tw<32, true, false>(t, [&](int i) {   // row 0's twiddle is 1 only when the tune bin is below 32
+                const int n = brev5(i);
+                const float4 w = *reinterpret_cast<const float4*>(twi + (n & ~1));
+                return (n & 1) ? make_float2(w.z, w.w) : make_float2(w.x, w.y);
+            });                                       // t[k1] = y[lane + 32*k1] for both frames
 
             // ---- overlap-save discard + placement (impl.hpp:117-138) --------------------------------
             const FrameOut2 oa = frame_out2<0>(2 * q, p.total_frames);
@@ -332,8 +342,7 @@ __device__ __forceinline__ void pair_body(const P& p, const N& nco) {
                 }
             }
         } else {
-            const float2* twi = tab + 1024 + lane;            // [R][32]  exp(+2 pi i lane k2 / M)
-            const float2* tw2 = tab + 1024 + R * 32 + lane;   // [32][32] exp(+2 pi i (lane % G) n1 / 32)
+            const float2* tw2 = tab + 1024 + R * 32 + lane;   // [32][32] exp(+2 pi i ((lane % G) n1 / 32 + n1 (lane / G) / M))
             // ---- spectrum to shared memory in natural order; only the rows the band cut will read -------
 #pragma unroll
             for (int k1 = 0; k1 < 32; k1++)
@@ -365,9 +374,7 @@ __device__ __forceinline__ void pair_body(const P& p, const N& nco) {
                 }
             }
             // ---- backward mfft-point transform: n = lane + 32*n2, k = k2 + R*k1 ------------------------
-            dit2<R, true>(y);                         // pass 1 over n2
-#pragma unroll
-            for (int k2 = 1; k2 < R; k2++) y[k2] = cmul2s(y[k2], twi[32 * k2]);   // exp(+2 pi i lane k2 / M)
+            dit2<R, true>(y);                         // pass 1 over n2; its twiddles exp(+2 pi i lane k2 / M) are part of tw2
 #pragma unroll
             for (int k2 = 0; k2 < R; k2++) sts2r<R>(S, lane * (R + 1) + k2, y[k2]);
             __syncwarp();
