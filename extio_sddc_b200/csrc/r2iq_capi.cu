@@ -531,17 +531,20 @@ int launch_wide_impl(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d
         if (d == 0) {
             // lane l of the backward 1024-point transforms plays residue (l - tunebin/4) mod 32 (r2iq_wide_pair.cu, D1)
             std::vector<float2> ti(1024);
+            const bool reader_side = kernel_generation() == 0;   // the packed kernels apply them after the transposition
             for (int k2 = 0; k2 < 32; k2++)
                 for (int l = 0; l < 32; l++) {
                     const long long n1 = ((l - tunebin / 4) % 1024 + 1024) % 1024;
                     const double th = 2.0 * kPiD * (double)((n1 * k2) % 1024) / 1024.0;
-                    ti[k2 * 32 + l] = make_float2((float)cos(th), (float)sin(th));
+                    // writer lane l stores row (l - tunebin/4) mod 32; reader lane k2 finds it there
+                    if (reader_side) ti[(int)(n1 & 31) * 32 + k2] = make_float2((float)cos(th), (float)sin(th));
+                    else ti[k2 * 32 + l] = make_float2((float)cos(th), (float)sin(th));
                 }
             CU(h, cudaMalloc(&ws.tw_inv, sizeof(float2) * ti.size()));
             CU(h, cudaMemcpy(ws.tw_inv, ti.data(), sizeof(float2) * ti.size(), cudaMemcpyHostToDevice));
         }
         if (d >= 1) {
-            const std::vector<float2> ta = build_tw_aux(d == 6 ? M : M / 4);
+            const std::vector<float2> ta = build_tw_aux(d == 6 ? M : M / 4, kernel_generation() == 0);
             CU(h, cudaMalloc(&ws.tw_sub, sizeof(float2) * ta.size()));
             CU(h, cudaMemcpy(ws.tw_sub, ta.data(), sizeof(float2) * ta.size(), cudaMemcpyHostToDevice));
         }

@@ -283,14 +283,13 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_pair_kernel
             __syncwarp();
             dit2<32, false>(v);
 #pragma unroll
-            for (int k2 = 1; k2 < 32; k2++) v[k2] = cmul2s(v[k2], tw1024[32 * k2 + lane]);
-#pragma unroll
             for (int k2 = 0; k2 < 32; k2++) pst(P, wbase + lane * 33 + k2, v[k2]);
             __syncwarp();
 #pragma unroll
             for (int n1 = 0; n1 < 32; n1++) v[brev5(n1)] = pld(P, wbase + n1 * 33 + lane);
             __syncwarp();
-            dit2<32, false>(v);
+            // inter-pass twiddles W_1024^(n1 lane) folded into the first stage of the second pass (dft_regs2.cuh)
+            dit2_tw<32, false>(v, [&](int i) { return tw1024[32 * brev5(i) + lane]; });
 #pragma unroll
             for (int k1 = 0; k1 < 32; k1++)                                         // bin 4 (lane + 32 k1) + warp
                 if (D == 0 || ((row_mask >> k1) & 1u)) pst(P, wbase + lane + 32 * k1, v[k1]);
@@ -311,8 +310,6 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_pair_kernel
                 t[brev5(k1)] = split_pq(a, b, __ldg(pq + mm));
             }
             dit2<32, true>(t);
-#pragma unroll
-            for (int k2 = 1; k2 < 32; k2++) t[k2] = cmul2s(t[k2], tabx[32 * k2 + lane]);   // residue (lane - tb4) mod 32
             team_barrier(team);                       // every mirror read of the team is done: the planes are free
             // ---------------- D2: transposition, second pass, W_4096^(-warp n), S_warp to the plane ------------
             const int n1_inv = (lane - tb4) & 31;
@@ -322,7 +319,9 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_pair_kernel
 #pragma unroll
             for (int n1 = 0; n1 < 32; n1++) t[brev5(n1)] = pld(P, wbase + n1 * 33 + lane);
             __syncwarp();
-            dit2<32, true>(t);
+            // inter-pass twiddles on the reading side (tw_inv row n = twiddle of the element read from row n, written by the
+            // lane that plays residue n), folded into the first stage
+            dit2_tw<32, true, false>(t, [&](int i) { return tabx[32 * brev5(i) + lane]; });
             if (warp) {
 #pragma unroll
                 for (int k1 = 0; k1 < 32; k1++) t[k1] = cmul_conj2s(t[k1], wpow(twq1, warp, lane + 32 * k1));
@@ -343,9 +342,7 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_pair_kernel
                 const c2 b = pld(P, mbase + mirror_slot(warp, mm));
                 y[brev_n(j, RB)] = split_pq(a, b, __ldg(pq + mm));
             }
-            dit2<R, true>(y);                                         // pass 1 over n2 (m' = lane + 32 n2)
-#pragma unroll
-            for (int k2 = 1; k2 < R; k2++) y[k2] = cmul2s(y[k2], tabx[k2 * 32 + lane]);   // exp(+2 pi i lane k2 / MS)
+            dit2<R, true>(y);                                         // pass 1 over n2 (m' = lane + 32 n2); its twiddles are part of the weights
             team_barrier(team);                       // every band read of the team is done: the planes are free
             c2 u[R];
             rscheme_pass2<R>(y, u, P, wbase, tabx + R * 32, lane);    // u[q] = S_warp[k2p + R h + 32 q]
@@ -406,8 +403,6 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_pair_kernel
                 }
                 __syncwarp();
                 dit2<R, true>(y);
-#pragma unroll
-                for (int k2 = 1; k2 < R; k2++) y[k2] = cmul2s(y[k2], tabx[k2 * 32 + lane]);
                 c2 u[R];
                 rscheme_pass2<R>(y, u, P, 0, tabx + R * 32, lane);
                 const int k2p = lane / G, h = lane % G;
