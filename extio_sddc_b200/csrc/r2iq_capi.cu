@@ -63,6 +63,7 @@ struct TableSet {   // device tables for one (decimation, tune bin)
     float2* gq = nullptr;
     float2* tw_inv = nullptr;
     float2* tw_aux = nullptr;
+    float4* pq_band = nullptr;   // d >= 1, shipped kernels: (P, Q) of band position m (bin tunebin + s(m)), m < mfft
     int band_lo = 0, band_hi = 0;
     uint32_t row_mask = 0xFFFFFFFFu;
 };
@@ -256,6 +257,7 @@ void free_tables(r2iq_cuda_t h) {
         cudaFree(kv.second.gck);
         cudaFree(kv.second.gp);
         cudaFree(kv.second.gq);
+        cudaFree(kv.second.pq_band);
         cudaFree(kv.second.tw_inv);
         cudaFree(kv.second.tw_aux);
     }
@@ -345,6 +347,17 @@ int get_tables(r2iq_cuda_t h, int d, int tunebin, TableSet* out) {
         const std::vector<float2> ta = build_tw_aux(M, pair_tables);
         CU(h, cudaMalloc(&ts.tw_aux, sizeof(float2) * ta.size()));
         CU(h, cudaMemcpy(ts.tw_aux, ta.data(), sizeof(float2) * ta.size(), cudaMemcpyHostToDevice));
+    }
+    if (d >= 1 && pair_tables) {
+        // the band cut reads (P, Q) in the order of the backward transform: position m = lane + 32 j holds bin
+        // tunebin + (m < mfft/2 ? m : m - mfft) -- one coalesced 16-byte load per bin and no index arithmetic
+        std::vector<float4> pqb(M);
+        for (int m = 0; m < M; m++) {
+            const int kk = (tunebin + (m < M / 2 ? m : m - M)) & (kHalfFft - 1);
+            pqb[m] = make_float4(gp[kk].x, gp[kk].y, gq[kk].x, gq[kk].y);
+        }
+        CU(h, cudaMalloc(&ts.pq_band, sizeof(float4) * M));
+        CU(h, cudaMemcpy(ts.pq_band, pqb.data(), sizeof(float4) * M, cudaMemcpyHostToDevice));
     }
     CU(h, cudaMalloc(&ts.gk, sizeof(float2) * kHalfFft));
     CU(h, cudaMalloc(&ts.gck, sizeof(float2) * kHalfFft));
@@ -592,6 +605,10 @@ int fused_params(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d_out
     p.gck = ts.gck;
     p.gp = ts.gp;
     p.gq = ts.gq;
+    if (ts.pq_band) {                     // r2iq_pair.cu, d >= 1: `gp` carries the band-ordered (P, Q) table, `gq` is unused
+        p.gp = reinterpret_cast<const float2*>(ts.pq_band);
+        p.gq = nullptr;
+    }
     p.tw_inv = ts.tw_inv;
     p.tw_aux = ts.tw_aux;
     p.tunebin = tunebin;

@@ -32,8 +32,8 @@ template <int W>
 __host__ __device__ constexpr int pair_warp_bytes() {
     return kTile * 16 + (W == 8 ? kPairBytes : 0) + 16;
 }
-// tables: d = 0: tw_fwd, tw_inv, gp, gq (4 x 8 KB); d >= 1: tw_fwd (8 KB) + tw_aux ((R + 32) x 256 B); gp/gq stay
-// in global memory there (R <= 16 loads per frame pair)
+// tables: d = 0: tw_fwd, tw_inv, gp, gq (4 x 8 KB); d >= 1: tw_fwd (8 KB) + tw_aux ((R + 32) x 256 B); (P, Q) stay in
+// global memory there, as ONE float4 table in band order behind `gp` (R <= 16 coalesced 16-byte loads per frame pair)
 // d = 0 keeps its four tables TRANSPOSED, [lane][34]: rows k and k+1 of a lane are 16 contiguous bytes, one LDS.128
 // (pitch 34 float2 = 272 B keeps the eight lanes of a quarter-warp on distinct bank groups)
 constexpr int kTabPitch = 34;
@@ -301,8 +301,8 @@ __device__ __forceinline__ void pair_body(const Params& p, const NcoParams& nco)
             {
                 const c2 a = lds2(S, kk);
                 const c2 b = lds2(S, (kHalfFft - kk) & (kHalfFft - 1));
-                const float2 P = __ldg(p.gp + kk);
-                const float2 Q = __ldg(p.gq + kk);
+                const float4 pq = __ldg(reinterpret_cast<const float4*>(p.gp) + m);   // (P, Q) in band order
+                const float2 P = make_float2(pq.x, pq.y), Q = make_float2(pq.z, pq.w);
                 r.re = fma2(bc(Q.y), b.im, fma2(bc(Q.x), b.re, fma2(bc(-P.y), a.im, mul2(bc(P.x), a.re))));
                 r.im = fma2(bc(Q.y), b.re, fma2(bc(-Q.x), b.im, fma2(bc(P.y), a.re, mul2(bc(P.x), a.im))));
             }
@@ -357,8 +357,8 @@ __device__ __forceinline__ void pair_body(const Params& p, const NcoParams& nco)
                 const int kk = (p.tunebin + s) & (kHalfFft - 1);         // wrapped bins meet P = Q = 0: zero fill
                 const c2 a = lds2(S, kk);
                 const c2 b = lds2(S, (kHalfFft - kk) & (kHalfFft - 1));
-                const float2 P = __ldg(p.gp + kk);
-                const float2 Q = __ldg(p.gq + kk);
+                const float4 pq = __ldg(reinterpret_cast<const float4*>(p.gp) + m);   // (P, Q) in band order
+                const float2 P = make_float2(pq.x, pq.y), Q = make_float2(pq.z, pq.w);
                 c2 r;
                 r.re = fma2(bc(Q.y), b.im, fma2(bc(Q.x), b.re, fma2(bc(-P.y), a.im, mul2(bc(P.x), a.re))));
                 r.im = fma2(bc(Q.y), b.re, fma2(bc(-Q.x), b.im, fma2(bc(P.y), a.re, mul2(bc(P.x), a.im))));
