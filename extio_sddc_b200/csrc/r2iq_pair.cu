@@ -39,7 +39,7 @@ __host__ __device__ constexpr int pair_warp_bytes() {
 constexpr int kTabPitch = 34;
 template <int D>
 __host__ __device__ constexpr int pair_table_float2() {
-    return D == 0 ? 4 * 32 * kTabPitch : D == 6 ? 1024 + 16 : 1024 + ((32 >> D) + 32) * 32;
+    return D == 0 ? 4 * 32 * kTabPitch : D == 6 ? 32 * kTabPitch + 16 : D == 1 ? 2048 : 2 * 32 * kTabPitch;
 }
 // d = 6: exp(+2 pi i j / 16), the 16-point backward transform's twiddles
 #define R2IQ_W16(j) {(float)cx_cos2pi(j, 16), (float)cx_sin2pi(j, 16)}
@@ -123,6 +123,8 @@ __device__ __forceinline__ void pair_body(const Params& p, const NcoParams& nco)
     const uint32_t dst = smem_u32(inA);
 
     // ---- tables -> shared memory ------------------------------------------------------------------------------
+    constexpr bool kTabT = D != 1;                    // tables transposed ([lane][34]); d = 1: [n][lane]
+    constexpr int kTab2 = kTabT ? 32 * kTabPitch : 1024;
     if constexpr (D == 0) {
         for (int i = threadIdx.x; i < 1024; i += W * 32) {
             const int o = (i & 31) * kTabPitch + (i >> 5);      // [row][lane] -> [lane][row]
@@ -132,11 +134,17 @@ __device__ __forceinline__ void pair_body(const Params& p, const NcoParams& nco)
             tab[96 * kTabPitch + o] = __ldg(p.gq + i);
         }
     } else if constexpr (D == 6) {
-        for (int i = threadIdx.x; i < 1024; i += W * 32) tab[i] = __ldg(p.tw_fwd + i);
-        if (threadIdx.x < 16) tab[1024 + threadIdx.x] = kW16[threadIdx.x];
+        for (int i = threadIdx.x; i < 1024; i += W * 32) tab[(i & 31) * kTabPitch + (i >> 5)] = __ldg(p.tw_fwd + i);
+        if (threadIdx.x < 16) tab[32 * kTabPitch + threadIdx.x] = kW16[threadIdx.x];
     } else {
-        for (int i = threadIdx.x; i < 1024; i += W * 32) tab[i] = __ldg(p.tw_fwd + i);
-        for (int i = threadIdx.x; i < (R + 32) * 32; i += W * 32) tab[1024 + i] = __ldg(p.tw_aux + i);
+        // the forward twiddles and the pass-2 weights ([32][32] behind the R unused rows of tw_aux); transposed like
+        // d = 0 (one LDS.128 per two entries) except at d = 1, where the aligned register quads cost spills
+        // (measured: 656 -> 618 Gsamples/s at d = 1, +1.5 / +3.4 / +0.4 / +0.9 % at d = 2..5)
+        for (int i = threadIdx.x; i < 1024; i += W * 32) {
+            const int o = kTabT ? (i & 31) * kTabPitch + (i >> 5) : i;
+            tab[o] = __ldg(p.tw_fwd + i);
+            tab[kTab2 + o] = __ldg(p.tw_aux + R * 32 + i);
+        }
     }
     if (lane == 0) {
         mbar_init(mbar, 1);
@@ -168,7 +176,15 @@ __device__ __forceinline__ void pair_body(const Params& p, const NcoParams& nco)
     if (lane == 0 && q < n_pairs) issue(q);
     uint32_t phase = 0;
 
-    const float2* twf = tab + (D == 0 ? lane * kTabPitch : lane);
+    const float2* twf = tab + (kTabT ? lane * kTabPitch : lane);
+    auto tw_at = [](const float2* t, int n) {         // entry n of this lane's table
+        if constexpr (kTabT) {
+            const float4 w = *reinterpret_cast<const float4*>(t + (n & ~1));   // one LDS.128 per two entries
+            return (n & 1) ? make_float2(w.z, w.w) : make_float2(w.x, w.y);
+        } else {
+            return t[32 * n];
+        }
+    };
     const uint32_t sgn = __float_as_uint(p.imag_sign) & 0x80000000u;   // sideband inversion as a sign-bit flip
 
     while (q < n_pairs) {
@@ -188,6 +204,8 @@ __device__ __forceinline__ void pair_body(const Params& p, const NcoParams& nco)
         }
 
         // ---- forward 1024-point transform of z = x[2n] + i x[2n+1] ------------------------------
+        // (128-bit stores of two neighbouring elements into a pitch-34 tile -- half the store instructions of the
+        // transposition, no extra moves -- measured at -3.4 ... +0.9 % over the decimations: the tile keeps 64-bit accesses)
         // (both radix-32 passes are straight-line code on purpose: running them through one copy of the butterflies in
         // a two-trip loop takes 6 KB off a 33..55 KB loop body that shares a 32 KB instruction cache, and costs
         // 7..46 % of the throughput -- loop-carried register moves, a weaker static schedule; measured, round 2)
@@ -199,7 +217,7 @@ __device__ __forceinline__ void pair_body(const Params& p, const NcoParams& nco)
         constexpr bool kFoldTw = D != 4 && D != 5;
         if constexpr (!kFoldTw) {
 #pragma unroll
-            for (int k2 = 1; k2 < 32; k2++) v[k2] = cmul2s(v[k2], twf[32 * k2]);
+            for (int k2 = 1; k2 < 32; k2++) v[k2] = cmul2s(v[k2], tw_at(twf, k2));
         }
 #pragma unroll
         for (int k2 = 0; k2 < 32; k2++) sts2(S, lane * 33 + k2, v[k2]);
@@ -209,13 +227,7 @@ __device__ __forceinline__ void pair_body(const Params& p, const NcoParams& nco)
         __syncwarp();
         if constexpr (kFoldTw) {
             dit2_tw<32, false>(v, [&](int i) {
-                const int n1 = brev5(i);
-                if constexpr (D == 0) {
-                    const float4 w = *reinterpret_cast<const float4*>(twf + (n1 & ~1));
-                    return (n1 & 1) ? make_float2(w.z, w.w) : make_float2(w.x, w.y);
-                } else {
-                    return twf[32 * n1];
-                }
+                return tw_at(twf, brev5(i));
             });
         } else {
             dit2<32, false>(v);
@@ -313,7 +325,7 @@ __device__ __forceinline__ void pair_body(const Params& p, const NcoParams& nco)
             }
             if (lane < 16) sts2r<1>(S, lane, r);                        // planes of 64 elements at the head of the tile
             __syncwarp();
-            const float2* w16 = tab + 1024;
+            const float2* w16 = tab + 32 * kTabPitch;
             c2 acc;
             acc.re = acc.im = bc(0.0f);
 #pragma unroll
@@ -342,7 +354,7 @@ __device__ __forceinline__ void pair_body(const Params& p, const NcoParams& nco)
                 }
             }
         } else {
-            const float2* tw2 = tab + 1024 + R * 32 + lane;   // [32][32] exp(+2 pi i ((lane % G) n1 / 32 + n1 (lane / G) / M))
+            const float2* tw2 = tab + kTab2 + (kTabT ? lane * kTabPitch : lane);   // exp(+2 pi i ((lane % G) n1 / 32 + n1 (lane / G) / M))
             // ---- spectrum to shared memory in natural order; only the rows the band cut will read -------
 #pragma unroll
             for (int k1 = 0; k1 < 32; k1++)
@@ -384,7 +396,7 @@ __device__ __forceinline__ void pair_body(const Params& p, const NcoParams& nco)
 #pragma unroll
             for (int n1 = 0; n1 < 32; n1++) {         // u_j = sum_r x[j + R*r] * exp(+2 pi i h (j + R*r) / 32)
                 const c2 x = lds2r<R>(S, n1 * (R + 1) + k2p);
-                const float2 w = tw2[32 * n1];
+                const float2 w = tw_at(tw2, n1);
                 const int j = n1 % R;
                 c2& u = t[brev_n(j, RB)];
                 if (n1 < R) {
