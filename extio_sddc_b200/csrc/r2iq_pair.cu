@@ -165,6 +165,10 @@ __device__ __forceinline__ void pair_body(const Params& p, const NcoParams& nco)
     };
 
     // ---- work: one pair at a time from the device-wide counter, one grab kept in flight ---------------------------
+    // (nvcc compiles atomicAdd into its warp-aggregated form, whose SHFL waits for the atomic's round trip on the spot:
+    // 4.3 % of the d = 0 kernel's stall samples sit on that instruction.  An inline-PTX atom that really stays in flight
+    // changed nothing, 531 vs 532 Gsamples/s -- the other warps of the scheduler cover the wait: the kernels are bound by
+    // issue slots and pipes, not by latency.  Measured round 2, tools/ncu_hot.py.)
     unsigned long long g0 = 0, g1 = 0, pend = 0;
     if (lane == 0) {
         g0 = atomicAdd(p.work_counter, 1ULL);
