@@ -72,6 +72,48 @@ __device__ __forceinline__ c2 lds2r(const u64* S, int idx) {
     return v;
 }
 
+// ---- 32-point inverse DFT across the LANES of a warp (d = 4, 5: mfft = 64, 32) -------------------------------------
+// Decimation in frequency, five butterfly stages at lane distances 16, 8, 4, 2, 1: lane m holds X[m] on entry and
+// x[brev5(lane)] = sum_m X[m] exp(+2 pi i m brev5(lane) / 32) on exit.  Per stage 4 SHFL (both frames' re and im) and 6
+// packed instructions: t = partner + sg * own  (sg = -1 in the upper lane of a pair: a - b there, a + b in the lower),
+// then t * w with w = 1 in the lower lane and exp(+2 pi i (lane mod dist) / (2 dist)) in the upper (last stage: w = 1).
+// ~50 instructions instead of the ~210 of the 32-term multiply-accumulate through shared memory it replaces.
+__device__ __forceinline__ c2 shfl_xor2(c2 v, int dist) {
+    float a, b, c, d;
+    upk(v.re, a, b);
+    upk(v.im, c, d);
+    a = __shfl_xor_sync(0xffffffffu, a, dist);
+    b = __shfl_xor_sync(0xffffffffu, b, dist);
+    c = __shfl_xor_sync(0xffffffffu, c, dist);
+    d = __shfl_xor_sync(0xffffffffu, d, dist);
+    return c2{pk(a, b), pk(c, d)};
+}
+__device__ __forceinline__ c2 warp_idft32(c2 x, const float2 (&w)[4], int lane) {
+#pragma unroll
+    for (int s = 0; s < 5; s++) {
+        const int dist = 16 >> s;
+        const c2 pr = shfl_xor2(x, dist);
+        const u64 sg = bc((lane & dist) ? -1.0f : 1.0f);
+        c2 t;
+        t.re = fma2(sg, x.re, pr.re);
+        t.im = fma2(sg, x.im, pr.im);
+        x = s < 4 ? cmul2s(t, w[s]) : t;
+    }
+    return x;
+}
+// this lane's stage twiddles (entries 0..3) and, for mfft = 32 R > 32, exp(+2 pi i lane e / mfft), e = 1..R-1 (entries 4..)
+__device__ __forceinline__ float2 warp_idft_twiddle(int lane, int e, int mfft) {
+    float sn, cs;
+    if (e >= 4) {
+        sincospif((float)(2 * lane * (e - 3)) / (float)mfft, &sn, &cs);
+        return make_float2(cs, sn);
+    }
+    const int dist = 16 >> e;
+    if (!(lane & dist)) return make_float2(1.0f, 0.0f);
+    sincospif((float)(lane & (dist - 1)) / (float)dist, &sn, &cs);
+    return make_float2(cs, sn);
+}
+
 }  // namespace
 
 // What the kernels really read, as their parameter block: FusedParams (the launchers' common currency, 152 bytes with
@@ -109,6 +151,11 @@ __device__ __forceinline__ void pair_body(const Params& p, const NcoParams& nco)
     constexpr int R = D == 6 ? 1 : 32 >> D;   // band bins per lane (d = 1..5; d = 6: one bin on each of 16 lanes)
     constexpr int G = 32 / R;             // lanes sharing one 32-point DFT in pass 2 of the backward transform
     constexpr int RB = ilog2(R);
+    // backward transform by shuffle butterflies (warp_idft32) for mfft = 64, 32: 1021 -> 1117 and 1048 -> 1152 Gsamples/s at
+    // d = 4, 5; at d = 3 (four transforms, 80 SHFL, stores of 32-byte runs) it loses, 992 -> 963
+    constexpr bool kCrossLane = D == 4 || D == 5;
+    // the conversion's bias removed in the first butterfly stage (dit2_biased): +1.0 ... +1.5 % at d = 1..3; -0.5 % at d = 0
+    constexpr bool kBiased = D != 0;
     static_assert(D == 0 || 2 * 32 * (R + 1) * 8 <= kLandOff, "backward transposition overlaps the landing zone");
     static_assert(D != 0 || !kLandInTile, "d = 0 uses the whole tile until the last pass: W = 8 only");
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -143,7 +190,11 @@ __device__ __forceinline__ void pair_body(const Params& p, const NcoParams& nco)
         for (int i = threadIdx.x; i < 1024; i += W * 32) {
             const int o = kTabT ? (i & 31) * kTabPitch + (i >> 5) : i;
             tab[o] = __ldg(p.tw_fwd + i);
-            tab[kTab2 + o] = __ldg(p.tw_aux + R * 32 + i);
+            if constexpr (!kCrossLane) tab[kTab2 + o] = __ldg(p.tw_aux + R * 32 + i);
+        }
+        if constexpr (kCrossLane) {          // the lane's twiddles of the cross-lane transform instead of the pass-2 weights
+            if (threadIdx.x < 32 * (3 + R))
+                tab[kTab2 + (threadIdx.x & 31) * kTabPitch + (threadIdx.x >> 5)] = warp_idft_twiddle(threadIdx.x & 31, threadIdx.x >> 5, M);
         }
     }
     if (lane == 0) {
@@ -201,7 +252,10 @@ __device__ __forceinline__ void pair_body(const Params& p, const NcoParams& nco)
         mbar_wait(mbar, phase);
         phase ^= 1;
 #pragma unroll
-        for (int j = 0; j < 32; j++) unpack_words(inA[lane + 32 * j], inB[lane + 32 * j], p.rand_mul, v[brev5(j)]);
+        for (int j = 0; j < 32; j++) {
+            if constexpr (kBiased) unpack_words_biased(inA[lane + 32 * j], inB[lane + 32 * j], p.rand_mul, v[brev5(j)]);
+            else unpack_words(inA[lane + 32 * j], inB[lane + 32 * j], p.rand_mul, v[brev5(j)]);
+        }
         __syncwarp();   // every lane has consumed its words: the buffer may be overwritten
         if constexpr (!kLandInTile) {
             if (lane == 0 && qn < n_pairs) issue(qn);
@@ -213,7 +267,8 @@ __device__ __forceinline__ void pair_body(const Params& p, const NcoParams& nco)
         // (both radix-32 passes are straight-line code on purpose: running them through one copy of the butterflies in
         // a two-trip loop takes 6 KB off a 33..55 KB loop body that shares a 32 KB instruction cache, and costs
         // 7..46 % of the throughput -- loop-carried register moves, a weaker static schedule; measured, round 2)
-        dit2<32, false>(v);
+        if constexpr (kBiased) dit2_biased<32, false>(v);   // the conversion's bias leaves in the first butterfly stage
+        else dit2<32, false>(v);
         // The inter-pass twiddles W_1024^(n1 lane) ride in the first stage of the second pass (dit2_tw, 32 packed
         // instructions fewer; the table is symmetric in (n1, k2), so the reader's lane takes the entry the writer's would
         // have).  Measured per decimation: +1.8 / +3.5 / +0.7 / +0.3 / -0.7 / -0.5 / +1.7 % at d = 0..6 -- d = 4, 5 keep
@@ -389,6 +444,37 @@ __device__ __forceinline__ void pair_body(const Params& p, const NcoParams& nco)
                     issue(qn);
                 }
             }
+            if constexpr (kCrossLane) {
+                // ---- d = 3, 4, 5: backward transform across the lanes (warp_idft32), nothing goes through shared memory.
+                // Output sample n = R k + e, band bin m = m' + 32 j:  x[R k + e] = sum_m' [W_M^(m' e) sum_j Y[m' + 32 j] W_R^(j e)]
+                // W_32^(m' k) -- an R-point transform over j in registers, a twiddle, and R 32-point transforms over the
+                // lanes; lane l ends with the R consecutive samples R brev5(l) .. R brev5(l) + R - 1.
+                const float4 w01 = *reinterpret_cast<const float4*>(tw2), w23 = *reinterpret_cast<const float4*>(tw2 + 2);
+                const float2 wsh[4] = {make_float2(w01.x, w01.y), make_float2(w01.z, w01.w), make_float2(w23.x, w23.y),
+                                       make_float2(w23.z, w23.w)};
+                c2 o[R];                                  // o[e] = output sample R * brev5(lane) + e
+                dit2<R, true>(y);                         // y[e] = sum_j Y[lane + 32 j] W_R^(j e)  (y was placed bit-reversed)
+#pragma unroll
+                for (int e = 0; e < R; e++) o[e] = warp_idft32(e ? cmul2s(y[e], tw2[3 + e]) : y[e], wsh, lane);
+                const FrameOut2 oa = frame_out2<D>(2 * q, p.total_frames);
+                const FrameOut2 ob = frame_out2<D>(2 * q + 1, p.total_frames);
+                const int idx0 = R * brev5(lane);
+                const bool keepA = idx0 >= oa.lo && idx0 < 3 * M / 4;       // lo and 3 mfft / 4 are multiples of R
+                const bool keepB = ob.live && idx0 >= ob.lo && idx0 < 3 * M / 4;
+                float2* const outA = p.out + (oa.base + idx0);
+                float2* const outB = p.out + (ob.base + idx0);
+#pragma unroll
+                for (int e = 0; e < R; e++) {
+                    if constexpr (kMix == 2)
+                        o[e] = direct_mix(o[e], direct_phasors(nco.nco_phase0, nco.nco_fc, oa.base + idx0 + e, ob.base + idx0 + e),
+                                          make_float2(1.0f, 0.0f), p.imag_sign);
+                    float ar, br, ai, bi;
+                    upk(o[e].re, ar, br);
+                    upk(o[e].im, ai, bi);
+                    if (keepA) outA[e] = kMix == 2 ? make_float2(ar, ai) : make_float2(ar, flip(ai, sgn));
+                    if (keepB) outB[e] = kMix == 2 ? make_float2(br, bi) : make_float2(br, flip(bi, sgn));
+                }
+            } else {
             // ---- backward mfft-point transform: n = lane + 32*n2, k = k2 + R*k1 ------------------------
             dit2<R, true>(y);                         // pass 1 over n2; its twiddles exp(+2 pi i lane k2 / M) are part of tw2
 #pragma unroll
@@ -444,6 +530,7 @@ __device__ __forceinline__ void pair_body(const Params& p, const NcoParams& nco)
                     outB[32 * q4] = vb;
                 }
             }
+            }   // R > 2
         }
         q = qn;
         qn = qnn;
