@@ -72,48 +72,6 @@ __device__ __forceinline__ c2 lds2r(const u64* S, int idx) {
     return v;
 }
 
-// ---- 32-point inverse DFT across the LANES of a warp (d = 4, 5: mfft = 64, 32) -------------------------------------
-// Decimation in frequency, five butterfly stages at lane distances 16, 8, 4, 2, 1: lane m holds X[m] on entry and
-// x[brev5(lane)] = sum_m X[m] exp(+2 pi i m brev5(lane) / 32) on exit.  Per stage 4 SHFL (both frames' re and im) and 6
-// packed instructions: t = partner + sg * own  (sg = -1 in the upper lane of a pair: a - b there, a + b in the lower),
-// then t * w with w = 1 in the lower lane and exp(+2 pi i (lane mod dist) / (2 dist)) in the upper (last stage: w = 1).
-// ~50 instructions instead of the ~210 of the 32-term multiply-accumulate through shared memory it replaces.
-__device__ __forceinline__ c2 shfl_xor2(c2 v, int dist) {
-    float a, b, c, d;
-    upk(v.re, a, b);
-    upk(v.im, c, d);
-    a = __shfl_xor_sync(0xffffffffu, a, dist);
-    b = __shfl_xor_sync(0xffffffffu, b, dist);
-    c = __shfl_xor_sync(0xffffffffu, c, dist);
-    d = __shfl_xor_sync(0xffffffffu, d, dist);
-    return c2{pk(a, b), pk(c, d)};
-}
-__device__ __forceinline__ c2 warp_idft32(c2 x, const float2 (&w)[4], int lane) {
-#pragma unroll
-    for (int s = 0; s < 5; s++) {
-        const int dist = 16 >> s;
-        const c2 pr = shfl_xor2(x, dist);
-        const u64 sg = bc((lane & dist) ? -1.0f : 1.0f);
-        c2 t;
-        t.re = fma2(sg, x.re, pr.re);
-        t.im = fma2(sg, x.im, pr.im);
-        x = s < 4 ? cmul2s(t, w[s]) : t;
-    }
-    return x;
-}
-// this lane's stage twiddles (entries 0..3) and, for mfft = 32 R > 32, exp(+2 pi i lane e / mfft), e = 1..R-1 (entries 4..)
-__device__ __forceinline__ float2 warp_idft_twiddle(int lane, int e, int mfft) {
-    float sn, cs;
-    if (e >= 4) {
-        sincospif((float)(2 * lane * (e - 3)) / (float)mfft, &sn, &cs);
-        return make_float2(cs, sn);
-    }
-    const int dist = 16 >> e;
-    if (!(lane & dist)) return make_float2(1.0f, 0.0f);
-    sincospif((float)(lane & (dist - 1)) / (float)dist, &sn, &cs);
-    return make_float2(cs, sn);
-}
-
 }  // namespace
 
 // What the kernels really read, as their parameter block: FusedParams (the launchers' common currency, 152 bytes with

@@ -255,8 +255,18 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_pair_kernel
         tab[i] = __ldg(p.tw1024 + i);
         tab[1024 + i] = __ldg(p.twq + i);
     }
-    for (int i = threadIdx.x; i < wide_tab_float2<D>() - 2048; i += kTeams * kTeamThreads)
-        tab[2048 + i] = __ldg((D == 0 ? p.tw_inv : p.tw_sub) + i);
+    // d = 4, 5 (1024 >> d = 64, 32 points per plane): the per-plane backward transform runs across the lanes
+    // (dual_frame.cuh: warp_idft32), its per-lane twiddles -- pitch 10: conflict-free 16-byte reads -- replace the weights
+    constexpr bool kCrossLane = D == 4 || D == 5;
+    constexpr int kXPitch = 10;
+    if constexpr (kCrossLane) {
+        constexpr int RX = (kWHalf >> D) / 4 / 32;
+        for (int i = threadIdx.x; i < 32 * (3 + RX); i += kTeams * kTeamThreads)
+            tab[2048 + (i & 31) * kXPitch + (i >> 5)] = warp_idft_twiddle(i & 31, i >> 5, (kWHalf >> D) / 4);
+    } else {
+        for (int i = threadIdx.x; i < wide_tab_float2<D>() - 2048; i += kTeams * kTeamThreads)
+            tab[2048 + i] = __ldg((D == 0 ? p.tw_inv : p.tw_sub) + i);
+    }
     const long long n_pairs = (p.total_frames + 1) / 2;
     if (tt == 0) s_pair[team] = (long long)atomicAdd(p.work_counter, 1ULL);
     __syncthreads();
@@ -343,8 +353,25 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_pair_kernel
                 y[brev_n(j, RB)] = split_pq(a, b, __ldg(pq + mm));
             }
             dit2<R, true>(y);                                         // pass 1 over n2 (m' = lane + 32 n2); its twiddles are part of the weights
-            team_barrier(team);                       // every band read of the team is done: the planes are free
             c2 u[R];
+            if constexpr (kCrossLane) {
+                // S_warp[R k + e] = sum_m' [W_MS^(m' e) y[e]] W_32^(m' k) over the lanes: lane l ends with samples R brev5(l) + e
+                const float2* xw = tabx + lane * kXPitch;
+                const float4 w01 = *reinterpret_cast<const float4*>(xw), w23 = *reinterpret_cast<const float4*>(xw + 2);
+                const float2 wsh[4] = {make_float2(w01.x, w01.y), make_float2(w01.z, w01.w), make_float2(w23.x, w23.y),
+                                       make_float2(w23.z, w23.w)};
+#pragma unroll
+                for (int e = 0; e < R; e++) u[e] = warp_idft32(e ? cmul2s(y[e], xw[3 + e]) : y[e], wsh, lane);
+                team_barrier(team);                   // every band read of the team is done: the planes are free
+#pragma unroll
+                for (int e = 0; e < R; e++) {
+                    const int n = R * brev5(lane) + e;
+                    c2 s = u[e];
+                    if (warp) s = cmul_conj2s(s, wpow(twq1, warp, n << D));
+                    pst(P, wbase + n, s);
+                }
+            } else {
+            team_barrier(team);                       // every band read of the team is done: the planes are free
             rscheme_pass2<R>(y, u, P, wbase, tabx + R * 32, lane);    // u[q] = S_warp[k2p + R h + 32 q]
             const int k2p = lane / G, h = lane % G;
 #pragma unroll
@@ -353,6 +380,7 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_pair_kernel
                 c2 s = u[qq];
                 if (warp) s = cmul_conj2s(s, wpow(twq1, warp, n << D));   // W_mfft^(-warp n') = W_4096^(-warp (n' << D))
                 pst(P, wbase + n, s);
+            }
             }
         }
         if constexpr (D <= 5) {
