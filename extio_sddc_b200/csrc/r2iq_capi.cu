@@ -341,7 +341,23 @@ int get_tables(r2iq_cuda_t h, int d, int tunebin, TableSet* out) {
                 tw[k2 * L + n1] = make_float2((float)cos(th), (float)sin(th));
             }
     }
-    if (d >= 1 && d <= 5) {
+    if (d == 5 && pair_tables) {
+        // r2iq_pair.cu, d = 5: lane c evaluates the band bin and the mirror bin of spectrum column c directly from the
+        // first forward pass: coefficients exp(-2 pi i n1 k / 1024), [c][n1] as (band.re, band.im, mirror.re, mirror.im)
+        std::vector<float4> zc(32 * 32);
+        for (int c = 0; c < 32; c++) {
+            const int mb = (c - tunebin) & 31, mm = (-c - tunebin) & 31;                 // band positions served by column c
+            const int kb = (tunebin + (mb < M / 2 ? mb : mb - M)) & (kHalfFft - 1);
+            const int km = (kHalfFft - ((tunebin + (mm < M / 2 ? mm : mm - M)) & (kHalfFft - 1))) & (kHalfFft - 1);
+            for (int n1 = 0; n1 < 32; n1++) {
+                const double tb_ = -2.0 * kPiD * (double)((n1 * kb) % kHalfFft) / (double)kHalfFft;
+                const double tm_ = -2.0 * kPiD * (double)((n1 * km) % kHalfFft) / (double)kHalfFft;
+                zc[c * 32 + n1] = make_float4((float)cos(tb_), (float)sin(tb_), (float)cos(tm_), (float)sin(tm_));
+            }
+        }
+        CU(h, cudaMalloc(&ts.tw_aux, sizeof(float4) * zc.size()));
+        CU(h, cudaMemcpy(ts.tw_aux, zc.data(), sizeof(float4) * zc.size(), cudaMemcpyHostToDevice));
+    } else if (d >= 1 && d <= 5) {
         // dual-frame kernels, backward transform mfft = 32*R on 32 lanes: pass-1 twiddles exp(+2 pi i lane k2 / mfft)
         // (k2 < R), then the pass-2 weights exp(+2 pi i (lane % G) n1 / 32), G = 32/R
         const std::vector<float2> ta = build_tw_aux(M, pair_tables);

@@ -39,7 +39,8 @@ __host__ __device__ constexpr int pair_warp_bytes() {
 constexpr int kTabPitch = 34;
 template <int D>
 __host__ __device__ constexpr int pair_table_float2() {
-    return D == 0 ? 4 * 32 * kTabPitch : D == 6 ? 32 * kTabPitch + 16 : D == 1 ? 2048 : 2 * 32 * kTabPitch;
+    // d = 5: [32 lanes][33] float4 coefficients of the directly evaluated bins + [32][kTabPitch] cross-lane twiddles
+    return D == 0 ? 4 * 32 * kTabPitch : D == 6 ? 32 * kTabPitch + 16 : D == 1 ? 2048 : D == 5 ? 32 * 33 * 2 + 32 * kTabPitch : 2 * 32 * kTabPitch;
 }
 // d = 6: exp(+2 pi i j / 16), the 16-point backward transform's twiddles
 #define R2IQ_W16(j) {(float)cx_cos2pi(j, 16), (float)cx_sin2pi(j, 16)}
@@ -112,6 +113,12 @@ __device__ __forceinline__ void pair_body(const Params& p, const NcoParams& nco)
     // backward transform by shuffle butterflies (warp_idft32) for mfft = 64, 32: 1021 -> 1117 and 1048 -> 1152 Gsamples/s at
     // d = 4, 5; at d = 3 (four transforms, 80 SHFL, stores of 32-byte runs) it loses, 992 -> 963
     constexpr bool kCrossLane = D == 4 || D == 5;
+    // d = 5 (mfft = 32): every column of the spectrum holds ONE band bin and ONE mirror bin, so the second forward pass is
+    // not run at all -- lane c evaluates those two bins directly from its column of the transposition, 2 x 32 complex
+    // multiply-accumulates with per-lane coefficients exp(-2 pi i n1 k / 1024) (inter-pass twiddle included; host table per
+    // tune bin) = 256 packed instructions instead of 124 + 388, and hands them to the lanes that need them by SHFL:
+    // no spectrum in shared memory, no band cut.
+    constexpr bool kDirect = D == 5;
     // the conversion's bias removed in the first butterfly stage (dit2_biased): +1.0 ... +1.5 % at d = 1..3; -0.5 % at d = 0
     constexpr bool kBiased = D != 0;
     static_assert(D == 0 || 2 * 32 * (R + 1) * 8 <= kLandOff, "backward transposition overlaps the landing zone");
@@ -129,7 +136,7 @@ __device__ __forceinline__ void pair_body(const Params& p, const NcoParams& nco)
 
     // ---- tables -> shared memory ------------------------------------------------------------------------------
     constexpr bool kTabT = D != 1;                    // tables transposed ([lane][34]); d = 1: [n][lane]
-    constexpr int kTab2 = kTabT ? 32 * kTabPitch : 1024;
+    constexpr int kTab2 = D == 5 ? 32 * 33 * 2 : kTabT ? 32 * kTabPitch : 1024;   // second table (d = 5: behind the coefficients)
     if constexpr (D == 0) {
         for (int i = threadIdx.x; i < 1024; i += W * 32) {
             const int o = (i & 31) * kTabPitch + (i >> 5);      // [row][lane] -> [lane][row]
@@ -145,10 +152,16 @@ __device__ __forceinline__ void pair_body(const Params& p, const NcoParams& nco)
         // the forward twiddles and the pass-2 weights ([32][32] behind the R unused rows of tw_aux); transposed like
         // d = 0 (one LDS.128 per two entries) except at d = 1, where the aligned register quads cost spills
         // (measured: 656 -> 618 Gsamples/s at d = 1, +1.5 / +3.4 / +0.4 / +0.9 % at d = 2..5)
+        if constexpr (kDirect) {
+            // tw_aux carries the coefficient table [lane][n1] (float4: band bin, mirror bin); pitch 33 float4 in shared memory
+            float4* cf = reinterpret_cast<float4*>(tab);
+            for (int i = threadIdx.x; i < 1024; i += W * 32) cf[(i >> 5) * 33 + (i & 31)] = __ldg(reinterpret_cast<const float4*>(p.tw_aux) + i);
+        } else {
         for (int i = threadIdx.x; i < 1024; i += W * 32) {
             const int o = kTabT ? (i & 31) * kTabPitch + (i >> 5) : i;
             tab[o] = __ldg(p.tw_fwd + i);
             if constexpr (!kCrossLane) tab[kTab2 + o] = __ldg(p.tw_aux + R * 32 + i);
+        }
         }
         if constexpr (kCrossLane) {          // the lane's twiddles of the cross-lane transform instead of the pass-2 weights
             if (threadIdx.x < 32 * (3 + R))
@@ -227,6 +240,67 @@ __device__ __forceinline__ void pair_body(const Params& p, const NcoParams& nco)
         // 7..46 % of the throughput -- loop-carried register moves, a weaker static schedule; measured, round 2)
         if constexpr (kBiased) dit2_biased<32, false>(v);   // the conversion's bias leaves in the first butterfly stage
         else dit2<32, false>(v);
+        if constexpr (kDirect) {
+#pragma unroll
+            for (int k2 = 0; k2 < 32; k2++) sts2(S, lane * 33 + k2, v[k2]);
+            __syncwarp();
+            const float4* cf = reinterpret_cast<const float4*>(tab) + lane * 33;
+            c2 zb, zm;                                // this column's band bin and mirror bin
+#pragma unroll
+            for (int n1 = 0; n1 < 32; n1++) {
+                const c2 x = lds2(S, n1 * 33 + lane);
+                const float4 c = cf[n1];
+                if (n1 == 0) {
+                    zb = cmul2s(x, make_float2(c.x, c.y));
+                    zm = cmul2s(x, make_float2(c.z, c.w));
+                } else {
+                    zb.re = fma2(bc(c.x), x.re, fma2(bc(-c.y), x.im, zb.re));
+                    zb.im = fma2(bc(c.x), x.im, fma2(bc(c.y), x.re, zb.im));
+                    zm.re = fma2(bc(c.z), x.re, fma2(bc(-c.w), x.im, zm.re));
+                    zm.im = fma2(bc(c.z), x.im, fma2(bc(c.w), x.re, zm.im));
+                }
+            }
+            __syncwarp();   // every lane is done with the tile: its tail takes the next pair of frames
+            if (lane == 0 && qn < n_pairs) {
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                issue(qn);
+            }
+            // band position m = lane: bin tunebin + s(m) sits in column (tunebin + m) mod 32, its mirror in column -(tunebin + m)
+            const int ca = (p.tunebin + lane) & 31, cb = (-(p.tunebin + lane)) & 31;
+            c2 a, b;
+            {
+                float r0, r1, i0, i1;
+                upk(zb.re, r0, r1);
+                upk(zb.im, i0, i1);
+                a.re = pk(__shfl_sync(0xffffffffu, r0, ca), __shfl_sync(0xffffffffu, r1, ca));
+                a.im = pk(__shfl_sync(0xffffffffu, i0, ca), __shfl_sync(0xffffffffu, i1, ca));
+                upk(zm.re, r0, r1);
+                upk(zm.im, i0, i1);
+                b.re = pk(__shfl_sync(0xffffffffu, r0, cb), __shfl_sync(0xffffffffu, r1, cb));
+                b.im = pk(__shfl_sync(0xffffffffu, i0, cb), __shfl_sync(0xffffffffu, i1, cb));
+            }
+            const float4 pq = __ldg(reinterpret_cast<const float4*>(p.gp) + lane);   // (P, Q) in band order
+            c2 y;
+            y.re = fma2(bc(pq.w), b.im, fma2(bc(pq.z), b.re, fma2(bc(-pq.y), a.im, mul2(bc(pq.x), a.re))));
+            y.im = fma2(bc(pq.w), b.re, fma2(bc(-pq.z), b.im, fma2(bc(pq.y), a.re, mul2(bc(pq.x), a.im))));
+            const float2* tw2 = tab + kTab2 + lane * kTabPitch;
+            const float4 w01 = *reinterpret_cast<const float4*>(tw2), w23 = *reinterpret_cast<const float4*>(tw2 + 2);
+            const float2 wsh[4] = {make_float2(w01.x, w01.y), make_float2(w01.z, w01.w), make_float2(w23.x, w23.y), make_float2(w23.z, w23.w)};
+            c2 o = warp_idft32(y, wsh, lane);          // output sample brev5(lane)
+            const FrameOut2 oa = frame_out2<D>(2 * q, p.total_frames);
+            const FrameOut2 ob = frame_out2<D>(2 * q + 1, p.total_frames);
+            const int idx0 = brev5(lane);
+            if constexpr (kMix == 2)
+                o = direct_mix(o, direct_phasors(nco.nco_phase0, nco.nco_fc, oa.base + idx0, ob.base + idx0), make_float2(1.0f, 0.0f), p.imag_sign);
+            float ar, br, ai, bi;
+            upk(o.re, ar, br);
+            upk(o.im, ai, bi);
+            if (idx0 >= oa.lo && idx0 < 3 * M / 4) p.out[oa.base + idx0] = kMix == 2 ? make_float2(ar, ai) : make_float2(ar, flip(ai, sgn));
+            if (ob.live && idx0 >= ob.lo && idx0 < 3 * M / 4) p.out[ob.base + idx0] = kMix == 2 ? make_float2(br, bi) : make_float2(br, flip(bi, sgn));
+            q = qn;
+            qn = qnn;
+            continue;
+        }
         // The inter-pass twiddles W_1024^(n1 lane) ride in the first stage of the second pass (dit2_tw, 32 packed
         // instructions fewer; the table is symmetric in (n1, k2), so the reader's lane takes the entry the writer's would
         // have).  Measured per decimation: +1.8 / +3.5 / +0.7 / +0.3 / -0.7 / -0.5 / +1.7 % at d = 0..6 -- d = 4, 5 keep
