@@ -96,6 +96,22 @@ def test_parity_matrix(op, d):
         check(got, ref, GAIN, (d, tb, rnd, lsb))
 
 
+@pytest.mark.parametrize("d", [4, 5, 6])
+def test_every_tune_bin_at_small_mfft(op, d):
+    """d = 4, 5 run their own code paths (r2iq_pair.cu: the backward transform across the lanes by shuffle butterflies; at
+    d = 5 band and mirror bins evaluated directly from the first forward pass with per-tune-bin coefficient tables) whose
+    lane arithmetic depends on the tune bin modulo 32 and on where the band wraps: every tune bin setFreqOffset can produce
+    (multiples of 4, Core/fft_mt_r2iq.cpp:101-109), one block with history, randomizer and sideband alternating."""
+    rng = np.random.default_rng(50 + d)
+    x = rng.integers(-20000, 20000, 2 * orc.TRANSFER_SAMPLES).astype(np.int16).reshape(2, -1)
+    hist = rng.integers(-3000, 3000, 1024).astype(np.int16)
+    for tb in range(0, 1024, 4):
+        rand, lsb = bool((tb >> 2) & 1), bool((tb >> 3) & 1)
+        got = run(op, x, d, tb, rand=rand, lsb=lsb, history=hist)
+        ref = orc.r2iq(x, d, tb, gain=GAIN, rand=rand, sideband=lsb, history=hist)
+        check(got, ref, GAIN, f"d={d} tunebin={tb}")
+
+
 def test_config1_hf_64msps(op):
     # BASELINE config 1: synthetic tone 64 Msps, decimation 2 (d=0), default tune and tuned to 5 MHz
     r = CudaR2IQ()

@@ -20,7 +20,7 @@ import re
 def short_name(n):
     """ncu's demangled name -> the form r2iq_cuda_kernel_name() reports ('r2iq_pair_kernel<0, 8, 0>')."""
     n = re.sub(r"^void ", "", n)
-    n = re.sub(r"\((?:r2iq::)?\w+\)$", "", n)
+    n = re.sub(r"\((?:[\w:]+(?:, )?)*\)$", "", n)
     return n.replace("r2iq::", "").replace("(int)", "").replace("(bool)", "")
 
 
@@ -127,6 +127,8 @@ for hdr, units, data in captures:
     e["d"] = d
     if d is not None:
         alg = blocks * 65536 * (2.0 + 8.0 / (1 << (d + 1)))
+        if "channels" in name:            # tools/chan_bench.py: 64 channels share one input stream
+            alg = blocks * 65536 * (2.0 + 64 * 8.0 / (1 << (d + 1)))
         e["algorithmic_bytes"] = alg
         e["dram_traffic_bytes"] = e["dram_read_bytes"] + e["dram_write_bytes"]
         e["traffic_over_algorithmic"] = round(e["dram_traffic_bytes"] / alg, 4)
