@@ -13,6 +13,15 @@
 //     block edge, 1024 samples), so the pair is 7168 (6144) contiguous bytes instead of 2 x 4096 -- 12.5 % less
 //     L2->SM traffic and the shared memory that makes room for the tables.
 //   * int16 -> float on the integer pipe (dual_frame.cuh: unpack_words) instead of the conversion unit.
+// Later in round 2 the loop bodies went on an instruction diet (the kernels are bound by issue slots, the FMA pipe and the
+// shared-memory data pipe together, never by HBM; every instruction taken out showed up in the time -- DESIGN.md section 4):
+//   * the kernel parameter block narrowed to what the kernel reads (PairParams; decided per decimation by measurement);
+//   * 32-bit frame arithmetic, warp-uniform store predicates, kept rows as a compile-time set;
+//   * inter-pass twiddles folded into the first butterfly stage of the following pass (dft_regs2.cuh: dit2_tw), backward
+//     pass-1 twiddles folded into the pass-2 weights, the conversion's bias folded into the first stage (dit2_biased);
+//   * (P, Q) in band order as one float4 table, twiddle tables transposed in shared memory (one LDS.128 per two entries);
+//   * d = 4, 5: the backward transform across the lanes by shuffle butterflies (dual_frame.cuh: warp_idft32);
+//   * d = 5: no second forward pass -- the one band bin and the one mirror bin of every spectrum column evaluated directly.
 // Reference lines replaced: Core/fft_mt_r2iq_impl.hpp:40-54,84-138 (see r2iq_kernels.cu).
 #include "dual_frame.cuh"
 #include "r2iq_kernels.cuh"
