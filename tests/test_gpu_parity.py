@@ -216,6 +216,11 @@ def test_empty_and_error_behaviour():
     # decimation is latched at TurnOn like the reference worker (impl.hpp:3-6)
     r.TurnOn(); r.setDecimate(1)
     assert r.out_per_block() == 32768 >> 3
+    # the kernels index frames with 32 bits: a launch of 2^31 frames or more (6.5 TB of samples) is refused before any
+    # memory is touched (the pointers below are never dereferenced)
+    with pytest.raises(capi.R2iqError) as ei:
+        r.process_device(0x1000, 50_000_000, 0x1000, 0)
+    assert ei.value.code == capi.E_INVALID
     r.TurnOff()
     r.close()
 
