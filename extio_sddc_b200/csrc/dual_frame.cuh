@@ -177,19 +177,23 @@ __device__ __forceinline__ c2 shfl_xor2(c2 v, int dist) {
     d = __shfl_xor_sync(0xffffffffu, d, dist);
     return c2{pk(a, b), pk(c, d)};
 }
-__device__ __forceinline__ c2 warp_idft32(c2 x, const float2 (&w)[4], int lane) {
+// NS butterfly stages: a 2^NS-point transform inside every aligned group of 2^NS lanes (NS = 4: the 16-point transform
+// of d = 6, run twice side by side; w[0..NS-2] are the lane's stage twiddles, distance 2^(NS-1) first)
+template <int NS>
+__device__ __forceinline__ c2 warp_idft(c2 x, const float2 (&w)[4], int lane) {
 #pragma unroll
-    for (int s = 0; s < 5; s++) {
-        const int dist = 16 >> s;
+    for (int s = 0; s < NS; s++) {
+        const int dist = (1 << (NS - 1)) >> s;
         const c2 pr = shfl_xor2(x, dist);
         const u64 sg = bc((lane & dist) ? -1.0f : 1.0f);
         c2 t;
         t.re = fma2(sg, x.re, pr.re);
         t.im = fma2(sg, x.im, pr.im);
-        x = s < 4 ? cmul2s(t, w[s]) : t;
+        x = s < NS - 1 ? cmul2s(t, w[s]) : t;
     }
     return x;
 }
+__device__ __forceinline__ c2 warp_idft32(c2 x, const float2 (&w)[4], int lane) { return warp_idft<5>(x, w, lane); }
 // this lane's stage twiddles (entries 0..3) and, for mfft = 32 R > 32, exp(+2 pi i lane e / mfft), e = 1..R-1 (entries 4..)
 __device__ __forceinline__ float2 warp_idft_twiddle(int lane, int e, int mfft) {
     float sn, cs;
@@ -197,8 +201,8 @@ __device__ __forceinline__ float2 warp_idft_twiddle(int lane, int e, int mfft) {
         sincospif((float)(2 * lane * (e - 3)) / (float)mfft, &sn, &cs);
         return make_float2(cs, sn);
     }
-    const int dist = 16 >> e;
-    if (!(lane & dist)) return make_float2(1.0f, 0.0f);
+    const int dist = (mfft == 16 ? 8 : 16) >> e;     // mfft = 16: four stages inside each half warp
+    if (dist == 0 || !(lane & dist)) return make_float2(1.0f, 0.0f);
     sincospif((float)(lane & (dist - 1)) / (float)dist, &sn, &cs);
     return make_float2(cs, sn);
 }

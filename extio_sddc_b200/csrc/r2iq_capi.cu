@@ -341,18 +341,28 @@ int get_tables(r2iq_cuda_t h, int d, int tunebin, TableSet* out) {
                 tw[k2 * L + n1] = make_float2((float)cos(th), (float)sin(th));
             }
     }
-    if (d == 5 && pair_tables) {
+    if (d >= 5 && pair_tables) {
         // r2iq_pair.cu, d = 5: lane c evaluates the band bin and the mirror bin of spectrum column c directly from the
         // first forward pass: coefficients exp(-2 pi i n1 k / 1024), [c][n1] as (band.re, band.im, mirror.re, mirror.im)
         std::vector<float4> zc(32 * 32);
         for (int c = 0; c < 32; c++) {
-            const int mb = (c - tunebin) & 31, mm = (-c - tunebin) & 31;                 // band positions served by column c
-            const int kb = (tunebin + (mb < M / 2 ? mb : mb - M)) & (kHalfFft - 1);
-            const int km = (kHalfFft - ((tunebin + (mm < M / 2 ? mm : mm - M)) & (kHalfFft - 1))) & (kHalfFft - 1);
+            // the band offset s in [-M/2, M/2) with tunebin + s = c (band bin) resp. = -c (mirror bin) modulo 32; at
+            // d = 6 (M = 16) half of the columns hold none: zero coefficients, the value is never fetched
+            auto offset = [&](int u, int* s_out) {
+                u &= 31;
+                if (u < M / 2) { *s_out = u; return true; }
+                if (u >= 32 - M / 2) { *s_out = u - 32; return true; }
+                return false;
+            };
+            int sb = 0, sm = 0;
+            const bool has_b = offset(c - tunebin, &sb), has_m = offset(-c - tunebin, &sm);
+            const int kb = (tunebin + sb) & (kHalfFft - 1);
+            const int km = (kHalfFft - ((tunebin + sm) & (kHalfFft - 1))) & (kHalfFft - 1);
             for (int n1 = 0; n1 < 32; n1++) {
                 const double tb_ = -2.0 * kPiD * (double)((n1 * kb) % kHalfFft) / (double)kHalfFft;
                 const double tm_ = -2.0 * kPiD * (double)((n1 * km) % kHalfFft) / (double)kHalfFft;
-                zc[c * 32 + n1] = make_float4((float)cos(tb_), (float)sin(tb_), (float)cos(tm_), (float)sin(tm_));
+                zc[c * 32 + n1] = make_float4(has_b ? (float)cos(tb_) : 0.f, has_b ? (float)sin(tb_) : 0.f,
+                                              has_m ? (float)cos(tm_) : 0.f, has_m ? (float)sin(tm_) : 0.f);
             }
         }
         CU(h, cudaMalloc(&ts.tw_aux, sizeof(float4) * zc.size()));

@@ -49,13 +49,8 @@ constexpr int kTabPitch = 34;
 template <int D>
 __host__ __device__ constexpr int pair_table_float2() {
     // d = 5: [32 lanes][33] float4 coefficients of the directly evaluated bins + [32][kTabPitch] cross-lane twiddles
-    return D == 0 ? 4 * 32 * kTabPitch : D == 6 ? 32 * kTabPitch + 16 : D == 1 ? 2048 : D == 5 ? 32 * 33 * 2 + 32 * kTabPitch : 2 * 32 * kTabPitch;
+    return D == 0 ? 4 * 32 * kTabPitch : D == 1 ? 2048 : D >= 5 ? 32 * 33 * 2 + 32 * kTabPitch : 2 * 32 * kTabPitch;
 }
-// d = 6: exp(+2 pi i j / 16), the 16-point backward transform's twiddles
-#define R2IQ_W16(j) {(float)cx_cos2pi(j, 16), (float)cx_sin2pi(j, 16)}
-__constant__ float2 kW16[16] = {R2IQ_W16(0), R2IQ_W16(1), R2IQ_W16(2),  R2IQ_W16(3),  R2IQ_W16(4),  R2IQ_W16(5),  R2IQ_W16(6),  R2IQ_W16(7),
-                                R2IQ_W16(8), R2IQ_W16(9), R2IQ_W16(10), R2IQ_W16(11), R2IQ_W16(12), R2IQ_W16(13), R2IQ_W16(14), R2IQ_W16(15)};
-#undef R2IQ_W16
 template <int D, int W>
 __host__ __device__ constexpr int pair_smem_bytes() {
     return pair_table_float2<D>() * 8 + W * pair_warp_bytes<W>();
@@ -127,7 +122,9 @@ __device__ __forceinline__ void pair_body(const Params& p, const NcoParams& nco)
     // multiply-accumulates with per-lane coefficients exp(-2 pi i n1 k / 1024) (inter-pass twiddle included; host table per
     // tune bin) = 256 packed instructions instead of 124 + 388, and hands them to the lanes that need them by SHFL:
     // no spectrum in shared memory, no band cut.
-    constexpr bool kDirect = D == 5;
+    // d = 6 (mfft = 16) the same way: a column holds at most one band bin and one mirror bin (zero coefficients where it
+    // holds none), and the 16-point backward transform runs inside each half warp.
+    constexpr bool kDirect = D >= 5;
     // the conversion's bias removed in the first butterfly stage (dit2_biased): +1.0 ... +1.5 % at d = 1..3; -0.5 % at d = 0
     constexpr bool kBiased = D != 0;
     static_assert(D == 0 || 2 * 32 * (R + 1) * 8 <= kLandOff, "backward transposition overlaps the landing zone");
@@ -145,7 +142,7 @@ __device__ __forceinline__ void pair_body(const Params& p, const NcoParams& nco)
 
     // ---- tables -> shared memory ------------------------------------------------------------------------------
     constexpr bool kTabT = D != 1;                    // tables transposed ([lane][34]); d = 1: [n][lane]
-    constexpr int kTab2 = D == 5 ? 32 * 33 * 2 : kTabT ? 32 * kTabPitch : 1024;   // second table (d = 5: behind the coefficients)
+    constexpr int kTab2 = D >= 5 ? 32 * 33 * 2 : kTabT ? 32 * kTabPitch : 1024;   // second table (d = 5, 6: behind the coefficients)
     if constexpr (D == 0) {
         for (int i = threadIdx.x; i < 1024; i += W * 32) {
             const int o = (i & 31) * kTabPitch + (i >> 5);      // [row][lane] -> [lane][row]
@@ -154,9 +151,6 @@ __device__ __forceinline__ void pair_body(const Params& p, const NcoParams& nco)
             tab[64 * kTabPitch + o] = __ldg(p.gp + i);
             tab[96 * kTabPitch + o] = __ldg(p.gq + i);
         }
-    } else if constexpr (D == 6) {
-        for (int i = threadIdx.x; i < 1024; i += W * 32) tab[(i & 31) * kTabPitch + (i >> 5)] = __ldg(p.tw_fwd + i);
-        if (threadIdx.x < 16) tab[32 * kTabPitch + threadIdx.x] = kW16[threadIdx.x];
     } else {
         // the forward twiddles and the pass-2 weights ([32][32] behind the R unused rows of tw_aux); transposed like
         // d = 0 (one LDS.128 per two entries) except at d = 1, where the aligned register quads cost spills
@@ -172,7 +166,7 @@ __device__ __forceinline__ void pair_body(const Params& p, const NcoParams& nco)
             if constexpr (!kCrossLane) tab[kTab2 + o] = __ldg(p.tw_aux + R * 32 + i);
         }
         }
-        if constexpr (kCrossLane) {          // the lane's twiddles of the cross-lane transform instead of the pass-2 weights
+        if constexpr (kCrossLane || kDirect) {   // the lane's twiddles of the cross-lane transform instead of the pass-2 weights
             if (threadIdx.x < 32 * (3 + R))
                 tab[kTab2 + (threadIdx.x & 31) * kTabPitch + (threadIdx.x >> 5)] = warp_idft_twiddle(threadIdx.x & 31, threadIdx.x >> 5, M);
         }
@@ -274,8 +268,11 @@ __device__ __forceinline__ void pair_body(const Params& p, const NcoParams& nco)
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 issue(qn);
             }
-            // band position m = lane: bin tunebin + s(m) sits in column (tunebin + m) mod 32, its mirror in column -(tunebin + m)
-            const int ca = (p.tunebin + lane) & 31, cb = (-(p.tunebin + lane)) & 31;
+            // band position m: bin tunebin + s(m) sits in column (tunebin + s(m)) mod 32, its mirror in column -(tunebin + s(m))
+            // (d = 5: m = lane and s = m mod 32; d = 6: both half warps serve m = lane mod 16)
+            const int mpos = lane & (M - 1);
+            const int sband = mpos < M / 2 ? mpos : mpos - M;
+            const int ca = (p.tunebin + sband) & 31, cb = (-(p.tunebin + sband)) & 31;
             c2 a, b;
             {
                 float r0, r1, i0, i1;
@@ -288,17 +285,17 @@ __device__ __forceinline__ void pair_body(const Params& p, const NcoParams& nco)
                 b.re = pk(__shfl_sync(0xffffffffu, r0, cb), __shfl_sync(0xffffffffu, r1, cb));
                 b.im = pk(__shfl_sync(0xffffffffu, i0, cb), __shfl_sync(0xffffffffu, i1, cb));
             }
-            const float4 pq = __ldg(reinterpret_cast<const float4*>(p.gp) + lane);   // (P, Q) in band order
+            const float4 pq = __ldg(reinterpret_cast<const float4*>(p.gp) + mpos);   // (P, Q) in band order
             c2 y;
             y.re = fma2(bc(pq.w), b.im, fma2(bc(pq.z), b.re, fma2(bc(-pq.y), a.im, mul2(bc(pq.x), a.re))));
             y.im = fma2(bc(pq.w), b.re, fma2(bc(-pq.z), b.im, fma2(bc(pq.y), a.re, mul2(bc(pq.x), a.im))));
             const float2* tw2 = tab + kTab2 + lane * kTabPitch;
             const float4 w01 = *reinterpret_cast<const float4*>(tw2), w23 = *reinterpret_cast<const float4*>(tw2 + 2);
             const float2 wsh[4] = {make_float2(w01.x, w01.y), make_float2(w01.z, w01.w), make_float2(w23.x, w23.y), make_float2(w23.z, w23.w)};
-            c2 o = warp_idft32(y, wsh, lane);          // output sample brev5(lane)
+            c2 o = warp_idft<D == 5 ? 5 : 4>(y, wsh, lane);   // output sample brev(lane) of the 32 (16) points
             const FrameOut2 oa = frame_out2<D>(2 * q, p.total_frames);
             const FrameOut2 ob = frame_out2<D>(2 * q + 1, p.total_frames);
-            const int idx0 = brev5(lane);
+            const int idx0 = D == 5 ? brev5(lane) : (lane < 16 ? brev_n(lane, 4) : M);   // d = 6: the upper half warp stores nothing
             if constexpr (kMix == 2)
                 o = direct_mix(o, direct_phasors(nco.nco_phase0, nco.nco_fc, oa.base + idx0, ob.base + idx0), make_float2(1.0f, 0.0f), p.imag_sign);
             float ar, br, ai, bi;
@@ -397,60 +394,6 @@ __device__ __forceinline__ void pair_body(const Params& p, const NcoParams& nco)
                 if (k1 >= 8 ? liveB : headB) {
                     float2 vb = kMix == 2 ? make_float2(br, bi) : make_float2(br, flip(bi, sgn));
                     outB[32 * k1] = vb;
-                }
-            }
-        } else if constexpr (D == 6) {
-            // ---- d = 6 (mfft 16 < 32 lanes): lane m < 16 cuts band bin m, then lane n < 16 sums its output sample
-            //      y[n] = sum_m Y[m] exp(+2 pi i m n / 16) from shared memory (16 broadcast reads); both frames packed
-#pragma unroll
-            for (int k1 = 0; k1 < 32; k1++)
-                if ((p.row_mask >> k1) & 1u) sts2(S, 32 * k1 + lane, v[k1]);
-            __syncwarp();
-            const int m = lane & 15;
-            const int s6 = m < 8 ? m : m - 16;                          // upper half of the band is below the tune bin
-            const int kk = (p.tunebin + s6) & (kHalfFft - 1);
-            c2 r;
-            {
-                const c2 a = lds2(S, kk);
-                const c2 b = lds2(S, (kHalfFft - kk) & (kHalfFft - 1));
-                const float4 pq = __ldg(reinterpret_cast<const float4*>(p.gp) + m);   // (P, Q) in band order
-                const float2 P = make_float2(pq.x, pq.y), Q = make_float2(pq.z, pq.w);
-                r.re = fma2(bc(Q.y), b.im, fma2(bc(Q.x), b.re, fma2(bc(-P.y), a.im, mul2(bc(P.x), a.re))));
-                r.im = fma2(bc(Q.y), b.re, fma2(bc(-Q.x), b.im, fma2(bc(P.y), a.re, mul2(bc(P.x), a.im))));
-            }
-            __syncwarp();   // every lane is done with the spectrum: the tile is free
-            if (lane == 0 && qn < n_pairs) {
-                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                issue(qn);
-            }
-            if (lane < 16) sts2r<1>(S, lane, r);                        // planes of 64 elements at the head of the tile
-            __syncwarp();
-            const float2* w16 = tab + 32 * kTabPitch;
-            c2 acc;
-            acc.re = acc.im = bc(0.0f);
-#pragma unroll
-            for (int mm = 0; mm < 16; mm++) {
-                const c2 x = lds2r<1>(S, mm);
-                const float2 w = w16[(mm * m) & 15];
-                acc.re = fma2(bc(w.x), x.re, fma2(bc(-w.y), x.im, acc.re));
-                acc.im = fma2(bc(w.x), x.im, fma2(bc(w.y), x.re, acc.im));
-            }
-            __syncwarp();
-            const FrameOut2 oa = frame_out2<6>(2 * q, p.total_frames);
-            const FrameOut2 ob = frame_out2<6>(2 * q + 1, p.total_frames);
-            if constexpr (kMix == 2)
-                acc = direct_mix(acc, direct_phasors(nco.nco_phase0, nco.nco_fc, oa.base + lane, ob.base + lane), make_float2(1.0f, 0.0f), p.imag_sign);
-            float ar, br, ai, bi;
-            upk(acc.re, ar, br);
-            upk(acc.im, ai, bi);
-            if (lane < 3 * M / 4) {
-                if (lane >= oa.lo) {
-                    float2 va = kMix == 2 ? make_float2(ar, ai) : make_float2(ar, flip(ai, sgn));
-                    p.out[oa.base + lane] = va;
-                }
-                if (ob.live && lane >= ob.lo) {
-                    float2 vb = kMix == 2 ? make_float2(br, bi) : make_float2(br, flip(bi, sgn));
-                    p.out[ob.base + lane] = vb;
                 }
             }
         } else {
