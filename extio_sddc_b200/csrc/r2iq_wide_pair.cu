@@ -86,13 +86,6 @@ __device__ __forceinline__ float2 csqr(float2 w) { return make_float2(fmaf(w.x, 
 __device__ __forceinline__ void team_barrier(int team) {
     asm volatile("bar.sync %0, %1;" ::"r"(team + 1), "r"(kTeamThreads) : "memory");
 }
-// W_4096^(r e) for r = 1..3 from the table of W_4096^e (e < 1024)
-__device__ __forceinline__ float2 wpow(const float2* twq1, int r, int e) {
-    const float2 w1 = twq1[e];
-    if (r == 1) return w1;
-    const float2 w2 = csqr(w1);
-    return r == 2 ? w2 : cmul(w1, w2);
-}
 // split + filter + band edge: Y = P a + Q conj(b), a = Z[k], b = Z[4096 - k]; pq = (P.re, P.im, Q.re, Q.im)
 __device__ __forceinline__ c2 split_pq(c2 a, c2 b, float4 pq) {
     c2 y;
@@ -332,12 +325,8 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_pair_kernel
             // inter-pass twiddles on the reading side (tw_inv row n = twiddle of the element read from row n, written by the
             // lane that plays residue n), folded into the first stage
             dit2_tw<32, true, false>(t, [&](int i) { return tabx[32 * brev5(i) + lane]; });
-            if (warp) {
 #pragma unroll
-                for (int k1 = 0; k1 < 32; k1++) t[k1] = cmul_conj2s(t[k1], wpow(twq1, warp, lane + 32 * k1));
-            }
-#pragma unroll
-            for (int k1 = 0; k1 < 32; k1++) pst(P, wbase + lane + 32 * k1, t[k1]);
+            for (int k1 = 0; k1 < 32; k1++) pst(P, wbase + lane + 32 * k1, t[k1]);   // W_4096^(-warp n) follows in phase E
         } else if constexpr (D <= 5) {
             constexpr int MS = M / 4;                                 // points per plane: 1024 >> D
             constexpr int R = MS / 32;                                // band bins of this plane per lane
@@ -366,9 +355,7 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_pair_kernel
 #pragma unroll
                 for (int e = 0; e < R; e++) {
                     const int n = R * brev5(lane) + e;
-                    c2 s = u[e];
-                    if (warp) s = cmul_conj2s(s, wpow(twq1, warp, n << D));
-                    pst(P, wbase + n, s);
+                    pst(P, wbase + n, u[e]);
                 }
             } else {
             team_barrier(team);                       // every band read of the team is done: the planes are free
@@ -377,9 +364,7 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_pair_kernel
 #pragma unroll
             for (int qq = 0; qq < R; qq++) {
                 const int n = k2p + R * h + 32 * qq;
-                c2 s = u[qq];
-                if (warp) s = cmul_conj2s(s, wpow(twq1, warp, n << D));   // W_mfft^(-warp n') = W_4096^(-warp (n' << D))
-                pst(P, wbase + n, s);
+                pst(P, wbase + n, u[qq]);
             }
             }
         }
@@ -398,7 +383,11 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_pair_kernel
             for (int i = 0; i < (MS + kTeamThreads - 1) / kTeamThreads; i++) {
                 const int n = tt + kTeamThreads * i;
                 if (MS >= kTeamThreads || n < MS) {
-                    const c2 s0 = pld(P, n), s1 = pld(P, kWPlane + n), s2 = pld(P, 2 * kWPlane + n), s3 = pld(P, 3 * kWPlane + n);
+                    // S_r[n] W_mfft^(-r n) = S_r[n] conj(W_4096^(r (n << D))): applied here, where all 128 threads share the work
+                    // (in phase D2 warp 3 carried 32 x (load + 7 scalar + 4 packed) and warp 0 nothing: the team waited for it)
+                    const float2 w1 = twq1[n << D], w2 = csqr(w1), w3 = cmul(w1, w2);
+                    const c2 s0 = pld(P, n), s1 = cmul_conj2s(pld(P, kWPlane + n), w1), s2 = cmul_conj2s(pld(P, 2 * kWPlane + n), w2),
+                             s3 = cmul_conj2s(pld(P, 3 * kWPlane + n), w3);
                     const c2 a0 = cadd(s0, s2), a1 = csub(s0, s2), a2 = cadd(s1, s3), a3 = csub(s1, s3);
                     if constexpr (kMix == 2) {
                         // sample n + MS a is 32 (4 i + (MS / 32) a) samples after sample tt: entries of nco_rot (< 96)
