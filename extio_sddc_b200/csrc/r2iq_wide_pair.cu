@@ -48,12 +48,14 @@ constexpr int kTeamThreads = 128;
 constexpr int kTeams = 3;
 constexpr int kTeamBytes = 2 * 4 * kWPlane * 8;     // four planes of (re_A, re_B) then four of (im_A, im_B)
 
-// tables in shared memory: W_1024 inter-pass twiddles | W_4096^n | d = 0: backward inter-pass twiddles of this tune bin,
-// d >= 1: the R-scheme twiddles and weights (build_tw_aux)
+// tables in shared memory: W_1024 inter-pass twiddles, transposed [lane][34] (one LDS.128 per two entries) | W_4096^n |
+// d = 0: backward inter-pass twiddles of this tune bin, d >= 1: the pass-2 weights of the R-scheme (build_tw_aux, second part)
+constexpr int kWTabPitch = 34;
+constexpr int kWTab1 = 32 * kWTabPitch;             // start of W_4096^n
+constexpr int kWTabX = kWTab1 + 1024;               // start of the per-decimation table
 template <int D>
 __host__ __device__ constexpr int wide_tab_float2() {
-    constexpr int S = D == 6 ? 64 : (kWHalf >> D) / 4;
-    return 2048 + (D == 0 ? 1024 : (S / 32 + 32) * 32);
+    return kWTabX + 1024;
 }
 template <int D>
 __host__ __device__ constexpr int wide_smem_bytes() {
@@ -230,9 +232,9 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_pair_kernel
     const int lane = tt & 31;
     const int warp = tt >> 5;                          // plane this warp transforms
     float2* tab = reinterpret_cast<float2*>(wsmem);
-    const float2* tw1024 = tab;
-    const float2* twq1 = tab + 1024;                   // W_4096^n
-    const float2* tabx = tab + 2048;                   // d = 0: tw_inv; d >= 1: tw_sub
+    const float2* tw1024 = tab + lane * kWTabPitch;    // this lane's row: entry n at tw1024[n]
+    const float2* twq1 = tab + kWTab1;                 // W_4096^n
+    const float2* tabx = tab + kWTabX;                 // d = 0: tw_inv; d >= 1: pass-2 weights
     Planes P;
     P.re = reinterpret_cast<float2*>(wsmem + wide_tab_float2<D>() * 8 + (size_t)team * kTeamBytes);
     P.im = P.re + 4 * kWPlane;
@@ -245,8 +247,8 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_pair_kernel
     const float4* pq = p.pq + warp * 1024;
 
     for (int i = threadIdx.x; i < 1024; i += kTeams * kTeamThreads) {
-        tab[i] = __ldg(p.tw1024 + i);
-        tab[1024 + i] = __ldg(p.twq + i);
+        tab[(i & 31) * kWTabPitch + (i >> 5)] = __ldg(p.tw1024 + i);
+        tab[kWTab1 + i] = __ldg(p.twq + i);
     }
     // d = 4, 5 (1024 >> d = 64, 32 points per plane): the per-plane backward transform runs across the lanes
     // (dual_frame.cuh: warp_idft32), its per-lane twiddles -- pitch 10: conflict-free 16-byte reads -- replace the weights
@@ -255,10 +257,12 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_pair_kernel
     if constexpr (kCrossLane) {
         constexpr int RX = (kWHalf >> D) / 4 / 32;
         for (int i = threadIdx.x; i < 32 * (3 + RX); i += kTeams * kTeamThreads)
-            tab[2048 + (i & 31) * kXPitch + (i >> 5)] = warp_idft_twiddle(i & 31, i >> 5, (kWHalf >> D) / 4);
+            tab[kWTabX + (i & 31) * kXPitch + (i >> 5)] = warp_idft_twiddle(i & 31, i >> 5, (kWHalf >> D) / 4);
     } else {
-        for (int i = threadIdx.x; i < wide_tab_float2<D>() - 2048; i += kTeams * kTeamThreads)
-            tab[2048 + i] = __ldg((D == 0 ? p.tw_inv : p.tw_sub) + i);
+        // d >= 1: only the [32][32] weights behind the R unused twiddle rows of tw_sub (their twiddles are folded in)
+        constexpr int kSkip = D == 0 ? 0 : (D == 6 ? 64 : (kWHalf >> D) / 4) / 32 * 32;
+        for (int i = threadIdx.x; i < 1024; i += kTeams * kTeamThreads)
+            tab[kWTabX + i] = __ldg((D == 0 ? p.tw_inv : p.tw_sub + kSkip) + i);
     }
     const long long n_pairs = (p.total_frames + 1) / 2;
     if (tt == 0) s_pair[team] = (long long)atomicAdd(p.work_counter, 1ULL);
@@ -292,7 +296,11 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_pair_kernel
             for (int n1 = 0; n1 < 32; n1++) v[brev5(n1)] = pld(P, wbase + n1 * 33 + lane);
             __syncwarp();
             // inter-pass twiddles W_1024^(n1 lane) folded into the first stage of the second pass (dft_regs2.cuh)
-            dit2_tw<32, false>(v, [&](int i) { return tw1024[32 * brev5(i) + lane]; });
+            dit2_tw<32, false>(v, [&](int i) {
+                const int n1 = brev5(i);
+                const float4 w = *reinterpret_cast<const float4*>(tw1024 + (n1 & ~1));
+                return (n1 & 1) ? make_float2(w.z, w.w) : make_float2(w.x, w.y);
+            });
 #pragma unroll
             for (int k1 = 0; k1 < 32; k1++)                                         // bin 4 (lane + 32 k1) + warp
                 if (D == 0 || ((row_mask >> k1) & 1u)) pst(P, wbase + lane + 32 * k1, v[k1]);
@@ -359,7 +367,7 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_pair_kernel
                 }
             } else {
             team_barrier(team);                       // every band read of the team is done: the planes are free
-            rscheme_pass2<R>(y, u, P, wbase, tabx + R * 32, lane);    // u[q] = S_warp[k2p + R h + 32 q]
+            rscheme_pass2<R>(y, u, P, wbase, tabx, lane);    // u[q] = S_warp[k2p + R h + 32 q]
             const int k2p = lane / G, h = lane % G;
 #pragma unroll
             for (int qq = 0; qq < R; qq++) {
@@ -421,7 +429,7 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_pair_kernel
                 __syncwarp();
                 dit2<R, true>(y);
                 c2 u[R];
-                rscheme_pass2<R>(y, u, P, 0, tabx + R * 32, lane);
+                rscheme_pass2<R>(y, u, P, 0, tabx, lane);
                 const int k2p = lane / G, h = lane % G;
                 c2 ph0;
                 if constexpr (kMix == 2) ph0 = direct_phasors(nco.nco_phase0, nco.nco_fc, oa.base + k2p + R * h, ob.base + k2p + R * h);
