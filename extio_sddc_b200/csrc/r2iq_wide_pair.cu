@@ -55,7 +55,12 @@ constexpr int kWTab1 = 32 * kWTabPitch;             // start of W_4096^n
 constexpr int kWTabX = kWTab1 + 1024;               // start of the per-decimation table
 template <int D>
 __host__ __device__ constexpr int wide_tab_float2() {
-    return kWTabX + 1024;
+    return kWTabX + 32 * kWTabPitch;
+}
+// entry n of a lane's row in a transposed table: one LDS.128 serves n and n + 1
+__device__ __forceinline__ float2 wtab_at(const float2* row, int n) {
+    const float4 w = *reinterpret_cast<const float4*>(row + (n & ~1));
+    return (n & 1) ? make_float2(w.z, w.w) : make_float2(w.x, w.y);
 }
 template <int D>
 __host__ __device__ constexpr int wide_smem_bytes() {
@@ -207,7 +212,7 @@ __device__ __forceinline__ void rscheme_pass2(c2 (&y)[R], c2 (&u)[R], const Plan
 #pragma unroll
     for (int n1 = 0; n1 < 32; n1++) {                     // u_j = sum_r x[j + R r] exp(+2 pi i h (j + R r) / 32)
         const c2 x = pld(P, base + n1 * (R + 1) + k2p);
-        const float2 w = wts[n1 * 32 + lane];
+        const float2 w = wtab_at(wts + lane * kWTabPitch, n1);
         c2& acc = u[brev_n(n1 % R, RB)];
         if (n1 < R) {
             acc = cmul2s(x, w);
@@ -261,8 +266,8 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_pair_kernel
     } else {
         // d >= 1: only the [32][32] weights behind the R unused twiddle rows of tw_sub (their twiddles are folded in)
         constexpr int kSkip = D == 0 ? 0 : (D == 6 ? 64 : (kWHalf >> D) / 4) / 32 * 32;
-        for (int i = threadIdx.x; i < 1024; i += kTeams * kTeamThreads)
-            tab[kWTabX + i] = __ldg((D == 0 ? p.tw_inv : p.tw_sub + kSkip) + i);
+        for (int i = threadIdx.x; i < 1024; i += kTeams * kTeamThreads)     // [n][lane] -> [lane][n]
+            tab[kWTabX + (i & 31) * kWTabPitch + (i >> 5)] = __ldg((D == 0 ? p.tw_inv : p.tw_sub + kSkip) + i);
     }
     const long long n_pairs = (p.total_frames + 1) / 2;
     if (tt == 0) s_pair[team] = (long long)atomicAdd(p.work_counter, 1ULL);
@@ -296,11 +301,7 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_pair_kernel
             for (int n1 = 0; n1 < 32; n1++) v[brev5(n1)] = pld(P, wbase + n1 * 33 + lane);
             __syncwarp();
             // inter-pass twiddles W_1024^(n1 lane) folded into the first stage of the second pass (dft_regs2.cuh)
-            dit2_tw<32, false>(v, [&](int i) {
-                const int n1 = brev5(i);
-                const float4 w = *reinterpret_cast<const float4*>(tw1024 + (n1 & ~1));
-                return (n1 & 1) ? make_float2(w.z, w.w) : make_float2(w.x, w.y);
-            });
+            dit2_tw<32, false>(v, [&](int i) { return wtab_at(tw1024, brev5(i)); });
 #pragma unroll
             for (int k1 = 0; k1 < 32; k1++)                                         // bin 4 (lane + 32 k1) + warp
                 if (D == 0 || ((row_mask >> k1) & 1u)) pst(P, wbase + lane + 32 * k1, v[k1]);
@@ -332,7 +333,7 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_pair_kernel
             __syncwarp();
             // inter-pass twiddles on the reading side (tw_inv row n = twiddle of the element read from row n, written by the
             // lane that plays residue n), folded into the first stage
-            dit2_tw<32, true, false>(t, [&](int i) { return tabx[32 * brev5(i) + lane]; });
+            dit2_tw<32, true, false>(t, [&](int i) { return wtab_at(tabx + lane * kWTabPitch, brev5(i)); });
 #pragma unroll
             for (int k1 = 0; k1 < 32; k1++) pst(P, wbase + lane + 32 * k1, t[k1]);   // W_4096^(-warp n) follows in phase E
         } else if constexpr (D <= 5) {
