@@ -23,9 +23,14 @@ struct FusedParams {
     const float2* gck;          // [1024]    (-i*W_2048^k) * gk[k]
     const float2* gp;           // [1024]    gk + gck   (dual-frame kernel: Y = gp*a + gq*conj(b))
     const float2* gq;           // [1024]    gk - gck
-    const float2* tw_inv;       // d=0: [32][32] conj(W_1024)^((lane-tunebin)*k2); d>=1: [32][L] conj(W_M)^(n1*k2)
-    const float2* tw_aux;       // d=1..5 dual-frame kernels: [R][32] exp(+2 pi i lane k2 / mfft), R = 32>>d, then
-                                // [32][32] exp(+2 pi i (lane % (32/R)) n1 / 32); else null
+                                // shipped kernels (r2iq_pair.cu), d >= 1: `gp` carries ONE float4 table (P, Q) in band order
+                                // ([mfft]: position m holds bin tunebin + s(m)), `gq` is null
+    const float2* tw_inv;       // d=0: [32][32] conj(W_1024)^((lane-tunebin)*k2) -- shipped kernels: in READER order, row n =
+                                // twiddle of the element read from row n of the transposition; d>=1: [32][L] conj(W_M)^(n1*k2)
+    const float2* tw_aux;       // d=1..4: [R][32] exp(+2 pi i lane k2 / mfft), R = 32>>d, then the pass-2 weights [32][32]
+                                // exp(+2 pi i (lane % (32/R)) n1 / 32) -- shipped kernels: times exp(+2 pi i n1 (lane / G) / mfft),
+                                // the folded pass-1 twiddle; d = 5, 6 (shipped kernels): [32 columns][32] float4 coefficients
+                                // exp(-2 pi i n1 k / 1024) of the column's band bin and mirror bin (direct evaluation)
     int tunebin;
     int band_lo, band_hi;       // forward-FFT bins [lo,hi) that feed the inverse transform
     uint32_t row_mask;          // bit k1 set: spectrum row [32*k1, 32*k1+32) holds a band bin or the mirror of one

@@ -51,8 +51,8 @@ const char* fused_kernel_name(int d, bool direct_mixer) {
 
 cudaError_t launch_fused(int d, const FusedParams& p, int sm_count, cudaStream_t stream) {
     // The shipped library has ONE kernel per decimation: r2iq_pair.cu -- 8 free-running warps per SM for d = 0, 12 for
-    // d = 1..6 (B200, 8192 blocks: 514 / 597 / 788 / 905 / 977 / 994 Gsamples/s at d = 0..5 against 454 / 601 / 759 /
-    // 865 / 929 / 963 of the round-1 kernels).
+    // d = 1..6 (B200, 8192 blocks: 529 / 663 / 855 / 989 / 1111 / 1284 / 1297 Gsamples/s at d = 0..6 against 454 / 601 /
+    // 759 / 865 / 929 / 963 / 833 of the round-1 kernels).
     if (g_kernel_gen == 0) return launch_pair(d, d == 0 ? 8 : 12, p, sm_count, stream);
 #ifdef R2IQ_AB_VARIANTS
     // Comparison builds (-DR2IQ_AB_VARIANTS, env R2IQ_KERNEL_GEN): 1 = first generation (r2iq_gen1.cu); 2 / 3 = first
