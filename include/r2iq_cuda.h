@@ -168,7 +168,9 @@ R2IQ_API int r2iq_cuda_process_rates(r2iq_cuda_t h, const int16_t* blocks, long 
  * ONE HANDLE, ONE STREAM: a handle's device-path launches share per-handle scratch (the work-counter ring, and in
  * R2IQ_NCO_REFERENCE mode the start-phasor buffer, whose upload also synchronises the stream), so all device-path calls
  * on one handle must be issued on the same stream, or be ordered by the caller.  Use one handle per stream for
- * concurrent work; handles share nothing.  (R2IQ_NCO_DIRECT and mixer-off launches touch no host state at all.) */
+ * concurrent work; handles share nothing.  (R2IQ_NCO_DIRECT and mixer-off launches touch no host state at all.)
+ * One launch takes at most 49,941,000 blocks (the kernels index frames with 32 bits; 6.5 TB of samples): more is
+ * R2IQ_E_INVALID. */
 R2IQ_API int r2iq_cuda_process_device(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d_iq_out, void* stream);
 
 /* Wideband channelizer: n_channels tuned channels from ONE input stream.  Channel c is tuned to tunebins[c]

@@ -409,7 +409,7 @@ def test_fine_tune_mixer_direct_mode(op):
     reduced in float64 on the device, inside the fused kernel's store epilogue.  Stated tolerance: rel-L2 <= 1e-6 and
     max-abs <= 1e-5 of full scale against the float64 ideal applied to the unmixed float32 stream -- at the start of the
     stream and after 2.7e8 output samples (phase carried over 65 calls); every decimation, sideband on and off, both
-    FFTN families (8192 mixes in a separate pass).  The reference's own mixer is further from that ideal than this one:
+    FFTN families (both mix in the store epilogue of their fused kernels).  The reference's own mixer is further from that ideal than this one:
     its phase increment and its 128-sample step are float32 values, so its frequency is off by a few 1e-8 relative and
     the two streams drift apart linearly (measured 1.2e-4 rel-L2 over 2e5 samples at d = 0) -- checked loosely."""
     from extio_sddc_b200 import capi as _capi
