@@ -180,7 +180,7 @@ R2IQ_API int r2iq_cuda_process_device(r2iq_cuda_t h, const int16_t* d_in, long n
  * [c*n_blocks*(32768>>d), (c+1)*n_blocks*(32768>>d)) complex floats.
  *   FFTN 2048, d >= 1: a single pass; the forward FFT of every frame is computed once and shared by all channels
  *                      (d = 5, 6: one channel per lane on the packed two-frame kernels; d = 1..4: lane groups).
- *   d = 0 or FFTN 8192: one launch of the single-channel kernel per channel (the reference's one operator per tuned
+ *   d = 0, 1 or FFTN 8192: one launch of the single-channel kernel per channel (the reference's one operator per tuned
  *                      instance; same result, forward FFT not shared).
  * Host-buffer form: history as r2iq_cuda_process (NULL = zeros; no state is carried).
  * Device form: d_in = [halfFft history | blocks], d_in and d_iq_out 16-byte aligned, asynchronous on `stream`. */
