@@ -1,115 +1,21 @@
-// r2iq_channels.cu -- wideband channelizer: many tuned DDC channels from ONE ADC stream.
+// r2iq_channels.cu -- wideband channelizer: many tuned DDC channels from ONE ADC stream (BASELINE config 4).
 //
-// The reference runs one fft_mt_r2iq per tuned channel, so C channels cost C forward FFTs of every
-// frame (Core/fft_mt_r2iq_impl.hpp:84-98).  Here a warp transforms a frame ONCE, leaves the 1024
-// half-spectrum bins Z in shared memory, and then serves the channels in groups of 2^d: each
-// channel's mfft-bin band is cut out at its own tune bin (same split / filter / edge zero-fill
-// arithmetic as the single-channel kernels: impl.hpp:76-96), staged, and the whole group is
-// transformed back at once by inverse_bands (32>>d lanes per channel).  Per channel the result is
-// the stream a separate operator tuned to that bin would produce.
-// Output is channel-major: channel c writes out[c*out_stride + ...].
+// The reference runs one fft_mt_r2iq per tuned channel, so C channels cost C forward FFTs of every frame
+// (Core/fft_mt_r2iq_impl.hpp:84-98).  Here a warp transforms a frame PAIR once (packed two-frame lanes, TMA-staged
+// input, as r2iq_pair.cu), forms the real-FFT split once, and serves every channel from it with the split / filter /
+// edge zero-fill arithmetic of the single-channel kernels (impl.hpp:76-96); per channel the result is the stream a
+// separate operator tuned to that bin would produce.  Output is channel-major: channel c writes out[c*out_stride + ...].
+//   d = 5, 6 (mfft 32, 16): r2iq_channels_lane_kernel -- a LANE per channel, backward transform in its registers, one TMA
+//                           bulk store per channel run;
+//   d = 2, 3, 4           : r2iq_channels_pair_kernel -- channels one after the other, backward transform across the lanes;
+//   d = 0, 1 (and FFTN 8192): one single-channel launch per channel (r2iq_capi.cu: launch_channels_impl).
+// (The first-generation kernel -- one scalar frame per warp, groups of 2^d channels cut, staged and transformed back
+// together -- is gone: 8.96 / 4.21 / 2.85 ms for 64 channels x 2048 blocks at d = 2 / 3 / 4 against 4.45 / 2.26 / 1.01.)
 #include "dual_frame.cuh"
 #include "r2iq_common.cuh"
 #include "work_dispenser.cuh"
 
 namespace r2iq {
-
-namespace {
-
-constexpr int kChWarps = 4;
-constexpr int kChThreads = kChWarps * 32;
-// per warp: transposition tile (kScratch) + staged bands (kStage) + the frame's spectrum (1024 bins)
-constexpr int kChWarpFloat2 = kScratch + kStage + kHalfFft;
-
-// Forward transform of frame f (same two radix-32 register passes as r2iq_fused_kernel).
-__device__ __forceinline__ void forward_frame_ch(const ChannelParams& p, long long f, int lane, float2* S,
-                                                 float2 (&v)[32]) {
-    const long long b = f / kFramesPerBlock;
-    const int k = (int)(f - b * kFramesPerBlock);
-    const uint32_t* src = p.in_words + b * (kTransferSamples / 2) + k * (kHop / 2) + lane;
-    uint32_t w[32];
-#pragma unroll
-    for (int j = 0; j < 32; j++) w[j] = __ldg(src + 32 * j);
-#pragma unroll
-    for (int j = 0; j < 32; j++) v[brev(j, 5)] = unpack_pair(w[j], p.rand_mul);
-    dit<32, false>(v);
-#pragma unroll
-    for (int k2 = 1; k2 < 32; k2++) v[k2] = cmul(v[k2], __ldg(&p.tw_fwd[k2 * 32 + lane]));
-#pragma unroll
-    for (int k2 = 0; k2 < 32; k2++) S[lane * 33 + k2] = v[k2];
-    __syncwarp();
-#pragma unroll
-    for (int n1 = 0; n1 < 32; n1++) v[brev(n1, 5)] = S[n1 * 33 + lane];
-    __syncwarp();
-    dit<32, false>(v);
-}
-
-}  // namespace
-
-template <int D>
-__global__ void __launch_bounds__(kChThreads, 2) r2iq_channels_kernel(const ChannelParams p) {
-    constexpr bool kDyn = true;   // frames from the device-wide counter (work_dispenser.cuh); warps run free
-    using G = Geo<D>;
-    constexpr int M = G::M;
-    constexpr int GROUP = G::ROUNDS;     // channels transformed back together
-    extern __shared__ float2 smem[];
-    const int lane = threadIdx.x & 31;
-    const int warp = threadIdx.x >> 5;
-    float2* S = smem + warp * kChWarpFloat2;
-    float2* stage = S + kScratch;
-    float2* Z = stage + kStage;
-
-    PairDispenser<kDyn, true, kChWarps> work;
-    work.init(p.work_counter, nullptr, lane, warp);
-    for (; work.more(p.total_frames); work.advance()) {
-        work.top(p.work_counter, nullptr);
-        const long long f = work.cur(warp);
-        {
-            float2 v[32];
-            forward_frame_ch(p, f, lane, S, v);
-#pragma unroll
-            for (int k1 = 0; k1 < 32; k1++) Z[32 * k1 + lane] = v[k1];
-        }
-        __syncwarp();
-        const FrameOut fo = frame_out<D>(f);
-        for (int c0 = 0; c0 < p.n_channels; c0 += GROUP) {
-            // cut the bands of channels c0 .. c0+GROUP-1: element e = lane + 32*i is bin m of channel j
-#pragma unroll 4
-            for (int i = 0; i < 32; i++) {
-                const int e = lane + 32 * i;
-                const int j = e / M;              // GROUP * M = 1024 elements for every d
-                const int m = e & (M - 1);
-                const int ch = c0 + j;
-                float2 y = make_float2(0.f, 0.f);
-                if (ch < p.n_channels) {
-                    const int s = m < M / 2 ? m : m - M;
-                    const int k = __ldg(&p.tunebins[ch]) + s;
-                    if (k >= 0 && k < kHalfFft) {      // outside: zero fill (impl.hpp:91-96)
-                        const float2 a = Z[k];
-                        const float2 b = Z[(kHalfFft - k) & (kHalfFft - 1)];
-                        const float2 c = __ldg(&p.ctab[k]);       // -i * W_2048^k
-                        const float2 h = __ldg(&p.gh[m]);         // 0.5 * H_d at inverse-FFT bin m
-                        const float ux = a.x + b.x, uy = a.y - b.y;
-                        const float wx = a.x - b.x, wy = a.y + b.y;
-                        const float xx = fmaf(c.x, wx, fmaf(-c.y, wy, ux));   // 2*X[k] = u + c*w
-                        const float xy = fmaf(c.x, wy, fmaf(c.y, wx, uy));
-                        y = make_float2(fmaf(h.x, xx, -h.y * xy), fmaf(h.x, xy, h.y * xx));
-                    }
-                }
-                stage[j * G::GS + m] = y;
-            }
-            inverse_bands<D, true>(lane, S, stage, p.tw_inv, p.imag_sign, [&](int g) {
-                Placement pl;
-                pl.out = p.out + (long long)(c0 + g) * p.out_stride;
-                pl.fo = fo;
-                pl.live = c0 + g < p.n_channels;
-                return pl;
-            });
-        }
-        __syncwarp();
-    }
-}
-
 
 // ---------------------------------------------------------------------------------------------------------------
 // d = 5 and 6 (mfft = 32 / 16: the "many narrow channels" case): ONE LANE PER CHANNEL on the packed two-frame lanes of
@@ -130,7 +36,6 @@ __global__ void __launch_bounds__(kChThreads, 2) r2iq_channels_kernel(const Chan
 namespace {
 using namespace dualf;
 constexpr int kLaneWarps = 7;
-constexpr int kLanePairBytes = (kHop + kFftN) * 2;                       // 7168: frames A and B of a pair
 template <int D>
 struct LaneGeo {
     static constexpr int M = kHalfFft >> D;
@@ -335,49 +240,221 @@ static cudaError_t launch_ch_lane(const ChannelParams& p, int sm_count, cudaStre
     return cudaGetLastError();
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// d = 2, 3, 4 (mfft 256, 128, 64): the channelizer on the packed two-frame generation (round 2).
+//   1. forward transform of a frame PAIR exactly as r2iq_pair.cu (TMA pair copy, integer-pipe conversion with the bias
+//      folded into the first butterfly stage, two radix-32 register passes, inter-pass twiddles folded into the second);
+//   2. the real-FFT split ONCE for all channels: X'[k] = (a + conj b) + c[k] (a - conj b), a = Z[k], b = Z[1024 - k],
+//      c = -i W_2048^k (the factor 1/2 lives in gh), written back to the warp's tile in natural order;
+//   3. per channel: the lane gathers its R = mfft / 32 band bins m = lane + 32 j around the channel's tune bin (zero
+//      outside [0, 1024): Core/fft_mt_r2iq_impl.hpp:91-96), multiplies by gh[m] (R per-lane constants) and runs the
+//      mfft-point backward transform as an R-point register DFT, a twiddle and R 32-point transforms ACROSS THE LANES
+//      (dual_frame.cuh: warp_idft32) -- nothing but the gather touches shared memory, so the spectrum stays where it is
+//      for the next channel; lane l stores the R consecutive samples R brev5(l) ... of both frames.
+// Per channel and frame pair ~145 / 290 / 610 instructions (d = 4 / 3 / 2) on top of ~1900 for the shared part, against
+// a whole single-channel kernel (1900 .. 2300) per channel.
+// ---------------------------------------------------------------------------------------------------------------
+namespace {
+constexpr int kCpWarps = 12;
+constexpr int kCpTabPitch = 34;
+constexpr int kCpXPitch = 12;                                            // per-lane cross-lane twiddles: 4 + (R - 1) <= 11 entries
+constexpr int kCpTabFloat2 = 32 * kCpTabPitch + 1024 + 32 * kCpXPitch;    // tw_fwd transposed | ctab | cross-lane twiddles
+constexpr int kCpMaxListed = 256;
+constexpr int kCpWarpBytes = kTile * 16 + 16;                            // tile (spectrum; the next pair lands in its tail) | mbarrier
+constexpr int kCpSmemBytes = kCpTabFloat2 * 8 + kCpMaxListed * 4 + kCpWarps * kCpWarpBytes;
+constexpr int kCpLandOff = kTile * 16 - (kHop + kFftN) * 2;
+}  // namespace
+
 template <int D>
-static cudaError_t setup_ch() {
-    cudaError_t e = cudaFuncSetAttribute(r2iq_channels_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         (int)(kChWarps * kChWarpFloat2 * sizeof(float2)));
+__global__ void __launch_bounds__(kCpWarps * 32, 1) r2iq_channels_pair_kernel(const ChannelParams p) {
+    constexpr int M = kHalfFft >> D;
+    constexpr int R = M / 32;
+    constexpr int RB = ilog2(R);
+    extern __shared__ __align__(128) unsigned char cp_smem[];
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    float2* tab = reinterpret_cast<float2*>(cp_smem);
+    const float2* twf = tab + lane * kCpTabPitch;
+    const float2* ctab = tab + 32 * kCpTabPitch;
+    const float2* xw = tab + 32 * kCpTabPitch + 1024 + lane * kCpXPitch;
+    int* listed = reinterpret_cast<int*>(cp_smem + kCpTabFloat2 * 8);
+    unsigned char* wbase = cp_smem + kCpTabFloat2 * 8 + kCpMaxListed * 4 + (size_t)warp * kCpWarpBytes;
+    u64* S = reinterpret_cast<u64*>(wbase);
+    const uint32_t* inA = reinterpret_cast<const uint32_t*>(wbase + kCpLandOff);
+    const uint32_t mbar = smem_u32(wbase + kCpWarpBytes - 16);
+    const uint32_t dst = smem_u32(inA);
+
+    for (int i = threadIdx.x; i < 1024; i += kCpWarps * 32) {
+        tab[(i & 31) * kCpTabPitch + (i >> 5)] = __ldg(p.tw_fwd + i);
+        tab[32 * kCpTabPitch + i] = __ldg(p.ctab + i);
+    }
+    for (int i = threadIdx.x; i < 32 * (3 + R); i += kCpWarps * 32)
+        tab[32 * kCpTabPitch + 1024 + (i & 31) * kCpXPitch + (i >> 5)] = warp_idft_twiddle(i & 31, i >> 5, M);
+    const bool in_smem = p.n_channels <= kCpMaxListed;
+    if (in_smem)
+        for (int i = threadIdx.x; i < p.n_channels; i += kCpWarps * 32) listed[i] = __ldg(p.tunebins + i);
+    if (lane == 0) {
+        mbar_init(mbar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+
+    FusedParams fp;                 // frame_src only reads in_words
+    fp.in_words = p.in_words;
+    const long long n_pairs = (p.total_frames + 1) / 2;
+    auto issue = [&](long long pair) {
+        const long long fa = 2 * pair;
+        const uint32_t* src = frame_src(fp, fa);
+        uint32_t bytes = kFrameBytes;
+        if (fa + 1 < p.total_frames) bytes += (uint32_t)(frame_src(fp, fa + 1) - src) * 4;
+        mbar_expect_tx(mbar, bytes);
+        tma_load_1d(dst, src, bytes, mbar);
+    };
+    unsigned long long g0 = 0, g1 = 0, pend = 0;
+    if (lane == 0) {
+        g0 = atomicAdd(p.work_counter, 1ULL);
+        g1 = atomicAdd(p.work_counter, 1ULL);
+        pend = atomicAdd(p.work_counter, 1ULL);
+    }
+    long long q = (long long)__shfl_sync(0xffffffffu, g0, 0);
+    long long qn = (long long)__shfl_sync(0xffffffffu, g1, 0);
+    if (lane == 0 && q < n_pairs) issue(q);
+    uint32_t phase = 0;
+    const uint32_t sgn = __float_as_uint(p.imag_sign) & 0x80000000u;
+
+    while (q < n_pairs) {
+        const long long qnn = (long long)__shfl_sync(0xffffffffu, pend, 0);
+        if (lane == 0) pend = atomicAdd(p.work_counter, 1ULL);
+        const int offB = ((uint32_t)(2 * q) % (uint32_t)kFramesPerBlock == kFramesPerBlock - 1) ? kHalfFft / 2 : kHop / 2;
+        const uint32_t* inB = inA + offB;
+        {
+            c2 v[32];
+            mbar_wait(mbar, phase);
+            phase ^= 1;
+#pragma unroll
+            for (int j = 0; j < 32; j++) unpack_words_biased(inA[lane + 32 * j], inB[lane + 32 * j], p.rand_mul, v[brev5(j)]);
+            __syncwarp();
+            // ---- forward 1024-point transform (r2iq_pair.cu) ----------------------------------------------------
+            dit2_biased<32, false>(v);
+#pragma unroll
+            for (int k2 = 0; k2 < 32; k2++) sts2(S, lane * 33 + k2, v[k2]);
+            __syncwarp();
+#pragma unroll
+            for (int n1 = 0; n1 < 32; n1++) v[brev5(n1)] = lds2(S, n1 * 33 + lane);
+            __syncwarp();
+            dit2_tw<32, false>(v, [&](int i) {
+                const int n1 = brev5(i);
+                const float4 w = *reinterpret_cast<const float4*>(twf + (n1 & ~1));
+                return (n1 & 1) ? make_float2(w.z, w.w) : make_float2(w.x, w.y);
+            });                                       // v[k1] = Z[32 k1 + lane]
+            // ---- real-FFT split, once for all channels ------------------------------------------------------------
+#pragma unroll
+            for (int k1 = 0; k1 < 32; k1++) sts2(S, 32 * k1 + lane, v[k1]);
+            __syncwarp();
+#pragma unroll
+            for (int k1 = 0; k1 < 32; k1++) {
+                const int k = 32 * k1 + lane;
+                const c2 a = v[k1];
+                const c2 b = lds2(S, (kHalfFft - k) & (kHalfFft - 1));
+                const float2 c = ctab[k];
+                const u64 ore = sub2(a.re, b.re), oim = add2(a.im, b.im);      // a - conj b
+                c2 x;
+                x.re = fma2(bc(c.x), ore, fma2(bc(-c.y), oim, add2(a.re, b.re)));
+                x.im = fma2(bc(c.x), oim, fma2(bc(c.y), ore, sub2(a.im, b.im)));
+                v[k1] = x;
+            }
+            __syncwarp();   // every mirror read is done: the tile takes the split spectrum
+#pragma unroll
+            for (int k1 = 0; k1 < 32; k1++) sts2(S, 32 * k1 + lane, v[k1]);
+            __syncwarp();
+        }
+        // ---- per channel: gather, filter, backward transform across the lanes, store ------------------------------
+        float2 gh[R];
+#pragma unroll
+        for (int j = 0; j < R; j++) gh[j] = __ldg(p.gh + lane + 32 * j);
+        const float4 w01 = *reinterpret_cast<const float4*>(xw), w23 = *reinterpret_cast<const float4*>(xw + 2);
+        const float2 wsh[4] = {make_float2(w01.x, w01.y), make_float2(w01.z, w01.w), make_float2(w23.x, w23.y), make_float2(w23.z, w23.w)};
+        const FrameOut2 oa = frame_out2<D>(2 * q, p.total_frames);
+        const FrameOut2 ob = frame_out2<D>(2 * q + 1, p.total_frames);
+        const int idx0 = R * brev5(lane);
+        const bool keepA = idx0 >= oa.lo && idx0 < 3 * M / 4;          // lo and 3 mfft / 4 are multiples of R
+        const bool keepB = ob.live && idx0 >= ob.lo && idx0 < 3 * M / 4;
+        for (int ch = 0; ch < p.n_channels; ch++) {
+            const int tb = in_smem ? listed[ch] : __ldg(p.tunebins + ch);
+            c2 y[R];
+#pragma unroll
+            for (int j = 0; j < R; j++) {
+                const int m = lane + 32 * j;
+                const int kk = tb + (m < M / 2 ? m : m - M);
+                const bool inside = (unsigned)kk < (unsigned)kHalfFft;       // bins outside [0, halfFft) are zero
+                const c2 x = lds2(S, kk & (kHalfFft - 1));
+                const float2 g = inside ? gh[j] : make_float2(0.0f, 0.0f);
+                y[brev_n(j, RB)] = cmul2s(x, g);
+            }
+            dit2<R, true>(y);                         // y[e] = sum_j Y[lane + 32 j] W_R^(j e)
+            float2* const outA = p.out + (size_t)ch * p.out_stride + (oa.base + idx0);
+            float2* const outB = p.out + (size_t)ch * p.out_stride + (ob.base + idx0);
+            // the lane's R consecutive samples of each frame leave as 16-byte stores (two samples; the run starts on a
+            // 16-byte boundary: R, mfft / 4 and the channel stride are even, the buffer is 16-byte aligned by contract)
+#pragma unroll
+            for (int e = 0; e < R; e += 2) {
+                const c2 o0 = warp_idft32(e ? cmul2s(y[e], xw[3 + e]) : y[e], wsh, lane);
+                const c2 o1 = warp_idft32(cmul2s(y[e + 1], xw[4 + e]), wsh, lane);
+                float ar0, br0, ai0, bi0, ar1, br1, ai1, bi1;
+                upk(o0.re, ar0, br0);
+                upk(o0.im, ai0, bi0);
+                upk(o1.re, ar1, br1);
+                upk(o1.im, ai1, bi1);
+                if (keepA) *reinterpret_cast<float4*>(outA + e) = make_float4(ar0, flip(ai0, sgn), ar1, flip(ai1, sgn));
+                if (keepB) *reinterpret_cast<float4*>(outB + e) = make_float4(br0, flip(bi0, sgn), br1, flip(bi1, sgn));
+            }
+        }
+        __syncwarp();   // every lane is done with the spectrum: the tail of the tile takes the next pair of frames
+        if (lane == 0 && qn < n_pairs) {
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            issue(qn);
+        }
+        q = qn;
+        qn = qnn;
+    }
+}
+
+template <int D>
+static cudaError_t setup_ch_pair() {
+    cudaError_t e = cudaFuncSetAttribute(r2iq_channels_pair_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, kCpSmemBytes);
     if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(r2iq_channels_kernel<D>, cudaFuncAttributePreferredSharedMemoryCarveout,
+    return cudaFuncSetAttribute(r2iq_channels_pair_kernel<D>, cudaFuncAttributePreferredSharedMemoryCarveout,
                                 cudaSharedmemCarveoutMaxShared);
+}
+
+template <int D>
+static cudaError_t launch_ch_pair(const ChannelParams& p, int sm_count, cudaStream_t stream) {
+    const long long n_pairs = (p.total_frames + 1) / 2;
+    long long grid = sm_count;                        // persistent: one CTA per SM
+    const long long want = (n_pairs + kCpWarps - 1) / kCpWarps;
+    if (grid > want) grid = want;
+    if (grid < 1) grid = 1;
+    cudaError_t e = cudaMemsetAsync(p.work_counter, 0, sizeof(unsigned long long), stream);
+    if (e != cudaSuccess) return e;
+    r2iq_channels_pair_kernel<D><<<(unsigned)grid, kCpWarps * 32, kCpSmemBytes, stream>>>(p);
+    return cudaGetLastError();
 }
 
 cudaError_t setup_channel_kernels() {
     cudaError_t e;
-    if ((e = setup_ch<1>()) != cudaSuccess) return e;
-    if ((e = setup_ch<2>()) != cudaSuccess) return e;
-    if ((e = setup_ch<3>()) != cudaSuccess) return e;
-    if ((e = setup_ch<4>()) != cudaSuccess) return e;
+    if ((e = setup_ch_pair<2>()) != cudaSuccess) return e;
+    if ((e = setup_ch_pair<3>()) != cudaSuccess) return e;
+    if ((e = setup_ch_pair<4>()) != cudaSuccess) return e;
     if ((e = setup_ch_lane<5>()) != cudaSuccess) return e;
     if ((e = setup_ch_lane<6>()) != cudaSuccess) return e;
     return cudaSuccess;
 }
 
-template <int D>
-static cudaError_t launch_ch(const ChannelParams& p, int sm_count, cudaStream_t stream) {
-    const size_t smem = kChWarps * kChWarpFloat2 * sizeof(float2);
-    int ctas = 1;
-    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas, r2iq_channels_kernel<D>, kChThreads, smem);
-    if (e != cudaSuccess) return e;
-    if (ctas < 1) ctas = 1;
-    long long want = (p.total_frames + kChWarps - 1) / kChWarps;
-    long long grid = (long long)sm_count * ctas;
-    if (grid > want) grid = want;
-    if (grid < 1) grid = 1;
-    e = cudaMemsetAsync(p.work_counter, 0, sizeof(unsigned long long), stream);
-    if (e != cudaSuccess) return e;
-    r2iq_channels_kernel<D><<<(unsigned)grid, kChThreads, smem, stream>>>(p);
-    return cudaGetLastError();
-}
-
 cudaError_t launch_channels(int d, const ChannelParams& p, int sm_count, cudaStream_t stream) {
     switch (d) {
-        case 1: return launch_ch<1>(p, sm_count, stream);
-        case 2: return launch_ch<2>(p, sm_count, stream);
-        case 3: return launch_ch<3>(p, sm_count, stream);
-        case 4: return launch_ch<4>(p, sm_count, stream);
+        case 2: return launch_ch_pair<2>(p, sm_count, stream);
+        case 3: return launch_ch_pair<3>(p, sm_count, stream);
+        case 4: return launch_ch_pair<4>(p, sm_count, stream);
         case 5: return launch_ch_lane<5>(p, sm_count, stream);
         case 6: return launch_ch_lane<6>(p, sm_count, stream);
         default: return cudaErrorInvalidValue;

@@ -178,8 +178,9 @@ R2IQ_API int r2iq_cuda_process_device(r2iq_cuda_t h, const int16_t* d_in, long n
  * separate fft_mt_r2iq tuned there would produce (Core/fft_mt_r2iq_impl.hpp:76-138) at the latched decimation, with
  * the current rand / sideband settings.  iq_out is channel-major: channel c occupies
  * [c*n_blocks*(32768>>d), (c+1)*n_blocks*(32768>>d)) complex floats.
- *   FFTN 2048, d >= 1: a single pass; the forward FFT of every frame is computed once and shared by all channels
- *                      (d = 5, 6: one channel per lane on the packed two-frame kernels; d = 1..4: lane groups).
+ *   FFTN 2048, d >= 2: a single pass; the forward FFT and the real-FFT split of every frame pair are computed once and
+ *                      shared by all channels (d = 5, 6: one channel per lane; d = 2..4: channel after channel, the
+ *                      backward transform across the lanes).
  *   d = 0, 1 or FFTN 8192: one launch of the single-channel kernel per channel (the reference's one operator per tuned
  *                      instance; same result, forward FFT not shared).
  * Host-buffer form: history as r2iq_cuda_process (NULL = zeros; no state is carried).

@@ -311,13 +311,14 @@ def test_full_size_properties(d):
 
 def test_config4_channelizer(op):
     """BASELINE config 4: many tuned DDC channels from one stream.  Every channel must equal an
-    independent reference run tuned to that bin (64 channels at d = 5; a subset at d = 3, 1 and 6;
+    independent reference run tuned to that bin (64 channels at d = 5; subsets at d = 1 ... 4 and 6;
     edge channels whose bands leave [0, halfFft) included)."""
     from extio_sddc_b200 import shard
     x = orc.rx888_blocks(2, 5, 256, randomized=True, seed=4)
     hist = np.random.default_rng(4).integers(-2000, 2000, 1024).astype(np.int16)
     for d, bins in ((5, shard.channel_tunebins(64)), (3, [0, 4, 60, 256, 1020] + shard.channel_tunebins(64)[::8]),
-                    (1, [0, 256, 768, 1020]), (6, shard.channel_tunebins(64) + [0, 1020] * 3)):
+                    (1, [0, 256, 768, 1020]), (6, shard.channel_tunebins(64) + [0, 1020] * 3),
+                    (2, [0, 4, 124, 128, 132, 256, 900, 1020]), (4, [0, 4, 28, 32, 36, 60, 256, 1000, 1016, 1020] + shard.channel_tunebins(64)[::4])):
         op.setDecimate(d); op.updateRand(True); op.setSideband(False)
         op.TurnOn()
         got = op.process_channels(x, bins, history=hist)
@@ -329,7 +330,7 @@ def test_config4_channelizer(op):
     # odd frame total (3 blocks = 129 frames: the last pair has one frame), lower sideband, more channels than one pass
     x3 = orc.rx888_blocks(3, 5, 256, randomized=False, seed=14)
     bins = shard.channel_tunebins(64) + [0, 4, 1016, 1020, 512, 500, 12]
-    for d in (5, 6):
+    for d in (5, 6, 4, 3, 2):
         op.setDecimate(d); op.updateRand(False); op.setSideband(True)
         op.TurnOn()
         got = op.process_channels(x3, bins, history=hist)
