@@ -16,7 +16,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIB_DIR = os.path.join(HERE, "lib")
 LIB_PATH = os.path.join(LIB_DIR, "libr2iq_cuda.so")
 # The shipped library: one fused kernel per (FFTN, decimation) plus channelizer, mixer pass and the C ABI.
-SOURCES = ["r2iq_pair.cu", "r2iq_launch.cu", "r2iq_channels.cu", "r2iq_wide_pair.cu", "r2iq_fft.cu", "r2iq_capi.cu", "fir_design.cpp"]
+SOURCES = ["r2iq_pair.cu", "r2iq_launch.cu", "r2iq_channels.cu", "r2iq_wide_pair.cu", "r2iq_wide_channels.cu", "r2iq_fft.cu", "r2iq_capi.cu", "fir_design.cpp"]
 # R2IQ_AB_VARIANTS=1 at build time adds the older kernel generations and their run-time switches (R2IQ_KERNEL_GEN,
 # R2IQ_VARIANT, R2IQ_CTAS_PER_SM) for comparison runs (tools/variant_sweep.py); `r2iq_cuda_version()` then says so.
 SOURCES += [os.path.join("wide_tu", f"r2iq_wide_pair_d{d}{m}.cu") for d in range(7) for m in ("", "m")]   # one module per kernel

@@ -153,6 +153,7 @@ struct r2iq_cuda_s {
     // FFTN 8192 family (r2iq_wide.cu)
     float2* d_twq = nullptr;                       // [3][1024] W_4096^(q n)
     float2* d_wctab = nullptr;                     // [2049] -i * W_8192^p
+    float2* d_wctab_full = nullptr;                // [4096] the same for every bin (FFTN 8192 channelizer)
     struct WideSet { float2* g = nullptr; float2* tw_sub = nullptr; float4* pq = nullptr; float2* tw_inv = nullptr; uint32_t row_mask[4] = {0, 0, 0, 0}; };
     std::map<long long, WideSet> wide_tables;      // per (filter version, d, tunebin)
     Slot slots[kSlots];
@@ -499,6 +500,29 @@ void nco_direct_advance(NcoState& s, size_t n_out) {
     s.phase = ph - floor(ph);
 }
 
+// FFTN 8192: the tables that depend on nothing but the size, once per handle
+int ensure_wide_static_tables(r2iq_cuda_t h) {
+    if (h->d_twq) return R2IQ_OK;
+    std::vector<float2> tq(3 * 1024), ct(2049), cf(4096);
+    for (int q = 1; q <= 3; q++)
+        for (int n = 0; n < 1024; n++) {
+            const double th = -2.0 * kPiD * (double)((q * n) % 4096) / 4096.0;
+            tq[(q - 1) * 1024 + n] = make_float2((float)cos(th), (float)sin(th));
+        }
+    for (int k = 0; k < 4096; k++) {
+        const double th = 2.0 * kPiD * (double)k / 8192.0;
+        cf[k] = make_float2((float)-sin(th), (float)-cos(th));          // -i * exp(-i th)
+        if (k <= 2048) ct[k] = cf[k];
+    }
+    CU(h, cudaMalloc(&h->d_twq, sizeof(float2) * tq.size()));
+    CU(h, cudaMalloc(&h->d_wctab, sizeof(float2) * ct.size()));
+    CU(h, cudaMalloc(&h->d_wctab_full, sizeof(float2) * cf.size()));
+    CU(h, cudaMemcpy(h->d_twq, tq.data(), sizeof(float2) * tq.size(), cudaMemcpyHostToDevice));
+    CU(h, cudaMemcpy(h->d_wctab, ct.data(), sizeof(float2) * ct.size(), cudaMemcpyHostToDevice));
+    CU(h, cudaMemcpy(h->d_wctab_full, cf.data(), sizeof(float2) * cf.size(), cudaMemcpyHostToDevice));
+    return R2IQ_OK;
+}
+
 // FFTN 8192: static twiddles once per handle, filter gains (and small-transform twiddles) per (d, tune bin).
 // The kernels index frames with 32 bits (dual_frame.cuh: frame_src): 2^31 frames is 6.5 TB of samples at FFTN 2048.
 constexpr long kMaxBlocksPerLaunch = 0x7fffffffL / 43 - 1;
@@ -508,22 +532,8 @@ int launch_wide_impl(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d
     if (n_blocks > kMaxBlocksPerLaunch) return fail(R2IQ_E_INVALID, "%ld blocks in one launch (at most %ld)", n_blocks, kMaxBlocksPerLaunch);
     const int d = h->latched_decimate;
     const int HF = 4096, M = HF >> d;
-    if (!h->d_twq) {
-        std::vector<float2> tq(3 * 1024), ct(2049);
-        for (int q = 1; q <= 3; q++)
-            for (int n = 0; n < 1024; n++) {
-                const double th = -2.0 * kPiD * (double)((q * n) % 4096) / 4096.0;
-                tq[(q - 1) * 1024 + n] = make_float2((float)cos(th), (float)sin(th));
-            }
-        for (int k = 0; k <= 2048; k++) {
-            const double th = 2.0 * kPiD * (double)k / 8192.0;
-            ct[k] = make_float2((float)-sin(th), (float)-cos(th));      // -i * exp(-i th)
-        }
-        CU(h, cudaMalloc(&h->d_twq, sizeof(float2) * tq.size()));
-        CU(h, cudaMalloc(&h->d_wctab, sizeof(float2) * ct.size()));
-        CU(h, cudaMemcpy(h->d_twq, tq.data(), sizeof(float2) * tq.size(), cudaMemcpyHostToDevice));
-        CU(h, cudaMemcpy(h->d_wctab, ct.data(), sizeof(float2) * ct.size(), cudaMemcpyHostToDevice));
-    }
+    int rc0 = ensure_wide_static_tables(h);
+    if (rc0 != R2IQ_OK) return rc0;
     const long long key = ((long long)h->hw_version[d] << 20) | ((long long)d << 16) | (long long)tunebin;
     r2iq_cuda_s::WideSet ws;
     auto it = h->wide_tables.find(key);
@@ -697,6 +707,59 @@ int launch_channels_impl(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, cons
     for (int c = 0; c < n_channels; c++)
         if (tunebins[c] < 0 || tunebins[c] >= half || (tunebins[c] & 3))
             return fail(R2IQ_E_INVALID, "channel %d: tune bin %d must be a multiple of 4 in [0,%d)", c, tunebins[c], half);
+    if (h->fftn == 8192 && d == 5 && n_channels >= 2) {
+        // FFTN 8192, d = 5: one forward transform and split per frame pair for all channels (r2iq_wide_channels.cu)
+        int rc = ensure_wide_static_tables(h);
+        if (rc != R2IQ_OK) return rc;
+        const int HF = 4096, M = HF >> d;
+        const long long gkey = ((long long)h->hw_version[d] << 4) | d | (1LL << 40);
+        float2* gh = nullptr;
+        auto git = h->gh_tables.find(gkey);
+        if (git != h->gh_tables.end()) gh = git->second;
+        else {
+            std::vector<float2> g(M);
+            for (int m = 0; m < M; m++) {
+                const int s = m < M / 2 ? m : m - M;
+                const std::complex<float> hh = h->hw[d][(s + HF) % HF];
+                g[m] = make_float2(0.5f * hh.real(), 0.5f * hh.imag());
+            }
+            CU(h, cudaMalloc(&gh, sizeof(float2) * M));
+            CU(h, cudaMemcpy(gh, g.data(), sizeof(float2) * M, cudaMemcpyHostToDevice));
+            h->gh_tables[gkey] = gh;
+        }
+        std::vector<int> key(tunebins, tunebins + n_channels);
+        int* d_list = nullptr;
+        auto lit = h->chan_lists.find(key);
+        if (lit != h->chan_lists.end()) d_list = lit->second;
+        else {
+            if (h->chan_lists.size() >= 256) {
+                CU(h, cudaDeviceSynchronize());
+                for (auto& kv : h->chan_lists) cudaFree(kv.second);
+                h->chan_lists.clear();
+            }
+            CU(h, cudaMalloc(&d_list, sizeof(int) * n_channels));
+            CU(h, cudaMemcpy(d_list, tunebins, sizeof(int) * n_channels, cudaMemcpyHostToDevice));
+            h->chan_lists[key] = d_list;
+        }
+        WideChannelParams p;
+        p.in_words = (const uint32_t*)d_in;
+        p.out = (float2*)d_out;
+        p.out_stride = (long long)n_blocks * ((kTransferSamples / 2) >> d);
+        p.total_frames = (long long)n_blocks * 11;
+        p.tw1024 = h->d_tw_fwd;
+        p.twq = h->d_twq;
+        p.ctab = h->d_wctab_full;
+        p.gh = gh;
+        p.tunebins = d_list;
+        p.n_channels = n_channels;
+        p.rand_mul = h->rand_on ? 0xFFFEu : 0u;
+        p.imag_sign = h->latched_sideband ? -1.0f : 1.0f;
+        p.work_counter = h->next_counter();
+        CU(h, launch_wide_channels(p, h->sm_count, stream));
+        h->stats.kernel_launches++;
+        h->stats.blocks_processed += (uint64_t)n_blocks;
+        return R2IQ_OK;
+    }
     if (h->fftn != kFftN || d <= 1) {
         // FFTN 8192, and d = 0, 1 (every channel needs a backward transform of the size of the forward one or half of it:
         // sharing the forward transform saves little, and the single-channel kernels are the faster code -- 64 channels,
@@ -854,7 +917,7 @@ int r2iq_cuda_create(const r2iq_cuda_config* cfg, r2iq_cuda_t* out) {
         return bail(fail(R2IQ_E_CUDA, "channelizer kernel setup: %s", cudaGetErrorString(e)));
     if ((e = setup_fused_kernels()) != cudaSuccess)
         return bail(fail(R2IQ_E_CUDA, "kernel setup: %s", cudaGetErrorString(e)));
-    if ((e = setup_wide_kernels()) != cudaSuccess)
+    if ((e = setup_wide_kernels()) != cudaSuccess || (e = setup_wide_channel_kernels()) != cudaSuccess)
         return bail(fail(R2IQ_E_CUDA, "FFTN 8192 kernel setup: %s", cudaGetErrorString(e)));
     // forward inter-pass twiddles exp(-2 pi i k2 l / 1024)
     std::vector<float2> tw(32 * 32);
@@ -894,6 +957,7 @@ int r2iq_cuda_destroy(r2iq_cuda_t h) {
     }
     cudaFree(h->d_twq);
     cudaFree(h->d_wctab);
+    cudaFree(h->d_wctab_full);
     for (int i = 0; i < kSlots; i++) {
         Slot& s = h->slots[i];
         cudaFree(s.d_out_rates);

@@ -1,0 +1,191 @@
+// r2iq_wide_channels.cu -- channelizer for FFTN = 8192 (the size the reference tree ships, Core/config.h:49) at d = 5
+// (mfft = 128: the "many narrow channels" case of BASELINE config 4).
+//
+// One single-channel launch per channel (r2iq_capi.cu) repeats the whole 4096-point forward transform for every channel.
+// Here a TEAM of four warps transforms a frame pair ONCE with the phases A and B of r2iq_wide_pair.cu, forms the real-FFT
+// split once -- X'[k] = (a + conj b) + c[k] (a - conj b), a = Z[k], b = Z[4096 - k], c = -i W_8192^k -- and leaves it in
+// its four planes (bin 4 m + r in plane r, slot m).  Then, channel after channel:
+//   * warp r gathers the 32 band bins of its plane around the channel's tune bin (a multiple of 4, so the band's bins
+//     4 m' + r are plane r shifted by tunebin / 4; zero outside [0, 4096): Core/fft_mt_r2iq_impl.hpp:91-96), multiplies by
+//     its per-lane filter constant 0.5 H_d and runs the 32-point per-plane backward transform across the lanes
+//     (dual_frame.cuh: warp_idft32); S_r goes to a 2 KB exchange area;                                         team barrier
+//   * 32 threads run the last radix-4 stage across the planes (with the twiddles W_4096^(-r n << 5)) and store the kept
+//     three quarters of both frames into the channel's output stream;                                          team barrier
+// Per channel that is ~130 instructions per warp instead of a whole single-channel kernel (~2300 per thread).
+// Worker-loop semantics per channel: Core/fft_mt_r2iq_impl.hpp:76-138.
+#define R2IQ_WIDE_HELPERS_ONLY
+#include "r2iq_wide_pair.cu"
+
+namespace r2iq {
+
+namespace {
+constexpr int kWcD = 5;
+constexpr int kWcM = kWHalf >> kWcD;                 // 128
+constexpr int kWcMS = kWcM / 4;                      // 32 points per plane
+constexpr int kWcXPitch = 10;
+constexpr int kWcListed = 256;
+constexpr int kWcTabFloat2 = kWTab1 + 1024 + 32 * kWcXPitch + kWcListed / 2;   // tw1024^T | W_4096^n | lane twiddles | tune bins
+constexpr int kWcXchBytes = 2 * 4 * kWcMS * 8;       // S_r of the four planes: re pairs, then im pairs
+constexpr int kWcSmemBytes = kWcTabFloat2 * 8 + kTeams * (kTeamBytes + kWcXchBytes);
+}  // namespace
+
+__global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_channels_kernel(const WideChannelParams p) {
+    constexpr int D = kWcD;
+    constexpr int M = kWcM;
+    constexpr int MS = kWcMS;
+    extern __shared__ __align__(128) unsigned char wcsmem[];
+    __shared__ long long s_pair[kTeams];
+    const int team = threadIdx.x / kTeamThreads;
+    const int tt = threadIdx.x % kTeamThreads;
+    const int lane = tt & 31;
+    const int warp = tt >> 5;                          // plane this warp transforms
+    float2* tab = reinterpret_cast<float2*>(wcsmem);
+    const float2* tw1024 = tab + lane * kWTabPitch;
+    const float2* twq1 = tab + kWTab1;
+    const float2* xw = tab + kWTab1 + 1024 + lane * kWcXPitch;
+    int* listed = reinterpret_cast<int*>(tab + kWTab1 + 1024 + 32 * kWcXPitch);
+    unsigned char* tbase = wcsmem + kWcTabFloat2 * 8 + (size_t)team * (kTeamBytes + kWcXchBytes);
+    Planes P;
+    P.re = reinterpret_cast<float2*>(tbase);
+    P.im = P.re + 4 * kWPlane;
+    float2* xre = reinterpret_cast<float2*>(tbase + kTeamBytes);     // [4][MS] (re_A, re_B)
+    float2* xim = xre + 4 * MS;                                      // [4][MS] (im_A, im_B)
+    const int wbase = warp * kWPlane;
+    const int mbase = ((4 - warp) & 3) * kWPlane;
+    const uint32_t sgn = __float_as_uint(p.imag_sign) & 0x80000000u;
+
+    for (int i = threadIdx.x; i < 1024; i += kTeams * kTeamThreads) {
+        tab[(i & 31) * kWTabPitch + (i >> 5)] = __ldg(p.tw1024 + i);
+        tab[kWTab1 + i] = __ldg(p.twq + i);
+    }
+    for (int i = threadIdx.x; i < 32 * 4; i += kTeams * kTeamThreads)
+        tab[kWTab1 + 1024 + (i & 31) * kWcXPitch + (i >> 5)] = warp_idft_twiddle(i & 31, i >> 5, MS);
+    const bool in_smem = p.n_channels <= kWcListed;
+    if (in_smem)
+        for (int i = threadIdx.x; i < p.n_channels; i += kTeams * kTeamThreads) listed[i] = __ldg(p.tunebins + i);
+    const long long n_pairs = (p.total_frames + 1) / 2;
+    if (tt == 0) s_pair[team] = (long long)atomicAdd(p.work_counter, 1ULL);
+    __syncthreads();
+
+    // this lane's band position inside its plane: slot offset s' in [-16, 16), bin offset s = 4 s' + r, filter index s mod M
+    const int sp = lane < MS / 2 ? lane : lane - MS;
+    const float2 g = __ldg(p.gh + ((4 * sp + warp) & (M - 1)));
+    const float4 w01 = *reinterpret_cast<const float4*>(xw), w23 = *reinterpret_cast<const float4*>(xw + 2);
+    const float2 wsh[4] = {make_float2(w01.x, w01.y), make_float2(w01.z, w01.w), make_float2(w23.x, w23.y), make_float2(w23.z, w23.w)};
+    // only the WideParams fields load_half / quarter_stage read
+    WideParams wp;
+    wp.in_words = p.in_words;
+    wp.total_frames = p.total_frames;
+
+    long long q = s_pair[team];
+    HalfWords w0;
+    load_half(wp, q < n_pairs ? q : 0, tt, 0, w0);
+    while (q < n_pairs) {
+        // ---------------- A: radix-4 DIF over the four quarters of both frames (r2iq_wide_pair.cu) ------------------
+        {
+            HalfWords w1;
+            load_half(wp, q, tt, 4, w1);
+            quarter_stage(w0, P, twq1, p.rand_mul, tt, 0);
+            quarter_stage(w1, P, twq1, p.rand_mul, tt, 4);
+        }
+        team_barrier(team);
+        if (tt == 0) s_pair[team] = (long long)atomicAdd(p.work_counter, 1ULL);   // read again after the channel loop
+
+        // ---------------- B: warp q transforms plane q; all rows back to the plane (mirror exchange) -------------------
+        c2 v[32];
+#pragma unroll
+        for (int j = 0; j < 32; j++) v[brev5(j)] = pld(P, wbase + lane + 32 * j);
+        __syncwarp();
+        dit2<32, false>(v);
+#pragma unroll
+        for (int k2 = 0; k2 < 32; k2++) pst(P, wbase + lane * 33 + k2, v[k2]);
+        __syncwarp();
+#pragma unroll
+        for (int n1 = 0; n1 < 32; n1++) v[brev5(n1)] = pld(P, wbase + n1 * 33 + lane);
+        __syncwarp();
+        dit2_tw<32, false>(v, [&](int i) { return wtab_at(tw1024, brev5(i)); });
+#pragma unroll
+        for (int k1 = 0; k1 < 32; k1++) pst(P, wbase + lane + 32 * k1, v[k1]);
+        team_barrier(team);
+
+        // ---------------- split, once for all channels: bin k = 4 mm + warp, its mirror in plane (4 - warp) & 3 ---------
+#pragma unroll
+        for (int k1 = 0; k1 < 32; k1++) {
+            const int mm = lane + 32 * k1;
+            const c2 a = v[k1];
+            const c2 b = pld(P, mbase + mirror_slot(warp, mm));
+            const float2 c = __ldg(p.ctab + 4 * mm + warp);
+            const u64 ore = sub2(a.re, b.re), oim = add2(a.im, b.im);      // a - conj b
+            c2 x;
+            x.re = fma2(bc(c.x), ore, fma2(bc(-c.y), oim, add2(a.re, b.re)));
+            x.im = fma2(bc(c.x), oim, fma2(bc(c.y), ore, sub2(a.im, b.im)));
+            v[k1] = x;
+        }
+        team_barrier(team);                           // every mirror read of the team is done: the planes take the split
+#pragma unroll
+        for (int k1 = 0; k1 < 32; k1++) pst(P, wbase + lane + 32 * k1, v[k1]);
+        __syncwarp();                                 // a warp gathers from its own plane only
+
+        const FrameOut2 oa = wide_frame_out<D>(2 * q, p.total_frames);
+        const FrameOut2 ob = wide_frame_out<D>(2 * q + 1, p.total_frames);
+        const KeepPair head{oa.lo == 0, ob.live && ob.lo == 0}, rest{true, ob.live};
+        // ---------------- per channel ------------------------------------------------------------------------------------
+        for (int ch = 0; ch < p.n_channels; ch++) {
+            const int tb4 = (in_smem ? listed[ch] : __ldg(p.tunebins + ch)) >> 2;
+            const int slot = tb4 + sp;
+            const bool inside = (unsigned)slot < 1024u;                   // bin 4 slot + warp inside [0, 4096)
+            const c2 x = pld(P, wbase + (slot & 1023));
+            const c2 y = cmul2s(x, inside ? g : make_float2(0.0f, 0.0f));
+            const c2 o = warp_idft32(y, wsh, lane);                        // S_warp[brev5(lane)]
+            {
+                float a0, a1, b0, b1;
+                upk(o.re, a0, a1);
+                upk(o.im, b0, b1);
+                xre[warp * MS + brev5(lane)] = make_float2(a0, a1);
+                xim[warp * MS + brev5(lane)] = make_float2(b0, b1);
+            }
+            team_barrier(team);
+            if (tt < MS) {
+                // last radix-4 stage across the planes: y[n + MS a] = sum_r i^(r a) S_r[n] W_128^(-r n), a = 0..2 kept
+                const int n = tt;
+                auto xld = [&](int r) {
+                    const float2 re = xre[r * MS + n], im = xim[r * MS + n];
+                    return c2{pk(re.x, re.y), pk(im.x, im.y)};
+                };
+                const float2 w1 = twq1[n << D], w2 = csqr(w1), w3 = cmul(w1, w2);
+                const c2 s0 = xld(0), s1 = cmul_conj2s(xld(1), w1), s2 = cmul_conj2s(xld(2), w2), s3 = cmul_conj2s(xld(3), w3);
+                const c2 a0 = cadd(s0, s2), a1 = csub(s0, s2), a2 = cadd(s1, s3), a3 = csub(s1, s3);
+                float2* const outA = p.out + (size_t)ch * p.out_stride + oa.base;
+                float2* const outB = p.out + (size_t)ch * p.out_stride + ob.base;
+                store_pair_rows(outA, outB, head, n, cadd(a0, a2), sgn);
+                store_pair_rows(outA, outB, rest, n + MS, c2{sub2(a1.re, a3.im), add2(a1.im, a3.re)}, sgn);      // a1 + i a3
+                store_pair_rows(outA, outB, rest, n + 2 * MS, csub(a0, a2), sgn);
+            }
+            team_barrier(team);                       // the exchange area is rewritten by the next channel
+        }
+        const long long qn = s_pair[team];
+        load_half(wp, qn < n_pairs ? qn : q, tt, 0, w0);
+        team_barrier(team);                           // the planes are rewritten by the next pair
+        q = qn;
+    }
+}
+
+cudaError_t setup_wide_channel_kernels() {
+    cudaError_t e = cudaFuncSetAttribute(r2iq_wide_channels_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kWcSmemBytes);
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(r2iq_wide_channels_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+}
+
+cudaError_t launch_wide_channels(const WideChannelParams& p, int sm_count, cudaStream_t stream) {
+    const long long n_pairs = (p.total_frames + 1) / 2;
+    long long grid = sm_count;                        // persistent: one CTA per SM
+    const long long want = (n_pairs + kTeams - 1) / kTeams;
+    if (grid > want) grid = want;
+    if (grid < 1) grid = 1;
+    cudaError_t e = cudaMemsetAsync(p.work_counter, 0, sizeof(unsigned long long), stream);
+    if (e != cudaSuccess) return e;
+    r2iq_wide_channels_kernel<<<(unsigned)grid, kTeams * kTeamThreads, kWcSmemBytes, stream>>>(p);
+    return cudaGetLastError();
+}
+
+}  // namespace r2iq

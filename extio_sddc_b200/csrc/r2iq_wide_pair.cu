@@ -227,6 +227,7 @@ __device__ __forceinline__ void rscheme_pass2(c2 (&y)[R], c2 (&u)[R], const Plan
 
 }  // namespace
 
+#ifndef R2IQ_WIDE_HELPERS_ONLY   // r2iq_wide_channels.cu includes this file for the helpers above only
 template <int D, int kMix>
 __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_pair_kernel(const WideParams p, const WideNco nco) {
     constexpr int M = kWHalf >> D;
@@ -531,5 +532,6 @@ const char* wide_kernel_name(int d, bool direct_mixer) {
     return n;
 }
 #endif
+#endif   // R2IQ_WIDE_HELPERS_ONLY
 
 }  // namespace r2iq
