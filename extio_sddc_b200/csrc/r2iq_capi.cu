@@ -707,8 +707,8 @@ int launch_channels_impl(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, cons
     for (int c = 0; c < n_channels; c++)
         if (tunebins[c] < 0 || tunebins[c] >= half || (tunebins[c] & 3))
             return fail(R2IQ_E_INVALID, "channel %d: tune bin %d must be a multiple of 4 in [0,%d)", c, tunebins[c], half);
-    if (h->fftn == 8192 && d == 5 && n_channels >= 2) {
-        // FFTN 8192, d = 5: one forward transform and split per frame pair for all channels (r2iq_wide_channels.cu)
+    if (h->fftn == 8192 && (d == 4 || d == 5) && n_channels >= 2) {
+        // FFTN 8192, d = 4, 5: one forward transform and split per frame pair for all channels (r2iq_wide_channels.cu)
         int rc = ensure_wide_static_tables(h);
         if (rc != R2IQ_OK) return rc;
         const int HF = 4096, M = HF >> d;
@@ -755,7 +755,7 @@ int launch_channels_impl(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, cons
         p.rand_mul = h->rand_on ? 0xFFFEu : 0u;
         p.imag_sign = h->latched_sideband ? -1.0f : 1.0f;
         p.work_counter = h->next_counter();
-        CU(h, launch_wide_channels(p, h->sm_count, stream));
+        CU(h, launch_wide_channels(d, p, h->sm_count, stream));
         h->stats.kernel_launches++;
         h->stats.blocks_processed += (uint64_t)n_blocks;
         return R2IQ_OK;

@@ -141,17 +141,17 @@ struct WideNco {
 cudaError_t setup_wide_kernels();
 cudaError_t launch_wide(int d, const WideParams& p, const WideNco& nco, int sm_count, cudaStream_t stream);
 
-// FFTN = 8192 channelizer at d = 5 (r2iq_wide_channels.cu): one forward transform and split per frame pair, every channel
+// FFTN = 8192 channelizer at d = 4, 5 (r2iq_wide_channels.cu): one forward transform and split per frame pair, every channel
 // served from it.
 struct WideChannelParams {
     const uint32_t* in_words;   // [2048 halo words | n_blocks * 32768 words]
-    float2* out;                // channel c writes out[c*out_stride + ...], n_blocks*(32768>>5) complex each
+    float2* out;                // channel c writes out[c*out_stride + ...], n_blocks*(32768>>d) complex each
     long long out_stride;
     long long total_frames;     // n_blocks * 11
     const float2* tw1024;       // [32][32] W_1024^(k2*lane)
     const float2* twq;          // [1024]   W_4096^n
     const float2* ctab;         // [4096]   -i * W_8192^k
-    const float2* gh;           // [128]    0.5 * H_5 at inverse-FFT bin m (lower half m, upper half m - 128)
+    const float2* gh;           // [mfft]   0.5 * H_d at inverse-FFT bin m (lower half m, upper half m - mfft)
     const int* tunebins;        // [n_channels] device array, multiples of 4 in [0, 4096)
     int n_channels;
     uint32_t rand_mul;
@@ -159,7 +159,7 @@ struct WideChannelParams {
     unsigned long long* work_counter;
 };
 cudaError_t setup_wide_channel_kernels();
-cudaError_t launch_wide_channels(const WideChannelParams& p, int sm_count, cudaStream_t stream);
+cudaError_t launch_wide_channels(int d, const WideChannelParams& p, int sm_count, cudaStream_t stream);   // d = 4, 5
 const char* wide_kernel_name(int d, bool direct_mixer = false);   // as profilers print it
 cudaError_t setup_wide_gen1_kernels();               // r2iq_wide.cu, comparison builds only
 cudaError_t launch_wide_gen1(int d, const WideParams& p, int sm_count, cudaStream_t stream);

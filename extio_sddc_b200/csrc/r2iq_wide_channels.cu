@@ -1,15 +1,15 @@
-// r2iq_wide_channels.cu -- channelizer for FFTN = 8192 (the size the reference tree ships, Core/config.h:49) at d = 5
-// (mfft = 128: the "many narrow channels" case of BASELINE config 4).
+// r2iq_wide_channels.cu -- channelizer for FFTN = 8192 (the size the reference tree ships, Core/config.h:49) at d = 4, 5
+// (mfft = 256, 128: the "many narrow channels" case of BASELINE config 4).
 //
 // One single-channel launch per channel (r2iq_capi.cu) repeats the whole 4096-point forward transform for every channel.
 // Here a TEAM of four warps transforms a frame pair ONCE with the phases A and B of r2iq_wide_pair.cu, forms the real-FFT
 // split once -- X'[k] = (a + conj b) + c[k] (a - conj b), a = Z[k], b = Z[4096 - k], c = -i W_8192^k -- and leaves it in
 // its four planes (bin 4 m + r in plane r, slot m).  Then, channel after channel:
-//   * warp r gathers the 32 band bins of its plane around the channel's tune bin (a multiple of 4, so the band's bins
+//   * warp r gathers the 32 (64) band bins of its plane around the channel's tune bin (a multiple of 4, so the band's bins
 //     4 m' + r are plane r shifted by tunebin / 4; zero outside [0, 4096): Core/fft_mt_r2iq_impl.hpp:91-96), multiplies by
 //     its per-lane filter constant 0.5 H_d and runs the 32-point per-plane backward transform across the lanes
-//     (dual_frame.cuh: warp_idft32); S_r goes to a 2 KB exchange area;                                         team barrier
-//   * 32 threads run the last radix-4 stage across the planes (with the twiddles W_4096^(-r n << 5)) and store the kept
+//     (dual_frame.cuh: warp_idft32); S_r goes to a 2 (4) KB exchange area;                                         team barrier
+//   * 32 (64) threads run the last radix-4 stage across the planes (with the twiddles W_4096^(-r (n << d))) and store the kept
 //     three quarters of both frames into the channel's output stream;                                          team barrier
 // Per channel that is ~130 instructions per warp instead of a whole single-channel kernel (~2300 per thread).
 // Worker-loop semantics per channel: Core/fft_mt_r2iq_impl.hpp:76-138.
@@ -19,20 +19,29 @@
 namespace r2iq {
 
 namespace {
-constexpr int kWcD = 5;
-constexpr int kWcM = kWHalf >> kWcD;                 // 128
-constexpr int kWcMS = kWcM / 4;                      // 32 points per plane
 constexpr int kWcXPitch = 10;
 constexpr int kWcListed = 256;
-constexpr int kWcTabFloat2 = kWTab1 + 1024 + 32 * kWcXPitch + kWcListed / 2;   // tw1024^T | W_4096^n | lane twiddles | tune bins
-constexpr int kWcXchBytes = 2 * 4 * kWcMS * 8;       // S_r of the four planes: re pairs, then im pairs
-constexpr int kWcSmemBytes = kWcTabFloat2 * 8 + kTeams * (kTeamBytes + kWcXchBytes);
+template <int D>
+struct WcGeo {
+    static constexpr int M = kWHalf >> D;             // 128 (d = 5), 256 (d = 4)
+    static constexpr int MS = M / 4;                  // points per plane
+    static constexpr int R = MS / 32;                 // band bins of a plane per lane
+    static constexpr int kXchBytes = 2 * 4 * MS * 8;  // S_r of the four planes: re pairs, then im pairs
+    // W_4096^n (8 KB) sits in shared memory where it fits beside the exchange area (d = 5: 4.2 ms against 4.7 ms with the
+    // table in global memory); at d = 4 the exchange area needs the room
+    static constexpr bool kTwqShared = D == 5;
+    static constexpr int kTabFloat2 = kWTab1 + 32 * kWcXPitch + kWcListed / 2 + (kTwqShared ? 1024 : 0);   // tw1024^T | lane twiddles | tune bins | W_4096^n
+    static constexpr int kSmemBytes = kTabFloat2 * 8 + kTeams * (kTeamBytes + kXchBytes);
+};
 }  // namespace
 
+template <int D>
 __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_channels_kernel(const WideChannelParams p) {
-    constexpr int D = kWcD;
-    constexpr int M = kWcM;
-    constexpr int MS = kWcMS;
+    using G = WcGeo<D>;
+    constexpr int M = G::M;
+    constexpr int MS = G::MS;
+    constexpr int R = G::R;
+    constexpr int RB = ilog2(R);
     extern __shared__ __align__(128) unsigned char wcsmem[];
     __shared__ long long s_pair[kTeams];
     const int team = threadIdx.x / kTeamThreads;
@@ -41,10 +50,10 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_channels_ke
     const int warp = tt >> 5;                          // plane this warp transforms
     float2* tab = reinterpret_cast<float2*>(wcsmem);
     const float2* tw1024 = tab + lane * kWTabPitch;
-    const float2* twq1 = tab + kWTab1;
-    const float2* xw = tab + kWTab1 + 1024 + lane * kWcXPitch;
-    int* listed = reinterpret_cast<int*>(tab + kWTab1 + 1024 + 32 * kWcXPitch);
-    unsigned char* tbase = wcsmem + kWcTabFloat2 * 8 + (size_t)team * (kTeamBytes + kWcXchBytes);
+    const float2* twq1 = G::kTwqShared ? tab + kWTab1 + 32 * kWcXPitch + kWcListed / 2 : p.twq;   // W_4096^n
+    const float2* xw = tab + kWTab1 + lane * kWcXPitch;
+    int* listed = reinterpret_cast<int*>(tab + kWTab1 + 32 * kWcXPitch);
+    unsigned char* tbase = wcsmem + G::kTabFloat2 * 8 + (size_t)team * (kTeamBytes + G::kXchBytes);
     Planes P;
     P.re = reinterpret_cast<float2*>(tbase);
     P.im = P.re + 4 * kWPlane;
@@ -56,10 +65,10 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_channels_ke
 
     for (int i = threadIdx.x; i < 1024; i += kTeams * kTeamThreads) {
         tab[(i & 31) * kWTabPitch + (i >> 5)] = __ldg(p.tw1024 + i);
-        tab[kWTab1 + i] = __ldg(p.twq + i);
+        if constexpr (G::kTwqShared) tab[kWTab1 + 32 * kWcXPitch + kWcListed / 2 + i] = __ldg(p.twq + i);
     }
-    for (int i = threadIdx.x; i < 32 * 4; i += kTeams * kTeamThreads)
-        tab[kWTab1 + 1024 + (i & 31) * kWcXPitch + (i >> 5)] = warp_idft_twiddle(i & 31, i >> 5, MS);
+    for (int i = threadIdx.x; i < 32 * (3 + R); i += kTeams * kTeamThreads)
+        tab[kWTab1 + (i & 31) * kWcXPitch + (i >> 5)] = warp_idft_twiddle(i & 31, i >> 5, MS);
     const bool in_smem = p.n_channels <= kWcListed;
     if (in_smem)
         for (int i = threadIdx.x; i < p.n_channels; i += kTeams * kTeamThreads) listed[i] = __ldg(p.tunebins + i);
@@ -67,9 +76,15 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_channels_ke
     if (tt == 0) s_pair[team] = (long long)atomicAdd(p.work_counter, 1ULL);
     __syncthreads();
 
-    // this lane's band position inside its plane: slot offset s' in [-16, 16), bin offset s = 4 s' + r, filter index s mod M
-    const int sp = lane < MS / 2 ? lane : lane - MS;
-    const float2 g = __ldg(p.gh + ((4 * sp + warp) & (M - 1)));
+    // this lane's R band positions inside its plane: slot offset s' in [-MS/2, MS/2), bin offset s = 4 s' + r, filter index s mod M
+    int sp[R];
+    float2 g[R];
+#pragma unroll
+    for (int j = 0; j < R; j++) {
+        const int m = lane + 32 * j;
+        sp[j] = m < MS / 2 ? m : m - MS;
+        g[j] = __ldg(p.gh + ((4 * sp[j] + warp) & (M - 1)));
+    }
     const float4 w01 = *reinterpret_cast<const float4*>(xw), w23 = *reinterpret_cast<const float4*>(xw + 2);
     const float2 wsh[4] = {make_float2(w01.x, w01.y), make_float2(w01.z, w01.w), make_float2(w23.x, w23.y), make_float2(w23.z, w23.w)};
     // only the WideParams fields load_half / quarter_stage read
@@ -132,21 +147,27 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_channels_ke
         // ---------------- per channel ------------------------------------------------------------------------------------
         for (int ch = 0; ch < p.n_channels; ch++) {
             const int tb4 = (in_smem ? listed[ch] : __ldg(p.tunebins + ch)) >> 2;
-            const int slot = tb4 + sp;
-            const bool inside = (unsigned)slot < 1024u;                   // bin 4 slot + warp inside [0, 4096)
-            const c2 x = pld(P, wbase + (slot & 1023));
-            const c2 y = cmul2s(x, inside ? g : make_float2(0.0f, 0.0f));
-            const c2 o = warp_idft32(y, wsh, lane);                        // S_warp[brev5(lane)]
-            {
+            c2 y[R];
+#pragma unroll
+            for (int j = 0; j < R; j++) {
+                const int slot = tb4 + sp[j];
+                const bool inside = (unsigned)slot < 1024u;               // bin 4 slot + warp inside [0, 4096)
+                const c2 x = pld(P, wbase + (slot & 1023));
+                y[brev_n(j, RB)] = cmul2s(x, inside ? g[j] : make_float2(0.0f, 0.0f));
+            }
+            dit2<R, true>(y);                         // y[e] = sum_j Y[lane + 32 j] W_R^(j e)
+#pragma unroll
+            for (int e = 0; e < R; e++) {
+                const c2 o = warp_idft32(e ? cmul2s(y[e], xw[3 + e]) : y[e], wsh, lane);   // S_warp[R brev5(lane) + e]
                 float a0, a1, b0, b1;
                 upk(o.re, a0, a1);
                 upk(o.im, b0, b1);
-                xre[warp * MS + brev5(lane)] = make_float2(a0, a1);
-                xim[warp * MS + brev5(lane)] = make_float2(b0, b1);
+                xre[warp * MS + R * brev5(lane) + e] = make_float2(a0, a1);
+                xim[warp * MS + R * brev5(lane) + e] = make_float2(b0, b1);
             }
             team_barrier(team);
             if (tt < MS) {
-                // last radix-4 stage across the planes: y[n + MS a] = sum_r i^(r a) S_r[n] W_128^(-r n), a = 0..2 kept
+                // last radix-4 stage across the planes: y[n + MS a] = sum_r i^(r a) S_r[n] W_mfft^(-r n), a = 0..2 kept
                 const int n = tt;
                 auto xld = [&](int r) {
                     const float2 re = xre[r * MS + n], im = xim[r * MS + n];
@@ -170,13 +191,15 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_channels_ke
     }
 }
 
-cudaError_t setup_wide_channel_kernels() {
-    cudaError_t e = cudaFuncSetAttribute(r2iq_wide_channels_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kWcSmemBytes);
+template <int D>
+static cudaError_t setup_wc() {
+    cudaError_t e = cudaFuncSetAttribute(r2iq_wide_channels_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, WcGeo<D>::kSmemBytes);
     if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(r2iq_wide_channels_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    return cudaFuncSetAttribute(r2iq_wide_channels_kernel<D>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
 }
 
-cudaError_t launch_wide_channels(const WideChannelParams& p, int sm_count, cudaStream_t stream) {
+template <int D>
+static cudaError_t launch_wc(const WideChannelParams& p, int sm_count, cudaStream_t stream) {
     const long long n_pairs = (p.total_frames + 1) / 2;
     long long grid = sm_count;                        // persistent: one CTA per SM
     const long long want = (n_pairs + kTeams - 1) / kTeams;
@@ -184,8 +207,20 @@ cudaError_t launch_wide_channels(const WideChannelParams& p, int sm_count, cudaS
     if (grid < 1) grid = 1;
     cudaError_t e = cudaMemsetAsync(p.work_counter, 0, sizeof(unsigned long long), stream);
     if (e != cudaSuccess) return e;
-    r2iq_wide_channels_kernel<<<(unsigned)grid, kTeams * kTeamThreads, kWcSmemBytes, stream>>>(p);
+    r2iq_wide_channels_kernel<D><<<(unsigned)grid, kTeams * kTeamThreads, WcGeo<D>::kSmemBytes, stream>>>(p);
     return cudaGetLastError();
+}
+
+cudaError_t setup_wide_channel_kernels() {
+    cudaError_t e = setup_wc<4>();
+    if (e != cudaSuccess) return e;
+    return setup_wc<5>();
+}
+
+cudaError_t launch_wide_channels(int d, const WideChannelParams& p, int sm_count, cudaStream_t stream) {
+    if (d == 4) return launch_wc<4>(p, sm_count, stream);
+    if (d == 5) return launch_wc<5>(p, sm_count, stream);
+    return cudaErrorInvalidValue;
 }
 
 }  // namespace r2iq

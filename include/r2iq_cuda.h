@@ -181,7 +181,7 @@ R2IQ_API int r2iq_cuda_process_device(r2iq_cuda_t h, const int16_t* d_in, long n
  *   FFTN 2048, d >= 2: a single pass; the forward FFT and the real-FFT split of every frame pair are computed once and
  *                      shared by all channels (d = 5, 6: one channel per lane; d = 2..4: channel after channel, the
  *                      backward transform across the lanes).
- *   FFTN 8192, d = 5:  a single pass as well (teams of four warps; r2iq_wide_channels.cu).
+ *   FFTN 8192, d = 4, 5: a single pass as well (teams of four warps; r2iq_wide_channels.cu).
  *   d = 0, 1 and the other FFTN 8192 decimations: one launch of the single-channel kernel per channel (the reference's
  *                      one operator per tuned instance; same result, forward FFT not shared).
  * Host-buffer form: history as r2iq_cuda_process (NULL = zeros; no state is carried).

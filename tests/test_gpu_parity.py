@@ -360,14 +360,14 @@ def test_config4_channelizer(op):
 
 def test_config4_channelizer_fftn8192():
     """The channelizer on the FFTN the reference tree ships (Core/config.h:49): every channel equals an independent
-    reference run at 8192 tuned to that bin (d = 5, 3 and 0; edge bins included)."""
+    reference run at 8192 tuned to that bin (d = 5, 4, 3 and 0; edge bins included)."""
     from extio_sddc_b200 import CudaR2IQ
     op8 = CudaR2IQ(device=0, fftn=8192)
     op8.Init(GAIN)
     x = orc.rx888_blocks(2, 5, 1024, fftn=8192, randomized=True, seed=41)
     hist = np.random.default_rng(41).integers(-2000, 2000, 4096).astype(np.int16)
     for d, bins in ((5, [0, 64, 1024, 2048, 3000, 4092, 4, 60, 68, 124, 128, 4032, 4088] + list(range(100, 4096, 331 * 4))[:8]),
-                    (3, [4, 1024, 4000]), (0, [1024, 0])):
+                    (4, [0, 4, 124, 128, 132, 252, 256, 2048, 3968, 4092]), (3, [4, 1024, 4000]), (0, [1024, 0])):
         op8.setDecimate(d); op8.updateRand(True); op8.setSideband(False)
         op8.TurnOn()
         got = op8.process_channels(x, bins, history=hist)
@@ -376,18 +376,19 @@ def test_config4_channelizer_fftn8192():
         for c, tb in enumerate(bins):
             ref = orc.r2iq(x, d, tb, gain=GAIN, rand=True, history=hist, fftn=8192)
             check(got[c], ref, GAIN, ("channelizer 8192", d, tb))
-    # d = 5 runs the shared-forward kernel (r2iq_wide_channels.cu): odd frame total (3 blocks = 33 frames), lower sideband,
+    # d = 4, 5 run the shared-forward kernel (r2iq_wide_channels.cu): odd frame total (3 blocks = 33 frames), lower sideband,
     # randomizer off, and agreement with the single-channel kernel
     x3 = orc.rx888_blocks(3, 5, 1024, fftn=8192, randomized=False, seed=43)
     bins = [0, 4, 1000, 2044, 2048, 2052, 4088, 4092]
-    op8.setDecimate(5); op8.updateRand(False); op8.setSideband(True)
-    op8.TurnOn()
-    got = op8.process_channels(x3, bins, history=hist)
-    single = op8.process_channels(x3, [1000], history=hist)[0]      # one channel: the single-channel launch
-    op8.TurnOff()
-    for c, tb in enumerate(bins):
-        check(got[c], orc.r2iq(x3, 5, tb, gain=GAIN, rand=False, sideband=True, history=hist, fftn=8192), GAIN, ("channelizer 8192 lsb", tb))
-    assert orc.rel_l2(got[2], single) < 1e-6
+    for d in (5, 4):
+        op8.setDecimate(d); op8.updateRand(False); op8.setSideband(True)
+        op8.TurnOn()
+        got = op8.process_channels(x3, bins, history=hist)
+        single = op8.process_channels(x3, [1000], history=hist)[0]      # one channel: the single-channel launch
+        op8.TurnOff()
+        for c, tb in enumerate(bins):
+            check(got[c], orc.r2iq(x3, d, tb, gain=GAIN, rand=False, sideband=True, history=hist, fftn=8192), GAIN, ("channelizer 8192 lsb", d, tb))
+        assert orc.rel_l2(got[2], single) < 1e-6
     op8.close()
 
 
