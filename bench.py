@@ -669,6 +669,38 @@ def run_ours(args, rank: int, local_rank: int, world: int):
             wop.TurnOff()
         wide = {"fftn": 8192, "value": round(world * len(DECIMS) * wblocks * 65536 / (wtot * 1e-3) / 1e9, 1), "unit": UNIT,
                 "per_decimation": wper, "note": "same capture and sweep on a handle created with fftn = 8192 (halfFft 4096)"}
+        if not args.no_channelizer:
+            # config 4 at the shipped FFTN: 64 channels at d = 5 from one forward transform per frame pair
+            # (r2iq_wide_channels.cu); one channel checked against the single-channel kernel on the same capture
+            wd = 5
+            wbins = [(64 * c) % 4096 for c in range(64)]
+            wper_ch = wblocks * (32768 >> wd)
+            wout = torch.empty(64 * wper_ch, dtype=torch.complex64, device=dev)
+            wop.setDecimate(wd)
+            wop.TurnOn()
+            for _ in range(2):
+                wop.process_channels_device(x.data_ptr(), wblocks, wbins, wout.data_ptr(), stream)
+            torch.cuda.synchronize()
+            w0 = torch.cuda.Event(enable_timing=True)
+            w1 = torch.cuda.Event(enable_timing=True)
+            w0.record()
+            for _ in range(3):
+                wop.process_channels_device(x.data_ptr(), wblocks, wbins, wout.data_ptr(), stream)
+            w1.record()
+            torch.cuda.synchronize()
+            wcms = w0.elapsed_time(w1) / 3
+            one = torch.empty(wper_ch, dtype=torch.complex64, device=dev)
+            wop.tunebin = wbins[17]
+            wop.process_device(x.data_ptr(), wblocks, one.data_ptr(), stream)
+            torch.cuda.synchronize()
+            a = torch.view_as_real(wout[17 * wper_ch:18 * wper_ch])
+            b = torch.view_as_real(one)
+            wrel = float(torch.linalg.vector_norm(a - b) / torch.linalg.vector_norm(b))
+            wop.TurnOff()
+            wide["channelizer"] = {"channels": 64, "d": wd, "blocks_per_gpu": wblocks, "ms": round(wcms, 3), "verified": wrel <= 1e-5,
+                                   "input_gsamples_s": round(wblocks * 65536 / (wcms * 1e-3) / 1e9, 2),
+                                   "note": "every rank its own capture (no sharding); one single-channel launch per channel costs 64 x the d = 5 time above"}
+            del wout, one
         wop.close()
 
     cpu_baseline = None
