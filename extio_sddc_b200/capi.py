@@ -67,6 +67,7 @@ _SIGNATURES = {
     "r2iq_cuda_out_per_block": (_L, [_VP]),
     "r2iq_cuda_process": (_I, [_VP, _VP, _L, _VP, _VP]),
     "r2iq_cuda_process_device": (_I, [_VP, _VP, _L, _VP, _VP]),
+    "r2iq_cuda_process_device_static": (_I, [_VP, _VP, _L, _VP, _VP]),
     "r2iq_cuda_process_rates": (_I, [_VP, _VP, _L, _VP, _VP, _I, _VP]),
     "r2iq_cuda_process_channels": (_I, [_VP, _VP, _L, _VP, _VP, _I, _VP]),
     "r2iq_cuda_process_channels_device": (_I, [_VP, _VP, _L, _VP, _I, _VP, _VP]),

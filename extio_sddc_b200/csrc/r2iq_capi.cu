@@ -1662,3 +1662,218 @@ float r2iq_cuda_freq_to_tunebin(float offset, int d, int* tunebin) {
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// r2iq_cuda_process_device_static: the device path without any allocation (include/r2iq_cuda.h).  No counterpart in
+// the reference.  The fused FFTN 2048 kernel of r2iq_pair.cu is launched
+// with its whole working set -- work counter and per-(filter, d, tune bin) tables -- inside g_static_scratch below
+// instead of the handle's cudaMalloc'ed buffers.  Nothing above this line is touched by it.
+//
+// Layout of the array (bytes):      0  work counter (8 used; cleared before every launch)
+//                                 256  d = 0: gp[1024] float2      d >= 1: (P, Q) in band order, float4[mfft] (<= 8 KB)
+//                                8448  d = 0: gq[1024] float2
+//                               16640  tw_inv[32][32] float2
+//                               24832  tw_aux (d = 1..4: (R + 32) * 32 float2 <= 12 KB; d = 5, 6: float4[1024] = 16 KB)
+//                               41216  end
+// ---------------------------------------------------------------------------------------------
+namespace {
+
+constexpr size_t kStCounter = 0;
+constexpr size_t kStP = 256;
+constexpr size_t kStQ = kStP + sizeof(float2) * kHalfFft;
+constexpr size_t kStTwInv = kStQ + sizeof(float2) * kHalfFft;
+constexpr size_t kStTwAux = kStTwInv + sizeof(float2) * 32 * 32;
+constexpr size_t kStEnd = kStTwAux + sizeof(float4) * 32 * 32;
+static_assert(kStEnd <= R2IQ_STATIC_SCRATCH_BYTES, "table set larger than the static scratch array");
+
+// In host code this name is only a stand-in for the device symbol: never pass it to a kernel -- static_scratch_address()
+// resolves the device address (cudaGetSymbolAddress) once per device.
+static __device__ __align__(256) unsigned char g_static_scratch[R2IQ_STATIC_SCRATCH_BYTES];
+
+constexpr int kStaticMaxDevices = 64;
+struct StaticDevice {
+    unsigned char* base = nullptr;        // device address of g_static_scratch on this device
+    bool tables_valid = false;            // the array holds the tables of (filter, d, tunebin)
+    int d = -1, tunebin = -1;
+    uint32_t row_mask = 0;
+    std::complex<float> filter[kHalfFft];
+};
+StaticDevice g_static_dev[kStaticMaxDevices];
+std::mutex g_static_mu;                                    // the staging image and the per-device records
+alignas(16) unsigned char g_static_img[kStEnd];            // host image of the tables on their way to the device
+
+// Set-up, once per device, with that device current (the caller holds a DeviceGuard).
+int static_scratch_address(r2iq_cuda_t h, StaticDevice& sd) {
+    if (sd.base) return R2IQ_OK;
+    unsigned char* ptr = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress((void**)&ptr, g_static_scratch);
+    if (e != cudaSuccess || !ptr) {
+        cudaGetLastError();
+        return fail(R2IQ_E_CUDA, "cudaGetSymbolAddress(static scratch) on device %d: %s", h->device,
+                    e == cudaSuccess ? "null address" : cudaGetErrorString(e));
+    }
+    sd.base = ptr;
+    return R2IQ_OK;
+}
+
+// The tables get_tables() builds for the shipped kernels, written into the host image (same float64 expressions, so a
+// launch from the array delivers the bits of a launch from the handle's tables).  Returns the row mask.
+uint32_t static_build_tables(const std::complex<float>* H, int d, int tunebin) {
+    const int M = kHalfFft >> d;
+    memset(g_static_img, 0, sizeof(g_static_img));
+    float2* gp = reinterpret_cast<float2*>(g_static_img + kStP);
+    float2* gq = reinterpret_cast<float2*>(g_static_img + kStQ);
+    float4* pqb = reinterpret_cast<float4*>(g_static_img + kStP);
+    float2* tw = reinterpret_cast<float2*>(g_static_img + kStTwInv);
+    uint32_t row_mask = 0;
+    // (P, Q) = gk +- (-i W_2048^k) gk of band offset s; outside [0, halfFft) the band is cut (impl.hpp:91-96)
+    auto pq_at = [&](int s, float2* P, float2* Q) {
+        const int k = tunebin + s;
+        *P = *Q = make_float2(0.f, 0.f);
+        if (k < 0 || k >= kHalfFft) return;
+        const std::complex<double> hh = std::complex<double>(H[(s + kHalfFft) % kHalfFft]) * 0.5;
+        const double th = 2.0 * kPiD * (double)k / (double)kFftN;
+        const std::complex<double> c(-sin(th), -cos(th));
+        const std::complex<double> gc = c * hh;
+        *P = make_float2((float)(hh.real() + gc.real()), (float)(hh.imag() + gc.imag()));
+        *Q = make_float2((float)(hh.real() - gc.real()), (float)(hh.imag() - gc.imag()));
+    };
+    for (int m = 0; m < M; m++) {
+        const int s = m < M / 2 ? m : m - M;
+        const int kk = (tunebin + s) & (kHalfFft - 1);
+        row_mask |= 1u << (kk >> 5);
+        row_mask |= 1u << (((kHalfFft - kk) & (kHalfFft - 1)) >> 5);
+        float2 P, Q;
+        pq_at(s, &P, &Q);
+        if (d == 0) {
+            if (tunebin + s >= 0 && tunebin + s < kHalfFft) {
+                gp[tunebin + s] = P;
+                gq[tunebin + s] = Q;
+            }
+        } else {
+            pqb[m] = make_float4(P.x, P.y, Q.x, Q.y);
+        }
+    }
+    if (d == 0) {
+        for (int n = 0; n < 32; n++)
+            for (int k2 = 0; k2 < 32; k2++) {
+                const int l = (n + tunebin) & 31;
+                const long long n1 = ((l - tunebin) % kHalfFft + kHalfFft) % kHalfFft;
+                const double th = 2.0 * kPiD * (double)((n1 * k2) % kHalfFft) / (double)kHalfFft;
+                tw[n * 32 + k2] = make_float2((float)cos(th), (float)sin(th));
+            }
+    } else {
+        const int L = d <= 5 ? (32 >> d) : 1;
+        for (int k2 = 0; k2 < 32; k2++)
+            for (int n1 = 0; n1 < L; n1++) {
+                const double th = 2.0 * kPiD * (double)((n1 * k2) % M) / (double)M;
+                tw[k2 * L + n1] = make_float2((float)cos(th), (float)sin(th));
+            }
+    }
+    if (d >= 5) {
+        float4* zc = reinterpret_cast<float4*>(g_static_img + kStTwAux);
+        for (int c = 0; c < 32; c++) {
+            auto offset = [&](int u, int* s_out) {
+                u &= 31;
+                if (u < M / 2) { *s_out = u; return true; }
+                if (u >= 32 - M / 2) { *s_out = u - 32; return true; }
+                return false;
+            };
+            int sb = 0, sm = 0;
+            const bool has_b = offset(c - tunebin, &sb), has_m = offset(-c - tunebin, &sm);
+            const int kb = (tunebin + sb) & (kHalfFft - 1);
+            const int km = (kHalfFft - ((tunebin + sm) & (kHalfFft - 1))) & (kHalfFft - 1);
+            for (int n1 = 0; n1 < 32; n1++) {
+                const double tb_ = -2.0 * kPiD * (double)((n1 * kb) % kHalfFft) / (double)kHalfFft;
+                const double tm_ = -2.0 * kPiD * (double)((n1 * km) % kHalfFft) / (double)kHalfFft;
+                zc[c * 32 + n1] = make_float4(has_b ? (float)cos(tb_) : 0.f, has_b ? (float)sin(tb_) : 0.f,
+                                              has_m ? (float)cos(tm_) : 0.f, has_m ? (float)sin(tm_) : 0.f);
+            }
+        }
+    } else if (d >= 1) {
+        const std::vector<float2> ta = build_tw_aux(M, true);
+        memcpy(g_static_img + kStTwAux, ta.data(), sizeof(float2) * ta.size());
+    }
+    return row_mask;
+}
+
+}  // namespace
+
+extern "C" int r2iq_cuda_process_device_static(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d_iq_out, void* stream) {
+    int rc = check_handle(h);
+    if (rc) return rc;
+    if (!h->on) return fail(R2IQ_E_STATE, "process called while the operator is off (call r2iq_cuda_turn_on)");
+    if (n_blocks < 0 || (n_blocks > 0 && (!d_in || !d_iq_out))) return fail(R2IQ_E_INVALID, "process_device_static: bad buffers");
+    if (((uintptr_t)d_in & 15) || ((uintptr_t)d_iq_out & 7))
+        return fail(R2IQ_E_INVALID, "process_device_static: input must be 16-byte and output 8-byte aligned");
+    if (n_blocks > R2IQ_STATIC_MAX_BLOCKS)
+        return fail(R2IQ_E_INVALID, "process_device_static: %ld blocks in one call, the static entry point takes at most %d "
+                    "(use r2iq_cuda_process_device for larger launches)", n_blocks, R2IQ_STATIC_MAX_BLOCKS);
+    if (h->fftn != kFftN)
+        return fail(R2IQ_E_INVALID, "process_device_static: the FFTN %d tables do not fit the %d-byte static scratch array "
+                    "(FFTN 2048 operators only)", h->fftn, R2IQ_STATIC_SCRATCH_BYTES);
+    if (h->device < 0 || h->device >= kStaticMaxDevices)
+        return fail(R2IQ_E_INVALID, "process_device_static: device %d (at most %d devices)", h->device, kStaticMaxDevices);
+    if (kernel_generation() != 0)
+        return fail(R2IQ_E_STATE, "process_device_static: comparison kernel generations use other table layouts");
+    if (n_blocks == 0) return R2IQ_OK;
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (h->nco.on && h->nco.mode != R2IQ_NCO_DIRECT)
+        return fail(R2IQ_E_STATE, "process_device_static: the R2IQ_NCO_REFERENCE fine-tune mixer needs start phasors that grow "
+                    "with the launch; switch to R2IQ_NCO_DIRECT or use r2iq_cuda_process_device");
+    DeviceGuard dg(h->device);
+    CU(h, dg.err);
+    std::lock_guard<std::mutex> slk(g_static_mu);
+    StaticDevice& sd = g_static_dev[h->device];
+    if ((rc = static_scratch_address(h, sd)) != R2IQ_OK) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int d = h->latched_decimate;
+    const int tunebin = h->tunebin.load();
+    const std::complex<float>* H = h->hw[d].data();
+    if (!sd.tables_valid || sd.d != d || sd.tunebin != tunebin || memcmp(sd.filter, H, sizeof(sd.filter)) != 0) {
+        sd.tables_valid = false;
+        sd.row_mask = static_build_tables(H, d, tunebin);
+        // pageable source: the call returns once the image sits in the driver's staging buffer; in stream order before the kernel
+        CU(h, cudaMemcpyAsync(sd.base + kStP, g_static_img + kStP, kStEnd - kStP, cudaMemcpyHostToDevice, st));
+        memcpy(sd.filter, H, sizeof(sd.filter));
+        sd.d = d;
+        sd.tunebin = tunebin;
+        sd.tables_valid = true;
+    }
+    // the array keeps the last call's contents: the counter must start at zero
+    CU(h, cudaMemsetAsync(sd.base + kStCounter, 0, 256, st));
+    const int M = kHalfFft >> d;
+    FusedParams p;
+    p.in_words = (const uint32_t*)d_in;
+    p.out = (float2*)d_iq_out;
+    p.total_frames = (long long)n_blocks * kFramesPerBlock;
+    p.tw_fwd = h->d_tw_fwd;               // a constant of the handle, uploaded by r2iq_cuda_create
+    p.gk = nullptr;                       // read by the comparison generations only
+    p.gck = nullptr;
+    p.gp = reinterpret_cast<const float2*>(sd.base + kStP);
+    p.gq = d == 0 ? reinterpret_cast<const float2*>(sd.base + kStQ) : nullptr;
+    p.tw_inv = reinterpret_cast<const float2*>(sd.base + kStTwInv);
+    p.tw_aux = d == 0 ? nullptr : reinterpret_cast<const float2*>(sd.base + kStTwAux);
+    p.tunebin = tunebin;
+    p.band_lo = tunebin - M / 2 < 0 ? 0 : tunebin - M / 2;
+    p.band_hi = tunebin + M / 2 > kHalfFft ? kHalfFft : tunebin + M / 2;
+    p.row_mask = sd.row_mask;
+    p.rand_mul = h->rand_on ? 0xFFFEu : 0u;
+    p.imag_sign = h->latched_sideband ? -1.0f : 1.0f;
+    p.work_counter = reinterpret_cast<unsigned long long*>(sd.base + kStCounter);
+    p.nco_starts = nullptr;
+    p.nco_tab = nullptr;
+    p.nco_rot = nullptr;
+    p.nco_phase0 = 0.0;
+    p.nco_fc = 0.0;
+    if (h->nco.on) {                      // direct-phase mixer in the store epilogue: d_rot was uploaded by set_fine_tune
+        p.nco_rot = (const float2*)h->nco.d_rot;
+        p.nco_phase0 = h->nco.phase;
+        p.nco_fc = (double)h->nco.fc;
+        nco_direct_advance(h->nco, (size_t)n_blocks * (size_t)((kTransferSamples / 2) >> d));
+    }
+    CU(h, launch_fused(d, p, h->sm_count, st));
+    h->stats.kernel_launches++;
+    h->stats.blocks_processed += (uint64_t)n_blocks;
+    return R2IQ_OK;
+}

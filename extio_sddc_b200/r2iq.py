@@ -201,6 +201,13 @@ class CudaR2IQ:
         capi.check(self._lib.r2iq_cuda_process_device(self._handle(), ctypes.c_void_p(d_in_ptr), int(n_blocks),
                                                       ctypes.c_void_p(d_out_ptr), ctypes.c_void_p(stream_ptr)))
 
+    def process_device_static(self, d_in_ptr: int, n_blocks: int, d_out_ptr: int, stream_ptr: int = 0) -> None:
+        """``process_device`` without any allocation (``r2iq_cuda_process_device_static``; no counterpart in the
+        reference): work counter and tables live in the library's static device array.  FFTN 2048, at most 8192
+        blocks per call; calls that overlap on the GPU race (include/r2iq_cuda.h)."""
+        capi.check(self._lib.r2iq_cuda_process_device_static(self._handle(), ctypes.c_void_p(d_in_ptr), int(n_blocks),
+                                                             ctypes.c_void_p(d_out_ptr), ctypes.c_void_p(stream_ptr)))
+
     def process_rates(self, blocks: np.ndarray, decimations, history: np.ndarray | None = None, outs=None) -> list:
         """One ADC stream at several output rates (``r2iq_cuda_process_rates``): the capture crosses PCIe once,
         every entry of ``decimations`` (indices 0..6) gets the stream ``process`` would give at that decimation.

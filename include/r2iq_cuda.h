@@ -173,6 +173,28 @@ R2IQ_API int r2iq_cuda_process_rates(r2iq_cuda_t h, const int16_t* blocks, long 
  * R2IQ_E_INVALID. */
 R2IQ_API int r2iq_cuda_process_device(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d_iq_out, void* stream);
 
+/* r2iq_cuda_process_device for callers that must not allocate.  NO COUNTERPART IN THE REFERENCE: added
+ * for code under CUDA graph capture, tight serving loops and harnesses that forbid cudaMalloc.
+ * Arguments, result and errors as r2iq_cuda_process_device (same kernel, same tables, same bits), but everything the
+ * launch needs beside the caller's buffers -- the work counter of the persistent kernel and the per-(filter, d, tune
+ * bin) tables, which r2iq_cuda_process_device builds into cudaMalloc'ed buffers on first use -- lives in ONE
+ * file-scope `static __device__` array of R2IQ_STATIC_SCRATCH_BYTES inside the library (every GPU that loads the
+ * library holds it until the process exits).  The call issues no cudaMalloc / cudaFree and no allocating library
+ * routine: a memset of the counter, the kernel, and -- only when the (filter, d, tune bin) differ from the last call
+ * on that device -- one cudaMemcpyAsync of the freshly built tables on `stream`.
+ * Limits, each R2IQ_E_INVALID / R2IQ_E_STATE with a message naming it:
+ *   - FFTN 2048 operators only: a table set is at most 41,216 bytes; the FFTN 8192 tables (~150 KB) do not fit.
+ *   - at most R2IQ_STATIC_MAX_BLOCKS blocks per call (1 GiB of samples); larger launches go through
+ *     r2iq_cuda_process_device.
+ *   - fine-tune mixer off or R2IQ_NCO_DIRECT; the R2IQ_NCO_REFERENCE form needs start phasors that grow with the launch.
+ * ALL calls in the process (all handles, all streams) on one device share the array, and it keeps the last call's
+ * contents: the counter is cleared by every call, the tables are replaced when they differ.  Calls that overlap on the
+ * GPU therefore RACE (two kernels on one counter; tables replaced under a running kernel): issue them on one stream,
+ * or order them yourself. */
+#define R2IQ_STATIC_SCRATCH_BYTES 49152
+#define R2IQ_STATIC_MAX_BLOCKS 8192
+R2IQ_API int r2iq_cuda_process_device_static(r2iq_cuda_t h, const int16_t* d_in, long n_blocks, float* d_iq_out, void* stream);
+
 /* Wideband channelizer: n_channels tuned channels from ONE input stream.  Channel c is tuned to tunebins[c]
  * (multiples of 4 in [0, halfFft), the value setFreqOffset would store in mtunebin) and receives exactly the stream a
  * separate fft_mt_r2iq tuned there would produce (Core/fft_mt_r2iq_impl.hpp:76-138) at the latched decimation, with
