@@ -128,7 +128,7 @@ int main() {
             // round 1 (one blocking launch per output slot, two host memcpys per block): 365 / 4769 Msps.  The producer
             // and the consumer of this test are single memcpy threads; thresholds sit well below what was measured
             // (profiles/r02_live_path.txt) so that a slower host does not fail the suite.
-            CHECK(msps > (d == 0 ? 1500.0 : 4000.0));
+            CHECK(msps > (d == 0 ? 1500.0 : 3000.0));   // measured 3514 / 6508-8388 (d = 5 is bound by this test's producer thread)
         }
     }
     {   // added latency at the RX-888's real rate: the producer publishes one block every 512 us, the consumer stamps
