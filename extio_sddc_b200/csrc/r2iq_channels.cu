@@ -270,6 +270,17 @@ __global__ void __launch_bounds__(kCpWarps * 32, 1) r2iq_channels_pair_kernel(co
     constexpr int M = kHalfFft >> D;
     constexpr int R = M / 32;
     constexpr int RB = ilog2(R);
+    // d = 2, 3: the backward transform is split the other way round -- band bin m = R a + j with a ACROSS THE LANES and j in
+    // registers, output sample n = n_lo + 32 n_hi with n_lo across the lanes: R cross-lane 32-point transforms first, then
+    // the twiddle exp(+2 pi i j n_lo / mfft) folded into an R-point register DFT over j.  Every store instruction then
+    // covers 32 CONSECUTIVE samples (256 bytes, 4 L1 wavefronts) instead of 16 bytes at a 64 / 32-byte stride from lanes in
+    // bit-reversed order (one wavefront per lane: the stores were 42 % of the L1 data pipe, which ran at 98 %:
+    // profiles/r02e_chan_kernels.json), the kept range [lo, 3 mfft / 4) is a warp-uniform set of rows n_hi, and the
+    // quarter of the register DFT's outputs that overlap-save discards is never computed.  The split spectrum is kept
+    // de-interleaved by k mod R (pitch 1024 / R + 16 / R: conflict-free for the split's writes and the strided gather).
+    constexpr bool kLaneLow = D <= 3;
+    constexpr int kSlotPitch = kHalfFft / R + 16 / R;
+    auto slot = [](int k) { return kLaneLow ? (k & (R - 1)) * kSlotPitch + (k >> RB) : k; };
     extern __shared__ __align__(128) unsigned char cp_smem[];
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
@@ -288,8 +299,10 @@ __global__ void __launch_bounds__(kCpWarps * 32, 1) r2iq_channels_pair_kernel(co
         tab[(i & 31) * kCpTabPitch + (i >> 5)] = __ldg(p.tw_fwd + i);
         tab[32 * kCpTabPitch + i] = __ldg(p.ctab + i);
     }
+    // d = 2, 3 (kLaneLow, below): entries 4.. are exp(+2 pi i n_lo j / mfft) for the lane's output residue n_lo = brev5(lane)
     for (int i = threadIdx.x; i < 32 * (3 + R); i += kCpWarps * 32)
-        tab[32 * kCpTabPitch + 1024 + (i & 31) * kCpXPitch + (i >> 5)] = warp_idft_twiddle(i & 31, i >> 5, M);
+        tab[32 * kCpTabPitch + 1024 + (i & 31) * kCpXPitch + (i >> 5)] =
+            warp_idft_twiddle(kLaneLow && (i >> 5) >= 4 ? (int)brev5(i & 31) : (i & 31), i >> 5, M);
     const bool in_smem = p.n_channels <= kCpMaxListed;
     if (in_smem)
         for (int i = threadIdx.x; i < p.n_channels; i += kCpWarps * 32) listed[i] = __ldg(p.tunebins + i);
@@ -365,13 +378,13 @@ __global__ void __launch_bounds__(kCpWarps * 32, 1) r2iq_channels_pair_kernel(co
             }
             __syncwarp();   // every mirror read is done: the tile takes the split spectrum
 #pragma unroll
-            for (int k1 = 0; k1 < 32; k1++) sts2(S, 32 * k1 + lane, v[k1]);
+            for (int k1 = 0; k1 < 32; k1++) sts2(S, slot(32 * k1 + lane), v[k1]);
             __syncwarp();
         }
         // ---- per channel: gather, filter, backward transform across the lanes, store ------------------------------
         float2 gh[R];
 #pragma unroll
-        for (int j = 0; j < R; j++) gh[j] = __ldg(p.gh + lane + 32 * j);
+        for (int j = 0; j < R; j++) gh[j] = __ldg(p.gh + (kLaneLow ? R * lane + j : lane + 32 * j));
         const float4 w01 = *reinterpret_cast<const float4*>(xw), w23 = *reinterpret_cast<const float4*>(xw + 2);
         const float2 wsh[4] = {make_float2(w01.x, w01.y), make_float2(w01.z, w01.w), make_float2(w23.x, w23.y), make_float2(w23.z, w23.w)};
         const FrameOut2 oa = frame_out2<D>(2 * q, p.total_frames);
@@ -381,6 +394,31 @@ __global__ void __launch_bounds__(kCpWarps * 32, 1) r2iq_channels_pair_kernel(co
         const bool keepB = ob.live && idx0 >= ob.lo && idx0 < 3 * M / 4;
         for (int ch = 0; ch < p.n_channels; ch++) {
             const int tb = in_smem ? listed[ch] : __ldg(p.tunebins + ch);
+            if constexpr (kLaneLow) {
+                c2 t[R];
+                const int m0 = tb + R * lane - (lane < 16 ? 0 : M);        // m = R lane + j; the upper half are the negative bins
+#pragma unroll
+                for (int j = 0; j < R; j++) {
+                    const int kk = m0 + j;
+                    const bool inside = (unsigned)kk < (unsigned)kHalfFft;   // bins outside [0, halfFft) are zero
+                    const c2 x = lds2(S, slot(kk & (kHalfFft - 1)));
+                    const float2 g = inside ? gh[j] : make_float2(0.0f, 0.0f);
+                    // T_j[n_lo] = sum_a Y[R a + j] exp(+2 pi i a n_lo / 32): lane l ends with n_lo = brev5(l)
+                    t[brev_n(j, RB)] = warp_idft32(cmul2s(x, g), wsh, lane);
+                }
+                // y[n_lo + 32 n_hi] = sum_j exp(+2 pi i j n_hi / R) [exp(+2 pi i j n_lo / mfft) T_j[n_lo]]
+                dit2_tw<R, true>(t, [&](int i) { return xw[3 + brev_n(i, RB)]; });
+                float2* const outA = p.out + (size_t)ch * p.out_stride + (oa.base + (int)brev5(lane));
+                float2* const outB = p.out + (size_t)ch * p.out_stride + (ob.base + (int)brev5(lane));
+#pragma unroll
+                for (int nh = 0; nh < 3 * R / 4; nh++) {
+                    float ar, br, ai, bi;
+                    upk(t[nh].re, ar, br);
+                    upk(t[nh].im, ai, bi);
+                    if (32 * nh >= oa.lo) outA[32 * nh] = make_float2(ar, flip(ai, sgn));
+                    if (ob.live && 32 * nh >= ob.lo) outB[32 * nh] = make_float2(br, flip(bi, sgn));
+                }
+            } else {
             c2 y[R];
 #pragma unroll
             for (int j = 0; j < R; j++) {
@@ -408,6 +446,7 @@ __global__ void __launch_bounds__(kCpWarps * 32, 1) r2iq_channels_pair_kernel(co
                 if (keepA) *reinterpret_cast<float4*>(outA + e) = make_float4(ar0, flip(ai0, sgn), ar1, flip(ai1, sgn));
                 if (keepB) *reinterpret_cast<float4*>(outB + e) = make_float4(br0, flip(bi0, sgn), br1, flip(bi1, sgn));
             }
+            }   // d = 4
         }
         __syncwarp();   // every lane is done with the spectrum: the tail of the tile takes the next pair of frames
         if (lane == 0 && qn < n_pairs) {
