@@ -10,7 +10,7 @@
 //   d = 2, 3, 4           : r2iq_channels_pair_kernel -- channels one after the other, backward transform across the lanes;
 //   d = 0, 1 (and FFTN 8192): one single-channel launch per channel (r2iq_capi.cu: launch_channels_impl).
 // (The first-generation kernel -- one scalar frame per warp, groups of 2^d channels cut, staged and transformed back
-// together -- is gone: 8.96 / 4.21 / 2.85 ms for 64 channels x 2048 blocks at d = 2 / 3 / 4 against 4.45 / 2.26 / 1.01.)
+// together -- is gone: 8.96 / 4.21 / 2.85 ms for 64 channels x 2048 blocks at d = 2 / 3 / 4 against 2.97 / 1.58 / 0.96.)
 #include "dual_frame.cuh"
 #include "r2iq_common.cuh"
 #include "work_dispenser.cuh"
@@ -245,14 +245,21 @@ static cudaError_t launch_ch_lane(const ChannelParams& p, int sm_count, cudaStre
 //   1. forward transform of a frame PAIR exactly as r2iq_pair.cu (TMA pair copy, integer-pipe conversion with the bias
 //      folded into the first butterfly stage, two radix-32 register passes, inter-pass twiddles folded into the second);
 //   2. the real-FFT split ONCE for all channels: X'[k] = (a + conj b) + c[k] (a - conj b), a = Z[k], b = Z[1024 - k],
-//      c = -i W_2048^k (the factor 1/2 lives in gh), written back to the warp's tile in natural order;
-//   3. per channel: the lane gathers its R = mfft / 32 band bins m = lane + 32 j around the channel's tune bin (zero
-//      outside [0, 1024): Core/fft_mt_r2iq_impl.hpp:91-96), multiplies by gh[m] (R per-lane constants) and runs the
-//      mfft-point backward transform as an R-point register DFT, a twiddle and R 32-point transforms ACROSS THE LANES
-//      (dual_frame.cuh: warp_idft32) -- nothing but the gather touches shared memory, so the spectrum stays where it is
-//      for the next channel; lane l stores the R consecutive samples R brev5(l) ... of both frames.
-// Per channel and frame pair ~145 / 290 / 610 instructions (d = 4 / 3 / 2) on top of ~1900 for the shared part, against
-// a whole single-channel kernel (1900 .. 2300) per channel.
+//      c = -i W_2048^k (the factor 1/2 lives in gh), written back to the warp's tile de-interleaved by k mod R;
+//   3. per channel the mfft-point backward transform is split as band bin m = R a + j, a ACROSS THE LANES and j in
+//      registers, output sample n = n_lo + 32 n_hi, n_lo across the lanes: lane a gathers its R consecutive band bins
+//      around the channel's tune bin (zero outside [0, 1024): Core/fft_mt_r2iq_impl.hpp:91-96), multiplies by gh[m] (R
+//      per-lane constants), runs R 32-point transforms ACROSS THE LANES (dual_frame.cuh: warp_idft32; lane l ends with
+//      n_lo = brev5(l)), then the twiddle exp(+2 pi i j n_lo / mfft) folded into an R-point register DFT over j
+//      (dit2_tw) -- nothing but the gather touches shared memory, so the spectrum stays where it is for the next
+//      channel.  Every store instruction covers 32 CONSECUTIVE samples, the kept range [lo, 3 mfft / 4) is a
+//      warp-uniform set of rows n_hi for d <= 3, and the quarter of the register DFT that overlap-save discards is
+//      never computed.
+//      (Until r02e the split was the other way round -- an R-point register DFT, then the cross-lane transforms, lane l
+//      ending with the R consecutive samples R brev5(l) ...: 16-byte stores at a 64 / 32-byte stride from lanes in
+//      bit-reversed order cost one L1 wavefront per LANE; at d = 2 they were 42 % of an L1 data pipe that ran at 98 %,
+//      MIO throttle 2.9 cycles per issue: profiles/r02e_chan_kernels.json.  4.45 / 2.26 / 1.01 -> 2.97 / 1.58 / 0.96 ms
+//      for 64 channels x 2048 blocks at d = 2 / 3 / 4.)
 // ---------------------------------------------------------------------------------------------------------------
 namespace {
 constexpr int kCpWarps = 12;
@@ -270,17 +277,10 @@ __global__ void __launch_bounds__(kCpWarps * 32, 1) r2iq_channels_pair_kernel(co
     constexpr int M = kHalfFft >> D;
     constexpr int R = M / 32;
     constexpr int RB = ilog2(R);
-    // d = 2, 3: the backward transform is split the other way round -- band bin m = R a + j with a ACROSS THE LANES and j in
-    // registers, output sample n = n_lo + 32 n_hi with n_lo across the lanes: R cross-lane 32-point transforms first, then
-    // the twiddle exp(+2 pi i j n_lo / mfft) folded into an R-point register DFT over j.  Every store instruction then
-    // covers 32 CONSECUTIVE samples (256 bytes, 4 L1 wavefronts) instead of 16 bytes at a 64 / 32-byte stride from lanes in
-    // bit-reversed order (one wavefront per lane: the stores were 42 % of the L1 data pipe, which ran at 98 %:
-    // profiles/r02e_chan_kernels.json), the kept range [lo, 3 mfft / 4) is a warp-uniform set of rows n_hi, and the
-    // quarter of the register DFT's outputs that overlap-save discards is never computed.  The split spectrum is kept
-    // de-interleaved by k mod R (pitch 1024 / R + 16 / R: conflict-free for the split's writes and the strided gather).
-    constexpr bool kLaneLow = D <= 3;
+    // the split spectrum is kept de-interleaved by k mod R (pitch 1024 / R + 16 / R: conflict-free for the split's writes
+    // and for the gather, whose lanes are R bins apart)
     constexpr int kSlotPitch = kHalfFft / R + 16 / R;
-    auto slot = [](int k) { return kLaneLow ? (k & (R - 1)) * kSlotPitch + (k >> RB) : k; };
+    auto slot = [](int k) { return (k & (R - 1)) * kSlotPitch + (k >> RB); };
     extern __shared__ __align__(128) unsigned char cp_smem[];
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
@@ -299,10 +299,10 @@ __global__ void __launch_bounds__(kCpWarps * 32, 1) r2iq_channels_pair_kernel(co
         tab[(i & 31) * kCpTabPitch + (i >> 5)] = __ldg(p.tw_fwd + i);
         tab[32 * kCpTabPitch + i] = __ldg(p.ctab + i);
     }
-    // d = 2, 3 (kLaneLow, below): entries 4.. are exp(+2 pi i n_lo j / mfft) for the lane's output residue n_lo = brev5(lane)
+    // entries 0..3: the lane's stage twiddles of warp_idft32; entries 4.. are exp(+2 pi i n_lo j / mfft) for the lane's output residue n_lo = brev5(lane)
     for (int i = threadIdx.x; i < 32 * (3 + R); i += kCpWarps * 32)
         tab[32 * kCpTabPitch + 1024 + (i & 31) * kCpXPitch + (i >> 5)] =
-            warp_idft_twiddle(kLaneLow && (i >> 5) >= 4 ? (int)brev5(i & 31) : (i & 31), i >> 5, M);
+            warp_idft_twiddle((i >> 5) >= 4 ? (int)brev5(i & 31) : (i & 31), i >> 5, M);
     const bool in_smem = p.n_channels <= kCpMaxListed;
     if (in_smem)
         for (int i = threadIdx.x; i < p.n_channels; i += kCpWarps * 32) listed[i] = __ldg(p.tunebins + i);
@@ -384,17 +384,14 @@ __global__ void __launch_bounds__(kCpWarps * 32, 1) r2iq_channels_pair_kernel(co
         // ---- per channel: gather, filter, backward transform across the lanes, store ------------------------------
         float2 gh[R];
 #pragma unroll
-        for (int j = 0; j < R; j++) gh[j] = __ldg(p.gh + (kLaneLow ? R * lane + j : lane + 32 * j));
+        for (int j = 0; j < R; j++) gh[j] = __ldg(p.gh + R * lane + j);
         const float4 w01 = *reinterpret_cast<const float4*>(xw), w23 = *reinterpret_cast<const float4*>(xw + 2);
         const float2 wsh[4] = {make_float2(w01.x, w01.y), make_float2(w01.z, w01.w), make_float2(w23.x, w23.y), make_float2(w23.z, w23.w)};
         const FrameOut2 oa = frame_out2<D>(2 * q, p.total_frames);
         const FrameOut2 ob = frame_out2<D>(2 * q + 1, p.total_frames);
-        const int idx0 = R * brev5(lane);
-        const bool keepA = idx0 >= oa.lo && idx0 < 3 * M / 4;          // lo and 3 mfft / 4 are multiples of R
-        const bool keepB = ob.live && idx0 >= ob.lo && idx0 < 3 * M / 4;
         for (int ch = 0; ch < p.n_channels; ch++) {
             const int tb = in_smem ? listed[ch] : __ldg(p.tunebins + ch);
-            if constexpr (kLaneLow) {
+            {
                 c2 t[R];
                 const int m0 = tb + R * lane - (lane < 16 ? 0 : M);        // m = R lane + j; the upper half are the negative bins
 #pragma unroll
@@ -407,46 +404,32 @@ __global__ void __launch_bounds__(kCpWarps * 32, 1) r2iq_channels_pair_kernel(co
                     t[brev_n(j, RB)] = warp_idft32(cmul2s(x, g), wsh, lane);
                 }
                 // y[n_lo + 32 n_hi] = sum_j exp(+2 pi i j n_hi / R) [exp(+2 pi i j n_lo / mfft) T_j[n_lo]]
-                dit2_tw<R, true>(t, [&](int i) { return xw[3 + brev_n(i, RB)]; });
+                if constexpr (R >= 4) {
+                    dit2_tw<R, true>(t, [&](int i) { return xw[3 + brev_n(i, RB)]; });
+                } else {                                  // R = 2: one butterfly, a' = a + w b, b' = 2 a - a'
+                    const float2 w = xw[4];
+                    const u64 ax = fma2(bc(w.x), t[1].re, fma2(bc(-w.y), t[1].im, t[0].re));
+                    const u64 ay = fma2(bc(w.x), t[1].im, fma2(bc(w.y), t[1].re, t[0].im));
+                    t[1].re = fma2(bc(2.0f), t[0].re, neg2(ax));
+                    t[1].im = fma2(bc(2.0f), t[0].im, neg2(ay));
+                    t[0].re = ax;
+                    t[0].im = ay;
+                }
                 float2* const outA = p.out + (size_t)ch * p.out_stride + (oa.base + (int)brev5(lane));
                 float2* const outB = p.out + (size_t)ch * p.out_stride + (ob.base + (int)brev5(lane));
 #pragma unroll
-                for (int nh = 0; nh < 3 * R / 4; nh++) {
+                for (int nh = 0; nh < (3 * R + 3) / 4; nh++) {
                     float ar, br, ai, bi;
                     upk(t[nh].re, ar, br);
                     upk(t[nh].im, ai, bi);
-                    if (32 * nh >= oa.lo) outA[32 * nh] = make_float2(ar, flip(ai, sgn));
-                    if (ob.live && 32 * nh >= ob.lo) outB[32 * nh] = make_float2(br, flip(bi, sgn));
+                    // d <= 3: mfft / 4 and 3 mfft / 4 are whole rows of 32 samples (warp-uniform); d = 4: half rows, per lane
+                    const int n = R >= 4 ? 32 * nh : 32 * nh + (int)brev5(lane);
+                    const bool in_a = n >= oa.lo && (R >= 4 || n < 3 * M / 4);
+                    const bool in_b = ob.live && n >= ob.lo && (R >= 4 || n < 3 * M / 4);
+                    if (in_a) outA[32 * nh] = make_float2(ar, flip(ai, sgn));
+                    if (in_b) outB[32 * nh] = make_float2(br, flip(bi, sgn));
                 }
-            } else {
-            c2 y[R];
-#pragma unroll
-            for (int j = 0; j < R; j++) {
-                const int m = lane + 32 * j;
-                const int kk = tb + (m < M / 2 ? m : m - M);
-                const bool inside = (unsigned)kk < (unsigned)kHalfFft;       // bins outside [0, halfFft) are zero
-                const c2 x = lds2(S, kk & (kHalfFft - 1));
-                const float2 g = inside ? gh[j] : make_float2(0.0f, 0.0f);
-                y[brev_n(j, RB)] = cmul2s(x, g);
             }
-            dit2<R, true>(y);                         // y[e] = sum_j Y[lane + 32 j] W_R^(j e)
-            float2* const outA = p.out + (size_t)ch * p.out_stride + (oa.base + idx0);
-            float2* const outB = p.out + (size_t)ch * p.out_stride + (ob.base + idx0);
-            // the lane's R consecutive samples of each frame leave as 16-byte stores (two samples; the run starts on a
-            // 16-byte boundary: R, mfft / 4 and the channel stride are even, the buffer is 16-byte aligned by contract)
-#pragma unroll
-            for (int e = 0; e < R; e += 2) {
-                const c2 o0 = warp_idft32(e ? cmul2s(y[e], xw[3 + e]) : y[e], wsh, lane);
-                const c2 o1 = warp_idft32(cmul2s(y[e + 1], xw[4 + e]), wsh, lane);
-                float ar0, br0, ai0, bi0, ar1, br1, ai1, bi1;
-                upk(o0.re, ar0, br0);
-                upk(o0.im, ai0, bi0);
-                upk(o1.re, ar1, br1);
-                upk(o1.im, ai1, bi1);
-                if (keepA) *reinterpret_cast<float4*>(outA + e) = make_float4(ar0, flip(ai0, sgn), ar1, flip(ai1, sgn));
-                if (keepB) *reinterpret_cast<float4*>(outB + e) = make_float4(br0, flip(bi0, sgn), br1, flip(bi1, sgn));
-            }
-            }   // d = 4
         }
         __syncwarp();   // every lane is done with the spectrum: the tail of the tile takes the next pair of frames
         if (lane == 0 && qn < n_pairs) {
