@@ -4,14 +4,19 @@
 // One single-channel launch per channel (r2iq_capi.cu) repeats the whole 4096-point forward transform for every channel.
 // Here a TEAM of four warps transforms a frame pair ONCE with the phases A and B of r2iq_wide_pair.cu, forms the real-FFT
 // split once -- X'[k] = (a + conj b) + c[k] (a - conj b), a = Z[k], b = Z[4096 - k], c = -i W_8192^k -- and leaves it in
-// its four planes (bin 4 m + r in plane r, slot m).  Then, channel after channel:
-//   * warp r gathers the 32 (64) band bins of its plane around the channel's tune bin (a multiple of 4, so the band's bins
-//     4 m' + r are plane r shifted by tunebin / 4; zero outside [0, 4096): Core/fft_mt_r2iq_impl.hpp:91-96), multiplies by
-//     its per-lane filter constant 0.5 H_d and runs the 32-point per-plane backward transform across the lanes
-//     (dual_frame.cuh: warp_idft32); S_r goes to a 2 (4) KB exchange area;                                         team barrier
-//   * 32 (64) threads run the last radix-4 stage across the planes (with the twiddles W_4096^(-r (n << d))) and store the kept
-//     three quarters of both frames into the channel's output stream;                                          team barrier
-// Per channel that is ~130 instructions per warp instead of a whole single-channel kernel (~2300 per thread).
+// its four planes (bin 4 m + r in plane r, slot m).  Then every WARP of the team serves whole channels (warp w the channels
+// w, w + 4, ...), without a barrier or a byte of shared-memory traffic beyond the gather:
+//   * it gathers the 32 (64) band bins of each of the four planes around the channel's tune bin (a multiple of 4, so the
+//     band's bins 4 m' + r are plane r shifted by tunebin / 4; zero outside [0, 4096): Core/fft_mt_r2iq_impl.hpp:91-96),
+//     multiplies by its per-lane filter constants 0.5 H_d and runs the four 32-point per-plane backward transforms across
+//     its lanes (dual_frame.cuh: warp_idft32) -- four independent shuffle chains in flight;
+//   * S_0..S_3 of its samples n = R brev5(lane) + e are then in its own registers: the last radix-4 stage across the planes
+//     (twiddles W_4096^(-r (n << d)), per-lane constants) and the stores of the kept three quarters of both frames follow
+//     in place.
+// ~330 instructions per channel and frame pair instead of a whole single-channel kernel (~2300 per thread): 64 channels x
+// 8192 blocks in 2.43 ms at d = 5 and 4.32 ms at d = 4 (64 single-channel launches: 44 / 46 ms; the first form of this
+// kernel -- warp r on plane r of one channel, S_r exchanged through shared memory between two team barriers per channel,
+// a dependent chain of ~1200 cycles per channel: 4.21 / 6.86 ms).
 // Worker-loop semantics per channel: Core/fft_mt_r2iq_impl.hpp:76-138.
 #define R2IQ_WIDE_HELPERS_ONLY
 #include "r2iq_wide_pair.cu"
@@ -26,12 +31,9 @@ struct WcGeo {
     static constexpr int M = kWHalf >> D;             // 128 (d = 5), 256 (d = 4)
     static constexpr int MS = M / 4;                  // points per plane
     static constexpr int R = MS / 32;                 // band bins of a plane per lane
-    static constexpr int kXchBytes = 2 * 4 * MS * 8;  // S_r of the four planes: re pairs, then im pairs
-    // W_4096^n (8 KB) sits in shared memory where it fits beside the exchange area (d = 5: 4.2 ms against 4.7 ms with the
-    // table in global memory); at d = 4 the exchange area needs the room
-    static constexpr bool kTwqShared = D == 5;
-    static constexpr int kTabFloat2 = kWTab1 + 32 * kWcXPitch + kWcListed / 2 + (kTwqShared ? 1024 : 0);   // tw1024^T | lane twiddles | tune bins | W_4096^n
-    static constexpr int kSmemBytes = kTabFloat2 * 8 + kTeams * (kTeamBytes + kXchBytes);
+    // tw1024^T | lane twiddles | tune bins | W_4096^n (8 KB: phase A reads all of it, the channel loop only its own entries)
+    static constexpr int kTabFloat2 = kWTab1 + 32 * kWcXPitch + kWcListed / 2 + 1024;
+    static constexpr int kSmemBytes = kTabFloat2 * 8 + kTeams * kTeamBytes;
 };
 }  // namespace
 
@@ -50,22 +52,20 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_channels_ke
     const int warp = tt >> 5;                          // plane this warp transforms
     float2* tab = reinterpret_cast<float2*>(wcsmem);
     const float2* tw1024 = tab + lane * kWTabPitch;
-    const float2* twq1 = G::kTwqShared ? tab + kWTab1 + 32 * kWcXPitch + kWcListed / 2 : p.twq;   // W_4096^n
+    const float2* twq1 = tab + kWTab1 + 32 * kWcXPitch + kWcListed / 2;   // W_4096^n
     const float2* xw = tab + kWTab1 + lane * kWcXPitch;
     int* listed = reinterpret_cast<int*>(tab + kWTab1 + 32 * kWcXPitch);
-    unsigned char* tbase = wcsmem + G::kTabFloat2 * 8 + (size_t)team * (kTeamBytes + G::kXchBytes);
+    unsigned char* tbase = wcsmem + G::kTabFloat2 * 8 + (size_t)team * kTeamBytes;
     Planes P;
     P.re = reinterpret_cast<float2*>(tbase);
     P.im = P.re + 4 * kWPlane;
-    float2* xre = reinterpret_cast<float2*>(tbase + kTeamBytes);     // [4][MS] (re_A, re_B)
-    float2* xim = xre + 4 * MS;                                      // [4][MS] (im_A, im_B)
     const int wbase = warp * kWPlane;
     const int mbase = ((4 - warp) & 3) * kWPlane;
     const uint32_t sgn = __float_as_uint(p.imag_sign) & 0x80000000u;
 
     for (int i = threadIdx.x; i < 1024; i += kTeams * kTeamThreads) {
         tab[(i & 31) * kWTabPitch + (i >> 5)] = __ldg(p.tw1024 + i);
-        if constexpr (G::kTwqShared) tab[kWTab1 + 32 * kWcXPitch + kWcListed / 2 + i] = __ldg(p.twq + i);
+        tab[kWTab1 + 32 * kWcXPitch + kWcListed / 2 + i] = __ldg(p.twq + i);
     }
     for (int i = threadIdx.x; i < 32 * (3 + R); i += kTeams * kTeamThreads)
         tab[kWTab1 + (i & 31) * kWcXPitch + (i >> 5)] = warp_idft_twiddle(i & 31, i >> 5, MS);
@@ -76,15 +76,6 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_channels_ke
     if (tt == 0) s_pair[team] = (long long)atomicAdd(p.work_counter, 1ULL);
     __syncthreads();
 
-    // this lane's R band positions inside its plane: slot offset s' in [-MS/2, MS/2), bin offset s = 4 s' + r, filter index s mod M
-    int sp[R];
-    float2 g[R];
-#pragma unroll
-    for (int j = 0; j < R; j++) {
-        const int m = lane + 32 * j;
-        sp[j] = m < MS / 2 ? m : m - MS;
-        g[j] = __ldg(p.gh + ((4 * sp[j] + warp) & (M - 1)));
-    }
     const float4 w01 = *reinterpret_cast<const float4*>(xw), w23 = *reinterpret_cast<const float4*>(xw + 2);
     const float2 wsh[4] = {make_float2(w01.x, w01.y), make_float2(w01.z, w01.w), make_float2(w23.x, w23.y), make_float2(w23.z, w23.w)};
     // only the WideParams fields load_half / quarter_stage read
@@ -139,50 +130,76 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_channels_ke
         team_barrier(team);                           // every mirror read of the team is done: the planes take the split
 #pragma unroll
         for (int k1 = 0; k1 < 32; k1++) pst(P, wbase + lane + 32 * k1, v[k1]);
-        __syncwarp();                                 // a warp gathers from its own plane only
 
         const FrameOut2 oa = wide_frame_out<D>(2 * q, p.total_frames);
         const FrameOut2 ob = wide_frame_out<D>(2 * q + 1, p.total_frames);
         const KeepPair head{oa.lo == 0, ob.live && ob.lo == 0}, rest{true, ob.live};
         // ---------------- per channel ------------------------------------------------------------------------------------
-        for (int ch = 0; ch < p.n_channels; ch++) {
-            const int tb4 = (in_smem ? listed[ch] : __ldg(p.tunebins + ch)) >> 2;
-            c2 y[R];
+        // A WARP serves a whole channel (warp w the channels w, w + 4, ...): it gathers the band bins of all four planes
+        // (read-only since the barrier above), runs the four per-plane transforms across its lanes -- four independent
+        // shuffle chains in flight -- and has S_0..S_3 of its samples n = R brev5(lane) + e in its own registers, so the last
+        // radix-4 stage needs no exchange and the channel loop no barrier.  (Until r02f warp r transformed plane r of ONE
+        // channel, S_r met in a shared-memory exchange area between two team barriers per channel: one dependent chain of
+        // ~1200 cycles per channel and team, barrier + scoreboard stalls 2.4 + 1.7 cycles per issue,
+        // profiles/r02e_chan_kernels.json.)
+        team_barrier(team);                           // every plane holds the split
+        // (per pair, not once per kernel: these registers would otherwise be live across phase B's 32-value register pass)
+        // this lane's R band positions inside a plane: slot offset s' in [-MS/2, MS/2); in plane r that is bin offset s = 4 s' + r,
+        // filter index s mod M.  In the channel loop a warp serves whole channels: all four planes, R bins each.
+        int sp[R];
+        float2 g[4][R];
 #pragma unroll
-            for (int j = 0; j < R; j++) {
-                const int slot = tb4 + sp[j];
-                const bool inside = (unsigned)slot < 1024u;               // bin 4 slot + warp inside [0, 4096)
-                const c2 x = pld(P, wbase + (slot & 1023));
-                y[brev_n(j, RB)] = cmul2s(x, inside ? g[j] : make_float2(0.0f, 0.0f));
+        for (int j = 0; j < R; j++) {
+            const int m = lane + 32 * j;
+            sp[j] = m < MS / 2 ? m : m - MS;
+#pragma unroll
+            for (int r = 0; r < 4; r++) g[r][j] = __ldg(p.gh + ((4 * sp[j] + r) & (M - 1)));
+        }
+        // twiddles of the last radix-4 stage for this lane's samples n = R brev5(lane) + e: W_4096^(r (n << d)), r = 1, 2, 3
+        float2 wq[R][3];
+#pragma unroll
+        for (int e = 0; e < R; e++) {
+            const float2 w1 = twq1[(R * brev5(lane) + e) << D];
+            wq[e][0] = w1;
+            wq[e][1] = csqr(w1);
+            wq[e][2] = cmul(w1, wq[e][1]);
+        }
+        for (int ch = warp; ch < p.n_channels; ch += 4) {
+            const int tb4 = (in_smem ? listed[ch] : __ldg(p.tunebins + ch)) >> 2;
+            c2 S[4][R];
+#pragma unroll
+            for (int r = 0; r < 4; r++) {
+                c2 y[R];
+#pragma unroll
+                for (int j = 0; j < R; j++) {
+                    const int slot = tb4 + sp[j];
+                    const bool inside = (unsigned)slot < 1024u;               // bin 4 slot + r inside [0, 4096)
+                    const c2 x = pld(P, r * kWPlane + (slot & 1023));
+                    y[brev_n(j, RB)] = cmul2s(x, inside ? g[r][j] : make_float2(0.0f, 0.0f));
+                }
+                dit2<R, true>(y);                         // y[e] = sum_j Y[lane + 32 j] W_R^(j e)
+#pragma unroll
+                for (int e = 0; e < R; e++) S[r][e] = y[e];
             }
-            dit2<R, true>(y);                         // y[e] = sum_j Y[lane + 32 j] W_R^(j e)
 #pragma unroll
             for (int e = 0; e < R; e++) {
-                const c2 o = warp_idft32(e ? cmul2s(y[e], xw[3 + e]) : y[e], wsh, lane);   // S_warp[R brev5(lane) + e]
-                float a0, a1, b0, b1;
-                upk(o.re, a0, a1);
-                upk(o.im, b0, b1);
-                xre[warp * MS + R * brev5(lane) + e] = make_float2(a0, a1);
-                xim[warp * MS + R * brev5(lane) + e] = make_float2(b0, b1);
+#pragma unroll
+                for (int r = 0; r < 4; r++)               // S_r[R brev5(lane) + e]
+                    S[r][e] = warp_idft32(e ? cmul2s(S[r][e], xw[3 + e]) : S[r][e], wsh, lane);
             }
-            team_barrier(team);
-            if (tt < MS) {
+            float2* const outA = p.out + (size_t)ch * p.out_stride + oa.base;
+            float2* const outB = p.out + (size_t)ch * p.out_stride + ob.base;
+#pragma unroll
+            for (int e = 0; e < R; e++) {
                 // last radix-4 stage across the planes: y[n + MS a] = sum_r i^(r a) S_r[n] W_mfft^(-r n), a = 0..2 kept
-                const int n = tt;
-                auto xld = [&](int r) {
-                    const float2 re = xre[r * MS + n], im = xim[r * MS + n];
-                    return c2{pk(re.x, re.y), pk(im.x, im.y)};
-                };
-                const float2 w1 = twq1[n << D], w2 = csqr(w1), w3 = cmul(w1, w2);
-                const c2 s0 = xld(0), s1 = cmul_conj2s(xld(1), w1), s2 = cmul_conj2s(xld(2), w2), s3 = cmul_conj2s(xld(3), w3);
+                const int n = R * brev5(lane) + e;
+                const c2 s0 = S[0][e], s1 = cmul_conj2s(S[1][e], wq[e][0]), s2 = cmul_conj2s(S[2][e], wq[e][1]),
+                         s3 = cmul_conj2s(S[3][e], wq[e][2]);
                 const c2 a0 = cadd(s0, s2), a1 = csub(s0, s2), a2 = cadd(s1, s3), a3 = csub(s1, s3);
-                float2* const outA = p.out + (size_t)ch * p.out_stride + oa.base;
-                float2* const outB = p.out + (size_t)ch * p.out_stride + ob.base;
                 store_pair_rows(outA, outB, head, n, cadd(a0, a2), sgn);
                 store_pair_rows(outA, outB, rest, n + MS, c2{sub2(a1.re, a3.im), add2(a1.im, a3.re)}, sgn);      // a1 + i a3
                 store_pair_rows(outA, outB, rest, n + 2 * MS, csub(a0, a2), sgn);
             }
-            team_barrier(team);                       // the exchange area is rewritten by the next channel
         }
         const long long qn = s_pair[team];
         load_half(wp, qn < n_pairs ? qn : q, tt, 0, w0);
