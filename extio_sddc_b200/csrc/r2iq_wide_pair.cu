@@ -251,6 +251,19 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_pair_kernel
     const uint32_t sgn = __float_as_uint(p.imag_sign) & 0x80000000u;
     const uint32_t row_mask = warp == 0 ? p.row_mask[0] : warp == 1 ? p.row_mask[1] : warp == 2 ? p.row_mask[2] : p.row_mask[3];
     const float4* pq = p.pq + warp * 1024;
+    // d = 3: the lane's (P, Q) of its four band bins are the same for every frame pair -- kept in registers instead of one
+    // L1 / L2 round trip per pair at the head of the short phase D: 650 -> 660 Gsamples/s.  (d = 4: no difference, d = 5:
+    // 798 -> 775 -- the registers cost more in phase B than the loads did.)
+    constexpr bool kPqRegs = D == 3;
+    constexpr int kPqN = kPqRegs ? (kWHalf >> D) / 4 / 32 : 1;
+    float4 pq_reg[kPqN];
+    if constexpr (kPqRegs) {
+#pragma unroll
+        for (int j = 0; j < kPqN; j++) {
+            const int m = lane + 32 * j, ms = (kWHalf >> D) / 4;
+            pq_reg[j] = __ldg(pq + ((tb4 + (m < ms / 2 ? m : m - ms)) & 1023));
+        }
+    }
 
     for (int i = threadIdx.x; i < 1024; i += kTeams * kTeamThreads) {
         tab[(i & 31) * kWTabPitch + (i >> 5)] = __ldg(p.tw1024 + i);
@@ -349,7 +362,7 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_pair_kernel
                 const int mm = (tb4 + (m < MS / 2 ? m : m - MS)) & 1023;
                 const c2 a = pld(P, wbase + mm);
                 const c2 b = pld(P, mbase + mirror_slot(warp, mm));
-                y[brev_n(j, RB)] = split_pq(a, b, __ldg(pq + mm));
+                y[brev_n(j, RB)] = split_pq(a, b, kPqRegs ? pq_reg[kPqRegs ? j : 0] : __ldg(pq + mm));
             }
             dit2<R, true>(y);                                         // pass 1 over n2 (m' = lane + 32 n2); its twiddles are part of the weights
             c2 u[R];
