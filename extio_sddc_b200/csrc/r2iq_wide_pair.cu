@@ -386,8 +386,10 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_pair_kernel
             const int k2p = lane / G, h = lane % G;
 #pragma unroll
             for (int qq = 0; qq < R; qq++) {
+                // lanes (k2p, h) and (k2p, h + 16 / R) are 16 samples apart = the same bank: bit 4 of n moves them apart
+                // (phase E reads 16 consecutive n per half warp: still one wavefront)
                 const int n = k2p + R * h + 32 * qq;
-                pst(P, wbase + n, u[qq]);
+                pst(P, wbase + (n ^ (((n >> 4) & 1) << (RB - 1))), u[qq]);
             }
             }
         }
@@ -409,8 +411,10 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_pair_kernel
                     // S_r[n] W_mfft^(-r n) = S_r[n] conj(W_4096^(r (n << D))): applied here, where all 128 threads share the work
                     // (in phase D2 warp 3 carried 32 x (load + 7 scalar + 4 packed) and warp 0 nothing: the team waited for it)
                     const float2 w1 = twq1[n << D], w2 = csqr(w1), w3 = cmul(w1, w2);
-                    const c2 s0 = pld(P, n), s1 = cmul_conj2s(pld(P, kWPlane + n), w1), s2 = cmul_conj2s(pld(P, 2 * kWPlane + n), w2),
-                             s3 = cmul_conj2s(pld(P, 3 * kWPlane + n), w3);
+                    constexpr int kSwz = (D >= 1 && D <= 3) ? ilog2(MS / 32) - 1 : -1;   // the R-scheme's bank swizzle (phase D2)
+                    const int ns = kSwz >= 0 ? n ^ (((n >> 4) & 1) << (kSwz >= 0 ? kSwz : 0)) : n;
+                    const c2 s0 = pld(P, ns), s1 = cmul_conj2s(pld(P, kWPlane + ns), w1), s2 = cmul_conj2s(pld(P, 2 * kWPlane + ns), w2),
+                             s3 = cmul_conj2s(pld(P, 3 * kWPlane + ns), w3);
                     const c2 a0 = cadd(s0, s2), a1 = csub(s0, s2), a2 = cadd(s1, s3), a3 = csub(s1, s3);
                     if constexpr (kMix == 2) {
                         // sample n + MS a is 32 (4 i + (MS / 32) a) samples after sample tt: entries of nco_rot (< 96)
