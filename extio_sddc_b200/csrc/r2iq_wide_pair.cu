@@ -177,6 +177,18 @@ __device__ __forceinline__ void load_half(const WideParams& p, long long pair, i
             w.b[jj][qq] = __ldg(srcB + 128 * jj + 1024 * qq);
         }
 }
+// Both frames of a pair (2 x 128 lines of 128 bytes) into L2, one line of each frame per thread: issued a phase and a half
+// before load_half reads them, so that the loads wait for an L2 hit and not for HBM (13 % of the d = 5 kernel's stall
+// samples sat on the first use of the loaded words: long scoreboard, tools/ncu_hot.py).  No registers are held.
+__device__ __forceinline__ void prefetch_pair_l2(const WideParams& p, long long pair, int tt) {
+    const long long fa = 2 * pair;
+    const uint32_t blk = (uint32_t)fa / (uint32_t)kWFrames;
+    const int kf = (int)((uint32_t)fa - blk * (uint32_t)kWFrames);
+    const uint32_t* srcA = p.in_words + (size_t)blk * (kTransferSamples / 2) + kf * kWHopWords + 32 * tt;
+    const int offB = fa + 1 >= p.total_frames ? 0 : (kf == kWFrames - 1 ? kWHalf / 2 : kWHopWords);
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(srcA));
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(srcA + offB));
+}
 // phase A on one half: radix-4 decimation in frequency over the quarters, twiddles, planes
 __device__ __forceinline__ void quarter_stage(const HalfWords& w, const Planes& P, const float2* twq1, uint32_t rand_mul, int tt, int j0) {
 #pragma unroll
@@ -321,6 +333,12 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_pair_kernel
                 if (D == 0 || ((row_mask >> k1) & 1u)) pst(P, wbase + lane + 32 * k1, v[k1]);
         }
         team_barrier(team);
+        // measured per decimation (B200, 8192 blocks): d = 3 665 -> 674, d = 5 799 -> 819, d = 6 725 -> 730 Gsamples/s; d = 0, 2, 4
+        // lose 0.5 - 0.9 % (two more LSU instructions per thread in kernels bound by that pipe), d = 1 is even
+        if constexpr (D == 3 || D >= 5) {
+            const long long qpf = s_pair[team];       // the next pair of this team (written after barrier A)
+            if (qpf < n_pairs) prefetch_pair_l2(p, qpf, tt);
+        }
 
         const FrameOut2 oa = wide_frame_out<D>(2 * q, p.total_frames);
         const FrameOut2 ob = wide_frame_out<D>(2 * q + 1, p.total_frames);
