@@ -392,6 +392,40 @@ def test_config4_channelizer_fftn8192():
     op8.close()
 
 
+def test_channelizer_more_than_256_channels(op):
+    """Channel lists longer than the 256 tune bins the channelizer kernels keep in shared memory are read from global memory
+    (the `in_smem == false` branch of r2iq_channels_lane_kernel, r2iq_channels_pair_kernel, r2iq_wide_channels_kernel): the
+    result must equal, bit for bit, the same channels computed in two shorter lists, and the oracle on a few of them."""
+    from extio_sddc_b200 import CudaR2IQ
+    x = orc.rx888_blocks(1, 5, 256, randomized=True, seed=77)
+    hist = np.random.default_rng(77).integers(-2000, 2000, 1024).astype(np.int16)
+    bins = [(12 * i) % 1024 for i in range(261)]
+    for d in (5, 3):
+        op.setDecimate(d); op.updateRand(True); op.setSideband(False)
+        op.TurnOn()
+        got = op.process_channels(x, bins, history=hist)
+        parts = np.concatenate([op.process_channels(x, bins[:130], history=hist), op.process_channels(x, bins[130:], history=hist)])
+        op.TurnOff()
+        assert got.shape == (261, 32768 >> d)                  # one block of complex64 per channel
+        assert np.array_equal(got, parts)
+        for c in (0, 129, 200, 260):
+            check(got[c], orc.r2iq(x, d, bins[c], gain=GAIN, rand=True, history=hist), GAIN, ("long channel list", d, bins[c]))
+    op8 = CudaR2IQ(device=0, fftn=8192)
+    op8.Init(GAIN)
+    x8 = orc.rx888_blocks(1, 5, 1024, fftn=8192, randomized=True, seed=78)
+    hist8 = np.random.default_rng(78).integers(-2000, 2000, 4096).astype(np.int16)
+    bins8 = [(44 * i) % 4096 for i in range(259)]
+    op8.setDecimate(5); op8.updateRand(True); op8.setSideband(False)
+    op8.TurnOn()
+    got = op8.process_channels(x8, bins8, history=hist8)
+    parts = np.concatenate([op8.process_channels(x8, bins8[:100], history=hist8), op8.process_channels(x8, bins8[100:], history=hist8)])
+    op8.TurnOff()
+    assert np.array_equal(got, parts)
+    for c in (0, 99, 258):
+        check(got[c], orc.r2iq(x8, 5, bins8[c], gain=GAIN, rand=True, history=hist8, fftn=8192), GAIN, ("long channel list 8192", bins8[c]))
+    op8.close()
+
+
 def test_fine_tune_mixer_bit_exact(op):
     """Next row: the residual NCO mixer RadioHandlerClass applies after the operator, run on
     the device (mode R2IQ_NCO_REFERENCE, the default).  Applied to the same IQ, the device result must equal the
