@@ -419,8 +419,11 @@ def test_channelizer_more_than_256_channels(op):
     op8.TurnOn()
     got = op8.process_channels(x8, bins8, history=hist8)
     parts = np.concatenate([op8.process_channels(x8, bins8[:100], history=hist8), op8.process_channels(x8, bins8[100:], history=hist8)])
+    few = [op8.process_channels(x8, bins8[:n], history=hist8) for n in (2, 3, 5)]     # fewer channels than warps in a team; a ragged last trip
     op8.TurnOff()
     assert np.array_equal(got, parts)
+    for f in few:
+        assert np.array_equal(f, got[:len(f)])
     for c in (0, 99, 258):
         check(got[c], orc.r2iq(x8, 5, bins8[c], gain=GAIN, rand=True, history=hist8, fftn=8192), GAIN, ("long channel list 8192", bins8[c]))
     op8.close()
