@@ -14,7 +14,7 @@
 //     (twiddles W_4096^(-r (n << d)), per-lane constants) and the stores of the kept three quarters of both frames follow
 //     in place.
 // ~330 instructions per channel and frame pair instead of a whole single-channel kernel (~2300 per thread): 64 channels x
-// 8192 blocks in 2.43 ms at d = 5 and 4.32 ms at d = 4 (64 single-channel launches: 44 / 46 ms; the first form of this
+// 8192 blocks in 2.43 ms at d = 5 and 4.01 ms at d = 4 (64 single-channel launches: 44 / 46 ms; the first form of this
 // kernel -- warp r on plane r of one channel, S_r exchanged through shared memory between two team barriers per channel,
 // a dependent chain of ~1200 cycles per channel: 4.21 / 6.86 ms).
 // Worker-loop semantics per channel: Core/fft_mt_r2iq_impl.hpp:76-138.
@@ -189,16 +189,50 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) r2iq_wide_channels_ke
             }
             float2* const outA = p.out + (size_t)ch * p.out_stride + oa.base;
             float2* const outB = p.out + (size_t)ch * p.out_stride + ob.base;
+            c2 row[3][R];
 #pragma unroll
             for (int e = 0; e < R; e++) {
                 // last radix-4 stage across the planes: y[n + MS a] = sum_r i^(r a) S_r[n] W_mfft^(-r n), a = 0..2 kept
-                const int n = R * brev5(lane) + e;
                 const c2 s0 = S[0][e], s1 = cmul_conj2s(S[1][e], wq[e][0]), s2 = cmul_conj2s(S[2][e], wq[e][1]),
                          s3 = cmul_conj2s(S[3][e], wq[e][2]);
                 const c2 a0 = cadd(s0, s2), a1 = csub(s0, s2), a2 = cadd(s1, s3), a3 = csub(s1, s3);
-                store_pair_rows(outA, outB, head, n, cadd(a0, a2), sgn);
-                store_pair_rows(outA, outB, rest, n + MS, c2{sub2(a1.re, a3.im), add2(a1.im, a3.re)}, sgn);      // a1 + i a3
-                store_pair_rows(outA, outB, rest, n + 2 * MS, csub(a0, a2), sgn);
+                row[0][e] = cadd(a0, a2);
+                row[1][e] = c2{sub2(a1.re, a3.im), add2(a1.im, a3.re)};      // a1 + i a3
+                row[2][e] = csub(a0, a2);
+            }
+            if constexpr (R == 2) {
+                // d = 4: lane l holds samples 2 brev5(l), + 1 -- 8-byte stores at a 16-byte stride from lanes in bit-reversed
+                // order are 8 L1 wavefronts each (data-pipe rule 1).  24 SHFL put sample pair l into lane l:
+                // six 16-byte stores of 512 consecutive bytes, 4 wavefronts each, instead of twelve at 8.
+                const int src = brev5(lane);
+#pragma unroll
+                for (int a = 0; a < 3; a++) {
+                    const KeepPair keep = a == 0 ? head : rest;
+                    float4 va, vb;
+#pragma unroll
+                    for (int e = 0; e < 2; e++) {
+                        float ar, br, ai, bi;
+                        upk(row[a][e].re, ar, br);
+                        upk(row[a][e].im, ai, bi);
+                        ar = __shfl_sync(0xffffffffu, ar, src);
+                        br = __shfl_sync(0xffffffffu, br, src);
+                        ai = __shfl_sync(0xffffffffu, ai, src);
+                        bi = __shfl_sync(0xffffffffu, bi, src);
+                        if (e == 0) { va.x = ar; va.y = flip(ai, sgn); vb.x = br; vb.y = flip(bi, sgn); }
+                        else { va.z = ar; va.w = flip(ai, sgn); vb.z = br; vb.w = flip(bi, sgn); }
+                    }
+                    // 16-byte aligned: sample index 2 lane + MS a, frame bases and the channel stride are even (header contract)
+                    if (keep.a) *reinterpret_cast<float4*>(outA + 2 * lane + MS * a) = va;
+                    if (keep.b) *reinterpret_cast<float4*>(outB + 2 * lane + MS * a) = vb;
+                }
+            } else {
+#pragma unroll
+                for (int e = 0; e < R; e++) {
+                    const int n = R * brev5(lane) + e;
+                    store_pair_rows(outA, outB, head, n, row[0][e], sgn);
+                    store_pair_rows(outA, outB, rest, n + MS, row[1][e], sgn);
+                    store_pair_rows(outA, outB, rest, n + 2 * MS, row[2][e], sgn);
+                }
             }
         }
         const long long qn = s_pair[team];
